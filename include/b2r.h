@@ -1,0 +1,170 @@
+/*
+ * b2r.h -- C ABI of the B200-native registration library (libb2r.so).
+ *
+ * This is the drop-in boundary for the registration stage of patricksko/PoseEstimator.
+ * The reference reaches this path through the pybind11 module `teaserpp_python`
+ * (TEASER++ C++/OpenMP) and through Open3D; each entry point below names the reference
+ * call it replaces.  Plain pointers and sizes only: no torch / numpy / C++ types.
+ *
+ *   reference call site (file:line under /root/reference/src/pose_estimator/EstimHelpers)
+ *   ------------------------------------------------------------------------------------
+ *   teaserpp_python.RobustRegistrationSolver.Params()      HelpersRealtime.py:158, registration_utils.py:251
+ *   teaserpp_python.RobustRegistrationSolver(params)       HelpersRealtime.py:165, registration_utils.py:260
+ *   solver.solve(src_corr, dst_corr)                       HelpersRealtime.py:166, registration_utils.py:261
+ *   solver.getSolution()                                   HelpersRealtime.py:167, registration_utils.py:262
+ *   solver.getRotationInliers()/getScaleInliers()/getTranslationInliers()   registration_utils.py:264-266
+ *   depth * scale, mask, RGBD -> cloud (back-projection)   RealSenseClass.py:56-67, registration_utils.py:54-90
+ *   remove_statistical_outlier(20, 1.0)                    RealSenseClass.py:68, registration_utils.py:93
+ *   voxel_down_sample(voxel)                               PoseEstimator.py:87,93
+ *   estimate_normals + compute_fpfh_feature                HelpersRealtime.py:215-224
+ *   get_correspondences (north-star: mutual NN on FPFH)    HelpersRealtime.py:194-213
+ *
+ * Conventions
+ *   - every function returns a b2r_status (0 = ok), never throws, never calls exit();
+ *   - a handle is bound to one CUDA device and one stream; thread-compatible per handle,
+ *     thread-safe across handles;
+ *   - point sets are 3xN float64, column-major (x,y,z of point i at 3*i..3*i+2) unless strides are given;
+ *   - there is NO CPU fallback: every entry point fails with B2R_ERR_CUDA when no device is usable.
+ */
+#ifndef B2R_H_
+#define B2R_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2R_VERSION 100 /* 0.1.0 */
+
+typedef struct b2r_solver b2r_solver; /* opaque */
+
+typedef enum b2r_status {
+  B2R_OK = 0,
+  B2R_ERR_INVALID_ARG = 1,
+  B2R_ERR_CUDA = 2,     /* CUDA runtime error; text in b2r_last_error() */
+  B2R_ERR_OOM = 3,
+  B2R_ERR_STATE = 4,    /* e.g. getter before solve, index out of range */
+  B2R_ERR_LIMIT = 5     /* problem exceeds a documented limit (N > 65535, search arena overflow) */
+} b2r_status;
+
+/* enum values follow TEASER++ */
+enum { B2R_ROT_GNC_TLS = 0, B2R_ROT_FGR = 1 };
+enum { B2R_TIM_CHAIN = 0, B2R_TIM_COMPLETE = 1 };
+enum { B2R_INLIER_PMC_EXACT = 0, B2R_INLIER_PMC_HEU = 1, B2R_INLIER_KCORE_HEU = 2, B2R_INLIER_NONE = 3 };
+
+/* RobustRegistrationSolver::Params -- same fields, same defaults (b2r_default_params). */
+typedef struct b2r_params {
+  double noise_bound;                /* 0.01 */
+  double cbar2;                      /* 1.0 */
+  int32_t estimate_scaling;          /* 1 (upstream default); the reference sets 0 */
+  int32_t rotation_estimation_algorithm; /* B2R_ROT_GNC_TLS */
+  double rotation_gnc_factor;        /* 1.4 */
+  int32_t rotation_max_iterations;   /* 100 */
+  double rotation_cost_threshold;    /* 1e-6 */
+  int32_t rotation_tim_graph;        /* B2R_TIM_CHAIN */
+  int32_t inlier_selection_mode;     /* B2R_INLIER_PMC_EXACT */
+  double kcore_heuristic_threshold;  /* 0.5 */
+  double max_clique_time_limit;      /* 3000 s; exact search stops (best-so-far kept, stats.exact_proven=0) */
+  int32_t max_clique_num_threads;    /* accepted for API parity; ignored on the GPU */
+  /* --- extensions (0 = default behaviour) --- */
+  double rotation_noise_bound;       /* GNC noise bound before the 2/scale factor; <=0 -> noise_bound.
+                                        Lets the host mirror upstream's in-place compounding (A.6-2). */
+  int32_t graph_exact_only;          /* 1: always evaluate both fp64 square roots (no sqrt-free filter) */
+  double graph_filter_tau;           /* ambiguity band of the sqrt-free filter; <=0 -> 1e-9 */
+} b2r_params;
+
+typedef struct b2r_solution {
+  double scale;
+  double rotation[9];   /* row-major 3x3 */
+  double translation[3];
+  int32_t valid;
+} b2r_solution;
+
+typedef struct b2r_stats {
+  int32_t n;                 /* correspondences */
+  int64_t n_edges;           /* edges of the consistency graph */
+  int32_t max_degree;
+  int32_t heuristic_lb;      /* clique size found by the greedy heuristic */
+  int32_t n_pruned;          /* vertices left after (lb-1)-core pruning */
+  int32_t omega;             /* maximum clique size proven by the exact search */
+  int32_t clique_size;
+  int32_t n_rot_tims;
+  int32_t n_rot_inliers;
+  int32_t n_trans_inliers;
+  int32_t gnc_iterations;
+  double gnc_cost;
+  int64_t bnb_nodes;         /* branch-and-bound nodes expanded */
+  int64_t graph_slow_pairs;  /* pairs the sqrt-free filter sent to the exact fp64 path */
+  int32_t exact_proven;      /* 1 unless the time limit stopped the exact search */
+  int32_t flags;             /* internal error bits, 0 when ok */
+} b2r_stats;
+
+typedef enum b2r_index_kind {
+  B2R_IDX_MAX_CLIQUE = 0,          /* original correspondence ids, ascending            (getInlierMaxClique) */
+  B2R_IDX_ROT_INLIERS = 1,         /* positions in the pruned TIM list with w >= 0.5    (getRotationInliers) */
+  B2R_IDX_ROT_INLIERS_MAP = 2,     /* max_clique[k] of those positions                  (getRotationInliersMap) */
+  B2R_IDX_TRANS_INLIERS = 3,       /* positions in the rotation-inlier list             (getTranslationInliers) */
+  B2R_IDX_TRANS_INLIERS_MAP = 4,   /* original ids of those                             (getTranslationInliersMap) */
+  B2R_IDX_DEGREES = 5              /* degree of every vertex, length n */
+} b2r_index_kind;
+
+void b2r_default_params(b2r_params* p);
+int b2r_version(void);
+/* number of usable CUDA devices (0 when none: the product then refuses to run) */
+int b2r_device_count(void);
+
+/* RobustRegistrationSolver(params).  `stream` is a cudaStream_t (NULL = a private non-blocking stream). */
+b2r_status b2r_create(const b2r_params* params, int device, void* stream, b2r_solver** out);
+b2r_status b2r_destroy(b2r_solver* s);
+/* solver.reset(params) */
+b2r_status b2r_reset(b2r_solver* s, const b2r_params* params);
+const char* b2r_last_error(const b2r_solver* s);
+
+/* solver.solve(src, dst): one registration, synchronous.
+ * element (r, c) of a 3xN operand is at base[r*row_stride + c*col_stride] (strides in elements);
+ * on_device != 0: pointers are device pointers on the handle's device. */
+b2r_status b2r_solve(b2r_solver* s, const double* src, const double* dst, int n,
+                     int64_t row_stride, int64_t col_stride, int on_device);
+
+/* Batch of independent registrations (detections / templates / frames).  Each operand is packed 3 x n[b]
+ * column-major.  _async only enqueues on the handle's stream (inputs must stay valid until b2r_sync). */
+b2r_status b2r_solve_batch(b2r_solver* s, int batch, const int* n, const double* const* src,
+                           const double* const* dst, int on_device);
+b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const double* const* src,
+                                 const double* const* dst, int on_device);
+b2r_status b2r_sync(b2r_solver* s);
+int b2r_batch_size(const b2r_solver* s);
+/* number of kernels this handle has launched since creation (bench.py's gpu_launches claim) */
+int64_t b2r_launch_count(const b2r_solver* s);
+
+/* getSolution() and friends; `idx` selects the problem of the last batch (0 for b2r_solve). */
+b2r_status b2r_get_solution(b2r_solver* s, int idx, b2r_solution* out);
+b2r_status b2r_get_stats(b2r_solver* s, int idx, b2r_stats* out);
+/* out == NULL: only *count is written. */
+b2r_status b2r_get_indices(b2r_solver* s, int idx, b2r_index_kind kind, int32_t* out, int32_t* count);
+/* consistency graph as bit rows: out[i*words_per_row + (j>>5)] bit (j&31); words_per_row >= ceil(n/32) */
+b2r_status b2r_get_adjacency(b2r_solver* s, int idx, uint32_t* out, int words_per_row);
+/* GNC weights of the pruned TIMs (length n_rot_tims) */
+b2r_status b2r_get_gnc_weights(b2r_solver* s, int idx, double* out);
+/* per-stage device times of the last batch in ms (needs b2r_set_profiling(s,1)):
+ * [0] upload [1] graph [2] degree [3] heuristic [4] prune+compact [5] exact search [6] canonical clique
+ * [7] rotation [8] translation [9] total */
+b2r_status b2r_set_profiling(b2r_solver* s, int on);
+b2r_status b2r_get_timings(b2r_solver* s, float* ms10);
+
+/* ---- pieces of the path exposed for sharding and tests -------------------------------------------- */
+/* Rows [row_begin,row_end) of the consistency graph of one problem into adj_out (device, pitch words per
+ * row, pitch % 4 == 0).  src/dst: device, packed 3xN.  Used by the row-sharded large-N path (config 5). */
+b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* dst_dev, int n,
+                          int row_begin, int row_end, uint32_t* adj_out_dev, int pitch_words);
+/* Continue a solve from a complete device adjacency (after the all-gather of row shards). */
+b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const double* dst_dev, int n,
+                                    const uint32_t* adj_dev, int pitch_words);
+/* words per adjacency row the library uses for n vertices (multiple of 4) */
+int b2r_pitch_words(int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2R_H_ */

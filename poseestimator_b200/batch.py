@@ -1,0 +1,154 @@
+"""Batched registration of independent detections / templates / frames (BASELINE.json config 4).
+
+The reference loops over templates one `run_teaser` call at a time
+(/root/reference/src/pose_estimator/EstimHelpers/PoseEstimator.py:90-114, registration_utils.py:359-408).
+Here the whole batch goes through one set of launches (grid.y = problem) on one stream, with one H2D copy in and
+one small D2H copy out.  Independent units shard across GPUs with no collective (`shard_round_robin`).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .teaser import RegistrationSolution, _Params
+
+
+def shard_round_robin(n_items: int, rank: int, world: int) -> range:
+    """Static round-robin assignment of independent work items (detections) to ranks -- no collective needed."""
+    return range(rank, n_items, world)
+
+
+def _pack(a) -> np.ndarray:
+    """3xN (any strides) -> packed column-major buffer (N,3) C-order."""
+    a = np.asarray(a, dtype=np.float64)
+    if a.ndim != 2 or a.shape[0] != 3:
+        raise TypeError(f"expected a (3, N) float64 array, got {a.shape}")
+    return np.ascontiguousarray(a.T)
+
+
+class BatchSolver:
+    """Many registrations per call through b2r_solve_batch (one handle = one device + one stream)."""
+
+    def __init__(self, params: "_Params | None" = None, device: int = 0, stream=None, profiling: bool = False):
+        L = _lib.lib()
+        if L.b2r_device_count() <= 0:
+            raise RuntimeError("poseestimator_b200: no CUDA device is visible and there is no CPU fallback")
+        self._params = (params or _Params())._copy()
+        self._h = C.c_void_p()
+        cp = self._params._to_c(0.0)
+        st = L.b2r_create(C.byref(cp), int(device), C.c_void_p(int(stream) if stream else None), C.byref(self._h))
+        if st != 0:
+            raise RuntimeError(f"poseestimator_b200: b2r_create failed ({_lib.STATUS_NAMES.get(st, st)})")
+        if profiling:
+            L.b2r_set_profiling(self._h, 1)
+        self.device = int(device)
+        self._keep = None
+        self._batch = 0
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                _lib.lib().b2r_destroy(h)
+            except Exception:  # noqa: BLE001
+                pass
+            self._h = None
+
+    # ---- host inputs ------------------------------------------------------------------------------------
+    def solve_async(self, problems):
+        """problems: sequence of (src, dst) 3xN arrays.  Enqueues H2D + all kernels + D2H; returns immediately."""
+        packed = [(_pack(s), _pack(d)) for s, d in problems]
+        return self.solve_packed_async(packed)
+
+    def solve_packed_async(self, packed):
+        """packed: sequence of (src, dst) already packed (N,3) C-order float64 arrays (no conversion cost)."""
+        B = len(packed)
+        n = (C.c_int * B)(*[p[0].shape[0] for p in packed])
+        sp = (C.c_void_p * B)(*[p[0].ctypes.data for p in packed])
+        dp = (C.c_void_p * B)(*[p[1].ctypes.data for p in packed])
+        self._keep = (packed, n, sp, dp)
+        self._batch = B
+        _lib.check(self._h, _lib.lib().b2r_solve_batch_async(self._h, B, n, sp, dp, 0))
+
+    # ---- device inputs (zero copy) ----------------------------------------------------------------------
+    def solve_device_async(self, n_list, src_ptrs, dst_ptrs, keep_alive=None):
+        """Device pointers to packed 3xN column-major float64 operands (e.g. torch tensors' data_ptr())."""
+        B = len(n_list)
+        n = (C.c_int * B)(*[int(x) for x in n_list])
+        sp = (C.c_void_p * B)(*[int(x) for x in src_ptrs])
+        dp = (C.c_void_p * B)(*[int(x) for x in dst_ptrs])
+        self._keep = (keep_alive, n, sp, dp)
+        self._batch = B
+        _lib.check(self._h, _lib.lib().b2r_solve_batch_async(self._h, B, n, sp, dp, 1))
+
+    def sync(self):
+        _lib.check(self._h, _lib.lib().b2r_sync(self._h))
+
+    def solve(self, problems):
+        self.solve_async(problems)
+        self.sync()
+        return self.solutions()
+
+    # ---- results ----------------------------------------------------------------------------------------
+    def solution(self, i: int) -> RegistrationSolution:
+        sol = _lib.B2RSolution()
+        _lib.check(self._h, _lib.lib().b2r_get_solution(self._h, i, C.byref(sol)))
+        return RegistrationSolution(sol.scale, np.array(sol.rotation[:]).reshape(3, 3), np.array(sol.translation[:]), sol.valid)
+
+    def solutions(self):
+        return [self.solution(i) for i in range(self._batch)]
+
+    def stats(self, i: int) -> dict:
+        st = _lib.B2RStats()
+        _lib.check(self._h, _lib.lib().b2r_get_stats(self._h, i, C.byref(st)))
+        return st.as_dict()
+
+    def indices(self, i: int, kind: int) -> np.ndarray:
+        L = _lib.lib()
+        cnt = C.c_int32()
+        _lib.check(self._h, L.b2r_get_indices(self._h, i, kind, None, C.byref(cnt)))
+        out = np.zeros(max(cnt.value, 1), np.int32)
+        _lib.check(self._h, L.b2r_get_indices(self._h, i, kind, C.c_void_p(out.ctypes.data), C.byref(cnt)))
+        return out[: cnt.value].copy()
+
+    def max_clique(self, i: int) -> np.ndarray:
+        return self.indices(i, _lib.IDX_MAX_CLIQUE)
+
+    def adjacency(self, i: int, n: int) -> np.ndarray:
+        W = (n + 31) // 32
+        out = np.zeros((n, W), np.uint32)
+        _lib.check(self._h, _lib.lib().b2r_get_adjacency(self._h, i, C.c_void_p(out.ctypes.data), W))
+        return out
+
+    def gnc_weights(self, i: int) -> np.ndarray:
+        T = self.stats(i)["n_rot_tims"]
+        out = np.zeros(max(T, 1))
+        _lib.check(self._h, _lib.lib().b2r_get_gnc_weights(self._h, i, C.c_void_p(out.ctypes.data)))
+        return out[:T]
+
+    def timings_ms(self) -> dict:
+        t = (C.c_float * 10)()
+        _lib.check(self._h, _lib.lib().b2r_get_timings(self._h, t))
+        names = ("upload", "graph", "degree", "heuristic", "prune_compact", "exact_search", "canonical", "rotation",
+                 "translation", "total")
+        return dict(zip(names, [float(x) for x in t]))
+
+    def launch_count(self) -> int:
+        return int(_lib.lib().b2r_launch_count(self._h))
+
+    # ---- row-sharded large problem (config 5) -----------------------------------------------------------
+    def graph_rows(self, src_ptr, dst_ptr, n, row_begin, row_end, out_ptr, pitch_words):
+        _lib.check(self._h, _lib.lib().b2r_graph_rows(self._h, C.c_void_p(src_ptr), C.c_void_p(dst_ptr), n, row_begin,
+                                                      row_end, C.c_void_p(out_ptr), pitch_words))
+
+    def solve_from_adjacency(self, src_ptr, dst_ptr, n, adj_ptr, pitch_words):
+        self._batch = 1
+        _lib.check(self._h, _lib.lib().b2r_solve_from_adjacency(self._h, C.c_void_p(src_ptr), C.c_void_p(dst_ptr), n,
+                                                                C.c_void_p(adj_ptr), pitch_words))
+        return self.solution(0)
+
+
+def pitch_words(n: int) -> int:
+    return int(_lib.lib().b2r_pitch_words(n))

@@ -1,0 +1,574 @@
+// C ABI of libb2r.so (include/b2r.h): handle, workspace, batching, result getters.
+// Host-side orchestration only; every stage is a kernel in graph.cu / clique.cu / rt.cu.
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace b2r;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+struct HostBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMallocHost(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+};
+
+__global__ void gather_points_kernel(const double* __restrict__ in, long long rs, long long cs, int n, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 3 * n) out[i] = in[(long long)(i % 3) * rs + (long long)(i / 3) * cs];
+}
+
+}  // namespace
+
+struct b2r_solver {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  b2r_params params;
+  KernelParams kp;
+  std::string err;
+  long long launches = 0;
+
+  // workspace capacity
+  int batch_cap = 0, n_cap = 0, pitch = 0;
+  long long tim_cap = 0;
+  DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena;
+  HostBuf h_state, h_desc, h_pts;
+  size_t arena_words_per_warp = 64 * 1024;
+  int bnb_blocks = 1;
+
+  // last batch
+  int batch = 0;
+  std::vector<int> n;
+  bool pending = false;
+  bool have_result = false;
+  const uint32_t* ext_adj = nullptr;  // solve_from_adjacency
+
+  bool profiling = false;
+  cudaEvent_t ev[10] = {};
+  bool ev_ready = false;
+  float timings[10] = {};
+};
+
+namespace {
+
+#define CK(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e__ = (call);                                                                     \
+    if (e__ != cudaSuccess) {                                                                     \
+      s->err = std::string(#call) + ": " + cudaGetErrorString(e__);                               \
+      return e__ == cudaErrorMemoryAllocation ? B2R_ERR_OOM : B2R_ERR_CUDA;                       \
+    }                                                                                             \
+  } while (0)
+
+b2r_status fail(b2r_solver* s, b2r_status code, const std::string& msg) {
+  if (s) s->err = msg;
+  return code;
+}
+
+void fill_kernel_params(b2r_solver* s) {
+  const b2r_params& p = s->params;
+  KernelParams& k = s->kp;
+  k.beta = 2 * p.noise_bound * sqrt(p.cbar2);  // (2*nb)*sqrt(cbar2), A.4-2
+  const double beta2 = k.beta * k.beta;
+  k.half_beta2 = 0.5 * beta2;
+  const double tau = p.graph_filter_tau > 0 ? p.graph_filter_tau : 1e-9;
+  k.stau = 0.5 * sqrt(tau);
+  k.stau_beta2 = k.stau * beta2;
+  k.noise_bound = p.noise_bound; k.cbar2 = p.cbar2;
+  k.rot_noise_bound = p.rotation_noise_bound;
+  k.gnc_factor = p.rotation_gnc_factor; k.cost_threshold = p.rotation_cost_threshold;
+  k.max_iterations = p.rotation_max_iterations;
+  k.tim_graph = p.rotation_tim_graph;
+  k.inlier_mode = p.inlier_selection_mode;
+  k.estimate_scaling = p.estimate_scaling;
+  k.kcore_threshold = p.kcore_heuristic_threshold;
+  const double lim = p.max_clique_time_limit;
+  k.time_limit_ns = (lim > 0 && lim < 1e9) ? (unsigned long long)(lim * 1e9) : 0ull;
+  k.exact_only = p.graph_exact_only;
+}
+
+b2r_status check_params(b2r_solver* s, const b2r_params* p) {
+  if (!p) return fail(s, B2R_ERR_INVALID_ARG, "params is NULL");
+  if (!(p->noise_bound != 0)) return fail(s, B2R_ERR_INVALID_ARG, "noise_bound must be non-zero");
+  if (!(p->rotation_gnc_factor > 1)) return fail(s, B2R_ERR_INVALID_ARG, "rotation_gnc_factor must be > 1");
+  if (p->rotation_estimation_algorithm != B2R_ROT_GNC_TLS)
+    return fail(s, B2R_ERR_INVALID_ARG, "only GNC_TLS rotation estimation is implemented (FGR is not on the reference's path)");
+  if (p->inlier_selection_mode < 0 || p->inlier_selection_mode > 3) return fail(s, B2R_ERR_INVALID_ARG, "bad inlier_selection_mode");
+  if (p->rotation_tim_graph < 0 || p->rotation_tim_graph > 1) return fail(s, B2R_ERR_INVALID_ARG, "bad rotation_tim_graph");
+  return B2R_OK;
+}
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+b2r_status ensure_workspace(b2r_solver* s, int batch, int n_max) {
+  const int pitch = b2r_pitch_words(n_max);
+  long long tim_cap = n_max;
+  if (s->params.rotation_tim_graph == B2R_TIM_COMPLETE) {
+    const long long full = (long long)n_max * (n_max - 1) / 2;
+    const long long lim = 1ll << 22;
+    tim_cap = full < lim ? (full > n_max ? full : n_max) : lim;
+  }
+  if (batch <= s->batch_cap && n_max <= s->n_cap && tim_cap <= s->tim_cap) return B2R_OK;
+  const int bc = batch > s->batch_cap ? batch : s->batch_cap;
+  const int nc = n_max > s->n_cap ? n_max : s->n_cap;
+  const int pc = b2r_pitch_words(nc);
+  const long long tc = tim_cap > s->tim_cap ? tim_cap : s->tim_cap;
+  (void)pitch;
+  CK(cudaStreamSynchronize(s->stream));
+  const size_t B = (size_t)bc;
+  CK(s->d_pts.ensure(B * 6 * nc * sizeof(double)));
+  CK(s->d_adj.ensure(B * nc * pc * sizeof(uint32_t)));
+  CK(s->d_cadj.ensure(B * nc * pc * sizeof(uint32_t)));
+  // ints per problem: deg, ids, clique (n each) + rot_inl (tim) + tls_id (4*tim)
+  CK(s->d_int.ensure(B * (3 * (size_t)nc + 5 * (size_t)tc) * sizeof(int)));
+  // doubles per problem: weights (tim), timx, timy, raw (3*tim each), tls_val (4*tim)
+  CK(s->d_dbl.ensure(B * (14 * (size_t)tc) * sizeof(double)));
+  CK(s->d_u8.ensure(B * 2 * (size_t)tc));
+  CK(s->d_state.ensure(B * sizeof(ProbState)));
+  CK(s->d_desc.ensure(B * sizeof(ProbDesc)));
+  CK(s->h_state.ensure(B * sizeof(ProbState)));
+  CK(s->h_desc.ensure(B * sizeof(ProbDesc)));
+  CK(s->h_pts.ensure(B * 6 * nc * sizeof(double)));
+  s->bnb_blocks = (int)(296 / B);
+  if (s->bnb_blocks < 1) s->bnb_blocks = 1;
+  if (s->bnb_blocks > 37) s->bnb_blocks = 37;
+  const char* ak = getenv("B2R_ARENA_KB");
+  if (ak && atoi(ak) > 0) s->arena_words_per_warp = (size_t)atoi(ak) * 256;
+  CK(s->d_arena.ensure(B * s->bnb_blocks * kBnbWarpsPerBlock * s->arena_words_per_warp * sizeof(uint32_t)));
+  s->batch_cap = bc; s->n_cap = nc; s->pitch = pc; s->tim_cap = tc;
+  return B2R_OK;
+}
+
+void build_desc(b2r_solver* s, int b, int n, const double* dsrc, const double* ddst, const uint32_t* ext_adj, int ext_pitch) {
+  ProbDesc& d = ((ProbDesc*)s->h_desc.p)[b];
+  const size_t nc = (size_t)s->n_cap, tc = (size_t)s->tim_cap, pc = (size_t)s->pitch;
+  d.src = dsrc; d.dst = ddst;
+  d.adj = ext_adj ? const_cast<uint32_t*>(ext_adj) : (uint32_t*)s->d_adj.p + (size_t)b * nc * pc;
+  d.cadj = (uint32_t*)s->d_cadj.p + (size_t)b * nc * pc;
+  int* ib = (int*)s->d_int.p + (size_t)b * (3 * nc + 5 * tc);
+  d.deg = ib; d.ids = ib + nc; d.clique = ib + 2 * nc; d.rot_inl = ib + 3 * nc; d.tls_id = ib + 3 * nc + tc;
+  double* db = (double*)s->d_dbl.p + (size_t)b * 14 * tc;
+  d.weights = db; d.timx = db + tc; d.timy = db + 4 * tc; d.raw = db + 7 * tc; d.tls_val = db + 10 * tc;
+  unsigned char* ub = (unsigned char*)s->d_u8.p + (size_t)b * 2 * tc;
+  d.rot_mask = ub; d.trans_mask = ub + tc;
+  d.st = (ProbState*)s->d_state.p + b;
+  d.n = n;
+  d.pitch = ext_adj ? ext_pitch : (int)pc;
+  d.tim_cap = (int)tc;
+  d.pad_ = 0;
+}
+
+b2r_status ensure_events(b2r_solver* s) {
+  if (s->ev_ready) return B2R_OK;
+  for (int i = 0; i < 10; ++i) CK(cudaEventCreate(&s->ev[i]));
+  s->ev_ready = true;
+  return B2R_OK;
+}
+
+// enqueue stages 1.. on descriptors already in h_desc
+b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph) {
+  cudaStream_t st = s->stream;
+  const bool prof = s->profiling;
+  CK(cudaMemsetAsync(s->d_state.p, 0, (size_t)batch * sizeof(ProbState), st));
+  CK(cudaMemcpyAsync(s->d_desc.p, s->h_desc.p, (size_t)batch * sizeof(ProbDesc), cudaMemcpyHostToDevice, st));
+  const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
+  if (prof) CK(cudaEventRecord(s->ev[1], st));
+  if (!skip_graph) s->launches += launch_tim_graph(dd, batch, n_max, s->kp, st);
+  if (prof) CK(cudaEventRecord(s->ev[2], st));
+  s->launches += launch_degree(dd, batch, n_max, st);
+  if (prof) CK(cudaEventRecord(s->ev[3], st));
+  s->launches += launch_clique(dd, batch, n_max, s->kp, (uint32_t*)s->d_arena.p, s->arena_words_per_warp, s->bnb_blocks, st,
+                               prof ? &s->ev[4] : nullptr);
+  s->launches += launch_rotation_translation(dd, batch, n_max, s->kp, st, prof ? &s->ev[8] : nullptr);
+  if (prof) CK(cudaEventRecord(s->ev[9], st));
+  CK(cudaMemcpyAsync(s->h_state.p, s->d_state.p, (size_t)batch * sizeof(ProbState), cudaMemcpyDeviceToHost, st));
+  CK(cudaGetLastError());
+  s->pending = true;
+  s->have_result = false;
+  return B2R_OK;
+}
+
+b2r_status check_index(b2r_solver* s, int idx) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
+  if (!s->have_result) return fail(s, B2R_ERR_STATE, "no solve has completed on this handle");
+  if (idx < 0 || idx >= s->batch) return fail(s, B2R_ERR_STATE, "problem index out of range");
+  return B2R_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void b2r_default_params(b2r_params* p) {
+  memset(p, 0, sizeof(*p));
+  p->noise_bound = 0.01; p->cbar2 = 1.0; p->estimate_scaling = 1;
+  p->rotation_estimation_algorithm = B2R_ROT_GNC_TLS;
+  p->rotation_gnc_factor = 1.4; p->rotation_max_iterations = 100; p->rotation_cost_threshold = 1e-6;
+  p->rotation_tim_graph = B2R_TIM_CHAIN; p->inlier_selection_mode = B2R_INLIER_PMC_EXACT;
+  p->kcore_heuristic_threshold = 0.5; p->max_clique_time_limit = 3000; p->max_clique_num_threads = 0;
+}
+
+int b2r_version(void) { return B2R_VERSION; }
+
+int b2r_device_count(void) {
+  int c = 0;
+  if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return c;
+}
+
+int b2r_pitch_words(int n) { return 4 * ((n + kTile - 1) / kTile); }
+
+b2r_status b2r_create(const b2r_params* params, int device, void* stream, b2r_solver** out) {
+  if (!out) return B2R_ERR_INVALID_ARG;
+  *out = nullptr;
+  b2r_solver* s = new b2r_solver();
+  b2r_params def;
+  if (!params) { b2r_default_params(&def); params = &def; }
+  b2r_status r = check_params(s, params);
+  if (r != B2R_OK) { delete s; return r; }
+  int cnt = 0;
+  if (cudaGetDeviceCount(&cnt) != cudaSuccess || cnt <= 0 || device < 0 || device >= cnt) {
+    cudaGetLastError();
+    delete s;
+    return B2R_ERR_CUDA;  // no CPU fallback by design
+  }
+  s->device = device;
+  if (cudaSetDevice(device) != cudaSuccess) { delete s; return B2R_ERR_CUDA; }
+  if (stream) { s->stream = (cudaStream_t)stream; s->own_stream = false; }
+  else {
+    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { delete s; return B2R_ERR_CUDA; }
+    s->own_stream = true;
+  }
+  s->params = *params;
+  fill_kernel_params(s);
+  *out = s;
+  return B2R_OK;
+}
+
+b2r_status b2r_destroy(b2r_solver* s) {
+  if (!s) return B2R_OK;
+  cudaSetDevice(s->device);
+  cudaStreamSynchronize(s->stream);
+  s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
+  s->d_state.release(); s->d_desc.release(); s->d_arena.release();
+  s->h_state.release(); s->h_desc.release(); s->h_pts.release();
+  if (s->ev_ready) for (int i = 0; i < 10; ++i) cudaEventDestroy(s->ev[i]);
+  if (s->own_stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return B2R_OK;
+}
+
+b2r_status b2r_reset(b2r_solver* s, const b2r_params* params) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  b2r_status r = check_params(s, params);
+  if (r != B2R_OK) return r;
+  if (s->pending) { r = b2r_sync(s); if (r != B2R_OK) return r; }
+  s->params = *params;
+  fill_kernel_params(s);
+  s->have_result = false; s->batch = 0;
+  return B2R_OK;
+}
+
+const char* b2r_last_error(const b2r_solver* s) { return s ? s->err.c_str() : "null handle"; }
+int b2r_batch_size(const b2r_solver* s) { return s ? s->batch : 0; }
+int64_t b2r_launch_count(const b2r_solver* s) { return s ? s->launches : 0; }
+
+b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const double* const* src,
+                                 const double* const* dst, int on_device) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (batch <= 0 || !n || !src || !dst) return fail(s, B2R_ERR_INVALID_ARG, "batch/n/src/dst");
+  if (s->params.estimate_scaling)
+    return fail(s, B2R_ERR_INVALID_ARG, "estimate_scaling=True is not implemented yet (the reference sets it to False)");
+  CK(cudaSetDevice(s->device));
+  if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
+  int n_max = 0;
+  size_t total = 0;
+  for (int b = 0; b < batch; ++b) {
+    if (n[b] < 2) return fail(s, B2R_ERR_INVALID_ARG, "every problem needs at least 2 correspondences");
+    if (n[b] > kMaxN) return fail(s, B2R_ERR_LIMIT, "N > 65535 correspondences is not supported");
+    if (!src[b] || !dst[b]) return fail(s, B2R_ERR_INVALID_ARG, "null point pointer");
+    n_max = n[b] > n_max ? n[b] : n_max;
+    total += (size_t)3 * n[b];
+  }
+  b2r_status r = ensure_workspace(s, batch, n_max);
+  if (r != B2R_OK) return r;
+  if (s->profiling) { r = ensure_events(s); if (r != B2R_OK) return r; CK(cudaEventRecord(s->ev[0], s->stream)); }
+  s->batch = batch;
+  s->n.assign(n, n + batch);
+  s->ext_adj = nullptr;
+  if (on_device) {
+    for (int b = 0; b < batch; ++b) build_desc(s, b, n[b], src[b], dst[b], nullptr, 0);
+  } else {
+    // pack all problems into one pinned staging block -> one H2D copy per operand
+    double* hs = (double*)s->h_pts.p;
+    double* hd = hs + total;
+    double* ds = (double*)s->d_pts.p;
+    double* dd = ds + total;
+    size_t off = 0;
+    for (int b = 0; b < batch; ++b) {
+      memcpy(hs + off, src[b], sizeof(double) * 3 * n[b]);
+      memcpy(hd + off, dst[b], sizeof(double) * 3 * n[b]);
+      build_desc(s, b, n[b], ds + off, dd + off, nullptr, 0);
+      off += (size_t)3 * n[b];
+    }
+    CK(cudaMemcpyAsync(ds, hs, sizeof(double) * 2 * total, cudaMemcpyHostToDevice, s->stream));
+  }
+  return enqueue_pipeline(s, batch, n_max, false);
+}
+
+b2r_status b2r_sync(b2r_solver* s) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  CK(cudaSetDevice(s->device));
+  CK(cudaStreamSynchronize(s->stream));
+  if (!s->pending) return B2R_OK;
+  s->pending = false;
+  if (s->profiling && s->ev_ready) {
+    for (int i = 0; i < 9; ++i) cudaEventElapsedTime(&s->timings[i], s->ev[i], s->ev[i + 1]);
+    cudaEventElapsedTime(&s->timings[9], s->ev[0], s->ev[9]);
+  }
+  s->have_result = true;
+  const ProbState* hs = (const ProbState*)s->h_state.p;
+  for (int b = 0; b < s->batch; ++b) {
+    const uint32_t f = hs[b].flags;
+    if (f & FLAG_COMPACT_TOO_LARGE) return fail(s, B2R_ERR_LIMIT, "pruned consistency graph exceeds 32768 vertices; exact clique search not supported at this size");
+    if (f & FLAG_ARENA_OVERFLOW) return fail(s, B2R_ERR_LIMIT, "exact clique search ran out of stack arena (set B2R_ARENA_KB to enlarge)");
+    if (f & FLAG_CANON_FAILED) return fail(s, B2R_ERR_STATE, "internal error: canonical clique reconstruction failed");
+    if (f & (1u << 4)) return fail(s, B2R_ERR_LIMIT, "COMPLETE TIM graph over the clique exceeds the workspace cap");
+  }
+  return B2R_OK;
+}
+
+b2r_status b2r_solve_batch(b2r_solver* s, int batch, const int* n, const double* const* src, const double* const* dst,
+                           int on_device) {
+  b2r_status r = b2r_solve_batch_async(s, batch, n, src, dst, on_device);
+  if (r != B2R_OK) return r;
+  return b2r_sync(s);
+}
+
+b2r_status b2r_solve(b2r_solver* s, const double* src, const double* dst, int n, int64_t row_stride, int64_t col_stride,
+                     int on_device) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!src || !dst) return fail(s, B2R_ERR_INVALID_ARG, "null point pointer");
+  if (n < 2) return fail(s, B2R_ERR_INVALID_ARG, "need at least 2 correspondences");
+  if (n > kMaxN) return fail(s, B2R_ERR_LIMIT, "N > 65535 correspondences is not supported");
+  const bool packed = (row_stride == 1 && col_stride == 3);
+  if (packed) return b2r_solve_batch(s, 1, &n, &src, &dst, on_device);
+  if (!on_device) {
+    std::vector<double> a((size_t)3 * n), b((size_t)3 * n);
+    for (int c = 0; c < n; ++c)
+      for (int r = 0; r < 3; ++r) {
+        a[(size_t)3 * c + r] = src[r * row_stride + c * col_stride];
+        b[(size_t)3 * c + r] = dst[r * row_stride + c * col_stride];
+      }
+    const double* pa = a.data(); const double* pb = b.data();
+    return b2r_solve_batch(s, 1, &n, &pa, &pb, 0);
+  }
+  // strided device input: gather into the workspace first
+  CK(cudaSetDevice(s->device));
+  if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
+  b2r_status r = ensure_workspace(s, 1, n);
+  if (r != B2R_OK) return r;
+  double* ds = (double*)s->d_pts.p;
+  double* dd = ds + (size_t)3 * n;
+  gather_points_kernel<<<(3 * n + 255) / 256, 256, 0, s->stream>>>(src, row_stride, col_stride, n, ds);
+  gather_points_kernel<<<(3 * n + 255) / 256, 256, 0, s->stream>>>(dst, row_stride, col_stride, n, dd);
+  s->launches += 2;
+  const double* pa = ds; const double* pb = dd;
+  return b2r_solve_batch(s, 1, &n, &pa, &pb, 1);
+}
+
+b2r_status b2r_get_solution(b2r_solver* s, int idx, b2r_solution* out) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  if (!out) return B2R_ERR_INVALID_ARG;
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  out->valid = st.valid;
+  if (st.valid) {
+    out->scale = st.scale;
+    memcpy(out->rotation, st.R, sizeof(double) * 9);
+    memcpy(out->translation, st.t, sizeof(double) * 3);
+  } else {  // upstream: default-constructed solution (s=1, R=I, t=0, valid=false)
+    out->scale = 1.0;
+    for (int i = 0; i < 9; ++i) out->rotation[i] = (i % 4 == 0) ? 1.0 : 0.0;
+    out->translation[0] = out->translation[1] = out->translation[2] = 0.0;
+  }
+  return B2R_OK;
+}
+
+b2r_status b2r_get_stats(b2r_solver* s, int idx, b2r_stats* out) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  if (!out) return B2R_ERR_INVALID_ARG;
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  memset(out, 0, sizeof(*out));
+  out->n = s->n[idx];
+  out->n_edges = (int64_t)(st.deg_sum / 2);
+  out->max_degree = st.max_deg;
+  out->heuristic_lb = st.lb;
+  out->n_pruned = st.n_alive;
+  out->omega = st.omega;
+  out->clique_size = st.clique_size;
+  out->n_rot_tims = st.n_rot_tims;
+  out->n_rot_inliers = st.n_rot_inl;
+  out->n_trans_inliers = st.n_trans_inl;
+  out->gnc_iterations = st.gnc_iters;
+  out->gnc_cost = st.gnc_cost;
+  out->bnb_nodes = (int64_t)st.bnb_nodes;
+  out->graph_slow_pairs = (int64_t)st.slow_pairs;
+  out->exact_proven = (st.flags & FLAG_TIME_LIMIT) ? 0 : 1;
+  out->flags = (int32_t)st.flags;
+  return B2R_OK;
+}
+
+b2r_status b2r_get_indices(b2r_solver* s, int idx, b2r_index_kind kind, int32_t* out, int32_t* count) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  const ProbDesc& d = ((const ProbDesc*)s->h_desc.p)[idx];
+  CK(cudaSetDevice(s->device));
+  const int C = st.clique_size > 0 ? st.clique_size : 0;
+  const int nr = st.n_rot_inl, M = st.n_rot_inl;
+  auto fetch_i = [&](const int* dev, int cnt, std::vector<int>& v) -> cudaError_t {
+    v.resize(cnt > 0 ? cnt : 0);
+    if (cnt <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemcpyAsync(v.data(), dev, sizeof(int) * cnt, cudaMemcpyDeviceToHost, s->stream);
+    if (e != cudaSuccess) return e;
+    return cudaStreamSynchronize(s->stream);
+  };
+  std::vector<int> res;
+  switch (kind) {
+    case B2R_IDX_MAX_CLIQUE: CK(fetch_i(d.clique, C, res)); break;
+    case B2R_IDX_DEGREES: CK(fetch_i(d.deg, s->n[idx], res)); break;
+    case B2R_IDX_ROT_INLIERS: CK(fetch_i(d.rot_inl, nr, res)); break;
+    case B2R_IDX_ROT_INLIERS_MAP: {
+      std::vector<int> cl, ri;
+      CK(fetch_i(d.clique, C, cl)); CK(fetch_i(d.rot_inl, nr, ri));
+      res.resize(ri.size());
+      for (size_t i = 0; i < ri.size(); ++i) res[i] = C ? cl[ri[i] % C] : -1;
+      break;
+    }
+    case B2R_IDX_TRANS_INLIERS:
+    case B2R_IDX_TRANS_INLIERS_MAP: {
+      std::vector<unsigned char> tm((size_t)(M > 0 ? M : 0));
+      if (M > 0) {
+        CK(cudaMemcpyAsync(tm.data(), d.trans_mask, (size_t)M, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+      }
+      std::vector<int> cl, ri;
+      if (kind == B2R_IDX_TRANS_INLIERS_MAP) { CK(fetch_i(d.clique, C, cl)); CK(fetch_i(d.rot_inl, nr, ri)); }
+      for (int i = 0; i < M; ++i)
+        if (tm[i]) res.push_back(kind == B2R_IDX_TRANS_INLIERS ? i : (C ? cl[ri[i] % C] : -1));
+      break;
+    }
+    default: return fail(s, B2R_ERR_INVALID_ARG, "unknown index kind");
+  }
+  if (count) *count = (int32_t)res.size();
+  if (out && !res.empty()) memcpy(out, res.data(), sizeof(int) * res.size());
+  return B2R_OK;
+}
+
+b2r_status b2r_get_adjacency(b2r_solver* s, int idx, uint32_t* out, int words_per_row) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  const int n = s->n[idx];
+  const int need = (n + 31) / 32;
+  if (!out || words_per_row < need) return fail(s, B2R_ERR_INVALID_ARG, "adjacency buffer too narrow");
+  const ProbDesc& d = ((const ProbDesc*)s->h_desc.p)[idx];
+  CK(cudaSetDevice(s->device));
+  memset(out, 0, sizeof(uint32_t) * (size_t)n * words_per_row);
+  CK(cudaMemcpy2DAsync(out, sizeof(uint32_t) * words_per_row, d.adj, sizeof(uint32_t) * d.pitch, sizeof(uint32_t) * need, n,
+                       cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return B2R_OK;
+}
+
+b2r_status b2r_get_gnc_weights(b2r_solver* s, int idx, double* out) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  const ProbDesc& d = ((const ProbDesc*)s->h_desc.p)[idx];
+  if (st.n_rot_tims <= 0) return B2R_OK;
+  CK(cudaSetDevice(s->device));
+  CK(cudaMemcpyAsync(out, d.weights, sizeof(double) * st.n_rot_tims, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return B2R_OK;
+}
+
+b2r_status b2r_set_profiling(b2r_solver* s, int on) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  s->profiling = on != 0;
+  return B2R_OK;
+}
+
+b2r_status b2r_get_timings(b2r_solver* s, float* ms10) {
+  if (!s || !ms10) return B2R_ERR_INVALID_ARG;
+  if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
+  memcpy(ms10, s->timings, sizeof(float) * 10);
+  return B2R_OK;
+}
+
+b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* dst_dev, int n, int row_begin, int row_end,
+                          uint32_t* adj_out_dev, int pitch_words) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!src_dev || !dst_dev || !adj_out_dev || n < 2 || row_begin < 0 || row_end > n || row_begin > row_end)
+    return fail(s, B2R_ERR_INVALID_ARG, "graph_rows arguments");
+  if (pitch_words < b2r_pitch_words(n) || (pitch_words & 3)) return fail(s, B2R_ERR_INVALID_ARG, "pitch_words must be >= b2r_pitch_words(n) and a multiple of 4");
+  CK(cudaSetDevice(s->device));
+  s->launches += launch_tim_graph_rows(src_dev, dst_dev, n, row_begin, row_end, adj_out_dev, pitch_words, s->kp, nullptr, s->stream);
+  CK(cudaGetLastError());
+  return B2R_OK;
+}
+
+b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const double* dst_dev, int n, const uint32_t* adj_dev,
+                                    int pitch_words) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!src_dev || !dst_dev || !adj_dev || n < 2) return fail(s, B2R_ERR_INVALID_ARG, "solve_from_adjacency arguments");
+  if (n > kMaxN) return fail(s, B2R_ERR_LIMIT, "N > 65535 correspondences is not supported");
+  if (pitch_words < b2r_pitch_words(n) || (pitch_words & 3)) return fail(s, B2R_ERR_INVALID_ARG, "pitch_words");
+  CK(cudaSetDevice(s->device));
+  if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
+  b2r_status r = ensure_workspace(s, 1, n);
+  if (r != B2R_OK) return r;
+  if (pitch_words != s->pitch && pitch_words > s->pitch) {
+    // compact adjacency rows use the workspace pitch; a wider external pitch would overflow them
+    return fail(s, B2R_ERR_INVALID_ARG, "external adjacency pitch wider than the workspace pitch");
+  }
+  if (s->profiling) { r = ensure_events(s); if (r != B2R_OK) return r; CK(cudaEventRecord(s->ev[0], s->stream)); }
+  s->batch = 1; s->n.assign(1, n);
+  build_desc(s, 0, n, src_dev, dst_dev, adj_dev, pitch_words);
+  r = enqueue_pipeline(s, 1, n, true);
+  if (r != B2R_OK) return r;
+  return b2r_sync(s);
+}
+
+}  // extern "C"

@@ -1,0 +1,103 @@
+// Internal declarations shared by the kernels of libb2r.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b2r.h"
+
+namespace b2r {
+
+constexpr int kTile = 128;            // consistency-graph tile edge (rows and columns per CTA)
+constexpr int kMaxN = 65535;          // degree / id packing in the clique kernels (16 + 16 bits)
+constexpr int kMaxCompactWords = 1024;  // register bitsets in the exact search: n' <= 32768
+
+// error / info bits in ProbState::flags
+enum : uint32_t {
+  FLAG_ARENA_OVERFLOW = 1u << 0,   // exact search ran out of per-warp stack
+  FLAG_TIME_LIMIT = 1u << 1,       // exact search stopped by max_clique_time_limit
+  FLAG_COMPACT_TOO_LARGE = 1u << 2,  // pruned graph wider than kMaxCompactWords
+  FLAG_CANON_FAILED = 1u << 3,     // canonicalisation could not build a clique of size omega (bug guard)
+};
+
+// Per-problem device state: written by the kernels, copied back once per batch.
+struct ProbState {
+  int n;
+  int W;                 // adjacency words per row in use (multiple of 4)
+  int max_deg;
+  int lb;                // heuristic lower bound (clique size)
+  unsigned long long heu_key;   // (size << 32) | (0xffffffff - seed): deterministic heuristic winner
+  unsigned long long deg_sum;   // 2 * edges
+  int T;                 // prune threshold used for the compact graph
+  int n_alive;           // compact graph size n'
+  int Wc;                // compact words per row (multiple of 4)
+  int omega;
+  int clique_size;
+  int n_rot_tims, n_rot_inl, n_trans_inl, gnc_iters;
+  double gnc_cost;
+  double scale, R[9], t[3];
+  int valid;
+  uint32_t flags;
+  unsigned long long bnb_nodes;
+  unsigned long long slow_pairs;
+  unsigned int root_counter;
+  unsigned int canon_next;
+  int canon_found;
+  int pad_;
+};
+
+// Per-problem pointers (device copies of host-built descriptors).
+struct ProbDesc {
+  const double* src;     // packed 3 x n, column-major
+  const double* dst;
+  uint32_t* adj;         // n x pitch words
+  int* deg;              // n
+  int* ids;              // compact id -> original id (n)
+  uint32_t* cadj;        // compact adjacency, n' x pitch words (first Wc used)
+  int* clique;           // output: original ids ascending (n)
+  double* weights;       // GNC weights (tim_cap)
+  double* timx;          // pruned TIMs for rotation, 3 x tim_cap
+  double* timy;
+  unsigned char* rot_mask;   // tim_cap
+  int* rot_inl;          // positions with w >= 0.5 (tim_cap)
+  unsigned char* trans_mask; // tim_cap
+  double* tls_val;       // adaptive voting scratch: 2 * tim_cap endpoints
+  int* tls_id;
+  double* raw;           // 3 x tim_cap raw translations
+  ProbState* st;
+  int n;
+  int pitch;             // words per adjacency row (multiple of 4)
+  int tim_cap;
+  int pad_;
+};
+
+struct KernelParams {
+  double beta;           // 2 * noise_bound * sqrt(cbar2)
+  double half_beta2;     // 0.5 * beta^2
+  double stau;           // sqrt(tau) / 2
+  double stau_beta2;     // stau * beta^2
+  double noise_bound, cbar2;
+  double rot_noise_bound;
+  double gnc_factor, cost_threshold;
+  int max_iterations;
+  int tim_graph;
+  int inlier_mode;
+  int estimate_scaling;
+  double kcore_threshold;
+  unsigned long long time_limit_ns;
+  int exact_only;
+};
+
+// launchers (each returns the number of kernels it enqueued)
+int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+int launch_tim_graph_rows(const double* src, const double* dst, int n, int row_begin, int row_end, uint32_t* adj,
+                          int pitch, const KernelParams& kp, unsigned long long* slow_pairs, cudaStream_t st);
+int launch_degree(const ProbDesc* d_desc, int batch, int n_max, cudaStream_t st);
+int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, uint32_t* arena,
+                  size_t arena_words_per_warp, int bnb_blocks_per_problem, cudaStream_t st, cudaEvent_t* ev /*4 or null*/);
+int launch_rotation_translation(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st,
+                                cudaEvent_t* ev /*1 or null*/);
+
+constexpr int kBnbWarpsPerBlock = 8;
+constexpr int kCanonWarps = 8;
+
+}  // namespace b2r

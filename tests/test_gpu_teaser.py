@@ -1,0 +1,319 @@
+"""GPU parity tests: CUDA path (through the C ABI / teaserpp_python surface) vs the CPU oracle.
+
+Bars (BASELINE.json north_star): adjacency, max-clique and index lists bit-exact; rotation within 1e-5 rad;
+translation within 1e-6 of the scene scale.
+"""
+import itertools
+
+import numpy as np
+import pytest
+
+from poseestimator_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+ROT_TOL = 1e-5          # rad
+TRANS_TOL_REL = 1e-6    # x scene scale
+
+
+def _params(tpp, nb, **kw):
+    p = tpp.RobustRegistrationSolver.Params()
+    p.noise_bound = nb
+    p.estimate_scaling = False
+    p.rotation_cost_threshold = 1e-12
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def _check_against_oracle(solver, sol, ref, pb):
+    assert np.array_equal(solver._adjacency_bits(), ref.adjacency)
+    assert solver.getInlierMaxClique() == ref.clique.tolist()
+    assert sol.valid == ref.valid
+    if ref.valid:
+        assert synth.rotation_error_rad(sol.rotation, ref.rotation) < ROT_TOL
+        assert np.linalg.norm(sol.translation - ref.translation) < TRANS_TOL_REL * pb.scene_scale
+        assert solver.getRotationInliers() == ref.rotation_inliers.tolist()
+        assert solver.getTranslationInliers() == ref.translation_inliers.tolist()
+        assert abs(solver.stats()["gnc_iterations"] - ref.gnc_iters) <= 1
+    assert solver.stats()["n_edges"] == ref.n_edges
+
+
+@pytest.mark.parametrize("n,ratio,seed", [(50, 0.3, 1), (129, 0.6, 2), (400, 0.6, 7), (1000, 0.5, 1000), (1000, 0.9, 3), (2049, 0.8, 4)])
+def test_solve_matches_oracle(oracle_mod, n, ratio, seed):
+    import teaserpp_python as tpp
+    pb = synth.make_problem(n, ratio, seed)
+    solver = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound))
+    sol = solver.solve(pb.src, pb.dst)
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12)
+    _check_against_oracle(solver, sol, ref, pb)
+    assert set(pb.inliers.tolist()) <= set(solver.getInlierMaxClique())
+
+
+def test_config3_full_size(oracle_mod):
+    """BASELINE config 3: N=5000, 95 % outliers."""
+    import teaserpp_python as tpp
+    pb = synth.config3()
+    solver = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound))
+    sol = solver.solve(pb.src, pb.dst)
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12,
+                           materialize_tims=0)
+    _check_against_oracle(solver, sol, ref, pb)
+    assert solver.getInlierMaxClique() == pb.inliers.tolist()
+    assert synth.rotation_error_rad(sol.rotation, pb.R) < 0.01
+
+
+def test_noisy_gnc_iterates(oracle_mod):
+    """Tight noise bound so that GNC really iterates and rejects TIMs."""
+    import teaserpp_python as tpp
+    pb = synth.make_problem(300, 0.3, 11, sigma=0.02)
+    nb = 0.03
+    solver = tpp.RobustRegistrationSolver(_params(tpp, nb))
+    sol = solver.solve(pb.src, pb.dst)
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=nb, estimate_scaling=0, rotation_cost_threshold=1e-12)
+    assert ref.gnc_iters > 3
+    _check_against_oracle(solver, sol, ref, pb)
+    w = np.zeros(solver.stats()["n_rot_tims"])
+    assert np.allclose(solver.getRotationInliersMask()[0], ref.rot_mask)
+
+
+@pytest.mark.parametrize("tau", [0.0, 1e-3, 0.5])
+def test_graph_filter_equals_exact_kernel(oracle_mod, tau):
+    """The sqrt-free filter (any ambiguity band) and the two-sqrt kernel give the same bits."""
+    import teaserpp_python as tpp
+    pb = synth.make_problem(777, 0.7, 21)
+    ref = oracle_mod.tim_graph(pb.src, pb.dst, pb.noise_bound)
+    a = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound, graph_exact_only=True))
+    a.solve(pb.src, pb.dst)
+    b = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound, graph_filter_tau=tau))
+    b.solve(pb.src, pb.dst)
+    assert np.array_equal(a._adjacency_bits(), ref)
+    assert np.array_equal(b._adjacency_bits(), ref)
+    if tau >= 1e-3:
+        assert b.stats()["graph_slow_pairs"] > 0
+
+
+def test_borderline_pairs_follow_reference_rounding(oracle_mod):
+    """Pairs constructed to sit exactly on / one ulp around the bound: verdicts must follow the fp64 reference order."""
+    import teaserpp_python as tpp
+    rng = np.random.default_rng(5)
+    n = 256
+    src = rng.uniform(-1, 1, (3, n))
+    dst = src.copy()
+    nb = 0.05
+    beta = 2 * nb
+    # stretch selected points so that | |dst_j-dst_0| - |src_j-src_0| | is beta +- few ulps
+    for j in range(1, n):
+        v = src[:, j] - src[:, 0]
+        L = np.linalg.norm(v)
+        target = L + beta * (1 + (j % 5 - 2) * 2.2e-16)
+        dst[:, j] = dst[:, 0] + v / L * target
+    ref = oracle_mod.tim_graph(src, dst, nb)
+    for kw in (dict(graph_exact_only=True), dict()):
+        s = tpp.RobustRegistrationSolver(_params(tpp, nb, **kw))
+        s.solve(src, dst)
+        assert np.array_equal(s._adjacency_bits(), ref)
+    alt = oracle_mod.tim_graph(src, dst, nb, variant=1)  # borderline counter: other association
+    print("borderline flips under x2+(y2+z2):", int((np.unpackbits((alt ^ ref).view(np.uint8))).sum()))
+
+
+def test_degenerate_inputs(oracle_mod):
+    import teaserpp_python as tpp
+    rng = np.random.default_rng(1)
+    src = rng.uniform(-1, 1, (3, 30)); dst = rng.uniform(-1, 1, (3, 30))
+    s = tpp.RobustRegistrationSolver(_params(tpp, 1e-9))
+    sol = s.solve(src, dst)
+    assert not sol.valid and np.array_equal(sol.rotation, np.eye(3)) and np.array_equal(sol.translation, np.zeros(3))
+    assert len(s.getInlierMaxClique()) <= 1 and s.getRotationInliers() == [] and s.getTranslationInliers() == []
+    assert list(s.getScaleInliers() or []) == []
+    R = synth.random_rotation(rng); t = np.array([0.3, -0.2, 0.1])
+    dst = R @ src + t[:, None]
+    s = tpp.RobustRegistrationSolver(_params(tpp, 0.01))
+    sol = s.solve(src, dst)
+    assert sol.valid and s.stats()["gnc_iterations"] == 0 and len(s.getInlierMaxClique()) == 30
+    assert synth.rotation_error_rad(sol.rotation, R) < 1e-7 and np.allclose(sol.translation, t, atol=1e-7)
+    src2 = src.copy(); src2[:, 1] = src2[:, 0]
+    sol = s.solve(src2, R @ src2 + t[:, None])
+    assert sol.valid and len(s.getInlierMaxClique()) == 30
+    for n in (2, 3):
+        s = tpp.RobustRegistrationSolver(_params(tpp, 0.01))
+        sol = s.solve(src[:, :n], dst[:, :n])
+        ref = oracle_mod.solve(src[:, :n], dst[:, :n], noise_bound=0.01, estimate_scaling=0, rotation_cost_threshold=1e-12)
+        assert sol.valid and len(s.getInlierMaxClique()) == n
+        assert synth.rotation_error_rad(sol.rotation, ref.rotation) < 1e-5 or n == 2
+    with pytest.raises(TypeError):
+        s.solve(np.zeros((4, 10)), np.zeros((4, 10)))
+    with pytest.raises(TypeError):
+        s.solve(np.zeros((3, 10)), np.zeros((3, 11)))
+
+
+def test_argument_layouts_and_reference_call_pattern(oracle_mod):
+    """The reference passes np.array([...]).T (F-order view); also C-order, float32 and a re-used solver."""
+    from teaserpp_python import _teaserpp as tpp
+    pb = synth.make_problem(200, 0.5, 31)
+    p = tpp.RobustRegistrationSolver.Params()
+    p.cbar2 = 1
+    p.noise_bound = float(pb.noise_bound)
+    p.estimate_scaling = False
+    p.rotation_estimation_algorithm = tpp.RotationEstimationAlgorithm.GNC_TLS
+    p.rotation_gnc_factor = 1.4
+    p.rotation_max_iterations = 100
+    p.rotation_cost_threshold = 1e-12
+    outs = []
+    for src, dst in ((pb.src, pb.dst), (np.ascontiguousarray(pb.src), np.ascontiguousarray(pb.dst)),
+                     (pb.src[:, ::1], np.asfortranarray(pb.dst))):
+        solver = tpp.RobustRegistrationSolver(p)
+        solver.solve(src, dst)
+        sol = solver.getSolution()
+        R_inl = list(solver.getRotationInliers() or [])
+        s_inl = list(solver.getScaleInliers() or [])
+        t_inl = list(solver.getTranslationInliers() or [])
+        outs.append((np.asarray(sol.rotation).copy(), np.asarray(sol.translation).reshape(3).copy(), R_inl, len(s_inl), t_inl))
+    for o in outs[1:]:
+        assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1]) and o[2:] == outs[0][2:]
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12,
+                           want_scale_mask=True)
+    assert outs[0][3] == ref.n_edges
+    solver = tpp.RobustRegistrationSolver(p)
+    solver.solve(pb.src, pb.dst)
+    A = np.unpackbits(ref.adjacency.view(np.uint8), axis=1, bitorder="little")[:, :200].astype(bool)
+    assert solver.getScaleInliers() == list(zip(*[x.tolist() for x in np.nonzero(np.triu(A, 1))]))
+    assert np.array_equal(solver.getScaleInliersMask()[0], ref.scale_mask.astype(bool))
+    assert solver.getInlierGraph() == [np.flatnonzero(r).tolist() for r in A]
+    assert np.array_equal(solver.getRotationInliersMap()[0], ref.clique[ref.rotation_inliers])
+    assert np.array_equal(solver.getTranslationInliersMap()[0], ref.clique[ref.rotation_inliers][ref.translation_inliers])
+
+
+def test_torch_cuda_inputs_zero_copy(oracle_mod):
+    import torch
+    import teaserpp_python as tpp
+    pb = synth.make_problem(300, 0.5, 41)
+    s = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound))
+    a = s.solve(pb.src, pb.dst)
+    ts = torch.from_numpy(np.ascontiguousarray(pb.src.T)).cuda().T   # (3,N) view with strides (1,3)
+    td = torch.from_numpy(np.ascontiguousarray(pb.dst.T)).cuda().T
+    s2 = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound))
+    b = s2.solve(ts, td)
+    assert np.array_equal(a.rotation, b.rotation) and np.array_equal(a.translation, b.translation)
+    tc = torch.from_numpy(np.ascontiguousarray(pb.src)).cuda()      # C-order (3,N): strided gather path
+    tdc = torch.from_numpy(np.ascontiguousarray(pb.dst)).cuda()
+    s3 = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound))
+    c = s3.solve(tc, tdc)
+    assert np.array_equal(a.rotation, c.rotation) and s3.getInlierMaxClique() == s.getInlierMaxClique()
+
+
+def _bits_from_dense(A):
+    n = A.shape[0]
+    W = (n + 31) // 32
+    pad = np.zeros((n, W * 32), np.uint8)
+    pad[:, :n] = A
+    return np.packbits(pad, axis=1, bitorder="little").view(np.uint32).reshape(n, W)
+
+
+def _clique_of_graph(A, mode=0, kcore_thr=0.5):
+    """Feed an explicit graph to the GPU clique stages through b2r_solve_from_adjacency."""
+    import torch
+    import teaserpp_python as tpp
+    from poseestimator_b200 import batch
+    n = A.shape[0]
+    pitch = batch.pitch_words(n)
+    bits = np.zeros((n, pitch), np.uint32)
+    bits[:, : (n + 31) // 32] = _bits_from_dense(A)
+    p = _params(tpp, 0.01, inlier_selection_mode=mode, kcore_heuristic_threshold=kcore_thr)
+    bs = batch.BatchSolver(p)
+    pts = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
+    adj = torch.from_numpy(bits.view(np.int32)).cuda()
+    torch.cuda.synchronize()
+    bs.solve_from_adjacency(pts.data_ptr(), pts.data_ptr(), n, adj.data_ptr(), pitch)
+    return bs.max_clique(0).tolist(), bs.stats(0)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_max_clique_random_graphs_with_ties(oracle_mod, seed):
+    """Exact search + canonical tie-break on graphs with many maximum cliques (heuristic alone is not enough)."""
+    rng = np.random.default_rng(100 + seed)
+    n = int(rng.integers(20, 400))
+    p = rng.uniform(0.05, 0.7) if n < 150 else rng.uniform(0.05, 0.3)
+    A = rng.random((n, n)) < p
+    A = np.triu(A, 1); A = A | A.T
+    want = oracle_mod.max_clique_bits(_bits_from_dense(A)).tolist()
+    got, st = _clique_of_graph(A)
+    assert got == want, (n, p, st)
+    assert st["exact_proven"] == 1
+
+
+def test_max_clique_planted_and_modes(oracle_mod):
+    rng = np.random.default_rng(3)
+    n = 600
+    A = rng.random((n, n)) < 0.05
+    A = np.triu(A, 1); A = A | A.T
+    planted = np.sort(rng.permutation(n)[:40])
+    A[np.ix_(planted, planted)] = True
+    np.fill_diagonal(A, False)
+    bits = _bits_from_dense(A)
+    got, st = _clique_of_graph(A)
+    assert got == planted.tolist() and st["omega"] == 40
+    for mode in (1, 3):
+        got, _ = _clique_of_graph(A, mode=mode)
+        assert got == oracle_mod.max_clique_bits(bits, mode=mode).tolist()
+    got, _ = _clique_of_graph(A, mode=2, kcore_thr=0.05)
+    assert got == oracle_mod.max_clique_bits(bits, mode=2, kcore_thr=0.05).tolist()
+    got, _ = _clique_of_graph(A, mode=2, kcore_thr=0.9)   # threshold not met -> heuristic fall-through
+    assert got == oracle_mod.max_clique_bits(bits, mode=2, kcore_thr=0.9).tolist()
+
+
+def test_batch_mixed_sizes_matches_single_solves(oracle_mod):
+    import teaserpp_python as tpp
+    from poseestimator_b200 import batch
+    pbs = [synth.config4_detection(0, d) for d in range(12)]
+    nb = pbs[0].noise_bound
+    bs = batch.BatchSolver(_params(tpp, nb))
+    sols = bs.solve([(p.src, p.dst) for p in pbs])
+    for i, pb in enumerate(pbs):
+        ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=nb, estimate_scaling=0, rotation_cost_threshold=1e-12)
+        assert bs.max_clique(i).tolist() == ref.clique.tolist()
+        assert np.array_equal(bs.adjacency(i, pb.src.shape[1]), ref.adjacency)
+        assert synth.rotation_error_rad(sols[i].rotation, ref.rotation) < ROT_TOL
+        assert np.linalg.norm(sols[i].translation - ref.translation) < TRANS_TOL_REL * pb.scene_scale
+    # a second batch on the same handle (workspace re-use) and determinism
+    sols2 = bs.solve([(p.src, p.dst) for p in pbs[:5]])
+    for a, b in zip(sols2, sols[:5]):
+        assert np.array_equal(a.rotation, b.rotation) and np.array_equal(a.translation, b.translation)
+
+
+def test_complete_tim_graph_and_none_mode(oracle_mod):
+    import teaserpp_python as tpp
+    pb = synth.make_problem(150, 0.4, 51)
+    for kw, okw in ((dict(rotation_tim_graph=tpp.RobustRegistrationSolver.INLIER_GRAPH_FORMULATION.COMPLETE), dict(rotation_tim_graph=1)),
+                    (dict(inlier_selection_mode=tpp.RobustRegistrationSolver.INLIER_SELECTION_MODE.NONE), dict(inlier_selection_mode=3))):
+        s = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound, **kw))
+        sol = s.solve(pb.src, pb.dst)
+        ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12, **okw)
+        assert s.getInlierMaxClique() == ref.clique.tolist()
+        assert synth.rotation_error_rad(sol.rotation, ref.rotation) < ROT_TOL
+        assert np.linalg.norm(sol.translation - ref.translation) < TRANS_TOL_REL * pb.scene_scale
+        assert s.getRotationInliers() == ref.rotation_inliers.tolist()
+
+
+def test_row_sharded_graph_equals_full(oracle_mod):
+    """Config-5 building block: rows computed in shards (as 4 ranks would) == full graph; solve continues from it."""
+    import torch
+    import teaserpp_python as tpp
+    from poseestimator_b200 import batch
+    pb = synth.make_problem(1500, 0.9, 61)
+    n = 1500
+    pitch = batch.pitch_words(n)
+    bs = batch.BatchSolver(_params(tpp, pb.noise_bound))
+    src = torch.from_numpy(np.ascontiguousarray(pb.src.T)).cuda()
+    dst = torch.from_numpy(np.ascontiguousarray(pb.dst.T)).cuda()
+    adj = torch.zeros((n, pitch), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    bounds = [0, 375, 750, 1125, 1500]
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        bs.graph_rows(src.data_ptr(), dst.data_ptr(), n, a, b, adj[a:b].data_ptr(), pitch)
+    sol = bs.solve_from_adjacency(src.data_ptr(), dst.data_ptr(), n, adj.data_ptr(), pitch)
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12)
+    got = adj.cpu().numpy().view(np.uint32)[:, : (n + 31) // 32]
+    assert np.array_equal(got, ref.adjacency)
+    assert bs.max_clique(0).tolist() == ref.clique.tolist()
+    assert synth.rotation_error_rad(sol.rotation, ref.rotation) < ROT_TOL
