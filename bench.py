@@ -44,28 +44,41 @@ GRAPH_FP64_OPS_PER_PAIR = 19  # 6 sub, 6 mul, 4 add, 1 sub, 1 abs,
 
 
 class ClockSampler(threading.Thread):
+    """nvidia-smi -lms 100 in the background during the timed region (B200_PROFILING.md clocks line)."""
+
     def __init__(self, index: int):
         super().__init__(daemon=True)
         self.index = index
-        self.stop_flag = False
         self.rows = []
+        self.proc = None
 
     def run(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-        while not self.stop_flag:
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:  # noqa: BLE001
+            pass
+
+    def stop(self):
+        if self.proc is not None:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                self.proc.terminate()
             except Exception:  # noqa: BLE001
                 pass
-            time.sleep(0.1)
+        self.join(timeout=2)
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        def num(x):
+            try:
+                return float(x)
+            except ValueError:
+                return None
+        sm = [num(r[0]) for r in self.rows if len(r) >= 6 and num(r[0]) is not None]
+        mx = [num(r[1]) for r in self.rows if len(r) >= 6 and num(r[1]) is not None]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) >= 6 and r[2 + i].lower().startswith("active")})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
@@ -177,7 +190,8 @@ def main():
     B = args.batch
     pbs = make_problems(B, rank)
     nb = pbs[0].noise_bound
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()  # a real stream handle: the library's kernels, the L2 flush and the events share it
+    torch.cuda.set_stream(stream)
     solver = b2batch.BatchSolver(solver_params(nb), device=local, stream=stream.cuda_stream, profiling=True)
 
     # ---- inputs resident in HBM ----------------------------------------------------------------------------
@@ -238,8 +252,7 @@ def main():
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     assert all(s.valid for s in sols)
-    sampler.stop_flag = True
-    sampler.join(timeout=2)
+    sampler.stop()
 
     # ---- single-registration latency through teaserpp_python ------------------------------------------------
     import teaserpp_python as tpp

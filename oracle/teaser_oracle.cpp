@@ -329,25 +329,43 @@ void core_numbers(const std::vector<std::vector<int>>& adj, std::vector<int>& co
   for (int v = 0; v < n; ++v) max_core = std::max(max_core, core[v]);
 }
 
-// Shared deterministic heuristic (documented deviation from PMC's own heuristic,
-// whose result depends on thread timing upstream): for every seed v, greedily
-// grow a clique inside N(v), always taking the candidate with the highest graph
-// degree (ties: lowest id).  Winner: largest clique, ties -> lowest seed id.
+// Shared deterministic heuristic (documented deviation from PMC's own heuristic, whose result depends on thread
+// timing upstream).  From a seed v, P = N(v); every round computes degP(w) = |N(w) & P| for all members:
+//   * members adjacent to every other member (degP == |P|-1) are all taken at once;
+//   * otherwise the member with the largest degP (ties: lowest id) is taken and P &= N(u).
+// Winner over the seeds: largest clique, ties -> lowest seed id.
 void greedy_from_seed(const BitGraph& G, const std::vector<int>& deg, int seed, std::vector<int>& out, int stop_below) {
+  (void)deg;
   const int W = G.W;
-  std::vector<u64> P(G.row(seed), G.row(seed) + W);
+  std::vector<u64> P(G.row(seed), G.row(seed) + W), U((size_t)W);
   out.clear(); out.push_back(seed);
   int cnt = popc(P.data(), W);
   while (cnt > 0) {
     if ((int)out.size() + cnt < stop_below) { out.clear(); return; }  // cannot even tie
-    int best = -1, bd = -1;
+    std::fill(U.begin(), U.end(), 0);
+    int best = -1, bd = -1, nU = 0;
     for (int w = 0; w < W; ++w) {
       u64 x = P[w];
-      while (x) { const int u = w * 64 + __builtin_ctzll(x); x &= x - 1; if (deg[u] > bd) { bd = deg[u]; best = u; } }
+      while (x) {
+        const int u = w * 64 + __builtin_ctzll(x); x &= x - 1;
+        const u64* r = G.row(u);
+        int c = 0;
+        for (int y = 0; y < W; ++y) c += __builtin_popcountll(r[y] & P[y]);
+        if (c > bd) { bd = c; best = u; }
+        if (c == cnt - 1) { U[w] |= (u64)1 << (u & 63); ++nU; }
+      }
     }
-    out.push_back(best);
-    const u64* r = G.row(best);
-    for (int w = 0; w < W; ++w) P[w] &= r[w];
+    if (nU > 0) {
+      for (int w = 0; w < W; ++w) {
+        u64 x = U[w];
+        while (x) { out.push_back(w * 64 + __builtin_ctzll(x)); x &= x - 1; }
+        P[w] &= ~U[w];
+      }
+    } else {
+      out.push_back(best);
+      const u64* r = G.row(best);
+      for (int w = 0; w < W; ++w) P[w] &= r[w];
+    }
     cnt = popc(P.data(), W);
   }
 }

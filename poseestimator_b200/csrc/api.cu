@@ -100,9 +100,15 @@ void fill_kernel_params(b2r_solver* s) {
   k.beta = 2 * p.noise_bound * sqrt(p.cbar2);  // (2*nb)*sqrt(cbar2), A.4-2
   const double beta2 = k.beta * k.beta;
   k.half_beta2 = 0.5 * beta2;
-  const double tau = p.graph_filter_tau > 0 ? p.graph_filter_tau : 1e-9;
-  k.stau = 0.5 * sqrt(tau);
-  k.stau_beta2 = k.stau * beta2;
+  {
+    unsigned long long bits;
+    memcpy(&bits, &beta2, sizeof(bits));
+    k.e_beta2 = (int)((bits >> 52) & 0x7ff);
+    // default band: |F| < 2^-24..2^-28 of Sigma^2; graph_filter_tau widens it (tests force the exact path with it)
+    int shift = 0;
+    if (p.graph_filter_tau > 0) { shift = (int)ceil(log2(p.graph_filter_tau) + 28.0); if (shift < 0) shift = 0; if (shift > 64) shift = 64; }
+    k.filter_shift = shift;
+  }
   k.noise_bound = p.noise_bound; k.cbar2 = p.cbar2;
   k.rot_noise_bound = p.rotation_noise_bound;
   k.gnc_factor = p.rotation_gnc_factor; k.cost_threshold = p.rotation_cost_threshold;

@@ -90,15 +90,23 @@ __device__ __forceinline__ void bs_keep_above(uint32_t (&X)[WPL], unsigned v, in
 // ---------------------------------------------------------------------------------------------------------
 // 1. greedy heuristic
 // ---------------------------------------------------------------------------------------------------------
+// One warp grows a clique from `seed` inside P = N(seed).  Every round it evaluates, for ALL members w of P at once
+// (independent row loads -> memory-level parallelism instead of a dependent chain), degP(w) = |N(w) & P|:
+//   * members adjacent to every other member (degP == |P|-1) are all taken in one go;
+//   * otherwise the member with the largest degP (ties: lowest id) is taken and P &= N(u).
+// A dominant clique is therefore swallowed in 2-4 rounds instead of |clique| dependent steps.
+// The same rule is restated in oracle/teaser_oracle.cpp (greedy_from_seed) for the PMC_HEU / KCORE_HEU modes.
 template <int WPL>
-__device__ __forceinline__ int greedy_grow(const ProbDesc& d, int W, int v, int lane, bool allow_abort, uint32_t (&Cb)[WPL],
-                                           bool record) {
+__device__ __forceinline__ int greedy_grow(const ProbDesc& d, int W, int v, int lane, bool strict, uint32_t* sP,
+                                           uint32_t (&Cb)[WPL], bool record) {
+  constexpr int UN = WPL <= 8 ? 4 : (WPL <= 16 ? 2 : 1);
   uint32_t P[WPL];
   const uint32_t* row0 = d.adj + (size_t)v * d.pitch;
 #pragma unroll
   for (int s = 0; s < WPL; ++s) {
     const int w = lane + 32 * s;
     P[s] = (w < W) ? row0[w] : 0u;
+    if (w < W) sP[w] = P[s];
     if (record) Cb[s] = 0u;
   }
   if (record && lane == ((v >> 5) & 31)) {
@@ -106,61 +114,222 @@ __device__ __forceinline__ int greedy_grow(const ProbDesc& d, int W, int v, int 
     for (int s = 0; s < WPL; ++s)
       if (s == (v >> 10)) Cb[s] |= 1u << (v & 31);
   }
+  __syncwarp();
   int size = 1;
   int cnt = bs_count<WPL>(P);
-  int step = 0;
-  int lbnow = allow_abort ? *(volatile int*)&d.st->lb : 0;
   while (cnt > 0) {
-    if (allow_abort) {
-      if ((step & 15) == 15) lbnow = *(volatile int*)&d.st->lb;
-      if (size + cnt < lbnow) return 0;  // cannot even tie the incumbent
-    }
-    unsigned key = 0;
+    const int lbnow = *(volatile int*)&d.st->lb;
+    if (strict ? (size + cnt <= lbnow) : (size + cnt < lbnow)) return 0;  // cannot improve (strict) / tie (non-strict)
+    unsigned best = 0;
+    uint32_t U[WPL];
 #pragma unroll
-    for (int s = 0; s < WPL; ++s) {
-      uint32_t bits = P[s];
-      const unsigned base = (unsigned)(lane + 32 * s) << 5;
-      while (bits) {
-        const unsigned id = base + (__ffs(bits) - 1);
-        bits &= bits - 1;
-        const unsigned k = ((unsigned)__ldg(&d.deg[id]) << 16) | (0xffffu - id);
-        key = max(key, k);
+    for (int s = 0; s < WPL; ++s) U[s] = 0u;
+    int wi = 0;
+    uint32_t word = sP[0];
+    for (;;) {
+      int ids[UN];
+#pragma unroll
+      for (int q = 0; q < UN; ++q) {
+        while (word == 0u && wi + 1 < W) { ++wi; word = sP[wi]; }
+        if (word) { ids[q] = 32 * wi + (__ffs(word) - 1); word &= word - 1; }
+        else ids[q] = -1;
+      }
+      if (ids[0] < 0) break;
+      int c[UN];
+#pragma unroll
+      for (int q = 0; q < UN; ++q) {
+        c[q] = 0;
+        if (ids[q] >= 0) {
+          const uint32_t* row = d.adj + (size_t)ids[q] * d.pitch;
+#pragma unroll
+          for (int s = 0; s < WPL; ++s) {
+            const int w = lane + 32 * s;
+            if (w < W) c[q] += __popc(P[s] & __ldg(row + w));
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < UN; ++q) {
+        if (ids[q] < 0) continue;
+        const int cq = __reduce_add_sync(FULL, c[q]);
+        const unsigned id = (unsigned)ids[q];
+        best = max(best, ((unsigned)cq << 16) | (0xffffu - id));
+        if (cq == cnt - 1 && lane == (int)((id >> 5) & 31)) {
+#pragma unroll
+          for (int s = 0; s < WPL; ++s)
+            if (s == (int)(id >> 10)) U[s] |= 1u << (id & 31);
+        }
       }
     }
-    key = __reduce_max_sync(FULL, key);
-    const unsigned u = 0xffffu - (key & 0xffffu);
-    ++size;
-    if (record && lane == (int)((u >> 5) & 31)) {
+    const int nU = bs_count<WPL>(U);
+    if (nU > 0) {
+      size += nU;
 #pragma unroll
-      for (int s = 0; s < WPL; ++s)
-        if (s == (int)(u >> 10)) Cb[s] |= 1u << (u & 31);
+      for (int s = 0; s < WPL; ++s) { P[s] &= ~U[s]; if (record) Cb[s] |= U[s]; }
+    } else {
+      const unsigned u = 0xffffu - (best & 0xffffu);
+      ++size;
+      if (record && lane == (int)((u >> 5) & 31)) {
+#pragma unroll
+        for (int s = 0; s < WPL; ++s)
+          if (s == (int)(u >> 10)) Cb[s] |= 1u << (u & 31);
+      }
+      bs_and_row<WPL>(P, d.adj + (size_t)u * d.pitch, W, lane);
     }
-    bs_and_row<WPL>(P, d.adj + (size_t)u * d.pitch, W, lane);
     cnt = bs_count<WPL>(P);
-    ++step;
+    __syncwarp();
+#pragma unroll
+    for (int s = 0; s < WPL; ++s) {
+      const int w = lane + 32 * s;
+      if (w < W) sP[w] = P[s];
+    }
+    __syncwarp();
   }
   return size;
 }
 
+// all_seeds == 0 (PMC_EXACT): 8 warps per problem, warp k starts from the highest-degree vertex of id class k
+//                             (picked by degree_kernel); the bound only has to be good, the exact search proves it.
+// all_seeds == 1 (PMC_HEU / KCORE_HEU): every vertex is a seed; winner = largest clique, ties -> lowest seed id.
 template <int WPL>
-__global__ void __launch_bounds__(256) heuristic_kernel(const ProbDesc* __restrict__ descs) {
+__global__ void __launch_bounds__(256) heuristic_kernel(const ProbDesc* __restrict__ descs, int all_seeds) {
+  extern __shared__ uint32_t sh[];
   const ProbDesc d = descs[blockIdx.y];
-  const int lane = threadIdx.x & 31;
-  const int v = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (v >= d.n) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int W = words_for(d.n);
-  if (d.deg[v] + 1 < *(volatile int*)&d.st->lb) return;
+  int v;
+  if (all_seeds) {
+    v = blockIdx.x * 8 + warp;
+    if (v >= d.n) return;
+    if (d.deg[v] + 1 < *(volatile int*)&d.st->lb) return;
+  } else {
+    const unsigned long long key = d.st->seed_key[warp];
+    if (key == 0ull) return;
+    v = (int)(0xffffffffu - (unsigned)(key & 0xffffffffu));
+  }
   uint32_t dummy[WPL];
-  const int size = greedy_grow<WPL>(d, W, v, lane, true, dummy, false);
+  const int size = greedy_grow<WPL>(d, W, v, lane, !all_seeds, sh + (size_t)warp * W, dummy, false);
   if (size > 0 && lane == 0) {
     atomicMax(&d.st->heu_key, ((unsigned long long)size << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
     atomicMax(&d.st->lb, size);
   }
 }
 
+// CTA-per-seed variant of the same greedy rule (PMC_EXACT path): the degP evaluation of one round is spread over 32
+// warps with 4 independent row loads in flight per warp, so a round costs a few L2 round trips instead of |P| of them.
+// grid = (seeds per problem, batch); seed k = highest-degree vertex of id class k (degree_kernel).
+constexpr int kHeuThreads = 1024;
+constexpr int kHeuSeeds = 4;   // of the 8 id classes; the bound only has to be good, the exact search proves it
+__global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const ProbDesc* __restrict__ descs) {
+  extern __shared__ uint32_t sh[];
+  const ProbDesc d = descs[blockIdx.y];
+  ProbState* st = d.st;
+  const unsigned long long skey = st->seed_key[blockIdx.x];
+  if (skey == 0ull) return;
+  const int v = (int)(0xffffffffu - (unsigned)(skey & 0xffffffffu));
+  const int n = d.n;
+  const int W = words_for(n);
+  const int Wb = (n + 31) >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = kHeuThreads / 32;
+  uint32_t* P = sh;                       // W
+  uint32_t* U = sh + W;                   // W
+  int* scan = (int*)(sh + 2 * W);         // 40
+  unsigned* s_best = (unsigned*)(scan + 40);
+  int* s_nU = (int*)(scan + 41);
+  int* s_lb = (int*)(scan + 42);
+  unsigned short* list = (unsigned short*)(scan + 48);  // n entries
+  const uint32_t* row0 = d.adj + (size_t)v * d.pitch;
+  for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] = row0[w];
+  __syncthreads();
+  int size = 1;
+  for (;;) {
+    // ascending member list + count
+    __shared__ int sh_base2;
+    if (threadIdx.x == 0) sh_base2 = 0;
+    __syncthreads();
+    for (int w0 = 0; w0 < Wb; w0 += kHeuThreads) {
+      const int w = w0 + threadIdx.x;
+      const uint32_t word = (w < Wb) ? P[w] : 0u;
+      const int c = __popc(word);
+      int incl = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+      if (lane == 31) scan[warp] = incl;
+      __syncthreads();
+      if (warp == 0) {
+        int x = scan[lane], xi = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, xi, o); if (lane >= o) xi += t; }
+        scan[lane] = xi - x;
+        if (lane == 31) scan[32] = xi;
+      }
+      __syncthreads();
+      int pos = sh_base2 + scan[warp] + incl - c;
+      uint32_t bits = word;
+      while (bits) { list[pos++] = (unsigned short)(32 * w + (__ffs(bits) - 1)); bits &= bits - 1; }
+      __syncthreads();
+      if (threadIdx.x == 0) sh_base2 += scan[32];
+      __syncthreads();
+    }
+    const int cnt = sh_base2;
+    if (cnt == 0) break;
+    if (threadIdx.x == 0) { *s_lb = *(volatile int*)&st->lb; *s_best = 0u; *s_nU = 0; }
+    for (int w = threadIdx.x; w < W; w += kHeuThreads) U[w] = 0u;
+    __syncthreads();
+    if (size + cnt <= *s_lb) return;  // another seed already reached this size: cannot improve
+    unsigned wbest = 0;
+    for (int m0 = warp; m0 < cnt; m0 += 4 * NW) {
+      int c[4];
+      int ids[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int m = m0 + q * NW;
+        ids[q] = m < cnt ? (int)list[m] : -1;
+        c[q] = 0;
+        if (ids[q] >= 0) {
+          const uint32_t* row = d.adj + (size_t)ids[q] * d.pitch;
+          for (int w = lane; w < W; w += 32) c[q] += __popc(__ldg(row + w) & P[w]);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (ids[q] < 0) continue;
+        const int cq = __reduce_add_sync(FULL, c[q]);
+        const unsigned id = (unsigned)ids[q];
+        wbest = max(wbest, ((unsigned)cq << 16) | (0xffffu - id));
+        if (cq == cnt - 1 && lane == 0) atomicOr(&U[id >> 5], 1u << (id & 31));
+      }
+    }
+    if (lane == 0 && wbest) atomicMax(s_best, wbest);
+    __syncthreads();
+    int nu = 0;
+    for (int w = threadIdx.x; w < Wb; w += kHeuThreads) nu += __popc(U[w]);
+    nu = __reduce_add_sync(FULL, nu);
+    if (lane == 0 && nu) atomicAdd(s_nU, nu);
+    __syncthreads();
+    const int nU = *s_nU;
+    if (nU > 0) {
+      size += nU;
+      for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= ~U[w];
+    } else {
+      const unsigned u = 0xffffu - (*s_best & 0xffffu);
+      size += 1;
+      const uint32_t* row = d.adj + (size_t)u * d.pitch;
+      for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= row[w];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    atomicMax(&st->heu_key, ((unsigned long long)size << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
+    atomicMax(&st->lb, size);
+  }
+}
+
 // Re-runs the winning seed and writes its clique (ascending ids).  PMC_HEU / KCORE_HEU fall-through only.
 template <int WPL>
 __global__ void __launch_bounds__(32) heuristic_replay_kernel(const ProbDesc* __restrict__ descs) {
+  extern __shared__ uint32_t sh[];
   const ProbDesc d = descs[blockIdx.x];
   const int lane = threadIdx.x;
   if (d.st->clique_size >= 0) return;  // already decided (k-core shortcut)
@@ -168,7 +337,9 @@ __global__ void __launch_bounds__(32) heuristic_replay_kernel(const ProbDesc* __
   const unsigned long long key = d.st->heu_key;
   const int seed = (int)(0xffffffffu - (unsigned)(key & 0xffffffffu));
   uint32_t Cb[WPL];
-  greedy_grow<WPL>(d, W, seed, lane, false, Cb, true);
+  if (lane == 0) d.st->lb = 0;  // replay must not abort against the bound it produced itself
+  __syncwarp();
+  greedy_grow<WPL>(d, W, seed, lane, false, sh, Cb, true);
   int off = 0;
   for (int w = 0; w < W; ++w) {
     uint32_t word = 0;
@@ -179,7 +350,7 @@ __global__ void __launch_bounds__(32) heuristic_replay_kernel(const ProbDesc* __
     if ((word >> lane) & 1) d.clique[off + __popc(word & ((1u << lane) - 1u))] = 32 * w + lane;
     off += __popc(word);
   }
-  if (lane == 0) { d.st->clique_size = off; d.st->omega = off; }
+  if (lane == 0) { d.st->clique_size = off; d.st->omega = off; d.st->lb = off; }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -745,22 +916,26 @@ static int wpl_for(int n_max) {
 }
 
 template <template <int> class Launcher>
-static void dispatch_wpl(int wpl, const ProbDesc* d_desc, dim3 grid, int block, cudaStream_t st) {
+static void dispatch_wpl(int wpl, const ProbDesc* d_desc, dim3 grid, int block, size_t smem, int arg, cudaStream_t st) {
   switch (wpl) {
-    case 1: Launcher<1>::go(d_desc, grid, block, st); break;
-    case 2: Launcher<2>::go(d_desc, grid, block, st); break;
-    case 4: Launcher<4>::go(d_desc, grid, block, st); break;
-    case 8: Launcher<8>::go(d_desc, grid, block, st); break;
-    case 16: Launcher<16>::go(d_desc, grid, block, st); break;
-    case 32: Launcher<32>::go(d_desc, grid, block, st); break;
-    default: Launcher<64>::go(d_desc, grid, block, st); break;
+    case 1: Launcher<1>::go(d_desc, grid, block, smem, arg, st); break;
+    case 2: Launcher<2>::go(d_desc, grid, block, smem, arg, st); break;
+    case 4: Launcher<4>::go(d_desc, grid, block, smem, arg, st); break;
+    case 8: Launcher<8>::go(d_desc, grid, block, smem, arg, st); break;
+    case 16: Launcher<16>::go(d_desc, grid, block, smem, arg, st); break;
+    case 32: Launcher<32>::go(d_desc, grid, block, smem, arg, st); break;
+    default: Launcher<64>::go(d_desc, grid, block, smem, arg, st); break;
   }
 }
 template <int WPL> struct HeuLaunch {
-  static void go(const ProbDesc* d, dim3 g, int b, cudaStream_t s) { heuristic_kernel<WPL><<<g, b, 0, s>>>(d); }
+  static void go(const ProbDesc* d, dim3 g, int b, size_t smem, int all_seeds, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(heuristic_kernel<WPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024); attr = true; }
+    heuristic_kernel<WPL><<<g, b, smem, s>>>(d, all_seeds);
+  }
 };
 template <int WPL> struct ReplayLaunch {
-  static void go(const ProbDesc* d, dim3 g, int b, cudaStream_t s) { heuristic_replay_kernel<WPL><<<g, b, 0, s>>>(d); }
+  static void go(const ProbDesc* d, dim3 g, int b, size_t smem, int, cudaStream_t s) { heuristic_replay_kernel<WPL><<<g, b, smem, s>>>(d); }
 };
 
 static size_t g_smem_optin = 0;
@@ -775,6 +950,7 @@ static size_t smem_optin_bytes() {
     cudaFuncSetAttribute(canon_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
     cudaFuncSetAttribute(prune_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cudaFuncSetAttribute(kcore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(heuristic_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
   }
   return g_smem_optin;
 }
@@ -800,11 +976,17 @@ int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelPara
     mark_undecided_kernel<<<(batch + 127) / 128, 128, 0, st>>>(d_desc, batch);
     ++launches;
   }
-  dispatch_wpl<HeuLaunch>(wpl, d_desc, gseed, 256, st);
+  const bool all_seeds = kp.inlier_mode != B2R_INLIER_PMC_EXACT;
+  if (all_seeds) {
+    dispatch_wpl<HeuLaunch>(wpl, d_desc, gseed, 256, (size_t)8 * W * 4, 1, st);
+  } else {
+    const size_t hs = (size_t)(2 * W + 64) * 4 + (size_t)2 * (n_max + 8);
+    heuristic_block_kernel<<<dim3(kHeuSeeds, batch), kHeuThreads, hs, st>>>(d_desc);
+  }
   ++launches;
   if (ev) cudaEventRecord(ev[0], st);
   if (kp.inlier_mode != B2R_INLIER_PMC_EXACT) {
-    dispatch_wpl<ReplayLaunch>(wpl, d_desc, dim3(batch), 32, st);
+    dispatch_wpl<ReplayLaunch>(wpl, d_desc, dim3(batch), 32, (size_t)W * 4, 0, st);
     ++launches;
     if (ev) for (int i = 1; i < 4; ++i) cudaEventRecord(ev[i], st);
     return launches;

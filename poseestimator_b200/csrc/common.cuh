@@ -26,6 +26,7 @@ struct ProbState {
   int max_deg;
   int lb;                // heuristic lower bound (clique size)
   unsigned long long heu_key;   // (size << 32) | (0xffffffff - seed): deterministic heuristic winner
+  unsigned long long seed_key[8];  // per id class (v & 7): (deg << 32) | (0xffffffff - v) of its highest-degree vertex
   unsigned long long deg_sum;   // 2 * edges
   int T;                 // prune threshold used for the compact graph
   int n_alive;           // compact graph size n'
@@ -73,8 +74,8 @@ struct ProbDesc {
 struct KernelParams {
   double beta;           // 2 * noise_bound * sqrt(cbar2)
   double half_beta2;     // 0.5 * beta^2
-  double stau;           // sqrt(tau) / 2
-  double stau_beta2;     // stau * beta^2
+  int e_beta2;           // biased fp64 exponent of beta^2
+  int filter_shift;      // widens the ambiguity band of the sqrt-free filter by 2^shift (tests)
   double noise_bound, cbar2;
   double rot_noise_bound;
   double gnc_factor, cost_threshold;

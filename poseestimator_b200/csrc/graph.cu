@@ -15,8 +15,10 @@
 // A and B are formed with exactly those roundings (__dmul_rn/__dadd_rn).  The two DSQRTs are avoided by a
 // sqrt-free sign test that is provably equivalent outside a tiny ambiguity band (DESIGN.md "graph filter"):
 //     D = A + B - beta^2,  F = D^2 - 4AB,  in  <=>  D <= 0  or  F <= 0,
-// trusted only when |F| > tau * (A + B + beta^2)^2 (tau = 1e-9, seven orders above the rounding error of F and
-// of the reference's own sqrt/sub); the rest (about 1e-8 of the pairs) take the exact two-sqrt path.
+// trusted only when |F| is at least 2^-28 of (A + B + beta^2)^2 (seven orders above the rounding error of F and of
+// the reference's own sqrt/sub); a 32-row chunk containing any other pair (about 1e-4 of the chunks) is redone with
+// the exact two-sqrt path.  The hot loop is branch-free: 20 FP64-pipe instructions per pair, the sign and band tests
+// run on the integer pipe.
 #include "common.cuh"
 
 namespace b2r {
@@ -31,21 +33,28 @@ __device__ __forceinline__ bool verdict_exact(double A, double B, double beta) {
   return fabs(__dsub_rn(a, b)) <= beta;
 }
 
-template <bool kExactOnly>
-__device__ __forceinline__ bool verdict(double A, double B, const KernelParams& kp, unsigned& slow) {
-  if (kExactOnly) return verdict_exact(A, B, kp.beta);
+// Fast verdict, FP64 pipe: 6 sub + 6 mul + 4 add (A, B in reference rounding) + S1, H, AB, F = 20 instructions.
+// Everything else runs on the integer pipe:  in = sign(H) | sign(F);  ambiguous <=> |F| < 2^-24 * Sigma^2 judged on the
+// biased exponents (eF < 2*max(e(S1), e(beta^2)) - 1047 + shift), or F not finite / subnormal.
+// Rigor (DESIGN.md "graph filter"): not ambiguous => |F| > 2^-28 * Sigma^2, seven orders of magnitude above both the
+// rounding error of F and the reference's own sqrt/sub rounding, so sign(F) decides exactly like the reference.
+__device__ __forceinline__ void verdict_fast(double A, double B, const KernelParams& kp, bool& in, bool& amb) {
   const double S1 = A + B;
-  const double H = fma(0.5, S1, -kp.half_beta2);       // D / 2
+  const double H = fma(0.5, S1, -kp.half_beta2);  // D / 2,  D = A + B - beta^2
   const double AB = A * B;
-  const double F = fma(H, H, -AB);                     // (D^2 - 4AB) / 4
-  const double Sg = fma(kp.stau, S1, kp.stau_beta2);   // sqrt(tau)/2 * (A + B + beta^2)
-  bool in = (H <= 0.0) | (F <= 0.0);
-  if (!(fabs(F) > Sg * Sg)) {                          // ambiguous (also catches NaN): exact path
-    in = verdict_exact(A, B, kp.beta);
-    ++slow;
-  }
-  return in;
+  const double F = fma(H, H, -AB);                // (D^2 - 4AB) / 4
+  const int hH = __double2hiint(H), hF = __double2hiint(F), hS = __double2hiint(S1);
+  in = (hH | hF) < 0;
+  const int eF = (hF >> 20) & 0x7ff;
+  const int eS = (hS >> 20) & 0x7ff;
+  const int thr = max(2 * max(eS, kp.e_beta2) - 1047 + kp.filter_shift, 1);
+  amb = (eF < thr) | (eF == 0x7ff);
 }
+
+#ifndef B2R_ROW_UNROLL
+#define B2R_ROW_UNROLL 8
+#endif
+constexpr int kRowUnroll = B2R_ROW_UNROLL;
 
 struct TilePts {
   double2 a[kTile];  // (sx, sy)
@@ -56,7 +65,8 @@ struct TilePts {
 // Computes one 128x128 tile: rows i0.., columns j0...  Thread t owns column j0+t.
 // dir[t] (shared) receives the 4 words of row i0+t for the column block; tw[0..3] (registers) the 4 words of
 // row j0+t for the row block (transposed tile).
-template <bool kExactOnly>
+// kInterior: every row and column of the tile is < n and the tile is off the diagonal -> no validity tests at all.
+template <bool kExactOnly, bool kInterior>
 __device__ __forceinline__ void compute_tile(const double* __restrict__ src, const double* __restrict__ dst, int n,
                                              int i0, int j0, const KernelParams& kp, TilePts& sp,
                                              uint32_t (*dir)[4], uint32_t tw[4], unsigned& slow) {
@@ -64,7 +74,7 @@ __device__ __forceinline__ void compute_tile(const double* __restrict__ src, con
   {  // stage the row points (coalesced 24-byte AoS reads), zero-fill past n
     const int i = i0 + t;
     double v[6] = {0, 0, 0, 0, 0, 0};
-    if (i < n) {
+    if (kInterior || i < n) {
       v[0] = src[3 * (size_t)i]; v[1] = src[3 * (size_t)i + 1]; v[2] = src[3 * (size_t)i + 2];
       v[3] = dst[3 * (size_t)i]; v[4] = dst[3 * (size_t)i + 1]; v[5] = dst[3 * (size_t)i + 2];
     }
@@ -74,30 +84,59 @@ __device__ __forceinline__ void compute_tile(const double* __restrict__ src, con
   }
   const int j = j0 + t;
   double xj = 0, yj = 0, zj = 0, uj = 0, vj = 0, wj = 0;
-  const bool jok = j < n;
+  const bool jok = kInterior || j < n;
   if (jok) {
     xj = src[3 * (size_t)j]; yj = src[3 * (size_t)j + 1]; zj = src[3 * (size_t)j + 2];
     uj = dst[3 * (size_t)j]; vj = dst[3 * (size_t)j + 1]; wj = dst[3 * (size_t)j + 2];
   }
   __syncthreads();
-#pragma unroll
+  // The hot loop must stay inside the instruction cache: the chunk loop is NOT unrolled and the row loop only
+  // kRowUnroll times (ncu on the fully unrolled version: 'no_instruction' was the top stall reason).
+#pragma unroll 1
   for (int c = 0; c < 4; ++c) {
-    uint32_t tword = 0, dword = 0;
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int il = 32 * c + k;
-      const double2 pa = sp.a[il], pb = sp.b[il], pc = sp.c[il];
-      const double A = sq3_ref(__dsub_rn(xj, pa.x), __dsub_rn(yj, pa.y), __dsub_rn(zj, pb.x));
-      const double B = sq3_ref(__dsub_rn(uj, pb.y), __dsub_rn(vj, pc.x), __dsub_rn(wj, pc.y));
-      const int i = i0 + il;
-      bool in = verdict<kExactOnly>(A, B, kp, slow);
-      in = in && jok && (i < n) && (i != j);
-      const uint32_t bal = __ballot_sync(0xffffffffu, in);
-      if (lane == k) dword = bal;
-      tword |= (in ? 1u : 0u) << k;
+    uint32_t tword = 0;
+    bool any_amb = false;
+    if (!kExactOnly) {
+#pragma unroll kRowUnroll
+      for (int k = 0; k < 32; ++k) {
+        const int il = 32 * c + k;
+        const double2 pa = sp.a[il], pb = sp.b[il], pc = sp.c[il];
+        const double A = sq3_ref(__dsub_rn(xj, pa.x), __dsub_rn(yj, pa.y), __dsub_rn(zj, pb.x));
+        const double B = sq3_ref(__dsub_rn(uj, pb.y), __dsub_rn(vj, pc.x), __dsub_rn(wj, pc.y));
+        bool in, amb;
+        verdict_fast(A, B, kp, in, amb);
+        if (!kInterior) {
+          const int i = i0 + il;
+          const bool ok = jok && (i < n) && (i != j);
+          in = in && ok; amb = amb && ok;
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, in);
+        if (lane == 0) dir[il][warp] = bal;
+        tword |= (in ? 1u : 0u) << k;
+        any_amb |= amb;
+      }
     }
-    dir[32 * c + lane][warp] = dword;
-    tw[c] = tword;
+    if (kExactOnly || __any_sync(0xffffffffu, any_amb)) {
+      // rare (about 1e-4 of the chunks): redo the 32 rows with the reference's two square roots
+      tword = 0;
+      if (!kExactOnly) ++slow;
+#pragma unroll 1
+      for (int k = 0; k < 32; ++k) {
+        const int il = 32 * c + k;
+        const double2 pa = sp.a[il], pb = sp.b[il], pc = sp.c[il];
+        const double A = sq3_ref(__dsub_rn(xj, pa.x), __dsub_rn(yj, pa.y), __dsub_rn(zj, pb.x));
+        const double B = sq3_ref(__dsub_rn(uj, pb.y), __dsub_rn(vj, pc.x), __dsub_rn(wj, pc.y));
+        const int i = i0 + il;
+        bool in = verdict_exact(A, B, kp.beta);
+        in = in && jok && (i < n) && (i != j);
+        const uint32_t bal = __ballot_sync(0xffffffffu, in);
+        if (lane == 0) dir[il][warp] = bal;
+        tword |= (in ? 1u : 0u) << k;
+      }
+    }
+    // tw[c] = tword without dynamic register indexing
+    tw[0] = c == 0 ? tword : tw[0]; tw[1] = c == 1 ? tword : tw[1];
+    tw[2] = c == 2 ? tword : tw[2]; tw[3] = c == 3 ? tword : tw[3];
   }
   __syncthreads();
 }
@@ -115,9 +154,10 @@ __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __rest
   const int tj = ti + p;
   __shared__ TilePts sp;
   __shared__ uint32_t dir[kTile][4];
-  uint32_t tw[4];
+  uint32_t tw[4] = {0u, 0u, 0u, 0u};
   unsigned slow = 0;
-  compute_tile<kExactOnly>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow);
+  if (ti != tj && (tj + 1) * kTile <= n) compute_tile<kExactOnly, true>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow);
+  else compute_tile<kExactOnly, false>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow);
   const int t = threadIdx.x;
   const int i = ti * kTile + t;
   if (i < n) *reinterpret_cast<uint4*>(d.adj + (size_t)i * d.pitch + 4 * tj) = *reinterpret_cast<const uint4*>(dir[t]);
@@ -125,7 +165,7 @@ __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __rest
     const int j = tj * kTile + t;
     if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * ti) = make_uint4(tw[0], tw[1], tw[2], tw[3]);
   }
-  if (!kExactOnly && slow) atomicAdd(&d.st->slow_pairs, (unsigned long long)slow);
+  if (!kExactOnly && slow && (threadIdx.x & 31) == 0) atomicAdd(&d.st->slow_pairs, 1024ull * slow);
 }
 
 // Row-sharded variant (config 5): full rows [row_begin,row_end), every column tile, no symmetry trick, so a rank
@@ -138,31 +178,55 @@ __global__ void __launch_bounds__(kTile) tim_graph_rows_kernel(const double* __r
   const int tj = blockIdx.x;
   __shared__ TilePts sp;
   __shared__ uint32_t dir[kTile][4];
-  uint32_t tw[4];
+  uint32_t tw[4] = {0u, 0u, 0u, 0u};
   unsigned slow = 0;
   // rows beyond row_end are computed but not stored (n_eff trick keeps the ballot uniform)
-  compute_tile<kExactOnly>(src, dst, n, i0, tj * kTile, kp, sp, dir, tw, slow);
+  compute_tile<kExactOnly, false>(src, dst, n, i0, tj * kTile, kp, sp, dir, tw, slow);
   const int i = i0 + threadIdx.x;
   if (i < row_end && i < n)
     *reinterpret_cast<uint4*>(adj + (size_t)(i - row_begin) * pitch + 4 * tj) = *reinterpret_cast<const uint4*>(dir[threadIdx.x]);
-  if (!kExactOnly && slow && slow_pairs) atomicAdd(slow_pairs, (unsigned long long)slow);
+  if (!kExactOnly && slow && slow_pairs && (threadIdx.x & 31) == 0) atomicAdd(slow_pairs, 1024ull * slow);
 }
 
-// Degrees: one warp per row, popcount over the row's words; also max degree and 2*edges per problem.
+// Degrees: one warp per row (8 rows per warp, 64 rows per CTA), popcount over the row's words.  Per problem it also
+// leaves max degree, 2*edges and -- for the clique heuristic -- the highest-degree vertex of each id class (v & 7).
+// Same-address atomics are reduced per CTA first (they serialise in L2 otherwise).
+constexpr int kDegRowsPerBlock = 64;
 __global__ void __launch_bounds__(256) degree_kernel(const ProbDesc* __restrict__ descs) {
   const ProbDesc d = descs[blockIdx.y];
-  const int lane = threadIdx.x & 31;
-  const int v = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (v >= d.n) return;
+  __shared__ unsigned long long s_key[8];
+  __shared__ unsigned long long s_sum;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int v0 = blockIdx.x * kDegRowsPerBlock;
+  if (v0 >= d.n) return;
+  if (threadIdx.x < 8) s_key[threadIdx.x] = 0ull;
+  if (threadIdx.x == 8) s_sum = 0ull;
+  __syncthreads();
   const int W = 4 * ((d.n + kTile - 1) / kTile);
-  const uint32_t* row = d.adj + (size_t)v * d.pitch;
-  int c = 0;
-  for (int w = lane; w < W; w += 32) c += __popc(row[w]);
-  c = __reduce_add_sync(0xffffffffu, c);
-  if (lane == 0) {
-    d.deg[v] = c;
-    atomicMax(&d.st->max_deg, c);
-    atomicAdd(&d.st->deg_sum, (unsigned long long)c);
+  unsigned long long wsum = 0;
+#pragma unroll 2
+  for (int k = 0; k < 8; ++k) {
+    const int v = v0 + warp * 8 + k;
+    if (v >= d.n) break;
+    const uint32_t* row = d.adj + (size_t)v * d.pitch;
+    int c = 0;
+    for (int w = lane; w < W; w += 32) c += __popc(row[w]);
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) {
+      d.deg[v] = c;
+      wsum += (unsigned long long)c;
+      atomicMax(&s_key[v & 7], ((unsigned long long)c << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
+    }
+  }
+  if (lane == 0) atomicAdd(&s_sum, wsum);
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    if (s_key[threadIdx.x]) atomicMax(&d.st->seed_key[threadIdx.x], s_key[threadIdx.x]);
+  } else if (threadIdx.x == 8) {
+    atomicAdd(&d.st->deg_sum, s_sum);
+    unsigned long long m = 0;
+    for (int k = 0; k < 8; ++k) m = s_key[k] > m ? s_key[k] : m;
+    atomicMax(&d.st->max_deg, (int)(m >> 32));
   }
 }
 
@@ -186,7 +250,7 @@ int launch_tim_graph_rows(const double* src, const double* dst, int n, int row_b
 }
 
 int launch_degree(const ProbDesc* d_desc, int batch, int n_max, cudaStream_t st) {
-  dim3 grid((n_max + 7) / 8, batch);
+  dim3 grid((n_max + kDegRowsPerBlock - 1) / kDegRowsPerBlock, batch);
   degree_kernel<<<grid, 256, 0, st>>>(d_desc);
   return 1;
 }
