@@ -15,9 +15,7 @@ from . import _lib
 from .teaser import RegistrationSolution, _Params
 
 
-def shard_round_robin(n_items: int, rank: int, world: int) -> range:
-    """Static round-robin assignment of independent work items (detections) to ranks -- no collective needed."""
-    return range(rank, n_items, world)
+from .sharded import shard_round_robin  # noqa: E402,F401  (kept here for callers of the batch module)
 
 
 def _pack(a) -> np.ndarray:
