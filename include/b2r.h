@@ -149,9 +149,9 @@ b2r_status b2r_get_adjacency(b2r_solver* s, int idx, uint32_t* out, int words_pe
 b2r_status b2r_get_gnc_weights(b2r_solver* s, int idx, double* out);
 /* per-stage device times of the last batch in ms (needs b2r_set_profiling(s,1)):
  * [0] upload [1] graph [2] degree [3] heuristic [4] prune+compact [5] exact search [6] canonical clique
- * [7] rotation [8] translation [9] total */
+ * [7] rotation [8] translation [9] total [10] scale vote (estimate_scaling=True only) [11] reserved */
 b2r_status b2r_set_profiling(b2r_solver* s, int on);
-b2r_status b2r_get_timings(b2r_solver* s, float* ms10);
+b2r_status b2r_get_timings(b2r_solver* s, float* ms12);
 
 /* ---- pieces of the path exposed for sharding and tests -------------------------------------------- */
 /* Rows [row_begin,row_end) of the consistency graph of one problem into adj_out (device, pitch words per

@@ -127,10 +127,10 @@ class BatchSolver:
         return out[:T]
 
     def timings_ms(self) -> dict:
-        t = (C.c_float * 10)()
+        t = (C.c_float * 12)()
         _lib.check(self._h, _lib.lib().b2r_get_timings(self._h, t))
         names = ("upload", "graph", "degree", "heuristic", "prune_compact", "exact_search", "canonical", "rotation",
-                 "translation", "total")
+                 "translation", "total", "scale_vote")
         return dict(zip(names, [float(x) for x in t]))
 
     def launch_count(self) -> int:

@@ -60,7 +60,7 @@ struct b2r_solver {
   // workspace capacity
   int batch_cap = 0, n_cap = 0, pitch = 0;
   long long tim_cap = 0;
-  DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena;
+  DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena, d_scale;
   HostBuf h_state, h_desc, h_pts;
   size_t arena_words_per_warp = 64 * 1024;
   int bnb_blocks = 1;
@@ -73,9 +73,9 @@ struct b2r_solver {
   const uint32_t* ext_adj = nullptr;  // solve_from_adjacency
 
   bool profiling = false;
-  cudaEvent_t ev[10] = {};
+  cudaEvent_t ev[12] = {};
   bool ev_ready = false;
-  float timings[10] = {};
+  float timings[12] = {};
 };
 
 namespace {
@@ -195,7 +195,7 @@ void build_desc(b2r_solver* s, int b, int n, const double* dsrc, const double* d
 
 b2r_status ensure_events(b2r_solver* s) {
   if (s->ev_ready) return B2R_OK;
-  for (int i = 0; i < 10; ++i) CK(cudaEventCreate(&s->ev[i]));
+  for (int i = 0; i < 12; ++i) CK(cudaEventCreate(&s->ev[i]));
   s->ev_ready = true;
   return B2R_OK;
 }
@@ -207,6 +207,14 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
   CK(cudaMemsetAsync(s->d_state.p, 0, (size_t)batch * sizeof(ProbState), st));
   CK(cudaMemcpyAsync(s->d_desc.p, s->h_desc.p, (size_t)batch * sizeof(ProbDesc), cudaMemcpyHostToDevice, st));
   const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
+  if (s->kp.estimate_scaling) {  // A.4-5: the scale vote comes first; the graph is its inlier mask
+    if (prof) CK(cudaEventRecord(s->ev[10], st));
+    CK(s->d_scale.ensure(scale_workspace_bytes(n_max)));
+    const ProbDesc* hd = (const ProbDesc*)s->h_desc.p;
+    for (int b = 0; b < batch; ++b)
+      s->launches += launch_scale_estimate(hd[b].src, hd[b].dst, hd[b].n, s->kp.beta, hd[b].st, s->d_scale.p, st);
+    if (prof) CK(cudaEventRecord(s->ev[11], st));
+  }
   if (prof) CK(cudaEventRecord(s->ev[1], st));
   if (!skip_graph) s->launches += launch_tim_graph(dd, batch, n_max, s->kp, st);
   if (prof) CK(cudaEventRecord(s->ev[2], st));
@@ -286,9 +294,9 @@ b2r_status b2r_destroy(b2r_solver* s) {
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->stream);
   s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
-  s->d_state.release(); s->d_desc.release(); s->d_arena.release();
+  s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
-  if (s->ev_ready) for (int i = 0; i < 10; ++i) cudaEventDestroy(s->ev[i]);
+  if (s->ev_ready) for (int i = 0; i < 12; ++i) cudaEventDestroy(s->ev[i]);
   if (s->own_stream) cudaStreamDestroy(s->stream);
   delete s;
   return B2R_OK;
@@ -313,8 +321,6 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
                                  const double* const* dst, int on_device) {
   if (!s) return B2R_ERR_INVALID_ARG;
   if (batch <= 0 || !n || !src || !dst) return fail(s, B2R_ERR_INVALID_ARG, "batch/n/src/dst");
-  if (s->params.estimate_scaling)
-    return fail(s, B2R_ERR_INVALID_ARG, "estimate_scaling=True is not implemented yet (the reference sets it to False)");
   CK(cudaSetDevice(s->device));
   if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
   int n_max = 0;
@@ -326,6 +332,8 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
     n_max = n[b] > n_max ? n[b] : n_max;
     total += (size_t)3 * n[b];
   }
+  if (s->params.estimate_scaling && scale_workspace_bytes(n_max) > (size_t)96 << 30)
+    return fail(s, B2R_ERR_LIMIT, "estimate_scaling=True: the 2P-endpoint vote for this N needs more than 96 GB of workspace");
   b2r_status r = ensure_workspace(s, batch, n_max);
   if (r != B2R_OK) return r;
   if (s->profiling) { r = ensure_events(s); if (r != B2R_OK) return r; CK(cudaEventRecord(s->ev[0], s->stream)); }
@@ -361,6 +369,11 @@ b2r_status b2r_sync(b2r_solver* s) {
   if (s->profiling && s->ev_ready) {
     for (int i = 0; i < 9; ++i) cudaEventElapsedTime(&s->timings[i], s->ev[i], s->ev[i + 1]);
     cudaEventElapsedTime(&s->timings[9], s->ev[0], s->ev[9]);
+    s->timings[10] = 0.f;
+    if (s->kp.estimate_scaling) {
+      cudaEventElapsedTime(&s->timings[10], s->ev[10], s->ev[11]);
+      s->timings[0] -= s->timings[10];  // the scale vote sits between the upload and graph events
+    }
   }
   s->have_result = true;
   const ProbState* hs = (const ProbState*)s->h_state.p;
@@ -536,10 +549,10 @@ b2r_status b2r_set_profiling(b2r_solver* s, int on) {
   return B2R_OK;
 }
 
-b2r_status b2r_get_timings(b2r_solver* s, float* ms10) {
-  if (!s || !ms10) return B2R_ERR_INVALID_ARG;
+b2r_status b2r_get_timings(b2r_solver* s, float* ms12) {
+  if (!s || !ms12) return B2R_ERR_INVALID_ARG;
   if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
-  memcpy(ms10, s->timings, sizeof(float) * 10);
+  memcpy(ms12, s->timings, sizeof(float) * 12);
   return B2R_OK;
 }
 
@@ -548,6 +561,7 @@ b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* ds
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!src_dev || !dst_dev || !adj_out_dev || n < 2 || row_begin < 0 || row_end > n || row_begin > row_end)
     return fail(s, B2R_ERR_INVALID_ARG, "graph_rows arguments");
+  if (s->params.estimate_scaling) return fail(s, B2R_ERR_INVALID_ARG, "the row-sharded path needs estimate_scaling=False (the scale vote is global)");
   if (pitch_words < b2r_pitch_words(n) || (pitch_words & 3)) return fail(s, B2R_ERR_INVALID_ARG, "pitch_words must be >= b2r_pitch_words(n) and a multiple of 4");
   CK(cudaSetDevice(s->device));
   s->launches += launch_tim_graph_rows(src_dev, dst_dev, n, row_begin, row_end, adj_out_dev, pitch_words, s->kp, nullptr, s->stream);
@@ -559,6 +573,7 @@ b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const 
                                     int pitch_words) {
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!src_dev || !dst_dev || !adj_dev || n < 2) return fail(s, B2R_ERR_INVALID_ARG, "solve_from_adjacency arguments");
+  if (s->params.estimate_scaling) return fail(s, B2R_ERR_INVALID_ARG, "the row-sharded path needs estimate_scaling=False (the scale vote is global)");
   if (n > kMaxN) return fail(s, B2R_ERR_LIMIT, "N > 65535 correspondences is not supported");
   if (pitch_words < b2r_pitch_words(n) || (pitch_words & 3)) return fail(s, B2R_ERR_INVALID_ARG, "pitch_words");
   CK(cudaSetDevice(s->device));

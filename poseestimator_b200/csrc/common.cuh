@@ -98,6 +98,15 @@ int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelPara
 int launch_rotation_translation(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st,
                                 cudaEvent_t* ev /*1 or null*/);
 
+// radix.cu: stable LSD sort of (u64 key, u32 payload) pairs on bits [begin_bit, end_bit); result in the alt buffers
+// when *in_alt.  table: radix_table_words(n) u32 words.
+size_t radix_table_words(size_t n);
+int radix_sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt, uint32_t* table, size_t n,
+                     int begin_bit, int end_bit, cudaStream_t st, bool* in_alt);
+// scale.cu: adaptive-voting scale estimate of one problem into st->scale
+size_t scale_workspace_bytes(int n);
+int launch_scale_estimate(const double* src, const double* dst, int n, double beta, ProbState* st, void* ws, cudaStream_t stream);
+
 constexpr int kBnbWarpsPerBlock = 8;
 constexpr int kCanonWarps = 8;
 

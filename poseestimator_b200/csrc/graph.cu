@@ -33,6 +33,13 @@ __device__ __forceinline__ bool verdict_exact(double A, double B, double beta) {
   return fabs(__dsub_rn(a, b)) <= beta;
 }
 
+// estimate_scaling=True (A.4-5 + A.7-3): the edge set is the scale-inlier mask |b/a - s| <= beta * (1/a),
+// s = the adaptive-voting estimate (scale.cu), every operation rounded as the reference's doubles are.
+__device__ __forceinline__ bool verdict_scale(double A, double B, double beta, double s) {
+  const double a = __dsqrt_rn(A), b = __dsqrt_rn(B);
+  return fabs(__dsub_rn(__ddiv_rn(b, a), s)) <= __dmul_rn(beta, __ddiv_rn(1.0, a));
+}
+
 // Fast verdict, FP64 pipe: 6 sub + 6 mul + 4 add (A, B in reference rounding) + S1, H, AB, F = 20 instructions.
 // Everything else runs on the integer pipe:  in = sign(H) | sign(F);  ambiguous <=> |F| < 2^-24 * Sigma^2 judged on the
 // biased exponents (eF < 2*max(e(S1), e(beta^2)) - 1047 + shift), or F not finite / subnormal.
@@ -66,10 +73,12 @@ struct TilePts {
 // dir[t] (shared) receives the 4 words of row i0+t for the column block; tw[0..3] (registers) the 4 words of
 // row j0+t for the row block (transposed tile).
 // kInterior: every row and column of the tile is < n and the tile is off the diagonal -> no validity tests at all.
-template <bool kExactOnly, bool kInterior>
+// kMode: 0 sqrt-free filter + exact fallback, 1 exact only, 2 scale-inlier verdict (estimate_scaling=True).
+template <int kMode, bool kInterior>
 __device__ __forceinline__ void compute_tile(const double* __restrict__ src, const double* __restrict__ dst, int n,
                                              int i0, int j0, const KernelParams& kp, TilePts& sp,
-                                             uint32_t (*dir)[4], uint32_t tw[4], unsigned& slow) {
+                                             uint32_t (*dir)[4], uint32_t tw[4], unsigned& slow, double s_hat = 1.0) {
+  constexpr bool kExactOnly = kMode != 0;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   {  // stage the row points (coalesced 24-byte AoS reads), zero-fill past n
     const int i = i0 + t;
@@ -127,7 +136,7 @@ __device__ __forceinline__ void compute_tile(const double* __restrict__ src, con
         const double A = sq3_ref(__dsub_rn(xj, pa.x), __dsub_rn(yj, pa.y), __dsub_rn(zj, pb.x));
         const double B = sq3_ref(__dsub_rn(uj, pb.y), __dsub_rn(vj, pc.x), __dsub_rn(wj, pc.y));
         const int i = i0 + il;
-        bool in = verdict_exact(A, B, kp.beta);
+        bool in = kMode == 2 ? verdict_scale(A, B, kp.beta, s_hat) : verdict_exact(A, B, kp.beta);
         in = in && jok && (i < n) && (i != j);
         const uint32_t bal = __ballot_sync(0xffffffffu, in);
         if (lane == 0) dir[il][warp] = bal;
@@ -142,8 +151,9 @@ __device__ __forceinline__ void compute_tile(const double* __restrict__ src, con
 }
 
 // Batched, symmetric: grid = (T(T+1)/2 for the largest problem, batch).
-template <bool kExactOnly>
+template <int kMode>
 __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  constexpr bool kExactOnly = kMode != 0;
   const ProbDesc d = descs[blockIdx.y];
   const int n = d.n;
   const int T = (n + kTile - 1) / kTile;
@@ -156,8 +166,9 @@ __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __rest
   __shared__ uint32_t dir[kTile][4];
   uint32_t tw[4] = {0u, 0u, 0u, 0u};
   unsigned slow = 0;
-  if (ti != tj && (tj + 1) * kTile <= n) compute_tile<kExactOnly, true>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow);
-  else compute_tile<kExactOnly, false>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow);
+  const double s_hat = kMode == 2 ? d.st->scale : 1.0;
+  if (ti != tj && (tj + 1) * kTile <= n) compute_tile<kMode, true>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow, s_hat);
+  else compute_tile<kMode, false>(d.src, d.dst, n, ti * kTile, tj * kTile, kp, sp, dir, tw, slow, s_hat);
   const int t = threadIdx.x;
   const int i = ti * kTile + t;
   if (i < n) *reinterpret_cast<uint4*>(d.adj + (size_t)i * d.pitch + 4 * tj) = *reinterpret_cast<const uint4*>(dir[t]);
@@ -181,7 +192,7 @@ __global__ void __launch_bounds__(kTile) tim_graph_rows_kernel(const double* __r
   uint32_t tw[4] = {0u, 0u, 0u, 0u};
   unsigned slow = 0;
   // rows beyond row_end are computed but not stored (n_eff trick keeps the ballot uniform)
-  compute_tile<kExactOnly, false>(src, dst, n, i0, tj * kTile, kp, sp, dir, tw, slow);
+  compute_tile<kExactOnly ? 1 : 0, false>(src, dst, n, i0, tj * kTile, kp, sp, dir, tw, slow);
   const int i = i0 + threadIdx.x;
   if (i < row_end && i < n)
     *reinterpret_cast<uint4*>(adj + (size_t)(i - row_begin) * pitch + 4 * tj) = *reinterpret_cast<const uint4*>(dir[threadIdx.x]);
@@ -233,8 +244,9 @@ __global__ void __launch_bounds__(256) degree_kernel(const ProbDesc* __restrict_
 int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
   const int T = (n_max + kTile - 1) / kTile;
   dim3 grid(T * (T + 1) / 2, batch);
-  if (kp.exact_only) tim_graph_kernel<true><<<grid, kTile, 0, st>>>(d_desc, kp);
-  else tim_graph_kernel<false><<<grid, kTile, 0, st>>>(d_desc, kp);
+  if (kp.estimate_scaling) tim_graph_kernel<2><<<grid, kTile, 0, st>>>(d_desc, kp);
+  else if (kp.exact_only) tim_graph_kernel<1><<<grid, kTile, 0, st>>>(d_desc, kp);
+  else tim_graph_kernel<0><<<grid, kTile, 0, st>>>(d_desc, kp);
   return 1;
 }
 

@@ -148,13 +148,13 @@ __global__ void __launch_bounds__(kRtThreads) rotation_kernel(const ProbDesc* __
   const int tid = threadIdx.x;
   const int C = st->clique_size;
   if (tid == 0) {
-    st->scale = 1.0;  // estimate_scaling handled upstream of this kernel (scale stage), default 1
+    if (!kp.estimate_scaling) st->scale = 1.0;  // else: written by the scale stage (scale.cu) before the graph kernel
     for (int i = 0; i < 9; ++i) st->R[i] = (i % 4 == 0) ? 1.0 : 0.0;
     st->t[0] = st->t[1] = st->t[2] = 0.0;
     st->valid = 0; st->n_rot_tims = 0; st->n_rot_inl = 0; st->n_trans_inl = 0; st->gnc_iters = 0; st->gnc_cost = 0.0;
   }
   if (C <= 1) return;  // A.5-6: solution stays invalid
-  const double scale = 1.0;
+  const double scale = kp.estimate_scaling ? st->scale : 1.0;
   const double inv_s = 1.0 / scale;
   long long Tll = kp.tim_graph == B2R_TIM_CHAIN ? (long long)C : (long long)C * (C - 1) / 2;
   if (Tll > d.tim_cap) {  // COMPLETE graph over a huge clique: report instead of truncating silently

@@ -317,3 +317,42 @@ def test_row_sharded_graph_equals_full(oracle_mod):
     assert np.array_equal(got, ref.adjacency)
     assert bs.max_clique(0).tolist() == ref.clique.tolist()
     assert synth.rotation_error_rad(sol.rotation, ref.rotation) < ROT_TOL
+
+
+# ---- estimate_scaling=True: adaptive voting over all TIM ratios ---------------------
+SCALE_TOL_REL = 1e-9
+
+
+@pytest.mark.parametrize("n,ratio,seed,gen_scale", [(40, 0.2, 21, 1.0), (200, 0.5, 22, 1.7), (333, 0.7, 23, 0.6), (1000, 0.5, 24, 2.5)])
+def test_scale_estimation_matches_oracle(oracle_mod, n, ratio, seed, gen_scale):
+    import teaserpp_python as tpp
+    pb = synth.make_problem(n, ratio, seed, scale=gen_scale)
+    solver = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound, estimate_scaling=True))
+    sol = solver.solve(pb.src, pb.dst)
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=1, rotation_cost_threshold=1e-12)
+    assert abs(sol.scale - ref.scale) < SCALE_TOL_REL * abs(ref.scale)
+    assert abs(sol.scale - gen_scale) < 0.05 * gen_scale
+    # the graph is the scale-inlier mask: bit-exact, and so is everything downstream
+    assert np.array_equal(solver._adjacency_bits(), ref.adjacency)
+    assert solver.getInlierMaxClique() == ref.clique.tolist()
+    assert sol.valid and ref.valid
+    assert synth.rotation_error_rad(sol.rotation, ref.rotation) < ROT_TOL
+    assert np.linalg.norm(sol.translation - ref.translation) < TRANS_TOL_REL * pb.scene_scale * max(1.0, gen_scale)
+    assert solver.getRotationInliers() == ref.rotation_inliers.tolist()
+    assert solver.getTranslationInliers() == ref.translation_inliers.tolist()
+    assert solver.stats()["n_edges"] == ref.n_edges
+    assert len(solver.getScaleInliers()) == ref.n_edges
+
+
+def test_scale_estimation_in_a_batch(oracle_mod):
+    """Problems of different sizes in one batch share the scale-vote workspace one after the other."""
+    import teaserpp_python as tpp
+    from poseestimator_b200 import batch as b2batch
+    pbs = [synth.make_problem(n, 0.4, 30 + i, scale=s) for i, (n, s) in enumerate([(150, 1.3), (64, 0.8), (300, 2.0)])]
+    bs = b2batch.BatchSolver(_params(tpp, pbs[0].noise_bound, estimate_scaling=True))
+    sols = bs.solve([(p.src, p.dst) for p in pbs])
+    for i, (pb, sol) in enumerate(zip(pbs, sols)):
+        ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=1, rotation_cost_threshold=1e-12)
+        assert abs(sol.scale - ref.scale) < SCALE_TOL_REL * abs(ref.scale)
+        assert bs.max_clique(i).tolist() == ref.clique.tolist()
+        assert np.array_equal(bs.adjacency(i, pb.src.shape[1]), ref.adjacency)
