@@ -164,6 +164,55 @@ b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const 
 /* words per adjacency row the library uses for n vertices (multiple of 4) */
 int b2r_pitch_words(int n);
 
+
+/* ---- pre-steps: what the reference does with Open3D between the detector's mask and solver.solve -----------------
+ * All point / feature buffers are DEVICE pointers on the handle's device unless stated; outputs are written in the
+ * canonical orders of oracle/presteps_oracle.cpp (row-major pixel order, ascending voxel key, neighbours by
+ * (distance^2, index)).  Calls are synchronous where they return a count to the host. */
+typedef struct b2r_camera {
+  double fx, fy, cx, cy;  /* pinhole intrinsics (RealSenseClass.py:45-51) */
+  double depth_scale;     /* metres per depth unit; applied in float32 like the reference's numpy expression */
+  double depth_trunc;     /* Open3D RGBDImage depth_trunc (3.0 on the camera path); <= 0: no truncation */
+  double zmin, zmax;      /* registration_utils.py:75 keeps zmin < z < zmax; both <= 0: no range test */
+} b2r_camera;
+
+/* depth u16 [H,W] (+ mask u8 [H,W], 0 = outside, may be NULL) -> points f64 [M,3] in row-major scan order inside the
+ * bbox [u0,u1) x [v0,v1); pixel_ids (v*W+u, may be NULL).  on_device == 0: depth/mask are host images.
+ * Replaces RealSenseClass.get_pcd_from_rgbd (RealSenseClass.py:56-67) / get_pointcloud (registration_utils.py:54-90). */
+b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* mask, int H, int W, int u0, int v0, int u1,
+                           int v1, const b2r_camera* cam, int on_device, double* points_dev, int32_t* pixel_ids_dev,
+                           int capacity, int* count_out);
+/* KDTreeFlann hybrid / knn search for every query: the max_nn (<= 128) nearest points, then d2 < radius^2 when
+ * radius > 0.  idx/d2: [nq, max_nn] (padding -1 / 0), cnt: [nq]. */
+b2r_status b2r_knn(b2r_solver* s, const double* pts_dev, int n, const double* queries_dev, int nq, int max_nn, double radius,
+                   int32_t* idx_dev, double* d2_dev, int32_t* cnt_dev);
+/* remove_statistical_outlier(nb_neighbors, std_ratio) (RealSenseClass.py:68, registration_utils.py:93).
+ * keep_dev [n] / avg_dev [n] / pts_out_dev [kept,3] / idx_out_dev [kept] are optional (NULL). */
+b2r_status b2r_statistical_outlier(b2r_solver* s, const double* pts_dev, int n, int nb_neighbors, double std_ratio,
+                                   uint8_t* keep_dev, double* avg_dev, double* pts_out_dev, int32_t* idx_out_dev, int* kept_out);
+/* voxel_down_sample(voxel) (PoseEstimator.py:87,93): out_dev [V,3] means in ascending voxel key order;
+ * voxel_of_point_dev [n], counts_dev [V] optional. */
+b2r_status b2r_voxel_down(b2r_solver* s, const double* pts_dev, int n, double voxel, double* out_dev,
+                          int32_t* voxel_of_point_dev, int32_t* counts_dev, int* n_voxels_out);
+/* estimate_normals(KDTreeSearchParamHybrid(radius, max_nn)) (HelpersRealtime.py:216-219).
+ * orient: 0 none, 1 towards view3, 2 away from view3. */
+b2r_status b2r_normals(b2r_solver* s, const double* pts_dev, int n, double radius, int max_nn, int orient, const double* view3,
+                       double* normals_dev);
+/* compute_fpfh_feature(KDTreeSearchParamHybrid(radius, max_nn)) (HelpersRealtime.py:221-224): fpfh_dev [33,n]
+ * (Open3D Feature.data layout); spfh_dev [33,n] optional. */
+b2r_status b2r_fpfh(b2r_solver* s, const double* pts_dev, const double* normals_dev, int n, double radius, int max_nn,
+                    double* fpfh_dev, double* spfh_dev);
+/* exact nearest neighbour in feature space (rows = descriptors, [n, dim]): fp64 direct differences, lowest index
+ * wins ties.  dist_dev optional. */
+b2r_status b2r_nn_exact(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
+                        double* dist_dev);
+/* pairs (i, nn01[i]) with nn10[nn01[i]] == i, ascending i -> pairs_dev [c,2] */
+b2r_status b2r_mutual_pairs(b2r_solver* s, const int32_t* nn01_dev, int na, const int32_t* nn10_dev, int nb, int32_t* pairs_dev,
+                            int* n_pairs_out);
+/* the 3xN operands of solver.solve from matched pairs (HelpersRealtime.py:142-143): src = a_pts[pairs[:,0]], dst = b_pts[pairs[:,1]] */
+b2r_status b2r_gather_correspondences(b2r_solver* s, const double* a_pts_dev, const double* b_pts_dev, const int32_t* pairs_dev,
+                                      int n_pairs, double* src_dev, double* dst_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,6 +28,11 @@ class B2RParams(C.Structure):
     ]
 
 
+class B2RCamera(C.Structure):
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("depth_scale", C.c_double),
+                ("depth_trunc", C.c_double), ("zmin", C.c_double), ("zmax", C.c_double)]
+
+
 class B2RSolution(C.Structure):
     _fields_ = [("scale", C.c_double), ("rotation", C.c_double * 9), ("translation", C.c_double * 3), ("valid", C.c_int32)]
 
@@ -51,6 +56,8 @@ EXPORTS = [
     "b2r_solve", "b2r_solve_batch", "b2r_solve_batch_async", "b2r_sync", "b2r_batch_size", "b2r_launch_count",
     "b2r_get_solution", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
     "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
+    "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
+    "b2r_mutual_pairs", "b2r_gather_correspondences",
 ]
 
 IDX_MAX_CLIQUE, IDX_ROT_INLIERS, IDX_ROT_INLIERS_MAP, IDX_TRANS_INLIERS, IDX_TRANS_INLIERS_MAP, IDX_DEGREES = range(6)
@@ -97,6 +104,16 @@ def lib():
     L.b2r_solve_from_adjacency.argtypes = [vp, vp, vp, i32, vp, i32]
     L.b2r_pitch_words.argtypes = [i32]
     L.b2r_pitch_words.restype = i32
+    d, ip = C.c_double, C.POINTER(C.c_int)
+    L.b2r_backproject.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, C.POINTER(B2RCamera), i32, vp, vp, i32, ip]
+    L.b2r_knn.argtypes = [vp, vp, i32, vp, i32, i32, d, vp, vp, vp]
+    L.b2r_statistical_outlier.argtypes = [vp, vp, i32, i32, d, vp, vp, vp, vp, ip]
+    L.b2r_voxel_down.argtypes = [vp, vp, i32, d, vp, vp, vp, ip]
+    L.b2r_normals.argtypes = [vp, vp, i32, d, i32, i32, vp, vp]
+    L.b2r_fpfh.argtypes = [vp, vp, vp, i32, d, i32, vp, vp]
+    L.b2r_nn_exact.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp]
+    L.b2r_mutual_pairs.argtypes = [vp, vp, i32, vp, i32, vp, ip]
+    L.b2r_gather_correspondences.argtypes = [vp, vp, vp, vp, i32, vp, vp]
     _lib = L
     return L
 

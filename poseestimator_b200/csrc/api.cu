@@ -12,34 +12,9 @@
 
 using namespace b2r;
 
-namespace {
+#include "solver.cuh"
 
-struct DevBuf {
-  void* p = nullptr;
-  size_t bytes = 0;
-  cudaError_t ensure(size_t need) {
-    if (need <= bytes) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr; bytes = 0;
-    cudaError_t e = cudaMalloc(&p, need);
-    if (e == cudaSuccess) bytes = need;
-    return e;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
-};
-struct HostBuf {
-  void* p = nullptr;
-  size_t bytes = 0;
-  cudaError_t ensure(size_t need) {
-    if (need <= bytes) return cudaSuccess;
-    if (p) cudaFreeHost(p);
-    p = nullptr; bytes = 0;
-    cudaError_t e = cudaMallocHost(&p, need);
-    if (e == cudaSuccess) bytes = need;
-    return e;
-  }
-  void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
-};
+namespace {
 
 __global__ void gather_points_kernel(const double* __restrict__ in, long long rs, long long cs, int n, double* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -48,51 +23,7 @@ __global__ void gather_points_kernel(const double* __restrict__ in, long long rs
 
 }  // namespace
 
-struct b2r_solver {
-  int device = 0;
-  cudaStream_t stream = nullptr;
-  bool own_stream = false;
-  b2r_params params;
-  KernelParams kp;
-  std::string err;
-  long long launches = 0;
-
-  // workspace capacity
-  int batch_cap = 0, n_cap = 0, pitch = 0;
-  long long tim_cap = 0;
-  DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena, d_scale;
-  HostBuf h_state, h_desc, h_pts;
-  size_t arena_words_per_warp = 64 * 1024;
-  int bnb_blocks = 1;
-
-  // last batch
-  int batch = 0;
-  std::vector<int> n;
-  bool pending = false;
-  bool have_result = false;
-  const uint32_t* ext_adj = nullptr;  // solve_from_adjacency
-
-  bool profiling = false;
-  cudaEvent_t ev[12] = {};
-  bool ev_ready = false;
-  float timings[12] = {};
-};
-
 namespace {
-
-#define CK(call)                                                                                  \
-  do {                                                                                            \
-    cudaError_t e__ = (call);                                                                     \
-    if (e__ != cudaSuccess) {                                                                     \
-      s->err = std::string(#call) + ": " + cudaGetErrorString(e__);                               \
-      return e__ == cudaErrorMemoryAllocation ? B2R_ERR_OOM : B2R_ERR_CUDA;                       \
-    }                                                                                             \
-  } while (0)
-
-b2r_status fail(b2r_solver* s, b2r_status code, const std::string& msg) {
-  if (s) s->err = msg;
-  return code;
-}
 
 void fill_kernel_params(b2r_solver* s) {
   const b2r_params& p = s->params;
@@ -294,7 +225,7 @@ b2r_status b2r_destroy(b2r_solver* s) {
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->stream);
   s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
-  s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release();
+  s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
   if (s->ev_ready) for (int i = 0; i < 12; ++i) cudaEventDestroy(s->ev[i]);
   if (s->own_stream) cudaStreamDestroy(s->stream);

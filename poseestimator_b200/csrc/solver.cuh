@@ -1,0 +1,83 @@
+// Internal: the solver handle behind include/b2r.h, shared by api.cu (registration) and presteps.cu / nn_gemm.cu.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace b2r {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+struct HostBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMallocHost(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+};
+
+}  // namespace b2r
+
+struct b2r_solver {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  b2r_params params;
+  b2r::KernelParams kp;
+  std::string err;
+  long long launches = 0;
+
+  // workspace capacity
+  int batch_cap = 0, n_cap = 0, pitch = 0;
+  long long tim_cap = 0;
+  b2r::DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena, d_scale, d_pre, d_nn;
+  b2r::HostBuf h_state, h_desc, h_pts;
+  size_t arena_words_per_warp = 64 * 1024;
+  int bnb_blocks = 1;
+
+  // last batch
+  int batch = 0;
+  std::vector<int> n;
+  bool pending = false;
+  bool have_result = false;
+  const uint32_t* ext_adj = nullptr;  // solve_from_adjacency
+
+  bool profiling = false;
+  cudaEvent_t ev[12] = {};
+  bool ev_ready = false;
+  float timings[12] = {};
+};
+
+
+#define CK(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e__ = (call);                                                                     \
+    if (e__ != cudaSuccess) {                                                                     \
+      s->err = std::string(#call) + ": " + cudaGetErrorString(e__);                               \
+      return e__ == cudaErrorMemoryAllocation ? B2R_ERR_OOM : B2R_ERR_CUDA;                       \
+    }                                                                                             \
+  } while (0)
+
+
+static inline b2r_status fail(b2r_solver* s, b2r_status code, const std::string& msg) {
+  if (s) s->err = msg;
+  return code;
+}
