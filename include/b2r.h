@@ -206,6 +206,15 @@ b2r_status b2r_fpfh(b2r_solver* s, const double* pts_dev, const double* normals_
  * wins ties.  dist_dev optional. */
 b2r_status b2r_nn_exact(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
                         double* dist_dev);
+/* the same result as b2r_nn_exact, found on the tensor cores: 3xTF32 tcgen05 GEMM fed by TMA keeps a per-row top-4
+ * shortlist of |fr_j|^2 - 2 fq_i.fr_j, then an exact fp64 re-rank in the oracle's order; rows whose shortlist cannot be
+ * proven complete fall back to exact brute force (*n_fallback_out, optional, counts them).  dim <= 40, else the exact
+ * kernel runs.  Replaces the feature matching of get_correspondences (HelpersRealtime.py:194-213). */
+b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
+                       double* dist_dev, int* n_fallback_out);
+/* both directions + mutual filter in one call: nn01 [na], nn10 [nb], pairs [c,2] ascending i */
+b2r_status b2r_mutual_nn(b2r_solver* s, const double* fa_dev, int na, const double* fb_dev, int nb, int dim, int32_t* nn01_dev,
+                         int32_t* nn10_dev, int32_t* pairs_dev, int* n_pairs_out, int* n_fallback_out);
 /* pairs (i, nn01[i]) with nn10[nn01[i]] == i, ascending i -> pairs_dev [c,2] */
 b2r_status b2r_mutual_pairs(b2r_solver* s, const int32_t* nn01_dev, int na, const int32_t* nn10_dev, int nb, int32_t* pairs_dev,
                             int* n_pairs_out);

@@ -57,7 +57,7 @@ EXPORTS = [
     "b2r_get_solution", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
     "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
-    "b2r_mutual_pairs", "b2r_gather_correspondences",
+    "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
 ]
 
 IDX_MAX_CLIQUE, IDX_ROT_INLIERS, IDX_ROT_INLIERS_MAP, IDX_TRANS_INLIERS, IDX_TRANS_INLIERS_MAP, IDX_DEGREES = range(6)
@@ -114,6 +114,8 @@ def lib():
     L.b2r_nn_exact.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp]
     L.b2r_mutual_pairs.argtypes = [vp, vp, i32, vp, i32, vp, ip]
     L.b2r_gather_correspondences.argtypes = [vp, vp, vp, vp, i32, vp, vp]
+    L.b2r_nn_gemm.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp, ip]
+    L.b2r_mutual_nn.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp, vp, ip, ip]
     _lib = L
     return L
 

@@ -1,0 +1,507 @@
+// Nearest neighbour in feature space on the tensor cores (north-star item (b)).
+//
+// Replaces the feature-matching step of get_correspondences (HelpersRealtime.py:194-213 /
+// registration_utils.py:177-196) in its north-star form: nn[i] = argmin_j ||fq_i - fr_j||^2, both directions, then the
+// mutual filter (presteps.cu).  The one dense contraction of the path, -2 * Fq * Fr^T, runs as a tcgen05 GEMM:
+//
+//   prep      f64 descriptors -> f32 -> 3xTF32 split, K-concatenated so that ONE GEMM with K = 3*40 (padded to 128)
+//             yields hi*hi + hi*lo + lo*hi (fp32-class accuracy from TF32 tensor cores), plus the squared norms
+//   gemm      one CTA per (128-query tile, range of 128-reference tiles): TMA (cp.async.bulk.tensor, 128B swizzle)
+//             stages the operands, one thread issues tcgen05.mma.kind::tf32 (M=128, N=128, K=8) into double-buffered
+//             TMEM accumulators, four epilogue warps read them back with tcgen05.ld and keep a per-row top-4 of
+//             ||fr_j||^2 - 2 fq_i.fr_j in registers -- the distance matrix never exists in memory
+//   finish    one warp per query: candidates of all column ranges, shortlist within the proven error margin of the
+//             approximate minimum, EXACT fp64 re-rank in the oracle's order (sequential sum of (a-b)^2, lowest index
+//             wins ties); rows whose shortlist cannot be proven complete are redone by exact brute force.
+// Result: indices identical to the exact fp64 search (tests compare with the oracle bit for bit).
+#include <cuda.h>
+#include <math_constants.h>
+
+#include "solver.cuh"
+
+namespace b2r {
+
+namespace {
+
+constexpr int kBM = 128;          // queries per CTA
+constexpr int kBN = 128;          // references per MMA tile
+constexpr int kKSeg = 40;         // one TF32 segment: feature dim padded to a multiple of 8
+constexpr int kKTot = 128;        // 3 segments (120) padded to four 128-byte swizzle atoms
+constexpr int kKBlocks = 4;       // 32 floats (128 B) each
+constexpr int kTopK = 4;
+constexpr int kMaxSplits = 16;
+constexpr int kGemmThreads = 192; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr uint32_t kTileBytes = kBM * 128;                 // one k-block of one operand tile: 128 rows x 128 B
+constexpr uint32_t kOperandBytes = kKBlocks * kTileBytes;  // 64 KB
+constexpr double kEpsRel = 2.0e-5;  // |D~_ij - D_ij| <= kEpsRel * (|fq_i|^2 + |fr_j|^2), see DESIGN.md "NN error bound"
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+               "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 columns of 32-bit accumulators -> 32 registers per thread (thread = lane/row, register = column)
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile with 128-byte swizzle (the layout TMA writes): rows 128 B apart, 8-row groups 1024 B apart.
+// bits [0,14) start address >> 4, [16,30) LBO >> 4 (= 1, ignored for swizzled K-major), [32,46) SBO >> 4 (= 64),
+// [46,48) descriptor version 1 (Blackwell), [61,64) layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::tf32, fp32 accumulate, A and B K-major: c_format [4,6) = 1, a_format [7,10) = 2, b_format [10,13) = 2,
+// n >> 3 at [17,23), m >> 4 at [24,29)
+__device__ __forceinline__ constexpr uint32_t umma_idesc_tf32(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+// ---- prep -----------------------------------------------------------------------------------------------------------
+// out: [n_pad][128] floats.  role 0 (left operand): [hi | hi | lo | 0]; role 1 (right operand): [hi | lo | hi | 0].
+__global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__ f, int n, int dim, int n_pad, float* __restrict__ out_l,
+                                                      float* __restrict__ out_r, float* __restrict__ norm, unsigned int* __restrict__ norm_max) {
+  const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (e >= (long long)n_pad * kKTot) return;
+  const int row = (int)(e / kKTot), k = (int)(e % kKTot);
+  const int seg = k / kKSeg, t = k % kKSeg;
+  float x = 0.f;
+  if (row < n && t < dim && seg < 3) x = (float)f[(size_t)row * dim + t];
+  const float hi = to_tf32(x);
+  const float lo = to_tf32(x - hi);
+  out_l[e] = seg == 2 ? lo : hi;
+  out_r[e] = seg == 1 ? lo : hi;
+  if (k == 0) {
+    float nv = CUDART_INF_F;
+    if (row < n) {
+      double s = 0;
+      for (int q = 0; q < dim; ++q) { const double v = f[(size_t)row * dim + q]; s += v * v; }
+      nv = (float)s;
+      atomicMax(norm_max, __float_as_uint(nv));  // non-negative floats order like their bit patterns
+    }
+    norm[row] = nv;
+  }
+}
+
+// ---- gemm + top-k epilogue --------------------------------------------------------------------------------------------
+struct GemmSmem {
+  uint64_t a_full, b_full[2], b_empty[2], acc_full[2], acc_empty[2];
+  uint32_t tmem_base;
+  float nr[2][kBN];
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const float* __restrict__ norm_r,
+               int n_ref, int col_tiles, int splits, float* __restrict__ cand_v, int* __restrict__ cand_j) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* sA = sm;
+  unsigned char* sB = sm + kOperandBytes;                 // 2 stages
+  GemmSmem* g = reinterpret_cast<GemmSmem*>(sm + 3 * kOperandBytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row_tile = blockIdx.x, split = blockIdx.y;
+  const int per = (col_tiles + splits - 1) / splits;
+  const int c0 = split * per;
+  const int c1 = min(c0 + per, col_tiles);
+  const int nt = max(c1 - c0, 0);
+
+  if (threadIdx.x == 0) {
+    mbar_init(&g->a_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&g->b_full[s], 1); mbar_init(&g->b_empty[s], 1); mbar_init(&g->acc_full[s], 1); mbar_init(&g->acc_empty[s], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM: 2 accumulator stages x 128 columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(256u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = g->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      if (nt > 0) mbar_expect_tx(&g->a_full, kOperandBytes);
+      for (int kb = 0; kb < kKBlocks && nt > 0; ++kb) tma_load_2d(&map_q, &g->a_full, sA + kb * kTileBytes, kb * 32, row_tile * kBM);
+      for (int t = 0; t < nt; ++t) {
+        const int s = t & 1;
+        const uint32_t ph = (t >> 1) & 1;
+        mbar_wait(&g->b_empty[s], ph ^ 1);
+        mbar_expect_tx(&g->b_full[s], kOperandBytes);
+        for (int kb = 0; kb < kKBlocks; ++kb)
+          tma_load_2d(&map_r, &g->b_full[s], sB + s * kOperandBytes + kb * kTileBytes, kb * 32, (c0 + t) * kBN);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      constexpr uint32_t idesc = umma_idesc_tf32(kBM, kBN);
+      if (nt > 0) mbar_wait(&g->a_full, 0);
+      for (int t = 0; t < nt; ++t) {
+        const int s = t & 1;
+        const uint32_t ph = (t >> 1) & 1;
+        mbar_wait(&g->b_full[s], ph);
+        mbar_wait(&g->acc_empty[s], ph ^ 1);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB + s * kOperandBytes);
+#pragma unroll
+        for (int kb = 0; kb < kKBlocks; ++kb) {
+          const uint64_t ad = umma_desc_sw128(a_base + kb * kTileBytes), bd = umma_desc_sw128(b_base + kb * kTileBytes);
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks)  // 8 tf32 = 32 bytes per step inside the 128-byte swizzle row: +2 in the encoded address
+            tc_mma_tf32(tmem + s * kBN, ad + 2 * ks, bd + 2 * ks, idesc, (kb | ks) != 0 ? 1u : 0u);
+        }
+        tc_commit(&g->b_empty[s]);   // operands consumed -> the producer may refill the stage
+        tc_commit(&g->acc_full[s]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {  // ===== epilogue: warps 2..5 own TMEM lane quarters 2,3,0,1 =====
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int e = threadIdx.x - 64;
+    float v0 = CUDART_INF_F, v1 = CUDART_INF_F, v2 = CUDART_INF_F, v3 = CUDART_INF_F;
+    int j0 = -1, j1 = -1, j2 = -1, j3 = -1;
+    for (int t = 0; t < nt; ++t) {
+      const int s = t & 1;
+      const uint32_t ph = (t >> 1) & 1;
+      const int jbase = (c0 + t) * kBN;
+      g->nr[s][e] = (jbase + e < n_ref) ? norm_r[jbase + e] : CUDART_INF_F;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      mbar_wait(&g->acc_full[s], ph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int ch = 0; ch < kBN / 32; ++ch) {
+        uint32_t acc[32];
+        tc_ld_32x32(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * kBN + ch * 32), acc);
+        tc_wait_ld();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const float v = fmaf(-2.f, __uint_as_float(acc[c]), g->nr[s][ch * 32 + c]);
+          if (v < v3) {
+            v3 = v; j3 = jbase + ch * 32 + c;
+            if (v3 < v2) { const float tv = v2; v2 = v3; v3 = tv; const int tj = j2; j2 = j3; j3 = tj; }
+            if (v2 < v1) { const float tv = v1; v1 = v2; v2 = tv; const int tj = j1; j1 = j2; j2 = tj; }
+            if (v1 < v0) { const float tv = v0; v0 = v1; v1 = tv; const int tj = j0; j0 = j1; j1 = tj; }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&g->acc_empty[s]);
+    }
+    const size_t o = ((size_t)(row_tile * kBM + row) * splits + split) * kTopK;
+    cand_v[o] = v0; cand_v[o + 1] = v1; cand_v[o + 2] = v2; cand_v[o + 3] = v3;
+    cand_j[o] = j0; cand_j[o + 1] = j1; cand_j[o + 2] = j2; cand_j[o + 3] = j3;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256u) : "memory");
+  }
+}
+
+// ---- finish: shortlist, exact re-rank, fallback -------------------------------------------------------------------------
+__device__ __forceinline__ double exact_d2(const double* __restrict__ a, const double* __restrict__ b, int dim) {
+  double s = 0;
+  for (int t = 0; t < dim; ++t) { const double d = __dsub_rn(a[t], b[t]); s = __dadd_rn(s, __dmul_rn(d, d)); }
+  return s;
+}
+
+constexpr int kFinWarps = 4;
+
+__global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double* __restrict__ fq, int nq, const double* __restrict__ fr, int nr,
+                                                                   int dim, const float* __restrict__ norm_q, const float* __restrict__ norm_r,
+                                                                   const unsigned int* __restrict__ norm_r_max, const float* __restrict__ cand_v,
+                                                                   const int* __restrict__ cand_j, int splits, int* __restrict__ nn,
+                                                                   double* __restrict__ dist, unsigned int* __restrict__ n_fallback) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int i = blockIdx.x * kFinWarps + warp;
+  if (i >= nq) return;
+  const int nc = splits * kTopK;
+  const double nqi = (double)norm_q[i];
+  const double nmax = (double)__uint_as_float(*norm_r_max);
+  // approximate minimum over all candidates; the smallest "4th best" over the column ranges bounds what was NOT kept
+  double vmin = CUDART_INF; int jmin = -1; double kept_bound = CUDART_INF;
+  for (int c = lane; c < nc; c += 32) {
+    const double v = (double)cand_v[(size_t)i * nc + c];
+    const int j = cand_j[(size_t)i * nc + c];
+    if (j >= 0 && (v < vmin || (v == vmin && (unsigned)j < (unsigned)jmin))) { vmin = v; jmin = j; }
+    if ((c & (kTopK - 1)) == kTopK - 1) kept_bound = fmin(kept_bound, j >= 0 ? v : CUDART_INF);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ov = __shfl_xor_sync(0xffffffffu, vmin, o); const int oj = __shfl_xor_sync(0xffffffffu, jmin, o);
+    if (ov < vmin || (ov == vmin && (unsigned)oj < (unsigned)jmin)) { vmin = ov; jmin = oj; }
+    kept_bound = fmin(kept_bound, __shfl_xor_sync(0xffffffffu, kept_bound, o));
+  }
+  double best = CUDART_INF; int bj = -1;
+  bool complete = jmin >= 0;
+  if (complete) {
+    // D~ = nq + v.  |D~ - D| <= eps_ij = kEpsRel * (nq + nr_j).  True minimiser j*: D~_ij* - eps_ij* <= D~_min + eps_i,jmin.
+    const double eps_min = kEpsRel * (nqi + (double)norm_r[jmin]);
+    const double eps_any = kEpsRel * (nqi + nmax);
+    // an un-kept reference has v >= kept_bound; it could only matter if kept_bound - eps_any <= vmin + eps_min
+    complete = kept_bound - eps_any > vmin + eps_min;
+    if (complete) {
+      for (int c = lane; c < nc; c += 32) {
+        const int j = cand_j[(size_t)i * nc + c];
+        if (j < 0) continue;
+        const double v = (double)cand_v[(size_t)i * nc + c];
+        if (v - kEpsRel * (nqi + (double)norm_r[j]) <= vmin + eps_min) {
+          const double d = exact_d2(fq + (size_t)i * dim, fr + (size_t)j * dim, dim);
+          if (d < best || (d == best && (unsigned)j < (unsigned)bj)) { best = d; bj = j; }
+        }
+      }
+    }
+  }
+  if (!complete) {  // warp-uniform: exact brute force over every reference
+    if (lane == 0) atomicAdd(n_fallback, 1u);
+    for (int j = lane; j < nr; j += 32) {
+      const double d = exact_d2(fq + (size_t)i * dim, fr + (size_t)j * dim, dim);
+      if (d < best || (d == best && (unsigned)j < (unsigned)bj)) { best = d; bj = j; }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double od = __shfl_xor_sync(0xffffffffu, best, o); const int oj = __shfl_xor_sync(0xffffffffu, bj, o);
+    if (od < best || (od == best && (unsigned)oj < (unsigned)bj)) { best = od; bj = oj; }
+  }
+  if (lane == 0) { nn[i] = bj; if (dist) dist[i] = best; }
+}
+
+}  // namespace
+
+}  // namespace b2r
+
+using namespace b2r;
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+    else
+      cudaGetLastError();
+  }
+  return fn;
+}
+
+// operand buffer [n_pad][128] f32, row-major; box = 32 floats (one 128-byte swizzle row) x 128 rows
+bool make_operand_map(CUtensorMap* m, const float* base, int n_pad) {
+  EncodeTiledFn fn = encode_tiled();
+  if (!fn) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)kKTot, (cuuint64_t)n_pad};
+  const cuuint64_t strides[1] = {(cuuint64_t)kKTot * sizeof(float)};
+  const cuuint32_t box[2] = {32, (cuuint32_t)kBM};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct Prepped {
+  float* l; float* r; float* norm; unsigned int* norm_max; int n, n_pad;
+};
+
+inline size_t pad256(size_t b) { return (b + 255) / 256 * 256; }
+
+size_t prepped_bytes(int n) {
+  const size_t n_pad = (size_t)(n + kBM - 1) / kBM * kBM;
+  return 2 * pad256(n_pad * kKTot * 4) + pad256(n_pad * 4) + 256;
+}
+
+char* carve_prepped(char* p, int n, Prepped* out) {
+  const size_t n_pad = (size_t)(n + kBM - 1) / kBM * kBM;
+  out->n = n; out->n_pad = (int)n_pad;
+  out->l = (float*)p; p += pad256(n_pad * kKTot * 4);
+  out->r = (float*)p; p += pad256(n_pad * kKTot * 4);
+  out->norm = (float*)p; p += pad256(n_pad * 4);
+  out->norm_max = (unsigned int*)p; p += 256;
+  return p;
+}
+
+int choose_splits(int row_tiles, int col_tiles) {
+  int s = 296 / (row_tiles > 0 ? row_tiles : 1);
+  if (s < 1) s = 1;
+  if (s > kMaxSplits) s = kMaxSplits;
+  if (s > col_tiles) s = col_tiles;
+  const int per = (col_tiles + s - 1) / s;
+  return (col_tiles + per - 1) / per;  // no empty split
+}
+
+size_t cand_bytes(int nq, int nr) {
+  const int rt = (nq + kBM - 1) / kBM, ct = (nr + kBN - 1) / kBN;
+  const int s = choose_splits(rt, ct);
+  return 2 * pad256((size_t)rt * kBM * s * kTopK * 4) + 256;
+}
+
+b2r_status launch_prep(b2r_solver* s, const double* f, int dim, Prepped& p) {
+  CK(cudaMemsetAsync(p.norm_max, 0, 4, s->stream));
+  const long long total = (long long)p.n_pad * kKTot;
+  nn_prep_kernel<<<(int)((total + 255) / 256), 256, 0, s->stream>>>(f, p.n, dim, p.n_pad, p.l, p.r, p.norm, p.norm_max);
+  ++s->launches;
+  return B2R_OK;
+}
+
+// nn[i] = exact argmin_j |fq_i - fr_j|^2 via the tensor-core shortlist.  scratch: cand_bytes(nq, nr) bytes.
+b2r_status launch_direction(b2r_solver* s, const double* fq, const Prepped& q, const double* fr, const Prepped& r, int dim, char* scratch,
+                            int* nn, double* dist, unsigned int* n_fallback) {
+  static bool attr = false;
+  const size_t smem = 3 * (size_t)kOperandBytes + sizeof(GemmSmem) + 1024;
+  if (!attr) { CK(cudaFuncSetAttribute(nn_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+  const int rt = q.n_pad / kBM, ct = r.n_pad / kBN;
+  const int splits = choose_splits(rt, ct);
+  float* cand_v = (float*)scratch;
+  int* cand_j = (int*)(scratch + pad256((size_t)rt * kBM * splits * kTopK * 4));
+  CUtensorMap mq, mr;
+  if (!make_operand_map(&mq, q.l, q.n_pad) || !make_operand_map(&mr, r.r, r.n_pad))
+    return fail(s, B2R_ERR_CUDA, "cuTensorMapEncodeTiled failed (driver entry point missing or bad operand buffer)");
+  nn_gemm_kernel<<<dim3(rt, splits), kGemmThreads, smem, s->stream>>>(mq, mr, r.norm, r.n, ct, splits, cand_v, cand_j);
+  nn_finish_kernel<<<(q.n + kFinWarps - 1) / kFinWarps, kFinWarps * 32, 0, s->stream>>>(fq, q.n, fr, r.n, dim, q.norm, r.norm, r.norm_max,
+                                                                                        cand_v, cand_j, splits, nn, dist, n_fallback);
+  s->launches += 2;
+  CK(cudaGetLastError());
+  return B2R_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
+                       double* dist_dev, int* n_fallback_out) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!fq_dev || !fr_dev || !nn_dev || nq < 0 || nr < 0 || dim < 1) return fail(s, B2R_ERR_INVALID_ARG, "nn_gemm arguments");
+  if (n_fallback_out) *n_fallback_out = 0;
+  if (nq == 0) return B2R_OK;
+  if (dim > kKSeg || nr == 0) return b2r_nn_exact(s, fq_dev, nq, fr_dev, nr, dim, nn_dev, dist_dev);  // K = 3 x 40 TF32 columns at most
+  CK(cudaSetDevice(s->device));
+  CK(s->d_nn.ensure(prepped_bytes(nq) + prepped_bytes(nr) + cand_bytes(nq, nr) + 1024));
+  char* p = (char*)s->d_nn.p;
+  Prepped q, r;
+  p = carve_prepped(p, nq, &q);
+  p = carve_prepped(p, nr, &r);
+  unsigned int* n_fb = (unsigned int*)p; p += 256;
+  CK(cudaMemsetAsync(n_fb, 0, 4, s->stream));
+  b2r_status st = launch_prep(s, fq_dev, dim, q);
+  if (st != B2R_OK) return st;
+  st = launch_prep(s, fr_dev, dim, r);
+  if (st != B2R_OK) return st;
+  st = launch_direction(s, fq_dev, q, fr_dev, r, dim, p, nn_dev, dist_dev, n_fb);
+  if (st != B2R_OK) return st;
+  if (n_fallback_out) {
+    unsigned int h = 0;
+    CK(cudaMemcpyAsync(&h, n_fb, 4, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    *n_fallback_out = (int)h;
+  }
+  return B2R_OK;
+}
+
+b2r_status b2r_mutual_nn(b2r_solver* s, const double* fa_dev, int na, const double* fb_dev, int nb, int dim, int32_t* nn01_dev,
+                         int32_t* nn10_dev, int32_t* pairs_dev, int* n_pairs_out, int* n_fallback_out) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!fa_dev || !fb_dev || !nn01_dev || !nn10_dev || !pairs_dev || !n_pairs_out || na < 0 || nb < 0 || dim < 1)
+    return fail(s, B2R_ERR_INVALID_ARG, "mutual_nn arguments");
+  *n_pairs_out = 0;
+  if (n_fallback_out) *n_fallback_out = 0;
+  if (na == 0 || nb == 0) return B2R_OK;
+  CK(cudaSetDevice(s->device));
+  if (dim > kKSeg) {
+    b2r_status st = b2r_nn_exact(s, fa_dev, na, fb_dev, nb, dim, nn01_dev, nullptr);
+    if (st != B2R_OK) return st;
+    st = b2r_nn_exact(s, fb_dev, nb, fa_dev, na, dim, nn10_dev, nullptr);
+    if (st != B2R_OK) return st;
+    return b2r_mutual_pairs(s, nn01_dev, na, nn10_dev, nb, pairs_dev, n_pairs_out);
+  }
+  const size_t cb = cand_bytes(na, nb) > cand_bytes(nb, na) ? cand_bytes(na, nb) : cand_bytes(nb, na);
+  CK(s->d_nn.ensure(prepped_bytes(na) + prepped_bytes(nb) + cb + 1024));
+  char* p = (char*)s->d_nn.p;
+  Prepped a, b;
+  p = carve_prepped(p, na, &a);
+  p = carve_prepped(p, nb, &b);
+  unsigned int* n_fb = (unsigned int*)p; p += 256;
+  CK(cudaMemsetAsync(n_fb, 0, 4, s->stream));
+  b2r_status st = launch_prep(s, fa_dev, dim, a);
+  if (st != B2R_OK) return st;
+  st = launch_prep(s, fb_dev, dim, b);
+  if (st != B2R_OK) return st;
+  st = launch_direction(s, fa_dev, a, fb_dev, b, dim, p, nn01_dev, nullptr, n_fb);   // same stream: scratch reuse is ordered
+  if (st != B2R_OK) return st;
+  st = launch_direction(s, fb_dev, b, fa_dev, a, dim, p, nn10_dev, nullptr, n_fb);
+  if (st != B2R_OK) return st;
+  st = b2r_mutual_pairs(s, nn01_dev, na, nn10_dev, nb, pairs_dev, n_pairs_out);  // synchronises
+  if (st != B2R_OK) return st;
+  if (n_fallback_out) {
+    unsigned int h = 0;
+    CK(cudaMemcpy(&h, n_fb, 4, cudaMemcpyDeviceToHost));
+    *n_fallback_out = (int)h;
+  }
+  return B2R_OK;
+}
+
+}  // extern "C"

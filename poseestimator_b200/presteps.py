@@ -185,18 +185,39 @@ class PreSteps:
         _lib.check(self._h, _lib.lib().b2r_mutual_pairs(self._h, nn01.data_ptr(), na, nn10.data_ptr(), nb, pairs.data_ptr(), C.byref(c)))
         return pairs[: c.value]
 
-    def mutual_nn(self, fa, fb, method="auto"):
-        """Mutual nearest neighbours of two descriptor sets (rows).  -> (pairs [c,2], nn01 [na], nn10 [nb])."""
-        nn01, _ = self.nn(fa, fb, method)
-        nn10, _ = self.nn(fb, fa, method)
-        return self.mutual_pairs(nn01, nn10), nn01, nn10
+    def nn_gemm(self, fq, fr):
+        """Same result as nn_exact through the tcgen05 3xTF32 GEMM shortlist + exact re-rank.  -> (nn, d2)."""
+        torch = _torch()
+        a, b = self._pts(fq), self._pts(fr)
+        assert a.shape[1] == b.shape[1]
+        nn = self._empty((a.shape[0],), torch.int32)
+        dist = self._empty((a.shape[0],), torch.float64)
+        fb = C.c_int(0)
+        _lib.check(self._h, _lib.lib().b2r_nn_gemm(self._h, a.data_ptr(), a.shape[0], b.data_ptr(), b.shape[0], a.shape[1],
+                                                   nn.data_ptr(), dist.data_ptr(), C.byref(fb)))
+        self.last_fallback_rows = fb.value
+        return nn, dist
 
-    def nn(self, fq, fr, method="auto"):
-        if method in ("auto", "gemm") and hasattr(_lib.lib(), "b2r_nn_gemm"):
-            return self.nn_gemm(fq, fr)
-        if method == "gemm":
-            raise RuntimeError("libb2r.so was built without the tensor-core NN kernel")
-        return self.nn_exact(fq, fr)
+    def mutual_nn(self, fa, fb, method="gemm"):
+        """Mutual nearest neighbours of two descriptor sets (one descriptor per row).
+        -> (pairs [c,2] int32 ascending i, nn01 [na], nn10 [nb]).  method: "gemm" (tensor cores + exact re-rank) or
+        "exact" (fp64 brute force); both return the oracle's indices."""
+        torch = _torch()
+        a, b = self._pts(fa), self._pts(fb)
+        assert a.shape[1] == b.shape[1]
+        if method == "exact":
+            nn01, _ = self.nn_exact(a, b)
+            nn10, _ = self.nn_exact(b, a)
+            return self.mutual_pairs(nn01, nn10), nn01, nn10
+        na, nb = a.shape[0], b.shape[0]
+        nn01 = self._empty((max(na, 1),), torch.int32)
+        nn10 = self._empty((max(nb, 1),), torch.int32)
+        pairs = self._empty((max(na, 1), 2), torch.int32)
+        c, fbk = C.c_int(0), C.c_int(0)
+        _lib.check(self._h, _lib.lib().b2r_mutual_nn(self._h, a.data_ptr(), na, b.data_ptr(), nb, a.shape[1], nn01.data_ptr(),
+                                                     nn10.data_ptr(), pairs.data_ptr(), C.byref(c), C.byref(fbk)))
+        self.last_fallback_rows = fbk.value
+        return pairs[: c.value], nn01[:na], nn10[:nb]
 
     def gather_correspondences(self, a_pts, b_pts, pairs):
         """-> (src, dst) packed [N,3] CUDA tensors (the 3xN column-major operands of solve)."""

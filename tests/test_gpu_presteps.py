@@ -218,3 +218,40 @@ def test_gather_correspondences(ps):
     pairs = np.stack([rng.permutation(50)[:20], rng.permutation(70)[:20]], 1).astype(np.int32)
     src, dst = ps.gather_correspondences(a, b, torch.from_numpy(pairs).cuda())
     assert np.array_equal(_np(src), a[pairs[:, 0]]) and np.array_equal(_np(dst), b[pairs[:, 1]])
+
+
+# ---- a-2 on the tensor cores: tcgen05 3xTF32 GEMM shortlist + exact re-rank must return the oracle's indices ---------
+@pytest.mark.parametrize("na,nb,kind", [(1, 1, "uniform"), (100, 37, "uniform"), (128, 128, "uniform"), (300, 1000, "uniform"),
+                                        (1000, 257, "hist"), (2500, 5000, "hist"), (5000, 4808, "hist"), (640, 700, "dups")])
+def test_nn_gemm_indices_equal_oracle(op, ps, na, nb, kind):
+    rng = np.random.default_rng(na * 7 + nb)
+    if kind == "uniform":
+        fa = rng.uniform(0, 100, size=(na, 33)); fb = rng.uniform(0, 100, size=(nb, 33))
+    else:   # FPFH-like: three 11-bin histograms summing to 200 each, many near-duplicates
+        base = rng.dirichlet(np.full(11, 0.3), size=(64, 3)).reshape(64, 33) * 200.0
+        fa = base[rng.integers(0, 64, na)] + rng.normal(0, 0.5 if kind == "hist" else 0.0, size=(na, 33))
+        fb = base[rng.integers(0, 64, nb)] + rng.normal(0, 0.5 if kind == "hist" else 0.0, size=(nb, 33))
+    pairs_ref, nn01_ref, nn10_ref = op.mutual_nn(fa, fb)
+    pairs, nn01, nn10 = ps.mutual_nn(fa, fb, method="gemm")
+    assert np.array_equal(_np(nn01), nn01_ref) and np.array_equal(_np(nn10), nn10_ref)
+    assert np.array_equal(_np(pairs), pairs_ref)
+    if kind == "dups":
+        assert ps.last_fallback_rows > 0       # exact duplicates cannot be separated by the shortlist: brute-force rows
+    elif kind == "uniform":
+        assert ps.last_fallback_rows == 0
+    nn, d2 = ps.nn_gemm(fa, fb)
+    nn_e, d2_e = ps.nn_exact(fa, fb)
+    assert np.array_equal(_np(nn), _np(nn_e)) and np.array_equal(_np(d2), _np(d2_e))
+
+
+def test_nn_gemm_on_real_fpfh(op, ps, frame):
+    """Config-2 shaped: FPFH of the voxelised scene cloud vs FPFH of the 5000-point CAD cloud."""
+    v = _cloud(op, frame)
+    nrm = op.normals(v, 0.01, 30, 1, (0, 0, 0))
+    fs = op.fpfh(v, nrm, 0.025, 100).T.copy()
+    fc = op.fpfh(frame.cad, frame.cad_normals, 0.025, 100).T.copy()
+    pairs_ref, nn01_ref, nn10_ref = op.mutual_nn(fs, fc)
+    pairs, nn01, nn10 = ps.mutual_nn(fs, fc, method="gemm")
+    assert np.array_equal(_np(nn01), nn01_ref) and np.array_equal(_np(nn10), nn10_ref)
+    assert np.array_equal(_np(pairs), pairs_ref)
+    assert pairs.shape[0] > 10
