@@ -829,19 +829,216 @@ __global__ void __launch_bounds__(256) gather_corr_kernel(const double* __restri
   for (int k = 0; k < 3; ++k) { src[3 * (size_t)m + k] = a_pts[3 * (size_t)i + k]; dst[3 * (size_t)m + k] = b_pts[3 * (size_t)j + k]; }
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// Grid-accelerated exact kNN for large clouds (the raw back-projected cloud has tens of thousands of points; brute
+// force is O(n^2)).  The points are binned into a uniform grid (cell edge h from the cloud's extent and K), sorted by
+// cell (radix.cu), and every query walks cubic shells of cells around its own cell until the K-th best distance is
+// provably final: every point within r*h of the query lies in the cells of shells 0..r.  Same candidate buffer / merge
+// as the brute-force kernel, same (d2, index) order, same fp64 distance expression -> identical output.
+// Everything is sized on the device (no host round trip): the dense cell table holds at most 2^24 cells.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr long long kGridMaxCells = 1ll << 24;
+inline size_t pad256_(size_t b) { return (b + 255) / 256 * 256; }
+
+struct GridDev {
+  double org[3];
+  double h;
+  int dim[3];
+  int pad_;
+};
+
+// single thread: grid geometry from the bounds
+__global__ void grid_setup_kernel(const unsigned long long* __restrict__ bounds, int n, int K, double radius, GridDev* __restrict__ g) {
+  double mn[3], mx[3], L[3];
+  for (int a = 0; a < 3; ++a) { mn[a] = ordered_key_inv(bounds[a]); mx[a] = ordered_key_inv(bounds[3 + a]); L[a] = mx[a] - mn[a]; }
+  const double A = L[0] * L[1] + L[1] * L[2] + L[0] * L[2];      // surface-like clouds: spacing ~ sqrt(area / n)
+  const double Lmax = fmax(L[0], fmax(L[1], L[2]));
+  double h;
+  if (A > 0) h = 2.0 * sqrt(A / (double)n) * sqrt((double)K / 3.14159265358979);
+  else h = Lmax > 0 ? Lmax / 64.0 : 1.0;
+  if (radius > 0 && radius < h) h = radius;
+  if (!(h > 0) || !(h == h)) h = 1.0;
+  long long d[3];
+  for (;;) {
+    long long cells = 1;
+    for (int a = 0; a < 3; ++a) { d[a] = (long long)floor(L[a] / h) + 1; if (d[a] < 1) d[a] = 1; cells = (d[a] > kGridMaxCells) ? kGridMaxCells + 1 : cells * d[a]; if (cells > kGridMaxCells) break; }
+    if (cells <= kGridMaxCells) break;
+    h *= 1.26;
+  }
+  for (int a = 0; a < 3; ++a) { g->org[a] = mn[a]; g->dim[a] = (int)d[a]; }
+  g->h = h; g->pad_ = 0;
+}
+
+__device__ __forceinline__ int grid_cell(double x, double org, double h) { return (int)fmin(fmax(floor((x - org) / h), -2.0e9), 2.0e9); }
+
+__global__ void __launch_bounds__(256) grid_key_kernel(const double* __restrict__ pts, int n, const GridDev* __restrict__ gp,
+                                                       unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const GridDev g = *gp;
+  int c[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) { c[a] = grid_cell(pts[3 * (size_t)i + a], g.org[a], g.h); c[a] = min(max(c[a], 0), g.dim[a] - 1); }
+  keys[i] = (unsigned long long)c[0] + (unsigned long long)g.dim[0] * ((unsigned long long)c[1] + (unsigned long long)g.dim[1] * (unsigned long long)c[2]);
+  vals[i] = (uint32_t)i;
+}
+
+// sorted copies of the points (coalesced shell scans) and the [start, end) range of every occupied cell
+__global__ void __launch_bounds__(256) grid_ranges_kernel(const double* __restrict__ pts, int n, const unsigned long long* __restrict__ keys,
+                                                          const uint32_t* __restrict__ sidx, double* __restrict__ spts, int2* __restrict__ cell_range) {
+  const int e = blockIdx.x * 256 + threadIdx.x;
+  if (e >= n) return;
+  const uint32_t i = sidx[e];
+  spts[3 * (size_t)e] = pts[3 * (size_t)i]; spts[3 * (size_t)e + 1] = pts[3 * (size_t)i + 1]; spts[3 * (size_t)e + 2] = pts[3 * (size_t)i + 2];
+  const unsigned long long k = keys[e];
+  if (e == 0 || keys[e - 1] != k) cell_range[k].x = e;
+  if (e == n - 1 || keys[e + 1] != k) cell_range[k].y = e + 1;
+}
+
+struct KnnGridSmem { KnnWarpSmem w[kKnnWarps]; };
+
+__global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* __restrict__ spts, const uint32_t* __restrict__ sidx, int n,
+                                                                  const GridDev* __restrict__ gp, const int2* __restrict__ cell_range,
+                                                                  const double* __restrict__ queries, int nq, int K, double radius,
+                                                                  int* __restrict__ idx_out, double* __restrict__ d2_out, int* __restrict__ cnt_out) {
+  extern __shared__ __align__(16) unsigned char knn_smem[];
+  KnnWarpSmem& w = reinterpret_cast<KnnWarpSmem*>(knn_smem)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const int q = blockIdx.x * kKnnWarps + (threadIdx.x >> 5);
+  if (q >= nq) return;
+  const GridDev g = *gp;
+  const double qx = queries[3 * (size_t)q], qy = queries[3 * (size_t)q + 1], qz = queries[3 * (size_t)q + 2];
+  const int cq0 = grid_cell(qx, g.org[0], g.h), cq1 = grid_cell(qy, g.org[1], g.h), cq2 = grid_cell(qz, g.org[2], g.h);
+  const bool use_r = radius > 0;
+  const double r2 = __dmul_rn(radius, radius);
+  // shells below r_first hold no cell, shells above r_last neither
+  const int o0 = max(max(-cq0, cq0 - (g.dim[0] - 1)), 0), o1 = max(max(-cq1, cq1 - (g.dim[1] - 1)), 0), o2 = max(max(-cq2, cq2 - (g.dim[2] - 1)), 0);
+  const int r_first = max(o0, max(o1, o2));
+  const int r_last = max(max(max(cq0, g.dim[0] - 1 - cq0), max(cq1, g.dim[1] - 1 - cq1)), max(cq2, g.dim[2] - 1 - cq2));
+  int cur = 0, a = 0, nb = 0;
+  unsigned long long tk = ~0ull; int ti = 0x7fffffff;
+  for (int r = r_first; r <= r_last; ++r) {
+    for (int dz = -r; dz <= r; ++dz) {
+      const int cz = cq2 + dz;
+      if (cz < 0 || cz >= g.dim[2]) continue;
+      for (int dy = -r; dy <= r; ++dy) {
+        const int cy = cq1 + dy;
+        if (cy < 0 || cy >= g.dim[1]) continue;
+        const bool face = (abs(dz) == r) || (abs(dy) == r);
+        // face rows of the shell: the whole x-run; interior rows: only the two end cells
+        const int n_runs = (face || r == 0) ? 1 : 2;
+        for (int run = 0; run < n_runs; ++run) {
+          int xlo, xhi;
+          if (face || r == 0) { xlo = cq0 - r; xhi = cq0 + r; }
+          else if (run == 0) { xlo = xhi = cq0 - r; }
+          else { xlo = xhi = cq0 + r; }
+          xlo = max(xlo, 0); xhi = min(xhi, g.dim[0] - 1);
+          if (xlo > xhi) continue;
+          const unsigned long long kbase = (unsigned long long)g.dim[0] * ((unsigned long long)cy + (unsigned long long)g.dim[1] * (unsigned long long)cz);
+          // cells of an x-run are consecutive keys, so their points are one contiguous range of the sorted array
+          int b = 0x7fffffff, e = 0;
+          for (int x = xlo + lane; x <= xhi; x += 32) {
+            const int2 cr = cell_range[kbase + (unsigned long long)x];
+            if (cr.y > cr.x) { b = min(b, cr.x); e = max(e, cr.y); }
+          }
+          b = __reduce_min_sync(FULL, b); e = __reduce_max_sync(FULL, e);
+          for (int s0 = b; s0 < e; s0 += 32) {
+            const int sp = s0 + lane;
+            bool qual = false;
+            unsigned long long key = 0; int id = 0;
+            if (sp < e) {
+              const double d2 = sq3_ref(__dsub_rn(spts[3 * (size_t)sp], qx), __dsub_rn(spts[3 * (size_t)sp + 1], qy), __dsub_rn(spts[3 * (size_t)sp + 2], qz));
+              key = (unsigned long long)__double_as_longlong(d2);
+              id = (int)sidx[sp];
+              qual = (!use_r || d2 < r2) && key_less(key, id, tk, ti);
+            }
+            const unsigned bal = __ballot_sync(FULL, qual);
+            if (bal) {
+              if (qual) { const int p = nb + __popc(bal & ((1u << lane) - 1u)); w.ck[p] = key; w.ci[p] = id; }
+              nb += __popc(bal);
+              __syncwarp();
+              if (nb > 32) {
+                a = knn_flush(w, cur, a, nb, K, lane);
+                nb = 0;
+                if (a == K) { tk = w.lk[cur][K - 1]; ti = w.li[cur][K - 1]; }
+              }
+            }
+          }
+        }
+      }
+    }
+    if (nb > 0) {
+      a = knn_flush(w, cur, a, nb, K, lane);
+      nb = 0;
+      if (a == K) { tk = w.lk[cur][K - 1]; ti = w.li[cur][K - 1]; }
+    }
+    // everything within reach = r*h (minus a rounding guard for the cell assignment) has been seen
+    const double reach = (double)r * g.h * (1.0 - 1e-9);
+    if (use_r && reach >= radius) break;
+    if (a == K && __longlong_as_double((long long)tk) <= reach * reach) break;
+  }
+  for (int t = lane; t < K; t += 32) {
+    idx_out[(size_t)q * K + t] = t < a ? w.li[cur][t] : -1;
+    d2_out[(size_t)q * K + t] = t < a ? __longlong_as_double((long long)w.lk[cur][t]) : 0.0;
+  }
+  if (lane == 0) cnt_out[q] = a;
+}
+
 size_t knn_smem_bytes() { return sizeof(double) * 3 * kKnnTile + sizeof(KnnWarpSmem) * kKnnWarps; }
+size_t knn_grid_smem_bytes() { return sizeof(KnnGridSmem); }
+size_t knn_grid_ws_bytes(int n) {
+  return 2 * pad256_((size_t)n * 8) + 2 * pad256_((size_t)n * 4) + pad256_(radix_table_words(n) * 4) + pad256_((size_t)n * 24) +
+         pad256_((size_t)kGridMaxCells * 8) + 1024;
+}
+
 
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------------------------
 // launchers used by the C ABI below
 // ------------------------------------------------------------------------------------------------------------------
-static int launch_knn(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
-                      cudaStream_t st) {
+constexpr int kKnnGridMinPoints = 4096;  // below this the brute-force kernel is faster than building a grid
+
+static int launch_knn_brute(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
+                            cudaStream_t st) {
   static bool attr = false;
   if (!attr) { cudaFuncSetAttribute(knn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)knn_smem_bytes()); attr = true; }
   knn_kernel<<<(nq + kKnnWarps - 1) / kKnnWarps, kKnnWarps * 32, knn_smem_bytes(), st>>>(pts, n, queries, nq, K, radius, idx, d2, cnt);
   return 1;
+}
+
+// ws: knn_grid_ws_bytes(n) bytes of device scratch (256-byte aligned)
+static int launch_knn_grid(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
+                           void* ws, cudaStream_t st) {
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(knn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)knn_grid_smem_bytes()); attr = true; }
+  char* p = (char*)ws;
+  auto take = [&](size_t bytes) { char* r = p; p += pad256_(bytes); return (void*)r; };
+  unsigned long long* keys = (unsigned long long*)take((size_t)n * 8);
+  unsigned long long* keys_alt = (unsigned long long*)take((size_t)n * 8);
+  uint32_t* vals = (uint32_t*)take((size_t)n * 4);
+  uint32_t* vals_alt = (uint32_t*)take((size_t)n * 4);
+  uint32_t* table = (uint32_t*)take(radix_table_words(n) * 4);
+  double* spts = (double*)take((size_t)n * 24);
+  int2* cell_range = (int2*)take((size_t)kGridMaxCells * 8);
+  unsigned long long* bounds = (unsigned long long*)take(64);
+  GridDev* g = (GridDev*)take(sizeof(GridDev));
+  const int tiles = (n + 255) / 256;
+  cudaMemsetAsync(bounds, 0xff, 24, st);
+  cudaMemsetAsync(bounds + 3, 0, 24, st);
+  cudaMemsetAsync(cell_range, 0, (size_t)kGridMaxCells * 8, st);
+  bounds_kernel<<<tiles < 296 ? tiles : 296, 256, 0, st>>>(pts, n, bounds);
+  grid_setup_kernel<<<1, 1, 0, st>>>(bounds, n, K, radius, g);
+  grid_key_kernel<<<tiles, 256, 0, st>>>(pts, n, g, keys, vals);
+  bool in_alt = false;
+  int launches = 3 + radix_sort_pairs((uint64_t*)keys, vals, (uint64_t*)keys_alt, vals_alt, table, (size_t)n, 0, 24, st, &in_alt);
+  const unsigned long long* sk = in_alt ? keys_alt : keys;
+  const uint32_t* sv = in_alt ? vals_alt : vals;
+  grid_ranges_kernel<<<tiles, 256, 0, st>>>(pts, n, sk, sv, spts, cell_range);
+  knn_grid_kernel<<<(nq + kKnnWarps - 1) / kKnnWarps, kKnnWarps * 32, knn_grid_smem_bytes(), st>>>(spts, sv, n, g, cell_range, queries, nq, K,
+                                                                                                    radius, idx, d2, cnt);
+  return launches + 2;
 }
 
 }  // namespace b2r
@@ -868,6 +1065,17 @@ b2r_status pre_ws(b2r_solver* s, size_t bytes, Carver* c) {
 }
 
 inline size_t pad256(size_t b) { return (b + 255) / 256 * 256; }
+
+// kNN dispatch: brute force for small clouds, uniform grid for large ones (identical results).  The grid scratch lives in
+// its own buffer (d_nn is free while the pre-steps run) so that callers keep using d_pre for their own arrays.
+b2r_status run_knn(b2r_solver* s, const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2,
+                   int* cnt, int force /*0 auto, 1 brute, 2 grid*/) {
+  const bool grid = force == 2 || (force == 0 && n >= kKnnGridMinPoints);
+  if (!grid) { s->launches += launch_knn_brute(pts, n, queries, nq, K, radius, idx, d2, cnt, s->stream); return B2R_OK; }
+  CK(s->d_grid.ensure(knn_grid_ws_bytes(n)));
+  s->launches += launch_knn_grid(pts, n, queries, nq, K, radius, idx, d2, cnt, s->d_grid.p, s->stream);
+  return B2R_OK;
+}
 
 }  // namespace
 
@@ -922,7 +1130,11 @@ b2r_status b2r_knn(b2r_solver* s, const double* pts_dev, int n, const double* qu
   if (max_nn < 1 || max_nn > kKnnMaxK) return fail(s, B2R_ERR_LIMIT, "knn: max_nn must be in [1, 128]");
   if (nq == 0) return B2R_OK;
   CK(cudaSetDevice(s->device));
-  s->launches += launch_knn(pts_dev, n, queries_dev, nq, max_nn, radius, idx_dev, d2_dev, cnt_dev, s->stream);
+  {
+    const char* f = getenv("B2R_KNN");
+    b2r_status r = run_knn(s, pts_dev, n, queries_dev, nq, max_nn, radius, idx_dev, d2_dev, cnt_dev, f ? (f[0] == 'b' ? 1 : (f[0] == 'g' ? 2 : 0)) : 0);
+    if (r != B2R_OK) return r;
+  }
   CK(cudaGetLastError());
   return B2R_OK;
 }
@@ -949,7 +1161,8 @@ b2r_status b2r_statistical_outlier(b2r_solver* s, const double* pts_dev, int n, 
   unsigned long long* ws = c.take<unsigned long long>(tiles + 2);
   int* d_count = c.take<int>(1);
   cudaStream_t st = s->stream;
-  s->launches += launch_knn(pts_dev, n, pts_dev, n, K, 0.0, idx, d2, cnt, st);
+  r = run_knn(s, pts_dev, n, pts_dev, n, K, 0.0, idx, d2, cnt, 0);
+  if (r != B2R_OK) return r;
   avg_dist_kernel<<<tiles, 256, 0, st>>>(d2, cnt, n, K, avg);
   outlier_threshold_kernel<<<1, 1024, 0, st>>>(avg, n, std_ratio, thr);
   outlier_keep_kernel<<<tiles, 256, 0, st>>>(avg, n, thr, keep);
@@ -1043,7 +1256,8 @@ b2r_status b2r_normals(b2r_solver* s, const double* pts_dev, int n, double radiu
   int* idx = c.take<int>((size_t)n * K);
   double* d2 = c.take<double>((size_t)n * K);
   int* cnt = c.take<int>(n);
-  s->launches += launch_knn(pts_dev, n, pts_dev, n, K, radius, idx, d2, cnt, s->stream);
+  r = run_knn(s, pts_dev, n, pts_dev, n, K, radius, idx, d2, cnt, 0);
+  if (r != B2R_OK) return r;
   const double vx = view3 ? view3[0] : 0, vy = view3 ? view3[1] : 0, vz = view3 ? view3[2] : 0;
   normals_kernel<<<(n + 127) / 128, 128, 0, s->stream>>>(pts_dev, n, idx, cnt, K, view3 ? orient : 0, vx, vy, vz, normals_dev);
   ++s->launches;
@@ -1067,7 +1281,8 @@ b2r_status b2r_fpfh(b2r_solver* s, const double* pts_dev, const double* normals_
   int* cnt = c.take<int>(n);
   double* spfh_t = c.take<double>((size_t)n * 33);
   cudaStream_t st = s->stream;
-  s->launches += launch_knn(pts_dev, n, pts_dev, n, K, radius, idx, d2, cnt, st);
+  r = run_knn(s, pts_dev, n, pts_dev, n, K, radius, idx, d2, cnt, 0);
+  if (r != B2R_OK) return r;
   const int blocks = (n + kFpWarps - 1) / kFpWarps;
   spfh_kernel<<<blocks, kFpWarps * 32, 0, st>>>(pts_dev, normals_dev, n, idx, cnt, K, spfh_t);
   fpfh_kernel<<<blocks, kFpWarps * 32, 0, st>>>(spfh_t, n, idx, d2, cnt, K, fpfh_dev);

@@ -95,6 +95,46 @@ def test_knn_descending_order_stress(op, ps):
     assert np.array_equal(_np(gi), ri) and np.array_equal(_np(gd), rd)
 
 
+@pytest.mark.parametrize("n,nq,K,radius,shape", [(6000, 6000, 20, 0.0, "surface"), (20000, 3000, 20, 0.0, "frame"), (9000, 9000, 30, 0.01, "surface"),
+                                                  (8000, 2000, 100, 0.025, "surface"), (5000, 500, 128, 0.0, "line"), (4100, 300, 16, 0.0, "dups"),
+                                                  (7000, 400, 12, 0.3, "outside")])
+def test_knn_grid_equals_oracle(op, ps, frame, n, nq, K, radius, shape):
+    """Clouds above 4096 points take the uniform-grid path; it must return exactly what brute force returns."""
+    rng = np.random.default_rng(n + K)
+    if shape == "frame":
+        f = frame
+        pts, _ = op.backproject(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale)
+        pts = pts[:: max(1, pts.shape[0] // n)][:n]
+    elif shape == "surface":
+        uv = rng.uniform(-0.15, 0.15, size=(n, 2))
+        pts = np.stack([uv[:, 0], uv[:, 1], 0.6 + 0.2 * uv[:, 0] * uv[:, 1] + rng.normal(0, 5e-4, n)], 1)
+    elif shape == "line":
+        pts = np.stack([np.linspace(0, 1, n), np.zeros(n), np.zeros(n)], 1)
+    elif shape == "dups":
+        pts = np.repeat(rng.uniform(-1, 1, size=(n // 50, 3)), 50, axis=0)
+        pts = np.vstack([pts, rng.uniform(-1, 1, size=(n - pts.shape[0], 3))])
+    else:
+        pts = rng.uniform(-0.5, 0.5, size=(n, 3))
+    n = pts.shape[0]
+    q = pts[rng.permutation(n)[:nq]] if shape != "outside" else rng.uniform(-3, 3, size=(nq, 3))
+    ri, rd, rc = op.knn(pts, q, K, radius)
+    gi, gd, gc = ps.knn(pts, q, K, radius)
+    assert np.array_equal(_np(gc), rc)
+    assert np.array_equal(_np(gi), ri)
+    assert np.array_equal(_np(gd), rd)
+
+
+def test_statistical_outlier_full_bbox_cloud(op, ps, frame):
+    """The whole back-projected bbox cloud (tens of thousands of points): grid kNN inside remove_statistical_outlier."""
+    f = frame
+    p, _ = op.backproject(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale)
+    keep_ref, avg_ref = op.statistical_outlier(p, 20, 1.0)
+    out, idx, keep, avg = ps.statistical_outlier(p, 20, 1.0)
+    assert np.array_equal(_np(avg), avg_ref)
+    assert np.array_equal(_np(keep).astype(bool), keep_ref)
+    assert np.array_equal(_np(out), p[keep_ref])
+
+
 # ---- statistical outlier removal ---------------------------------------------------------------------------------
 def test_statistical_outlier_bit_exact(op, ps, frame):
     f = frame
