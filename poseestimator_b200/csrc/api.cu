@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "common.cuh"
@@ -51,6 +52,22 @@ void fill_kernel_params(b2r_solver* s) {
   const double lim = p.max_clique_time_limit;
   k.time_limit_ns = (lim > 0 && lim < 1e9) ? (unsigned long long)(lim * 1e9) : 0ull;
   k.exact_only = p.graph_exact_only;
+  {
+    const char* v1 = getenv("B2R_GRAPH_V1");
+    k.graph_v1 = (v1 && v1[0] == '1') ? 1 : 0;
+    // v2 band: |F| < 2^(max(2 e(H) - 1023, e(beta^4)) - 22 + shift), compared on the high words of H and F
+    const double beta4 = beta2 * beta2;
+    unsigned long long bits;
+    memcpy(&bits, &beta4, sizeof(bits));
+    long long e4 = (long long)((bits >> 52) & 0x7ff);
+    long long k1 = 1045 - (long long)k.filter_shift;
+    if (k1 < 0) k1 = 0;
+    long long k2 = e4 + 1023;
+    if (k2 < k1) k2 = k1;
+    if (k2 > 4095) k2 = 4095;
+    k.band_k1 = (unsigned)(k1 << 20);
+    k.band_k2 = (unsigned)(k2 << 20);
+  }
 }
 
 b2r_status check_params(b2r_solver* s, const b2r_params* p) {
@@ -279,12 +296,29 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
     double* hd = hs + total;
     double* ds = (double*)s->d_pts.p;
     double* dd = ds + total;
+    std::vector<size_t> offs((size_t)batch);
     size_t off = 0;
     for (int b = 0; b < batch; ++b) {
-      memcpy(hs + off, src[b], sizeof(double) * 3 * n[b]);
-      memcpy(hd + off, dst[b], sizeof(double) * 3 * n[b]);
+      offs[b] = off;
       build_desc(s, b, n[b], ds + off, dd + off, nullptr, 0);
       off += (size_t)3 * n[b];
+    }
+    // staging copy: the only host-side work proportional to the input; spread it over a few threads when it is large
+    auto pack = [&](int b0, int b1) {
+      for (int b = b0; b < b1; ++b) {
+        memcpy(hs + offs[b], src[b], sizeof(double) * 3 * n[b]);
+        memcpy(hd + offs[b], dst[b], sizeof(double) * 3 * n[b]);
+      }
+    };
+    unsigned nthr = std::thread::hardware_concurrency();
+    if (nthr > 8) nthr = 8;
+    if ((unsigned)batch < nthr) nthr = (unsigned)batch;
+    if (total * sizeof(double) * 2 < (1u << 20) || nthr <= 1) pack(0, batch);
+    else {
+      std::vector<std::thread> th;
+      for (unsigned t = 1; t < nthr; ++t) th.emplace_back(pack, (int)((size_t)batch * t / nthr), (int)((size_t)batch * (t + 1) / nthr));
+      pack(0, (int)((size_t)batch / nthr));
+      for (auto& x : th) x.join();
     }
     CK(cudaMemcpyAsync(ds, hs, sizeof(double) * 2 * total, cudaMemcpyHostToDevice, s->stream));
   }

@@ -86,6 +86,8 @@ struct KernelParams {
   double kcore_threshold;
   unsigned long long time_limit_ns;
   int exact_only;
+  int graph_v1;           // 1: the first filter kernel (one column per thread), kept for A/B measurements
+  unsigned band_k1, band_k2;  // high-word constants of the v2 ambiguity band (api.cu fill_kernel_params)
 };
 
 // launchers (each returns the number of kernels it enqueued)

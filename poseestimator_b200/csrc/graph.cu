@@ -150,6 +150,141 @@ __device__ __forceinline__ void compute_tile(const double* __restrict__ src, con
   __syncthreads();
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// v2 of the filter kernel (mode 0 only): one CTA owns 128 rows x TWO adjacent 128-column blocks, every thread two
+// columns, so each broadcast LDS of a row point feeds two pairs.  Inside the filter A and B are formed with FMA
+// (3 FP64 instructions each instead of 5): |A' - A_ref| <= 6u*A moves the real verdict function by at most
+// 3.3e-16 (sqrt(A)+sqrt(B)), which the ambiguity band absorbs with six orders of magnitude to spare (DESIGN.md "graph
+// filter"); ambiguous chunks are redone with the reference's exact roundings, as before.  The band test runs on the
+// high words only: |F| < 2^-22 * max(H^2, beta^4) judged on biased exponents, 5 integer instructions per pair.
+// Per pair: 16 FP64-pipe instructions (was 20) and ~11 others (was ~25): the FP64 pipe is the only bound left.
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void verdict_fast2(double dx, double dy, double dz, double du, double dv, double dw, const KernelParams& kp,
+                                              bool& in, bool& amb) {
+  const double A = fma(dz, dz, fma(dy, dy, dx * dx));
+  const double B = fma(dw, dw, fma(dv, dv, du * du));
+  const double S1 = A + B;
+  const double H = fma(0.5, S1, -kp.half_beta2);
+  const double AB = A * B;
+  const double F = fma(H, H, -AB);
+  const unsigned hH = (unsigned)__double2hiint(H), hF = (unsigned)__double2hiint(F);
+  in = (int)(hH | hF) < 0;
+  const unsigned thr = max(hH << 1, kp.band_k2) - kp.band_k1;   // ((max(2 e(H), e(beta^4) + 1023) - 1045 + shift) << 20)
+  amb = (hF & 0x7fffffffu) < thr;
+}
+
+template <bool kInterior>
+__device__ __forceinline__ void compute_tile2(const double* __restrict__ src, const double* __restrict__ dst, int n, int i0, int j0,
+                                              const KernelParams& kp, TilePts& sp, uint32_t (*dir)[8], uint32_t tw[8], unsigned& slow) {
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  {
+    const int i = i0 + t;
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    if (kInterior || i < n) {
+      v[0] = src[3 * (size_t)i]; v[1] = src[3 * (size_t)i + 1]; v[2] = src[3 * (size_t)i + 2];
+      v[3] = dst[3 * (size_t)i]; v[4] = dst[3 * (size_t)i + 1]; v[5] = dst[3 * (size_t)i + 2];
+    }
+    sp.a[t] = make_double2(v[0], v[1]);
+    sp.b[t] = make_double2(v[2], v[3]);
+    sp.c[t] = make_double2(v[4], v[5]);
+  }
+  const int ja = j0 + t, jb = j0 + kTile + t;
+  const bool oka = kInterior || ja < n, okb = kInterior || jb < n;
+  double xa = 0, ya = 0, za = 0, ua = 0, va = 0, wa = 0, xb = 0, yb = 0, zb = 0, ub = 0, vb = 0, wb = 0;
+  if (oka) {
+    xa = src[3 * (size_t)ja]; ya = src[3 * (size_t)ja + 1]; za = src[3 * (size_t)ja + 2];
+    ua = dst[3 * (size_t)ja]; va = dst[3 * (size_t)ja + 1]; wa = dst[3 * (size_t)ja + 2];
+  }
+  if (okb) {
+    xb = src[3 * (size_t)jb]; yb = src[3 * (size_t)jb + 1]; zb = src[3 * (size_t)jb + 2];
+    ub = dst[3 * (size_t)jb]; vb = dst[3 * (size_t)jb + 1]; wb = dst[3 * (size_t)jb + 2];
+  }
+  __syncthreads();
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t worda = 0, wordb = 0;
+    bool any_amb = false;
+#pragma unroll 4
+    for (int k = 0; k < 32; ++k) {
+      const int il = 32 * c + k;
+      const double2 pa = sp.a[il], pb = sp.b[il], pc = sp.c[il];
+      bool ina, amba, inb, ambb;
+      verdict_fast2(xa - pa.x, ya - pa.y, za - pb.x, ua - pb.y, va - pc.x, wa - pc.y, kp, ina, amba);
+      verdict_fast2(xb - pa.x, yb - pa.y, zb - pb.x, ub - pb.y, vb - pc.x, wb - pc.y, kp, inb, ambb);
+      if (!kInterior) {
+        const int i = i0 + il;
+        const bool ra = oka && (i < n) && (i != ja), rb = okb && (i < n) && (i != jb);
+        ina = ina && ra; amba = amba && ra; inb = inb && rb; ambb = ambb && rb;
+      }
+      const uint32_t bala = __ballot_sync(0xffffffffu, ina), balb = __ballot_sync(0xffffffffu, inb);
+      if (lane == 0) { dir[il][warp] = bala; dir[il][4 + warp] = balb; }
+      worda |= (ina ? 1u : 0u) << k;
+      wordb |= (inb ? 1u : 0u) << k;
+      any_amb |= amba | ambb;
+    }
+    if (__any_sync(0xffffffffu, any_amb)) {  // rare: redo the 32 rows with the reference's roundings and square roots
+      worda = wordb = 0;
+      ++slow;
+#pragma unroll 1
+      for (int k = 0; k < 32; ++k) {
+        const int il = 32 * c + k;
+        const double2 pa = sp.a[il], pb = sp.b[il], pc = sp.c[il];
+        const int i = i0 + il;
+        const double Aa = sq3_ref(__dsub_rn(xa, pa.x), __dsub_rn(ya, pa.y), __dsub_rn(za, pb.x));
+        const double Ba = sq3_ref(__dsub_rn(ua, pb.y), __dsub_rn(va, pc.x), __dsub_rn(wa, pc.y));
+        const double Ab = sq3_ref(__dsub_rn(xb, pa.x), __dsub_rn(yb, pa.y), __dsub_rn(zb, pb.x));
+        const double Bb = sq3_ref(__dsub_rn(ub, pb.y), __dsub_rn(vb, pc.x), __dsub_rn(wb, pc.y));
+        const bool ina = verdict_exact(Aa, Ba, kp.beta) && oka && (i < n) && (i != ja);
+        const bool inb = verdict_exact(Ab, Bb, kp.beta) && okb && (i < n) && (i != jb);
+        const uint32_t bala = __ballot_sync(0xffffffffu, ina), balb = __ballot_sync(0xffffffffu, inb);
+        if (lane == 0) { dir[il][warp] = bala; dir[il][4 + warp] = balb; }
+        worda |= (ina ? 1u : 0u) << k;
+        wordb |= (inb ? 1u : 0u) << k;
+      }
+    }
+    tw[0] = c == 0 ? worda : tw[0]; tw[1] = c == 1 ? worda : tw[1]; tw[2] = c == 2 ? worda : tw[2]; tw[3] = c == 3 ? worda : tw[3];
+    tw[4] = c == 0 ? wordb : tw[4]; tw[5] = c == 1 ? wordb : tw[5]; tw[6] = c == 2 ? wordb : tw[6]; tw[7] = c == 3 ? wordb : tw[7];
+  }
+  __syncthreads();
+}
+
+// work items of one problem: row block bi with the column-block pairs (bi + 2k, bi + 2k + 1), k = 0 .. ceil((T - bi)/2) - 1
+__host__ __device__ inline int graph2_items(int T) { return (T / 2) * (T / 2 + 1) + ((T & 1) ? (T + 1) / 2 : 0); }
+
+__global__ void __launch_bounds__(kTile) tim_graph2_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  const int n = d.n;
+  const int T = (n + kTile - 1) / kTile;
+  int p = blockIdx.x;
+  int bi = 0, rowlen = (T + 1) / 2;
+  while (bi < T && p >= rowlen) { p -= rowlen; ++bi; rowlen = (T - bi + 1) / 2; }
+  if (bi >= T) return;
+  const int bj = bi + 2 * p;
+  __shared__ TilePts sp;
+  __shared__ __align__(16) uint32_t dir[kTile][8];
+  uint32_t tw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  unsigned slow = 0;
+  if (bj != bi && (bj + 2) * kTile <= n) compute_tile2<true>(d.src, d.dst, n, bi * kTile, bj * kTile, kp, sp, dir, tw, slow);
+  else compute_tile2<false>(d.src, d.dst, n, bi * kTile, bj * kTile, kp, sp, dir, tw, slow);
+  const int t = threadIdx.x;
+  const int i = bi * kTile + t;
+  if (i < n) {
+    uint32_t* row = d.adj + (size_t)i * d.pitch + 4 * bj;
+    *reinterpret_cast<uint4*>(row) = *reinterpret_cast<const uint4*>(&dir[t][0]);
+    if (bj + 1 < T) *reinterpret_cast<uint4*>(row + 4) = *reinterpret_cast<const uint4*>(&dir[t][4]);
+  }
+  if (bj != bi) {
+    const int j = bj * kTile + t;
+    if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[0], tw[1], tw[2], tw[3]);
+  }
+  if (bj + 1 < T) {
+    const int j = (bj + 1) * kTile + t;
+    if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[4], tw[5], tw[6], tw[7]);
+  }
+  if (slow && (threadIdx.x & 31) == 0) atomicAdd(&d.st->slow_pairs, 2048ull * slow);
+}
+
 // Batched, symmetric: grid = (T(T+1)/2 for the largest problem, batch).
 template <int kMode>
 __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
@@ -246,7 +381,8 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
   dim3 grid(T * (T + 1) / 2, batch);
   if (kp.estimate_scaling) tim_graph_kernel<2><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.exact_only) tim_graph_kernel<1><<<grid, kTile, 0, st>>>(d_desc, kp);
-  else tim_graph_kernel<0><<<grid, kTile, 0, st>>>(d_desc, kp);
+  else if (kp.graph_v1) tim_graph_kernel<0><<<grid, kTile, 0, st>>>(d_desc, kp);
+  else tim_graph2_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
   return 1;
 }
 
