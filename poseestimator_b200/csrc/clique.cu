@@ -753,22 +753,30 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
     return;
   }
   const int np = st->n_alive, Wc = st->Wc;
-  uint32_t* Pb = sh;  // Wc words
-  const AdjView A = stage_adjacency(d, np, Wc, sh + Wc, smem_words - Wc);
-  int* plist = d.rot_inl;  // scratch, free until the rotation stage
+  uint32_t* Pb = sh;        // Wc words: candidate set
+  uint32_t* Rb = sh + Wc;   // Wc words: members chosen so far (compact ids)
+  const AdjView A = stage_adjacency(d, np, Wc, sh + 2 * Wc, smem_words - 2 * (size_t)Wc);
+  int* plist = d.rot_inl;   // scratch, free until the rotation stage
+  int* deg_in = d.tls_id;   // scratch (>= n ints): degree of every member inside P
   uint32_t* ar = arena + ((size_t)blockIdx.x * kCanonWarps + warp) * arena_words_per_warp;
   const unsigned long long deadline = kp.time_limit_ns ? globaltimer_ns() + kp.time_limit_ns : 0ull;
   for (int w = threadIdx.x; w < Wc; w += blockDim.x) {
     uint32_t x = 0u;
     if (32 * w < np) x = (np - 32 * w >= 32) ? 0xffffffffu : ((1u << (np - 32 * w)) - 1u);
     Pb[w] = x;
+    Rb[w] = 0u;
   }
   if (threadIdx.x == 0) { cs.need = st->omega; cs.outc = 0; cs.fail = 0; }
   __syncthreads();
 
+  // Lexicographically smallest maximum clique of P.  Three moves, repeated:
+  //  (a) peel P to its (need-1)-core;
+  //  (b) members adjacent to every other member of P belong to every maximum clique of P: take them all at once
+  //      (sorted(U + C') < sorted(U + C'') iff sorted(C') < sorted(C''), so removing U keeps the order of the rest);
+  //  (c) otherwise the smallest id that still extends to a clique of the required size is the next member
+  //      (decision searches, one warp per candidate).
   while (cs.need > 0 && !cs.fail) {
     const int need = cs.need;
-    // peel P to its (need-1)-core; the last pass (no change) leaves |P| and the minimum inner degree
     for (;;) {
       __syncthreads();
       if (threadIdx.x == 0) { cs.changed = 0; cs.cntP = 0; cs.mincnt = 0x7fffffff; }
@@ -781,7 +789,7 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
         c = __reduce_add_sync(FULL, c);
         if (lane == 0) {
           if (c < need - 1) { atomicAnd(&Pb[v >> 5], ~(1u << (v & 31))); cs.changed = 1; }
-          else { atomicAdd(&cs.cntP, 1); atomicMin(&cs.mincnt, c); }
+          else { atomicAdd(&cs.cntP, 1); atomicMin(&cs.mincnt, c); deg_in[v] = c; }
         }
       }
       __syncthreads();
@@ -789,7 +797,37 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
     }
     const int cntP = cs.cntP;
     if (cntP < need) { if (threadIdx.x == 0) cs.fail = 1; __syncthreads(); break; }
-    // ascending list of P's members
+    if (cs.mincnt == cntP - 1) {  // P is a clique (of exactly `need` vertices, omega being the maximum)
+      for (int w = threadIdx.x; w < Wc; w += blockDim.x) Rb[w] |= Pb[w];
+      __syncthreads();
+      if (threadIdx.x == 0) { cs.outc += cntP; cs.need = (cntP == need) ? 0 : -1; }
+      __syncthreads();
+      if (cs.need < 0) { if (threadIdx.x == 0) cs.fail = 1; __syncthreads(); }
+      break;
+    }
+    // (b) universal members
+    if (threadIdx.x == 0) cs.found = 0;
+    __syncthreads();
+    {
+      int took = 0;
+      for (int v = threadIdx.x; v < np; v += blockDim.x) {
+        if (((Pb[v >> 5] >> (v & 31)) & 1) && deg_in[v] == cntP - 1) {
+          atomicOr(&Rb[v >> 5], 1u << (v & 31));
+          atomicAnd(&Pb[v >> 5], ~(1u << (v & 31)));
+          ++took;
+        }
+      }
+      if (took) atomicAdd(&cs.found, took);
+    }
+    __syncthreads();
+    if (cs.found > 0) {
+      const int took = cs.found;
+      __syncthreads();
+      if (threadIdx.x == 0) { cs.outc += took; cs.need -= took; }
+      __syncthreads();
+      continue;
+    }
+    // (c) ascending list of P's members, then the smallest feasible one
     if (warp == 0) {
       int off = 0;
       for (int w0 = 0; w0 < Wc; w0 += 32) {
@@ -809,13 +847,6 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
       }
     }
     __syncthreads();
-    if (cntP == need && cs.mincnt == need - 1) {  // P is exactly a clique of the required size
-      for (int i = threadIdx.x; i < cntP; i += blockDim.x) d.clique[cs.outc + i] = d.ids[plist[i]];
-      __syncthreads();
-      if (threadIdx.x == 0) { cs.outc += cntP; cs.need = 0; }
-      __syncthreads();
-      break;
-    }
     if (threadIdx.x == 0) { cs.found = 0x7fffffff; cs.next = 0u; }
     __syncthreads();
     if (Wc <= 32) canon_candidates<1>(d, A, Wc, Pb, plist, &cs, ar, arena_words_per_warp, deadline, lane);
@@ -834,8 +865,28 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
       else if (w == (vs >> 5)) x &= ~((2u << (vs & 31)) - 1u);
       Pb[w] = x;
     }
-    if (threadIdx.x == 0) { d.clique[cs.outc] = d.ids[vs]; cs.outc += 1; cs.need -= 1; }
+    if (threadIdx.x == 0) { Rb[vs >> 5] |= 1u << (vs & 31); cs.outc += 1; cs.need -= 1; }
     __syncthreads();
+  }
+  __syncthreads();
+  // emit the members in ascending compact id == ascending original id
+  if (!cs.fail && warp == 0) {
+    int off = 0;
+    for (int w0 = 0; w0 < Wc; w0 += 32) {
+      const int w = w0 + lane;
+      const uint32_t word = (w < Wc) ? Rb[w] : 0u;
+      const int c = __popc(word);
+      int incl = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(FULL, incl, o);
+        if (lane >= o) incl += t;
+      }
+      int pos = off + incl - c;
+      uint32_t bits = word;
+      while (bits) { d.clique[pos++] = d.ids[32 * w + (__ffs(bits) - 1)]; bits &= bits - 1; }
+      off += __shfl_sync(FULL, incl, 31);
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) {

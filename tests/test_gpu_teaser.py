@@ -356,3 +356,25 @@ def test_scale_estimation_in_a_batch(oracle_mod):
         assert abs(sol.scale - ref.scale) < SCALE_TOL_REL * abs(ref.scale)
         assert bs.max_clique(i).tolist() == ref.clique.tolist()
         assert np.array_equal(bs.adjacency(i, pb.src.shape[1]), ref.adjacency)
+
+
+def test_non_unique_maximum_clique_is_canonical_and_fast(oracle_mod):
+    """Seeds whose consistency graph has several maximum cliques (an outlier consistent with all but one inlier): the
+    answer must be the lexicographically smallest one, as in the oracle, and the canonicalisation must not fall back to
+    hundreds of serial decision searches (it took 150 ms per batch before the universal-member shortcut)."""
+    import teaserpp_python as tpp
+    from poseestimator_b200 import batch as b2batch
+    pbs = [synth.make_problem(5000, 0.95, 105000 + i) for i in range(16)]
+    bs = b2batch.BatchSolver(_params(tpp, pbs[0].noise_bound), profiling=True)
+    bs.solve([(p.src, p.dst) for p in pbs])
+    sols = bs.solve([(p.src, p.dst) for p in pbs])
+    tm = bs.timings_ms()
+    n_multi = 0
+    for i, pb in enumerate(pbs):
+        ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12,
+                               materialize_tims=0, want_adjacency=False)
+        assert bs.max_clique(i).tolist() == ref.clique.tolist()
+        assert sols[i].valid
+        n_multi += bs.stats(i)["n_pruned"] > bs.stats(i)["omega"]
+    assert n_multi >= 1, "no problem of this batch has extra vertices in its (omega-1)-core; pick other seeds"
+    assert tm["canonical"] < 5.0 and tm["exact_search"] < 5.0, tm

@@ -1,0 +1,124 @@
+"""Multi-GPU checks and measurements (run under torchrun, one rank per GPU):
+
+  config 4  batched detections (N ~ U{200..1000}, outliers ~ U[0.3,0.9]) sharded round-robin over ranks, no collective
+  config 5  one N=20000 problem, consistency graph row-sharded, ONE all-gather of the bit rows (NCCL), replicated solve;
+            verified against the single-GPU solve of the same problem (adjacency + clique + pose)
+
+Prints one JSON object per config on rank 0.  Times are device-side (CUDA events), max over ranks.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=40)
+    ap.add_argument("--dets", type=int, default=64)
+    ap.add_argument("--n5", type=int, default=20000)
+    ap.add_argument("--skip5", action="store_true")
+    args = ap.parse_args()
+    import torch
+    import torch.distributed as dist
+    from poseestimator_b200 import batch as b2batch, sharded, synth
+    import bench
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxr(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- config 4 ----------------
+    stream = torch.cuda.Stream(); torch.cuda.set_stream(stream)
+    frames = list(sharded.shard_round_robin(args.frames, rank, world))      # whole frames per rank: 64 detections = one batch
+    pbs = {f: [synth.config4_detection(f, d) for d in range(args.dets)] for f in frames[:8]}   # 8 distinct frames, reused
+    keys = list(pbs.keys())
+    nb = pbs[keys[0]][0].noise_bound
+    solver = b2batch.BatchSolver(bench.solver_params(nb), device=local, stream=stream.cuda_stream)
+    packed = {f: [(np.ascontiguousarray(p.src.T), np.ascontiguousarray(p.dst.T)) for p in pbs[f]] for f in keys}
+    for f in keys[:2]:
+        solver.solve_packed_async(packed[f]); solver.sync()
+    barrier()
+    lat = []
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    t0 = time.perf_counter()
+    n_valid = 0
+    for i, f in enumerate(frames):
+        t1 = time.perf_counter()
+        solver.solve_packed_async(packed[keys[i % len(keys)]]); solver.sync()
+        sols = solver.solutions()
+        lat.append((time.perf_counter() - t1) * 1e3)
+        n_valid += sum(s.valid for s in sols)
+    e1.record(stream); torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    ms = maxr(e0.elapsed_time(e1))
+    tot = torch.tensor([len(frames) * args.dets, n_valid], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot)
+    p50 = maxr(statistics.median(lat)) if lat else 0.0
+    if rank == 0:
+        print(json.dumps({"config": 4, "n_gpus": world, "frames": args.frames, "detections_per_frame": args.dets,
+                          "registrations_per_s": float(tot[0]) / (ms * 1e-3), "frame_ms_p50": p50, "ms_per_detection_p50": p50 / args.dets,
+                          "valid": int(tot[1]), "total": int(tot[0]), "scaling": "weak-ish (frames split over ranks, no collective)"}), flush=True)
+
+    # ---------------- config 5 ----------------
+    if not args.skip5:
+        n = args.n5
+        pb = synth.make_problem(n, 0.95, 20000)
+        src = torch.from_numpy(np.ascontiguousarray(pb.src.T)).cuda(); dst = torch.from_numpy(np.ascontiguousarray(pb.dst.T)).cuda()
+        s5 = b2batch.BatchSolver(bench.solver_params(pb.noise_bound), device=local, profiling=True)
+        torch.cuda.synchronize()
+        sol, full = sharded.solve_row_sharded(s5, src, dst, n)      # warm-up (allocations, NCCL channels)
+        barrier()
+        times = []
+        for _ in range(5):
+            barrier()
+            t1 = time.perf_counter()
+            sol, full = sharded.solve_row_sharded(s5, src, dst, n)
+            torch.cuda.synchronize()
+            times.append(maxr((time.perf_counter() - t1) * 1e3))
+        clique_sh = s5.max_clique(0)
+        st_sh = s5.stats(0)
+        # single-GPU reference on this rank
+        s1 = b2batch.BatchSolver(bench.solver_params(pb.noise_bound), device=local, profiling=True)
+        s1.solve_device_async([n], [src.data_ptr()], [dst.data_ptr()]); s1.sync()
+        t1 = time.perf_counter(); s1.solve_device_async([n], [src.data_ptr()], [dst.data_ptr()]); s1.sync(); one_ms = (time.perf_counter() - t1) * 1e3
+        ref = s1.solution(0)
+        W = (n + 31) // 32
+        adj1 = s1.adjacency(0, n)
+        adj_sh = full.cpu().numpy().view(np.uint32)[:n, :W]
+        ok = bool(np.array_equal(adj1, adj_sh)) and clique_sh.tolist() == s1.max_clique(0).tolist() and \
+            synth.rotation_error_rad(sol.rotation, ref.rotation) < 1e-9 and np.allclose(sol.translation, ref.translation, atol=1e-12)
+        okt = torch.tensor([1.0 if ok else 0.0], device="cuda")
+        if world > 1:
+            dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            print(json.dumps({"config": 5, "n_gpus": world, "n": n, "sharded_solve_ms_median": statistics.median(times),
+                              "single_gpu_solve_ms": one_ms, "single_gpu_stage_ms": {k: round(v, 3) for k, v in s1.timings_ms().items()},
+                              "adjacency_bytes": int(n * s5.stats(0)["n"] // 8), "identical_to_single_gpu_on_all_ranks": bool(okt.item() == 1.0),
+                              "clique_size": st_sh["clique_size"], "edges": st_sh["n_edges"]}), flush=True)
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
