@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libb2r.so")
+LIB_PATH = os.environ.get("B2R_LIB") or os.path.join(_HERE, "csrc", "libb2r.so")  # B2R_LIB: A/B builds of the same library (tools/)
 
 
 class B2RParams(C.Structure):

@@ -51,10 +51,14 @@ void fill_kernel_params(b2r_solver* s) {
   k.kcore_threshold = p.kcore_heuristic_threshold;
   const double lim = p.max_clique_time_limit;
   k.time_limit_ns = (lim > 0 && lim < 1e9) ? (unsigned long long)(lim * 1e9) : 0ull;
-  k.exact_only = p.graph_exact_only;
+  k.exact_only = p.graph_exact_only == 1;
+  k.filter_tau_min = p.graph_filter_tau > 0 ? p.graph_filter_tau : 0.0;
   {
-    const char* v1 = getenv("B2R_GRAPH_V1");
-    k.graph_v1 = (v1 && v1[0] == '1') ? 1 : 0;
+    // filter generation: params.graph_exact_only = 3 / 2 or B2R_GRAPH_V = 1 / 2 select the older fp64 filters (A/B runs, tests)
+    const char* gv = getenv("B2R_GRAPH_V");
+    const int v = p.graph_exact_only == 3 ? 1 : p.graph_exact_only == 2 ? 2 : (gv && gv[0] >= '1' && gv[0] <= '3') ? gv[0] - '0' : 3;
+    k.graph_v1 = v == 1;
+    k.graph_v2 = v == 2;
     // v2 band: |F| < 2^(max(2 e(H) - 1023, e(beta^4)) - 22 + shift), compared on the high words of H and F
     const double beta4 = beta2 * beta2;
     unsigned long long bits;

@@ -43,7 +43,9 @@ struct ProbState {
   unsigned int root_counter;
   unsigned int canon_next;
   int canon_found;
-  int pad_;
+  int use32;             // graph filter v3: 1 when the packed-fp32 filter may decide pairs of this problem (graph_prep_kernel)
+  double ctr[6];         // centre of the bounding boxes of src (0..2) and dst (3..5): the fp32 copies are taken relative to it
+  float f32c[8];         // v3 constants: -2 beta^2, beta^4, beta^2, a3, a2, a1, a0 (band polynomial), k (info)
 };
 
 // Per-problem pointers (device copies of host-built descriptors).
@@ -87,6 +89,8 @@ struct KernelParams {
   unsigned long long time_limit_ns;
   int exact_only;
   int graph_v1;           // 1: the first filter kernel (one column per thread), kept for A/B measurements
+  int graph_v2;           // 1: the fp64 filter with two columns per thread (v2) instead of the packed-fp32 filter (v3)
+  double filter_tau_min;  // graph_filter_tau of the params (0 = none): lower limit of v3's band tau_G (tests widen it)
   unsigned band_k1, band_k2;  // high-word constants of the v2 ambiguity band (api.cu fill_kernel_params)
 };
 

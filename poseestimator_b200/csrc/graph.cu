@@ -19,6 +19,8 @@
 // the reference's own sqrt/sub); a 32-row chunk containing any other pair (about 1e-4 of the chunks) is redone with
 // the exact two-sqrt path.  The hot loop is branch-free: 20 FP64-pipe instructions per pair, the sign and band tests
 // run on the integer pipe.
+#include <math_constants.h>
+
 #include "common.cuh"
 
 namespace b2r {
@@ -285,6 +287,306 @@ __global__ void __launch_bounds__(kTile) tim_graph2_kernel(const ProbDesc* __res
   if (slow && (threadIdx.x & 31) == 0) atomicAdd(&d.st->slow_pairs, 2048ull * slow);
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// v3 of the filter kernel (mode 0 only): the same 128 x 256 tile and sign test, evaluated in PACKED FP32.
+//
+// v2 is bound by the FP64 pipe (64 lanes per SM per clock, 16 instructions per pair).  The verdict of almost every pair
+// is decided by a wide margin, so v3 evaluates the sign test in fp32 on the FMA pipe with `*.f32x2` instructions (FADD2 /
+// FMUL2 / FFMA2: the two columns of a thread travel in one 64-bit register pair, the row value is a scalar broadcast
+// operand) and keeps fp64 only for the ambiguous 32-row chunks.  Per TWO pairs: 6 FADD2 (differences), 6 FMUL2/FFMA2 (A, B),
+//     Dm = A - B,  S1 = A + B,  L = fma(-2 beta^2, S1, beta^4),  Dm2 = Dm * Dm,  G = Dm2 + L     (G = D^2 - 4AB, D = S1 - beta^2)
+//     thr = fma(Dm2, a3, fma(S1, fma(S1, a2, a1), a0))                                            (error band, below)
+// = 20 packed instructions, then per pair  in = (S1 < beta^2) | (G < 0),  ambiguous = !(|G| >= thr).
+//
+// Rigor (DESIGN.md "graph filter v3").  The fp32 copies are taken relative to the centre of each cloud's bounding box
+// (graph_prep_kernel); M = largest |centred coordinate|, u = 2^-24, e = 2.001 u M bounds the absolute error of a computed
+// coordinate difference (two conversions + one subtraction; its relative part is u).  Then
+//   |A~ - A| <= 3.4642 e a + 6.00001 e^2 + 5.001 u A <= 8.47 u A + 3.47 u M^2      (a = sqrt(A); e a <= (e/2M) A + e M/2)
+// so the errors of A~ and B~ together are below  E = alpha S1~ + gamma,  alpha = 8.5 u, gamma = 7 u M^2.  Propagating E and
+// every fp32 rounding through Dm, Dm2, L and G gives
+//   |G~ - G| <= 4.02 u Dm~^2 + 2 E |Dm~| + 2 E^2 + 2.95 beta^2 E + 3.02 u beta^4
+//            <= (4.02 u + 1/k) Dm~^2 + (2 + k) E^2 + 2.95 beta^2 E + 3.02 u beta^4            (2 E |Dm| <= k E^2 + Dm^2 / k, any k > 0)
+// and thr is twice that bound with (4 + k) in place of (2 + k), a polynomial in S1~ and Dm2~ with positive coefficients
+// (rounded up).  A pair outside the band has |G| >= 0.49 thr, which (i) fixes the sign of G, (ii) when G > 0 puts
+// |S1 - beta^2| >= 0.7 sqrt(thr) > 1.12 E + u beta^2, more than the error of the computed S1~ < beta^2 test, and
+// (iii) exceeds 1e-12 (S1 + beta^2)^2, three hundred times the 3.7e-15 (S1 + beta^2)^2 within which the reference's own
+// fp64 roundings (two square roots, one subtraction, the roundings of A and B) could flip the verdict.  k is chosen per
+// problem to balance the two AM-GM terms at a typical pair on the decision boundary; any k keeps the bound valid.
+// Problems with non-finite coordinates, M >= 1e8, beta outside [1e-6, 1e8] or a test-widened band >= 2^-6 run the fp64
+// filter (v2) instead; NaN in G or thr reads as ambiguous.
+// ------------------------------------------------------------------------------------------------------------------
+#define B2R_F2_OP2(name, ptx)                                                                                          \
+  __device__ __forceinline__ float2 name(float2 a, float2 b) {                                                        \
+    float2 r;                                                                                                          \
+    asm("{.reg .b64 ra, rb, rc; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; " ptx " rc, ra, rb; mov.b64 {%0,%1}, rc;}"  \
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));                                             \
+    return r;                                                                                                          \
+  }
+B2R_F2_OP2(f2add, "add.rn.f32x2")
+B2R_F2_OP2(f2sub, "sub.rn.f32x2")
+B2R_F2_OP2(f2mul, "mul.rn.f32x2")
+__device__ __forceinline__ float2 f2fma(float2 a, float2 b, float2 c) {
+  float2 r;
+  asm("{.reg .b64 ra, rb, rc, rd; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mov.b64 rc, {%6,%7}; fma.rn.f32x2 rd, ra, rb, rc; "
+      "mov.b64 {%0,%1}, rd;}"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return r;
+}
+__device__ __forceinline__ float2 f2bc(float v) { return make_float2(v, v); }
+// w |= bit when p, as one predicated LOP3 (the compiler's own choice was SEL + SHF + LOP3)
+__device__ __forceinline__ void set_bit_if(uint32_t& w, bool p, uint32_t bit) {
+  asm("{.reg .pred q; setp.ne.u32 q, %1, 0; @q or.b32 %0, %0, %2;}" : "+r"(w) : "r"((uint32_t)p), "r"(bit));
+}
+
+#ifndef B2R_G3_UNROLL
+#define B2R_G3_UNROLL 16
+#endif
+#ifndef B2R_G3_MINB
+#define B2R_G3_MINB 4
+#endif
+
+constexpr int kG3Unroll = B2R_G3_UNROLL;
+
+struct TilePts32 {
+  float4 a[kTile];  // (sx, sy, sz, dx) relative to the cloud centres
+  float2 b[kTile];  // (dy, dz)
+};
+
+// One CTA per problem: bounding boxes of src and dst -> centres, M, and the constants of the fp32 filter (ProbState).
+__global__ void __launch_bounds__(256) graph_prep_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.x];
+  const int n = d.n;
+  double mn[6], mx[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { mn[k] = CUDART_INF; mx[k] = -CUDART_INF; }
+  bool bad = false;
+  for (int i = threadIdx.x; i < n; i += 256) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double a = d.src[3 * (size_t)i + k], b = d.dst[3 * (size_t)i + k];
+      bad |= !(fabs(a) <= 1.79e308) | !(fabs(b) <= 1.79e308);
+      mn[k] = fmin(mn[k], a); mx[k] = fmax(mx[k], a);
+      mn[3 + k] = fmin(mn[3 + k], b); mx[3 + k] = fmax(mx[3 + k], b);
+    }
+  }
+  __shared__ double s_mn[8][6], s_mx[8][6];
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+      mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { s_mn[threadIdx.x >> 5][k] = mn[k]; s_mx[threadIdx.x >> 5][k] = mx[k]; }
+  }
+  if (bad) atomicOr(&s_bad, 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    ProbState* st = d.st;
+    double M = 0.0;
+    for (int k = 0; k < 6; ++k) {
+      double lo = s_mn[0][k], hi = s_mx[0][k];
+      for (int w = 1; w < 8; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
+      const double c = 0.5 * lo + 0.5 * hi;
+      st->ctr[k] = c;
+      M = fmax(M, fmax(hi - c, c - lo));
+    }
+    const double u = 5.9604644775390625e-8;  // 2^-24
+    const double beta = fabs(kp.beta), beta2 = beta * beta, beta4 = beta2 * beta2;
+    const double tmin = kp.filter_tau_min;
+    const bool ok = !s_bad && n > 0 && M < 1e8 && beta >= 1e-6 && beta <= 1e8 && tmin < 0.015625;
+    st->use32 = ok ? 1 : 0;
+    if (ok) {
+      const double alpha = 8.5 * u, gamma = 7.0 * u * M * M;
+      const double s_typ = 2.0 * M * M;                         // a typical S1; only steers k
+      double k = beta * sqrt(2.0 * s_typ) / (alpha * s_typ + gamma);
+      if (!(k >= 8.0)) k = 8.0;                                 // a3 < 1/2
+      if (k > 1e12) k = 1e12;
+      const double pad = 1.0 + 1e-5;                            // covers the fp32 evaluation of the band polynomial
+      // band in (Dm^2, S1):  thr = a3 Dm^2 + a2 S1^2 + a1 S1 + a0;  with Dm^2 <= |G| (1 + 2u) - L it becomes a polynomial
+      // in S1 alone that |G| is compared with:  |G| >= (q(S1) - a3 L) / (1 - a3 (1 + 2u))
+      const double a3 = 2.0 * (4.03 * u + 1.0001 / k);
+      const double a2 = 2.0 * (4.0 + k) * alpha * alpha + tmin;
+      const double a1 = 2.0 * (2.0 * (4.0 + k) * alpha * gamma + 2.95 * beta2 * alpha) + 2.0 * tmin * beta2;
+      const double a0 = 2.0 * ((4.0 + k) * gamma * gamma + 2.95 * beta2 * gamma + 3.02 * u * beta4) + tmin * beta4;
+      const double den = 1.0 - a3 * (1.0 + 2.0 * u);
+      st->f32c[0] = __double2float_rn(-2.0 * beta2);
+      st->f32c[1] = __double2float_rn(beta4);
+      st->f32c[2] = __double2float_rn(beta2);
+      st->f32c[3] = __double2float_ru(a2 / den * pad);
+      st->f32c[4] = __double2float_ru((a1 + a3 * 2.0 * beta2 * (1.0 + 3.0 * u)) / den * pad);
+      st->f32c[5] = __double2float_ru((a0 - a3 * beta4 * (1.0 - 3.0 * u)) / den + 1.01 * u * beta4);
+      st->f32c[6] = (float)a3;
+      st->f32c[7] = (float)k;
+    }
+  }
+}
+
+// 32 x 32 bit transpose across a warp: lane r returns the word whose bit c is bit r of lane c's x (5 shuffle steps).
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const uint32_t m = s == 16 ? 0x0000ffffu : s == 8 ? 0x00ff00ffu : s == 4 ? 0x0f0f0f0fu : s == 2 ? 0x33333333u : 0x55555555u;
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s);
+    x = (lane & s) ? ((x & ~m) | ((y & ~m) >> s)) : ((x & m) | ((y & m) << s));
+  }
+  return x;
+}
+
+// dirT[w][r]: word w (column block a: 0..3, b: 4..7 by warp) of tile row r.  The hot loop has no warp-synchronous
+// instruction (a ballot per row split it into one basic block per row and serialised the rows): every thread collects the
+// verdict bits of its two columns over 32 rows, then the warp transposes the 32 x 32 bit block with shuffles.
+template <bool kInterior>
+__device__ __forceinline__ void compute_tile3(const double* __restrict__ src, const double* __restrict__ dst, int n, int i0, int j0,
+                                              const ProbState* __restrict__ st, const KernelParams& kp, TilePts32& sp,
+                                              uint32_t (*dirT)[kTile], uint32_t tw[8], unsigned& slow) {
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const double c0 = st->ctr[0], c1 = st->ctr[1], c2 = st->ctr[2], c3 = st->ctr[3], c4 = st->ctr[4], c5 = st->ctr[5];
+  {
+    const int i = i0 + t;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    float2 b = make_float2(0.f, 0.f);
+    if (kInterior || i < n) {
+      a.x = __double2float_rn(src[3 * (size_t)i] - c0); a.y = __double2float_rn(src[3 * (size_t)i + 1] - c1);
+      a.z = __double2float_rn(src[3 * (size_t)i + 2] - c2); a.w = __double2float_rn(dst[3 * (size_t)i] - c3);
+      b.x = __double2float_rn(dst[3 * (size_t)i + 1] - c4); b.y = __double2float_rn(dst[3 * (size_t)i + 2] - c5);
+    }
+    sp.a[t] = a;
+    sp.b[t] = b;
+  }
+  const int ja = j0 + t, jb = j0 + kTile + t;
+  const bool oka = kInterior || ja < n, okb = kInterior || jb < n;
+  float2 X = f2bc(0.f), Y = X, Z = X, U = X, V = X, W = X;
+  if (oka) {
+    X.x = __double2float_rn(src[3 * (size_t)ja] - c0); Y.x = __double2float_rn(src[3 * (size_t)ja + 1] - c1);
+    Z.x = __double2float_rn(src[3 * (size_t)ja + 2] - c2); U.x = __double2float_rn(dst[3 * (size_t)ja] - c3);
+    V.x = __double2float_rn(dst[3 * (size_t)ja + 1] - c4); W.x = __double2float_rn(dst[3 * (size_t)ja + 2] - c5);
+  }
+  if (okb) {
+    X.y = __double2float_rn(src[3 * (size_t)jb] - c0); Y.y = __double2float_rn(src[3 * (size_t)jb + 1] - c1);
+    Z.y = __double2float_rn(src[3 * (size_t)jb + 2] - c2); U.y = __double2float_rn(dst[3 * (size_t)jb] - c3);
+    V.y = __double2float_rn(dst[3 * (size_t)jb + 1] - c4); W.y = __double2float_rn(dst[3 * (size_t)jb + 2] - c5);
+  }
+  const float k1 = st->f32c[0], k0 = st->f32c[1], b2 = st->f32c[2], q2 = st->f32c[3], q1 = st->f32c[4], q0 = st->f32c[5];
+  __syncthreads();
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t worda = 0, wordb = 0, ambwa = 0, ambwb = 0;
+    bool any_amb = false;
+#pragma unroll kG3Unroll
+    for (int k = 0; k < 32; ++k) {
+      const int il = 32 * c + k;
+      const float4 pa = sp.a[il];
+      const float2 pb = sp.b[il];
+      const float2 d0 = f2sub(X, f2bc(pa.x)), d1 = f2sub(Y, f2bc(pa.y)), d2 = f2sub(Z, f2bc(pa.z));
+      const float2 d3 = f2sub(U, f2bc(pa.w)), d4 = f2sub(V, f2bc(pb.x)), d5 = f2sub(W, f2bc(pb.y));
+      const float2 A = f2fma(d2, d2, f2fma(d1, d1, f2mul(d0, d0)));
+      const float2 B = f2fma(d5, d5, f2fma(d4, d4, f2mul(d3, d3)));
+      const float2 Dm = f2sub(A, B), S1 = f2add(A, B);
+      const float2 G = f2fma(Dm, Dm, f2fma(f2bc(k1), S1, f2bc(k0)));
+      const float2 T = f2fma(S1, f2fma(S1, f2bc(q2), f2bc(q1)), f2bc(q0));
+      const bool ina = (S1.x < b2) | (G.x < 0.f), inb = (S1.y < b2) | (G.y < 0.f);
+      const bool amba = !(fabsf(G.x) >= T.x), ambb = !(fabsf(G.y) >= T.y);
+      set_bit_if(worda, ina, 1u << k);
+      set_bit_if(wordb, inb, 1u << k);
+      if (kInterior) any_amb |= amba | ambb;
+      else { set_bit_if(ambwa, amba, 1u << k); set_bit_if(ambwb, ambb, 1u << k); }
+    }
+    uint32_t maska = 0xffffffffu, maskb = 0xffffffffu;
+    if (!kInterior) {  // rows past n, the diagonal and columns past n carry no pair
+      const int r0 = i0 + 32 * c;
+      const uint32_t rows = n - r0 >= 32 ? 0xffffffffu : (n - r0 <= 0 ? 0u : ((1u << (n - r0)) - 1u));
+      maska = oka ? rows : 0u;
+      maskb = okb ? rows : 0u;
+      if (ja >= r0 && ja < r0 + 32) maska &= ~(1u << (ja - r0));
+      if (jb >= r0 && jb < r0 + 32) maskb &= ~(1u << (jb - r0));
+      worda &= maska; wordb &= maskb;
+      any_amb = ((ambwa & maska) | (ambwb & maskb)) != 0u;
+    }
+    if (__any_sync(0xffffffffu, any_amb)) {  // rare: redo the 32 rows in fp64 with the reference's roundings and square roots
+      worda = wordb = 0;
+      ++slow;
+      double xa = 0, ya = 0, za = 0, ua = 0, va = 0, wa = 0, xb = 0, yb = 0, zb = 0, ub = 0, vb = 0, wb = 0;
+      if (oka) {
+        xa = src[3 * (size_t)ja]; ya = src[3 * (size_t)ja + 1]; za = src[3 * (size_t)ja + 2];
+        ua = dst[3 * (size_t)ja]; va = dst[3 * (size_t)ja + 1]; wa = dst[3 * (size_t)ja + 2];
+      }
+      if (okb) {
+        xb = src[3 * (size_t)jb]; yb = src[3 * (size_t)jb + 1]; zb = src[3 * (size_t)jb + 2];
+        ub = dst[3 * (size_t)jb]; vb = dst[3 * (size_t)jb + 1]; wb = dst[3 * (size_t)jb + 2];
+      }
+#pragma unroll 1
+      for (int k = 0; k < 32; ++k) {
+        const int i = i0 + 32 * c + k;
+        const size_t ii = (kInterior || i < n) ? (size_t)i : 0;
+        const double px = src[3 * ii], py = src[3 * ii + 1], pz = src[3 * ii + 2];
+        const double qx = dst[3 * ii], qy = dst[3 * ii + 1], qz = dst[3 * ii + 2];
+        const double Aa = sq3_ref(__dsub_rn(xa, px), __dsub_rn(ya, py), __dsub_rn(za, pz));
+        const double Ba = sq3_ref(__dsub_rn(ua, qx), __dsub_rn(va, qy), __dsub_rn(wa, qz));
+        const double Ab = sq3_ref(__dsub_rn(xb, px), __dsub_rn(yb, py), __dsub_rn(zb, pz));
+        const double Bb = sq3_ref(__dsub_rn(ub, qx), __dsub_rn(vb, qy), __dsub_rn(wb, qz));
+        worda |= (verdict_exact(Aa, Ba, kp.beta) ? 1u : 0u) << k;
+        wordb |= (verdict_exact(Ab, Bb, kp.beta) ? 1u : 0u) << k;
+      }
+      worda &= maska; wordb &= maskb;
+    }
+    dirT[warp][32 * c + lane] = warp_transpose32(worda, lane);
+    dirT[4 + warp][32 * c + lane] = warp_transpose32(wordb, lane);
+    tw[0] = c == 0 ? worda : tw[0]; tw[1] = c == 1 ? worda : tw[1]; tw[2] = c == 2 ? worda : tw[2]; tw[3] = c == 3 ? worda : tw[3];
+    tw[4] = c == 0 ? wordb : tw[4]; tw[5] = c == 1 ? wordb : tw[5]; tw[6] = c == 2 ? wordb : tw[6]; tw[7] = c == 3 ? wordb : tw[7];
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kTile, B2R_G3_MINB) tim_graph3_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  const int n = d.n;
+  const int T = (n + kTile - 1) / kTile;
+  int p = blockIdx.x;
+  int bi = 0, rowlen = (T + 1) / 2;
+  while (bi < T && p >= rowlen) { p -= rowlen; ++bi; rowlen = (T - bi + 1) / 2; }
+  if (bi >= T) return;
+  const int bj = bi + 2 * p;
+  __shared__ union { TilePts p64; TilePts32 p32; } sp;
+  __shared__ __align__(16) union { uint32_t rows[kTile][8]; uint32_t cols[8][kTile]; } dir;
+  uint32_t tw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  unsigned slow = 0;
+  const int t = threadIdx.x;
+  uint4 lo, hi;
+  if (d.st->use32) {
+    if (bj != bi && (bj + 2) * kTile <= n) compute_tile3<true>(d.src, d.dst, n, bi * kTile, bj * kTile, d.st, kp, sp.p32, dir.cols, tw, slow);
+    else compute_tile3<false>(d.src, d.dst, n, bi * kTile, bj * kTile, d.st, kp, sp.p32, dir.cols, tw, slow);
+    lo = make_uint4(dir.cols[0][t], dir.cols[1][t], dir.cols[2][t], dir.cols[3][t]);
+    hi = make_uint4(dir.cols[4][t], dir.cols[5][t], dir.cols[6][t], dir.cols[7][t]);
+  } else {
+    compute_tile2<false>(d.src, d.dst, n, bi * kTile, bj * kTile, kp, sp.p64, dir.rows, tw, slow);
+    lo = *reinterpret_cast<const uint4*>(&dir.rows[t][0]);
+    hi = *reinterpret_cast<const uint4*>(&dir.rows[t][4]);
+  }
+  const int i = bi * kTile + t;
+  if (i < n) {
+    uint32_t* row = d.adj + (size_t)i * d.pitch + 4 * bj;
+    *reinterpret_cast<uint4*>(row) = lo;
+    if (bj + 1 < T) *reinterpret_cast<uint4*>(row + 4) = hi;
+  }
+  if (bj != bi) {
+    const int j = bj * kTile + t;
+    if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[0], tw[1], tw[2], tw[3]);
+  }
+  if (bj + 1 < T) {
+    const int j = (bj + 1) * kTile + t;
+    if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[4], tw[5], tw[6], tw[7]);
+  }
+  if (slow && (threadIdx.x & 31) == 0) atomicAdd(&d.st->slow_pairs, 2048ull * slow);
+}
+
 // Batched, symmetric: grid = (T(T+1)/2 for the largest problem, batch).
 template <int kMode>
 __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
@@ -382,7 +684,12 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
   if (kp.estimate_scaling) tim_graph_kernel<2><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.exact_only) tim_graph_kernel<1><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.graph_v1) tim_graph_kernel<0><<<grid, kTile, 0, st>>>(d_desc, kp);
-  else tim_graph2_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
+  else if (kp.graph_v2) tim_graph2_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
+  else {
+    graph_prep_kernel<<<batch, 256, 0, st>>>(d_desc, kp);
+    tim_graph3_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
+    return 2;
+  }
   return 1;
 }
 

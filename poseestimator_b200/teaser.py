@@ -92,7 +92,7 @@ class _Params:
             rotation_cost_threshold=float(self.rotation_cost_threshold), rotation_tim_graph=int(self.rotation_tim_graph),
             inlier_selection_mode=mode, kcore_heuristic_threshold=float(self.kcore_heuristic_threshold),
             max_clique_time_limit=float(self.max_clique_time_limit), max_clique_num_threads=int(self.max_clique_num_threads),
-            rotation_noise_bound=float(rotation_noise_bound), graph_exact_only=int(bool(self.graph_exact_only)),
+            rotation_noise_bound=float(rotation_noise_bound), graph_exact_only=int(self.graph_exact_only),
             graph_filter_tau=float(self.graph_filter_tau),
         )
 

@@ -93,6 +93,54 @@ def test_graph_filter_equals_exact_kernel(oracle_mod, tau):
         assert b.stats()["graph_slow_pairs"] > 0
 
 
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("n,ratio,seed", [(300, 0.5, 31), (1111, 0.8, 32)])
+def test_every_filter_generation_matches_oracle(oracle_mod, mode, n, ratio, seed):
+    """graph_exact_only = 0 (packed-fp32 filter v3), 1 (two square roots), 2 / 3 (fp64 filters v2 / v1): same bits."""
+    import teaserpp_python as tpp
+    pb = synth.make_problem(n, ratio, seed)
+    ref = oracle_mod.tim_graph(pb.src, pb.dst, pb.noise_bound)
+    s = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound, graph_exact_only=mode))
+    s.solve(pb.src, pb.dst)
+    assert np.array_equal(s._adjacency_bits(), ref)
+
+
+@pytest.mark.parametrize("offset,extent,nb", [
+    (0.0, 1.0, 0.05),          # ordinary
+    (1.0e4, 1.0, 0.05),        # cloud far from the origin: the fp32 copies are centred, the filter still decides
+    (0.0, 50.0, 1e-3),         # extent / noise bound = 5e4: wide band, most chunks redone in fp64
+    (3.0e6, 2.0e3, 1e-4),      # band saturates -> everything through the exact path
+    (0.0, 1e-3, 1e-7),         # beta below the fp32 filter's range -> fp64 filter
+    (0.0, 0.0, 0.05),          # all points identical (M = 0)
+])
+def test_fp32_filter_bands_and_fallbacks(oracle_mod, offset, extent, nb):
+    """The packed-fp32 filter is only a filter: whatever its band does, the bits are the fp64 reference's."""
+    import teaserpp_python as tpp
+    rng = np.random.default_rng(77)
+    n = 333
+    src = offset + rng.uniform(-extent, extent, (3, n))
+    R = synth.random_rotation(rng)
+    dst = R @ src + rng.uniform(-1, 1, (3, 1)) * extent + rng.normal(0, nb / 4, (3, n))
+    dst[:, : n // 2] = offset + rng.uniform(-2 * extent, 2 * extent, (3, n // 2))
+    ref = oracle_mod.tim_graph(src, dst, nb)
+    s = tpp.RobustRegistrationSolver(_params(tpp, nb))
+    s.solve(src, dst)
+    assert np.array_equal(s._adjacency_bits(), ref)
+
+
+def test_fp32_filter_non_finite_input(oracle_mod):
+    """inf / NaN coordinates: the prep kernel routes the problem to the fp64 path; verdicts follow IEEE compares."""
+    import teaserpp_python as tpp
+    rng = np.random.default_rng(78)
+    n = 140
+    src = rng.uniform(-1, 1, (3, n)); dst = src + rng.normal(0, 0.01, (3, n))
+    src[0, 5] = np.inf; dst[1, 77] = np.nan
+    ref = oracle_mod.tim_graph(src, dst, 0.05)
+    s = tpp.RobustRegistrationSolver(_params(tpp, 0.05, inlier_selection_mode=tpp.RobustRegistrationSolver.INLIER_SELECTION_MODE.NONE))
+    s.solve(src, dst)
+    assert np.array_equal(s._adjacency_bits(), ref)
+
+
 def test_borderline_pairs_follow_reference_rounding(oracle_mod):
     """Pairs constructed to sit exactly on / one ulp around the bound: verdicts must follow the fp64 reference order."""
     import teaserpp_python as tpp
@@ -109,7 +157,7 @@ def test_borderline_pairs_follow_reference_rounding(oracle_mod):
         target = L + beta * (1 + (j % 5 - 2) * 2.2e-16)
         dst[:, j] = dst[:, 0] + v / L * target
     ref = oracle_mod.tim_graph(src, dst, nb)
-    for kw in (dict(graph_exact_only=True), dict()):
+    for kw in (dict(graph_exact_only=True), dict(), dict(graph_exact_only=2), dict(graph_exact_only=3)):
         s = tpp.RobustRegistrationSolver(_params(tpp, nb, **kw))
         s.solve(src, dst)
         assert np.array_equal(s._adjacency_bits(), ref)
