@@ -1,0 +1,338 @@
+// =============================================================================
+// oracle/refine_oracle.cpp  --  TEST INFRASTRUCTURE ONLY.  NOT PRODUCT CODE.
+//
+// CPU restatement of what the reference does right AFTER TEASER++ on every template
+// (SURVEY.md section 8f, rows f-1 and f-3):
+//   registration_icp(src, dst, 0.05, H, PointToPoint, max_iteration=1000)   PoseEstimator.py:97-101, main_realsense.py:112-115
+//   alignment_score / nn_residuals / voxel_coverage                         HelpersRealtime.py:100-130
+//   chamfer_distance                                                        registration_utils.py:276-280
+//   cloud_resolution                                                        registration_utils.py:229-240, HelpersRealtime.py:179-190
+//   pca_axes / initial_align_centroid_pca                                   registration_utils.py:290-343
+// (paths under /root/reference/src/pose_estimator/EstimHelpers/).
+//
+// The scoring, Chamfer, resolution and PCA functions are plain numpy / scipy in the reference: tests/golden/make_golden_refine.py
+// executes the reference's own function bodies on seeded clouds and this file is checked against those vectors (PINNED).
+// registration_icp lives in Open3D (hint ==0.19.0, not on this machine): its loop is restated from the published
+// algorithm (RegistrationICP + GetRegistrationResultAndCorrespondences + TransformationEstimationPointToPoint =
+// Eigen::umeyama without scaling) -- PARITY UNPINNED for that function; validated by ground-truth recovery and
+// against a numpy restatement in tests/test_oracle_refine.py.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline legs may load this library.
+// Build: oracle/Makefile (-O3 -fopenmp -ffp-contract=off).
+// =============================================================================
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <vector>
+#include <omp.h>
+
+namespace {
+
+inline double sq3(double x, double y, double z) { return (x * x + y * y) + z * z; }
+
+// nearest neighbour of q in pts: smallest (d2, index); d2 in the (dx*dx + dy*dy) + dz*dz order, differences pts - q
+inline int nn_one(const double* pts, int n, const double* q, double* d2_out) {
+  double best = std::numeric_limits<double>::infinity();
+  int bj = -1;
+  for (int j = 0; j < n; ++j) {
+    const double d2 = sq3(pts[3 * j] - q[0], pts[3 * j + 1] - q[1], pts[3 * j + 2] - q[2]);
+    if (d2 < best) { best = d2; bj = j; }
+  }
+  *d2_out = best;
+  return bj;
+}
+
+// Open3D PointCloud::Transform: p' = T * (x, y, z, 1), column by column, then / w (w == 1 for rigid T)
+inline void xform(const double* T, const double* p, double* o) {
+  for (int r = 0; r < 3; ++r) o[r] = ((T[4 * r] * p[0] + T[4 * r + 1] * p[1]) + T[4 * r + 2] * p[2]) + T[4 * r + 3];
+}
+
+// one-sided Jacobi SVD of a 3x3, A = U S V^T (singular values descending); enough for Umeyama
+void svd3(const double* A, double* U, double* S, double* V) {
+  double a[3][3], v[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i][j] = A[3 * i + j];
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    double off = 0;
+    for (int p = 0; p < 2; ++p) for (int q = p + 1; q < 3; ++q) {
+      double al = 0, be = 0, ga = 0;
+      for (int i = 0; i < 3; ++i) { al += a[i][p] * a[i][p]; be += a[i][q] * a[i][q]; ga += a[i][p] * a[i][q]; }
+      if (ga == 0) continue;
+      off = std::max(off, std::fabs(ga) / std::sqrt(al * be + 1e-300));
+      const double zeta = (be - al) / (2 * ga);
+      const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1 + zeta * zeta));
+      const double c = 1 / std::sqrt(1 + t * t), s = c * t;
+      for (int i = 0; i < 3; ++i) {
+        const double x = a[i][p], y = a[i][q];
+        a[i][p] = c * x - s * y; a[i][q] = s * x + c * y;
+        const double vx = v[i][p], vy = v[i][q];
+        v[i][p] = c * vx - s * vy; v[i][q] = s * vx + c * vy;
+      }
+    }
+    if (off < 1e-16) break;
+  }
+  double sv[3]; int ord[3] = {0, 1, 2};
+  for (int j = 0; j < 3; ++j) sv[j] = std::sqrt(a[0][j] * a[0][j] + a[1][j] * a[1][j] + a[2][j] * a[2][j]);
+  std::sort(ord, ord + 3, [&](int x, int y) { return sv[x] > sv[y]; });
+  double u[3][3];
+  for (int jj = 0; jj < 3; ++jj) {
+    const int j = ord[jj];
+    S[jj] = sv[j];
+    for (int i = 0; i < 3; ++i) { V[3 * i + jj] = v[i][j]; u[i][jj] = sv[j] > 0 ? a[i][j] / sv[j] : 0; }
+  }
+  auto nrm = [&](int j) { return std::sqrt(u[0][j] * u[0][j] + u[1][j] * u[1][j] + u[2][j] * u[2][j]); };
+  if (nrm(0) < 0.5) { u[0][0] = 1; u[1][0] = 0; u[2][0] = 0; }
+  if (nrm(1) < 0.5 || S[1] <= 1e-12 * S[0]) {
+    const double ax = std::fabs(u[0][0]), ay = std::fabs(u[1][0]), az = std::fabs(u[2][0]);
+    double e[3] = {0, 0, 0};
+    if (ax <= ay && ax <= az) e[0] = 1; else if (ay <= az) e[1] = 1; else e[2] = 1;
+    const double d = e[0] * u[0][0] + e[1] * u[1][0] + e[2] * u[2][0];
+    double w[3] = {e[0] - d * u[0][0], e[1] - d * u[1][0], e[2] - d * u[2][0]};
+    const double nw = std::sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+    for (int i = 0; i < 3; ++i) u[i][1] = w[i] / nw;
+  }
+  if (nrm(2) < 0.5 || S[2] <= 1e-12 * S[0]) {
+    u[0][2] = u[1][0] * u[2][1] - u[2][0] * u[1][1];
+    u[1][2] = u[2][0] * u[0][1] - u[0][0] * u[2][1];
+    u[2][2] = u[0][0] * u[1][1] - u[1][0] * u[0][1];
+  }
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) U[3 * i + j] = u[i][j];
+}
+
+inline double det3(const double* M) {
+  return M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
+}
+
+// cyclic Jacobi eigen-decomposition of a symmetric 3x3: C = Q diag(w) Q^T (columns of Q = eigenvectors, unsorted)
+void eig3(const double* C, double* w, double* Q) {
+  double a[3][3], q[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i][j] = C[3 * i + j];
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    const double off = std::fabs(a[0][1]) + std::fabs(a[0][2]) + std::fabs(a[1][2]);
+    const double dia = std::fabs(a[0][0]) + std::fabs(a[1][1]) + std::fabs(a[2][2]);
+    if (off <= 1e-300 || off <= 1e-17 * dia) break;
+    for (int p = 0; p < 2; ++p) for (int r = p + 1; r < 3; ++r) {
+      if (a[p][r] == 0) continue;
+      const double theta = (a[r][r] - a[p][p]) / (2 * a[p][r]);
+      const double t = (theta >= 0 ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(1 + theta * theta));
+      const double c = 1 / std::sqrt(1 + t * t), s = c * t;
+      for (int k = 0; k < 3; ++k) { const double x = a[k][p], y = a[k][r]; a[k][p] = c * x - s * y; a[k][r] = s * x + c * y; }
+      for (int k = 0; k < 3; ++k) { const double x = a[p][k], y = a[r][k]; a[p][k] = c * x - s * y; a[r][k] = s * x + c * y; }
+      for (int k = 0; k < 3; ++k) { const double x = q[k][p], y = q[k][r]; q[k][p] = c * x - s * y; q[k][r] = s * x + c * y; }
+    }
+  }
+  for (int i = 0; i < 3; ++i) { w[i] = a[i][i]; for (int j = 0; j < 3; ++j) Q[3 * i + j] = q[i][j]; }
+}
+
+}  // namespace
+
+extern "C" {
+
+int orcr_num_threads() { return omp_get_max_threads(); }
+
+// cKDTree(dst).query(src, k=1) / compute_point_cloud_distance: Euclidean distance to, and index of, the nearest point
+void orcr_nn(const double* q, int nq, const double* pts, int n, double* dist, int* idx) {
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < nq; ++i) {
+    double d2;
+    const int j = nn_one(pts, n, q + 3 * i, &d2);
+    if (dist) dist[i] = std::sqrt(d2);
+    if (idx) idx[i] = j;
+  }
+}
+
+void orcr_transform(const double* T16, const double* in, int n, double* out) {
+  for (int i = 0; i < n; ++i) { double o[3]; xform(T16, in + 3 * i, o); out[3 * i] = o[0]; out[3 * i + 1] = o[1]; out[3 * i + 2] = o[2]; }
+}
+
+// Eigen::umeyama(src, dst, with_scaling=false) over the correspondences (i, corr[i]) with corr[i] >= 0 -> 4x4 row-major
+void orcr_umeyama(const double* src, const double* dst, const int* corr, int ns, double* T16) {
+  double ms[3] = {0, 0, 0}, md[3] = {0, 0, 0};
+  int m = 0;
+  for (int i = 0; i < ns; ++i) if (corr[i] >= 0) {
+    for (int k = 0; k < 3; ++k) { ms[k] += src[3 * i + k]; md[k] += dst[3 * corr[i] + k]; }
+    ++m;
+  }
+  for (int k = 0; k < 16; ++k) T16[k] = (k % 5 == 0) ? 1.0 : 0.0;
+  if (m == 0) return;
+  for (int k = 0; k < 3; ++k) { ms[k] /= m; md[k] /= m; }
+  double H[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // sigma = (1/m) sum (dst - md)(src - ms)^T
+  for (int i = 0; i < ns; ++i) if (corr[i] >= 0) {
+    const double a[3] = {src[3 * i] - ms[0], src[3 * i + 1] - ms[1], src[3 * i + 2] - ms[2]};
+    const double* d = dst + 3 * corr[i];
+    const double b[3] = {d[0] - md[0], d[1] - md[1], d[2] - md[2]};
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) H[3 * r + c] += b[r] * a[c];
+  }
+  for (int k = 0; k < 9; ++k) H[k] /= m;
+  double U[9], S[3], V[9];
+  svd3(H, U, S, V);
+  const double sgn = det3(U) * det3(V) < 0 ? -1.0 : 1.0;
+  double R[9];
+  for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c)
+    R[3 * r + c] = U[3 * r] * V[3 * c] + U[3 * r + 1] * V[3 * c + 1] + sgn * U[3 * r + 2] * V[3 * c + 2];
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) T16[4 * r + c] = R[3 * r + c];
+    T16[4 * r + 3] = md[r] - (R[3 * r] * ms[0] + R[3 * r + 1] * ms[1] + R[3 * r + 2] * ms[2]);
+  }
+}
+
+static void icp_eval(const double* cur, int ns, const double* dst, int nd, double max_dist, int* corr, double* fitness, double* rmse, int* ncorr) {
+  const double r2 = max_dist * max_dist;
+  std::vector<double> d2v(ns);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < ns; ++i) {
+    double d2;
+    const int j = nn_one(dst, nd, cur + 3 * i, &d2);
+    corr[i] = (j >= 0 && d2 < r2) ? j : -1;   // SearchHybrid(point, max_dist, 1): nearest, strictly inside the radius
+    d2v[i] = d2;
+  }
+  double err = 0; int m = 0;
+  for (int i = 0; i < ns; ++i) if (corr[i] >= 0) { err += d2v[i]; ++m; }
+  *ncorr = m;
+  *fitness = m ? (double)m / (double)ns : 0.0;
+  *rmse = m ? std::sqrt(err / (double)m) : 0.0;
+}
+
+// Open3D RegistrationICP, point to point.  T_out row-major 4x4.  Returns the number of loop iterations executed.
+int orcr_icp(const double* src, int ns, const double* dst, int nd, double max_dist, const double* init16, int max_iter,
+             double rel_fitness, double rel_rmse, double* T_out, double* fitness_out, double* rmse_out, int* ncorr_out, int* corr_out) {
+  double T[16];
+  for (int k = 0; k < 16; ++k) T[k] = init16 ? init16[k] : ((k % 5 == 0) ? 1.0 : 0.0);
+  std::vector<double> cur(src, src + (size_t)3 * ns), tmp((size_t)3 * ns);
+  bool ident = true;
+  for (int k = 0; k < 16; ++k) ident = ident && T[k] == ((k % 5 == 0) ? 1.0 : 0.0);
+  if (!ident) { orcr_transform(T, cur.data(), ns, tmp.data()); cur.swap(tmp); }
+  std::vector<int> corr(ns);
+  double fit, rmse; int m;
+  icp_eval(cur.data(), ns, dst, nd, max_dist, corr.data(), &fit, &rmse, &m);
+  int it = 0;
+  for (; it < max_iter; ++it) {
+    double Uq[16], Tn[16];
+    orcr_umeyama(cur.data(), dst, corr.data(), ns, Uq);
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) {
+      double s = 0;
+      for (int k = 0; k < 4; ++k) s += Uq[4 * r + k] * T[4 * k + c];
+      Tn[4 * r + c] = s;
+    }
+    std::memcpy(T, Tn, sizeof(T));
+    orcr_transform(Uq, cur.data(), ns, tmp.data()); cur.swap(tmp);
+    const double pf = fit, pr = rmse;
+    icp_eval(cur.data(), ns, dst, nd, max_dist, corr.data(), &fit, &rmse, &m);
+    if (std::fabs(pf - fit) < rel_fitness && std::fabs(pr - rmse) < rel_rmse) { ++it; break; }
+  }
+  std::memcpy(T_out, T, sizeof(T));
+  *fitness_out = fit; *rmse_out = rmse; *ncorr_out = m;
+  if (corr_out) std::memcpy(corr_out, corr.data(), sizeof(int) * ns);
+  return it;
+}
+
+// numpy.percentile(..., method="linear") on an ascending array: virtual index (n-1)*q, numpy's two-sided _lerp
+static double np_quantile_sorted(const double* a, int n, double q) {
+  const double vi = (double)(n - 1) * q;
+  double lo = std::floor(vi);
+  if (lo > n - 1) lo = n - 1;
+  const int i0 = (int)lo, i1 = std::min(i0 + 1, n - 1);
+  const double t = vi - lo, A = a[i0], B = a[i1], d = B - A;
+  return t >= 0.5 ? B - d * (1 - t) : A + d * t;
+}
+static double np_median_sorted(const double* a, int n) {
+  if (n & 1) return a[n / 2];
+  return (a[n / 2 - 1] + a[n / 2]) / 2.0;
+}
+
+// voxel_coverage (HelpersRealtime.py:108-110): len(np.unique(np.floor(points / voxel).astype(np.int32), axis=0))
+int orcr_voxel_coverage(const double* pts, int n, double voxel) {
+  struct K { int32_t x, y, z; };
+  std::vector<K> k(n);
+  for (int i = 0; i < n; ++i) {
+    k[i].x = (int32_t)std::floor(pts[3 * i] / voxel); k[i].y = (int32_t)std::floor(pts[3 * i + 1] / voxel); k[i].z = (int32_t)std::floor(pts[3 * i + 2] / voxel);
+  }
+  std::sort(k.begin(), k.end(), [](const K& a, const K& b) { return a.x != b.x ? a.x < b.x : (a.y != b.y ? a.y < b.y : a.z < b.z); });
+  int c = 0;
+  for (int i = 0; i < n; ++i) if (i == 0 || k[i].x != k[i - 1].x || k[i].y != k[i - 1].y || k[i].z != k[i - 1].z) ++c;
+  return c;
+}
+
+// alignment_score (HelpersRealtime.py:112-130).  out5 = {median, p90, cov_aligned, cov_full, score}
+void orcr_alignment_score(const double* src_aligned, int ns, const double* src_down, int ns2, const double* dst, int nd, double voxel, double* out5) {
+  std::vector<double> d(ns);
+  orcr_nn(src_aligned, ns, dst, nd, d.data(), nullptr);
+  std::sort(d.begin(), d.end());
+  const double med = np_median_sorted(d.data(), ns), p90 = np_quantile_sorted(d.data(), ns, 0.9);
+  const int ca = orcr_voxel_coverage(src_aligned, ns, voxel), cf = orcr_voxel_coverage(src_down, ns2, voxel);
+  const double cov_norm = (double)ca / (double)std::max(cf, 1);
+  out5[0] = med; out5[1] = p90; out5[2] = ca; out5[3] = cf;
+  out5[4] = (med + 0.3 * p90) + 0.5 * (1.0 - cov_norm);
+}
+
+// chamfer_distance (registration_utils.py:276-280): mean NN distance src->dst + mean NN distance dst->src
+double orcr_chamfer(const double* a, int na, const double* b, int nb) {
+  std::vector<double> d1(na), d2(nb);
+  orcr_nn(a, na, b, nb, d1.data(), nullptr);
+  orcr_nn(b, nb, a, na, d2.data(), nullptr);
+  double s1 = 0, s2 = 0;
+  for (double v : d1) s1 += v;
+  for (double v : d2) s2 += v;
+  return s1 / na + s2 / nb;
+}
+
+// cloud_resolution (registration_utils.py:229-240): median over sub-sampled points of the distances to their k nearest
+// other points (the k+1 nearest including the point itself, first dropped)
+double orcr_cloud_resolution(const double* pts, int n, int k) {
+  if (n < 2) return 0.005;
+  const int step = std::max(1, n / 5000);
+  const int K = std::min(k + 1, n);
+  std::vector<double> all;
+  for (int i = 0; i < n; i += step) {
+    std::vector<std::pair<double, int>> d(n);
+    for (int j = 0; j < n; ++j) d[j] = {sq3(pts[3 * j] - pts[3 * i], pts[3 * j + 1] - pts[3 * i + 1], pts[3 * j + 2] - pts[3 * i + 2]), j};
+    std::partial_sort(d.begin(), d.begin() + K, d.end());
+    for (int t = 1; t < K; ++t) all.push_back(std::sqrt(d[t].first));
+  }
+  if (all.empty()) return 0.005;
+  std::sort(all.begin(), all.end());
+  return np_median_sorted(all.data(), (int)all.size());
+}
+
+// pca_axes (registration_utils.py:290-310): R columns = principal directions by decreasing variance, det = +1; s = sqrt(eigenvalues)
+void orcr_pca_axes(const double* pts, int n, double* R9, double* s3, double* centroid3) {
+  double c[3] = {0, 0, 0};
+  for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) c[k] += pts[3 * i + k];
+  for (int k = 0; k < 3; ++k) c[k] /= n;
+  double C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < n; ++i) {
+    const double x[3] = {pts[3 * i] - c[0], pts[3 * i + 1] - c[1], pts[3 * i + 2] - c[2]};
+    for (int r = 0; r < 3; ++r) for (int q = 0; q < 3; ++q) C[3 * r + q] += x[r] * x[q];
+  }
+  const double den = (double)std::max(n - 1, 1);
+  for (int k = 0; k < 9; ++k) C[k] /= den;
+  double w[3], Q[9];
+  eig3(C, w, Q);
+  int ord[3] = {0, 1, 2};
+  std::sort(ord, ord + 3, [&](int a, int b) { return w[a] > w[b]; });
+  for (int jj = 0; jj < 3; ++jj) { for (int i = 0; i < 3; ++i) R9[3 * i + jj] = Q[3 * i + ord[jj]]; s3[jj] = std::sqrt(std::max(w[ord[jj]], 0.0)); }
+  if (det3(R9) < 0) for (int i = 0; i < 3; ++i) R9[3 * i + 2] = -R9[3 * i + 2];
+  if (centroid3) for (int k = 0; k < 3; ++k) centroid3[k] = c[k];
+}
+
+// initial_align_centroid_pca (registration_utils.py:314-343) -> T0 row-major 4x4
+void orcr_pca_align(const double* src, int ns, const double* dst, int nd, double* T16) {
+  double Rs[9], Rd[9], ss[3], sd[3], cs[3], cd[3];
+  orcr_pca_axes(src, ns, Rs, ss, cs);
+  orcr_pca_axes(dst, nd, Rd, sd, cd);
+  double Ra[9];
+  std::memcpy(Ra, Rs, sizeof(Ra));
+  for (int j = 0; j < 3; ++j) {
+    const double dot = Rs[j] * Rd[j] + Rs[3 + j] * Rd[3 + j] + Rs[6 + j] * Rd[6 + j];
+    if (dot < 0) for (int i = 0; i < 3; ++i) Ra[3 * i + j] = -Ra[3 * i + j];
+  }
+  if (det3(Ra) < 0) for (int i = 0; i < 3; ++i) Ra[3 * i + 2] = -Ra[3 * i + 2];
+  for (int k = 0; k < 16; ++k) T16[k] = (k % 5 == 0) ? 1.0 : 0.0;
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) T16[4 * r + c] = Rd[3 * r] * Ra[3 * c] + Rd[3 * r + 1] * Ra[3 * c + 1] + Rd[3 * r + 2] * Ra[3 * c + 2];
+    T16[4 * r + 3] = cd[r] - (T16[4 * r] * cs[0] + T16[4 * r + 1] * cs[1] + T16[4 * r + 2] * cs[2]);
+  }
+}
+
+}  // extern "C"
