@@ -224,6 +224,43 @@ b2r_status b2r_mutual_pairs(b2r_solver* s, const int32_t* nn01_dev, int na, cons
 b2r_status b2r_gather_correspondences(b2r_solver* s, const double* a_pts_dev, const double* b_pts_dev, const int32_t* pairs_dev,
                                       int n_pairs, double* src_dev, double* dst_dev);
 
+/* ---- refinement and scoring right after solver.solve (what the reference does per template, PoseEstimator.py:97-108) ------
+ * Point buffers are DEVICE pointers ([n,3] float64); 4x4 matrices are HOST, row-major.  All calls are synchronous. */
+typedef struct b2r_icp_result {
+  double transformation[16];  /* icp_result.transformation */
+  double fitness;             /* correspondences / source points */
+  double inlier_rmse;
+  int32_t n_corr;
+  int32_t iterations;         /* loop iterations executed */
+  int32_t converged;          /* 1: relative fitness / rmse criterion met; 0: stopped by max_iteration */
+  int32_t pad_;
+} b2r_icp_result;
+
+/* pcd.transform(T): p' = T * (x, y, z, 1) */
+b2r_status b2r_transform_points(b2r_solver* s, const double* T16, const double* in_dev, int n, double* out_dev);
+/* nearest reference point of every query (exact fp64, lowest index on ties): squared distance and / or index.
+ * cKDTree(ref).query(q, k=1) (HelpersRealtime.py:103-104), pcd.compute_point_cloud_distance (registration_utils.py:277-278). */
+b2r_status b2r_nn_distance(b2r_solver* s, const double* q_dev, int nq, const double* ref_dev, int nr, double* dist2_dev, int32_t* idx_dev);
+/* o3d.pipelines.registration.registration_icp(src, dst, max_dist, init, TransformationEstimationPointToPoint(),
+ * ICPConvergenceCriteria(relative_fitness, relative_rmse, max_iteration)) (PoseEstimator.py:97-101, main_realsense.py:112-115).
+ * init16 NULL = identity; corr_dev [ns] optional: nearest target index of every source point, -1 outside max_dist. */
+b2r_status b2r_icp(b2r_solver* s, const double* src_dev, int ns, const double* dst_dev, int nd, double max_dist, const double* init16,
+                   int max_iter, double rel_fitness, double rel_rmse, b2r_icp_result* out, int32_t* corr_dev);
+/* voxel_coverage (HelpersRealtime.py:108-110): distinct floor(p / voxel) int32 triples */
+b2r_status b2r_voxel_coverage(b2r_solver* s, const double* pts_dev, int n, double voxel, int* count_out);
+/* alignment_score (HelpersRealtime.py:112-130): out5 = {median, p90, cov_aligned, cov_full, score} (numpy median / percentile) */
+b2r_status b2r_alignment_score(b2r_solver* s, const double* src_aligned_dev, int ns, const double* src_down_dev, int ns2,
+                               const double* dst_dev, int nd, double voxel, double* out5);
+/* chamfer_distance (registration_utils.py:276-280) */
+b2r_status b2r_chamfer(b2r_solver* s, const double* a_dev, int na, const double* b_dev, int nb, double* out);
+/* cloud_resolution(pcd, k) (registration_utils.py:229-240) */
+b2r_status b2r_cloud_resolution(b2r_solver* s, const double* pts_dev, int n, int k, double* out);
+/* pca_axes (registration_utils.py:290-310): R9 columns = principal axes by decreasing variance (det +1), s3 = sqrt(eigenvalues),
+ * c3 = centroid; s3 / c3 optional */
+b2r_status b2r_pca_axes(b2r_solver* s, const double* pts_dev, int n, double* R9, double* s3, double* c3);
+/* initial_align_centroid_pca (registration_utils.py:314-343) -> T0 (src -> dst) */
+b2r_status b2r_pca_align(b2r_solver* s, const double* src_dev, int ns, const double* dst_dev, int nd, double* T16);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,11 @@ class B2RSolution(C.Structure):
     _fields_ = [("scale", C.c_double), ("rotation", C.c_double * 9), ("translation", C.c_double * 3), ("valid", C.c_int32)]
 
 
+class B2RIcpResult(C.Structure):
+    _fields_ = [("transformation", C.c_double * 16), ("fitness", C.c_double), ("inlier_rmse", C.c_double), ("n_corr", C.c_int32),
+                ("iterations", C.c_int32), ("converged", C.c_int32), ("pad_", C.c_int32)]
+
+
 class B2RStats(C.Structure):
     _fields_ = [
         ("n", C.c_int32), ("n_edges", C.c_int64), ("max_degree", C.c_int32), ("heuristic_lb", C.c_int32),
@@ -58,6 +63,8 @@ EXPORTS = [
     "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
+    "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
+    "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align",
 ]
 
 IDX_MAX_CLIQUE, IDX_ROT_INLIERS, IDX_ROT_INLIERS_MAP, IDX_TRANS_INLIERS, IDX_TRANS_INLIERS_MAP, IDX_DEGREES = range(6)
@@ -116,6 +123,15 @@ def lib():
     L.b2r_gather_correspondences.argtypes = [vp, vp, vp, vp, i32, vp, vp]
     L.b2r_nn_gemm.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp, ip]
     L.b2r_mutual_nn.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp, vp, ip, ip]
+    L.b2r_transform_points.argtypes = [vp, vp, vp, i32, vp]
+    L.b2r_nn_distance.argtypes = [vp, vp, i32, vp, i32, vp, vp]
+    L.b2r_icp.argtypes = [vp, vp, i32, vp, i32, d, vp, i32, d, d, C.POINTER(B2RIcpResult), vp]
+    L.b2r_voxel_coverage.argtypes = [vp, vp, i32, d, ip]
+    L.b2r_alignment_score.argtypes = [vp, vp, i32, vp, i32, vp, i32, d, vp]
+    L.b2r_chamfer.argtypes = [vp, vp, i32, vp, i32, C.POINTER(C.c_double)]
+    L.b2r_cloud_resolution.argtypes = [vp, vp, i32, i32, C.POINTER(C.c_double)]
+    L.b2r_pca_axes.argtypes = [vp, vp, i32, vp, vp, vp]
+    L.b2r_pca_align.argtypes = [vp, vp, i32, vp, i32, vp]
     _lib = L
     return L
 

@@ -246,7 +246,7 @@ b2r_status b2r_destroy(b2r_solver* s) {
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->stream);
   s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
-  s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release();
+  s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release(); s->d_refine.release(); s->h_refine.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
   if (s->ev_ready) for (int i = 0; i < 12; ++i) cudaEventDestroy(s->ev[i]);
   if (s->own_stream) cudaStreamDestroy(s->stream);

@@ -1079,6 +1079,14 @@ b2r_status run_knn(b2r_solver* s, const double* pts, int n, const double* querie
 
 }  // namespace
 
+namespace b2r {
+// kNN dispatch for the other translation units (refine.cu)
+b2r_status internal_knn(b2r_solver* s, const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx,
+                        double* d2, int* cnt) {
+  return run_knn(s, pts, n, queries, nq, K, radius, idx, d2, cnt, 0);
+}
+}  // namespace b2r
+
 extern "C" {
 
 b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* mask, int H, int W, int u0, int v0, int u1, int v1,

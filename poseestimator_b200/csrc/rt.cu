@@ -9,6 +9,7 @@
 #include <math_constants.h>
 
 #include "common.cuh"
+#include "linalg.cuh"
 
 namespace b2r {
 
@@ -59,85 +60,6 @@ __device__ double block_max(double v, double* red) {
   return m;
 }
 
-__device__ __forceinline__ double det3(const double* M) {
-  return M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
-}
-
-// R = V diag(1,1,det(U)det(V)) U^T from the SVD H = U S V^T (one-sided Jacobi on the columns of H).
-__device__ void rotation_from_H(const double* H, double* R) {
-  double a[3][3], v[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j) a[i][j] = H[3 * i + j];
-  for (int sweep = 0; sweep < 40; ++sweep) {
-    double off = 0;
-#pragma unroll
-    for (int pq = 0; pq < 3; ++pq) {
-      const int p = pq == 2 ? 1 : 0, q = pq == 0 ? 1 : 2;
-      const double alpha = a[0][p] * a[0][p] + a[1][p] * a[1][p] + a[2][p] * a[2][p];
-      const double beta = a[0][q] * a[0][q] + a[1][q] * a[1][q] + a[2][q] * a[2][q];
-      const double gamma = a[0][p] * a[0][q] + a[1][p] * a[1][q] + a[2][p] * a[2][q];
-      if (gamma != 0.0) {
-        off = fmax(off, fabs(gamma) * rsqrt(alpha * beta + 1e-300));
-        const double zeta = (beta - alpha) / (2 * gamma);
-        const double tt = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1 + zeta * zeta));
-        const double c = rsqrt(1 + tt * tt), s = c * tt;
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-          const double x = a[i][p], y = a[i][q];
-          a[i][p] = c * x - s * y; a[i][q] = s * x + c * y;
-          const double vx = v[i][p], vy = v[i][q];
-          v[i][p] = c * vx - s * vy; v[i][q] = s * vx + c * vy;
-        }
-      }
-    }
-    if (off < 1e-16) break;
-  }
-  double sv[3];
-#pragma unroll
-  for (int j = 0; j < 3; ++j) sv[j] = sqrt(a[0][j] * a[0][j] + a[1][j] * a[1][j] + a[2][j] * a[2][j]);
-  // order columns by decreasing singular value (3-element sorting network on indices)
-  int o0 = 0, o1 = 1, o2 = 2;
-  if (sv[o0] < sv[o1]) { int t = o0; o0 = o1; o1 = t; }
-  if (sv[o1] < sv[o2]) { int t = o1; o1 = o2; o2 = t; }
-  if (sv[o0] < sv[o1]) { int t = o0; o0 = o1; o1 = t; }
-  const int ord[3] = {o0, o1, o2};
-  double U[9], V[9];
-#pragma unroll
-  for (int jj = 0; jj < 3; ++jj) {
-    int j = ord[jj];
-    double s = 0, c0 = 0, c1 = 0, c2 = 0, w0 = 0, w1 = 0, w2 = 0;
-#pragma unroll
-    for (int q = 0; q < 3; ++q)
-      if (q == j) { s = sv[q]; c0 = a[0][q]; c1 = a[1][q]; c2 = a[2][q]; w0 = v[0][q]; w1 = v[1][q]; w2 = v[2][q]; }
-    const double inv = s > 0 ? 1.0 / s : 0.0;
-    U[jj] = c0 * inv; U[3 + jj] = c1 * inv; U[6 + jj] = c2 * inv;
-    V[jj] = w0; V[3 + jj] = w1; V[6 + jj] = w2;
-  }
-  const double s0 = sv[o0], s1 = sv[o1], s2 = sv[o2];
-  // complete U when H is (numerically) rank deficient, so that R stays a rotation
-  if (!(s0 > 0)) { U[0] = 1; U[3] = 0; U[6] = 0; }
-  if (!(s1 > 1e-12 * s0) || !(s0 > 0)) {
-    const double ax = fabs(U[0]), ay = fabs(U[3]), az = fabs(U[6]);
-    double e0 = 0, e1 = 0, e2 = 0;
-    if (ax <= ay && ax <= az) e0 = 1; else if (ay <= az) e1 = 1; else e2 = 1;
-    const double dd = e0 * U[0] + e1 * U[3] + e2 * U[6];
-    double w0 = e0 - dd * U[0], w1 = e1 - dd * U[3], w2 = e2 - dd * U[6];
-    const double nw = rsqrt(w0 * w0 + w1 * w1 + w2 * w2);
-    U[1] = w0 * nw; U[4] = w1 * nw; U[7] = w2 * nw;
-  }
-  if (!(s2 > 1e-12 * s0) || !(s0 > 0)) {
-    U[2] = U[3] * U[7] - U[6] * U[4];
-    U[5] = U[6] * U[1] - U[0] * U[7];
-    U[8] = U[0] * U[4] - U[3] * U[1];
-  }
-  if (det3(U) * det3(V) < 0) { V[2] = -V[2]; V[5] = -V[5]; V[8] = -V[8]; }
-#pragma unroll
-  for (int r = 0; r < 3; ++r)
-#pragma unroll
-    for (int c = 0; c < 3; ++c) R[3 * r + c] = V[3 * r] * U[3 * c] + V[3 * r + 1] * U[3 * c + 1] + V[3 * r + 2] * U[3 * c + 2];
-}
 
 __global__ void __launch_bounds__(kRtThreads) rotation_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
   const ProbDesc d = descs[blockIdx.x];
