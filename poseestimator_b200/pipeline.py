@@ -152,3 +152,60 @@ class FrameRegistration:
         T[:3, :3] = sol.scale * sol.rotation
         T[:3, 3] = sol.translation
         return T
+
+
+class TemplateMatcher:
+    """`PoseEstimator.find_best_template_teaser` on the GPU (/root/reference/src/pose_estimator/EstimHelpers/PoseEstimator.py:85-116):
+
+        dst_down = dst_cloud.voxel_down_sample(voxel)
+        for every template:  src_down = src.voxel_down_sample(voxel);  H = run_teaser(src_down, dst_down, voxel)
+                             T = registration_icp(src_down, dst_down, 0.05, H, PointToPoint, max_iteration=1000).transformation
+                             score = alignment_score(src_down.transform(T), src_down, dst_down, voxel);  keep the lowest score
+        return best H (the TEASER++ pose, as the reference does) and its src_down
+
+    Templates are the batch axis: their voxel clouds, normals and FPFH descriptors are computed once and stay resident.  The
+    correspondence step is the north-star's mutual nearest neighbour on FPFH."""
+
+    def __init__(self, templates, config: "PipelineConfig | None" = None, device: int = 0, icp_distance: float = 0.05,
+                 icp_max_iteration: int = 1000, template_view=(0.0, 0.0, 0.0)):
+        from .refine import Refiner
+        self.cfg = config or PipelineConfig()
+        self.icp_distance = float(icp_distance)          # PoseEstimator.py:98
+        self.icp_max_iteration = int(icp_max_iteration)  # PoseEstimator.py:100
+        self.regs = [FrameRegistration(t, config=self.cfg, device=device, template_view=template_view) for t in templates if t is not None]
+        self.rf = Refiner(device)
+
+    def run_teaser(self, k: int, dst_down, dst_desc):
+        """run_teaser(source=template k, target=dst_down) -> (4x4 H, solution, n_corr)  (HelpersRealtime.py:132-172)."""
+        reg = self.regs[k]
+        pairs, _, _ = reg.ps.mutual_nn(reg.template_desc, dst_desc, method=self.cfg.nn_method)
+        n = int(pairs.shape[0])
+        if n < 3:
+            return np.eye(4), RegistrationSolution(), n
+        src, dst = reg.ps.gather_correspondences(reg.template, dst_down, pairs)
+        reg.solver.solve_device_async([n], [src.data_ptr()], [dst.data_ptr()], keep_alive=(src, dst))
+        reg.solver.sync()
+        sol = reg.solver.solution(0)
+        return reg.transform(sol), sol, n
+
+    def find_best_template_teaser(self, dst_cloud, details: bool = False):
+        """dst_cloud: [n,3] scene points (numpy or CUDA tensor).  -> (H_best, src_down_best) (+ per-template records)."""
+        if not self.regs:
+            return (np.eye(4), None, []) if details else (np.eye(4), None)
+        r0 = self.regs[0]
+        dst_down, _, _ = r0.ps.voxel_down(dst_cloud, self.cfg.voxel)                       # PoseEstimator.py:87
+        _, dst_desc = r0.features(dst_down)
+        best = dict(T=np.eye(4), score=np.inf, src=None, idx=-1)
+        recs = []
+        for k, reg in enumerate(self.regs):
+            H, sol, n_corr = self.run_teaser(k, dst_down, dst_desc)
+            icp = self.rf.registration_icp(reg.template, dst_down, self.icp_distance, H, max_iteration=self.icp_max_iteration)
+            src_aligned = self.rf.transform(reg.template, icp.transformation)
+            score = self.rf.alignment_score(src_aligned, reg.template, dst_down, self.cfg.voxel)
+            recs.append(dict(template=k, n_corr=n_corr, valid=bool(sol.valid), H=H, T_icp=icp.transformation, fitness=icp.fitness,
+                             inlier_rmse=icp.inlier_rmse, icp_iterations=icp.iterations, score=score))
+            if score < best["score"]:
+                best.update(score=score, T=H, src=reg.template, idx=k)
+        if details:
+            return best["T"], best["src"], recs
+        return best["T"], best["src"]

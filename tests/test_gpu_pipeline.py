@@ -58,3 +58,54 @@ def test_pipeline_degenerate_frames():
     tiny = np.zeros_like(f.mask); tiny[240, 320] = 255; tiny[240, 321] = 255
     r = reg.register(f.depth, tiny, None, f.fx, f.fy, f.cx, f.cy, f.depth_scale)
     assert not r.solution.valid and r.n_raw <= 2
+
+
+def test_find_best_template_matches_oracle_loop(oracle_mod):
+    """PoseEstimator.find_best_template_teaser: three templates (the right box, a wrong box, a half-size box); every stage of
+    the loop -- TEASER pose, ICP refinement, alignment score, the arg-min -- against the oracle's."""
+    from oracle import presteps as op
+    from oracle import refine as orf
+    from poseestimator_b200.pipeline import PipelineConfig, TemplateMatcher
+    cfg = PipelineConfig()
+    f = synth.make_frame(seed=2)
+    wrong = synth.make_frame(seed=3, size=(0.22, 0.22, 0.06)).cad
+    small = synth.make_frame(seed=4, size=(0.15, 0.075, 0.05)).cad
+    raw, _ = op.backproject(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale, cfg.depth_trunc)
+    keep, _ = op.statistical_outlier(raw, cfg.outlier_nb, cfg.outlier_std)
+    dst_cloud = raw[keep]
+    tm = TemplateMatcher([wrong, f.cad, small], config=cfg, icp_max_iteration=60)
+    H, src_best, recs = tm.find_best_template_teaser(dst_cloud, details=True)
+    # oracle loop
+    rn, rfp = cfg.normal_radius_mult * cfg.voxel, cfg.fpfh_radius_mult * cfg.voxel
+    dst_down, _, _ = op.voxel_down(dst_cloud, cfg.voxel)
+    f_d = op.fpfh(dst_down, op.normals(dst_down, rn, cfg.normal_max_nn, 1, (0, 0, 0)), rfp, cfg.fpfh_max_nn).T.copy()
+    scores = []
+    for k, cad in enumerate([wrong, f.cad, small]):
+        src_down, _, _ = op.voxel_down(cad, cfg.voxel)
+        f_s = op.fpfh(src_down, op.normals(src_down, rn, cfg.normal_max_nn, 2, (0, 0, 0)), rfp, cfg.fpfh_max_nn).T.copy()
+        pairs, _, _ = op.mutual_nn(f_s, f_d)
+        assert recs[k]["n_corr"] == pairs.shape[0]
+        Ho = np.eye(4)
+        determined = False
+        if pairs.shape[0] >= 3:
+            ref = oracle_mod.solve(src_down[pairs[:, 0]].T, dst_down[pairs[:, 1]].T, noise_bound=cfg.noise_bound_mult * cfg.voxel,
+                                   estimate_scaling=0, rotation_cost_threshold=1e-12)
+            assert recs[k]["valid"] == bool(ref.valid)
+            if ref.valid:
+                Ho[:3, :3] = ref.rotation; Ho[:3, 3] = ref.translation
+            determined = len(ref.clique) >= 3      # a 2-clique gives collinear TIMs: rank-1 H, the rotation about them is free
+        if determined or pairs.shape[0] < 3:
+            assert synth.rotation_error_rad(recs[k]["H"][:3, :3], Ho[:3, :3]) < 1e-5
+            assert np.linalg.norm(recs[k]["H"][:3, 3] - Ho[:3, 3]) < 1e-6
+        # ICP and score from the GPU's own H (the oracle's H differs in the last bits; ICP from each converges to the same pose)
+        icp = orf.icp(src_down, dst_down, 0.05, recs[k]["H"], 60)
+        assert recs[k]["icp_iterations"] == icp.iterations
+        assert np.allclose(recs[k]["T_icp"], icp.transformation, atol=1e-9)
+        sc = orf.alignment_score(orf.transform(recs[k]["T_icp"], src_down), src_down, dst_down, cfg.voxel)["score"]
+        assert recs[k]["score"] == sc
+        scores.append(sc)
+    # the winner is whatever the reference's score prefers (a full box seen from one side is penalised by its hidden faces)
+    kb = int(np.argmin(scores))
+    assert np.array_equal(H, recs[kb]["H"])
+    assert np.array_equal(src_best.cpu().numpy(), op.voxel_down([wrong, f.cad, small][kb], cfg.voxel)[0])
+    assert recs[1]["fitness"] > 0.3 and recs[1]["inlier_rmse"] < 0.05
