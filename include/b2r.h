@@ -261,6 +261,18 @@ b2r_status b2r_pca_axes(b2r_solver* s, const double* pts_dev, int n, double* R9,
 /* initial_align_centroid_pca (registration_utils.py:314-343) -> T0 (src -> dst) */
 b2r_status b2r_pca_align(b2r_solver* s, const double* src_dev, int ns, const double* dst_dev, int nd, double* T16);
 
+/* ---- CAD depth render (replaces the Filament OffscreenRenderer of PoseEstimator.py:118-141 / template_creation.py:188-233) ---
+ * verts_dev [nv,3] f64 model frame, tris_dev [nt,3] i32, T16 = model -> camera (HOST, row-major; OpenCV camera: x right, y down,
+ * z forward).  depth_dev [H,W] f32: view-space z of the nearest surface on the ray ((u-cx)/fx, (v-cy)/fy, 1) of every pixel with
+ * z_near < z < z_far, 0 where there is none (render_to_depth_image(z_in_view_space=True) after depth_trunc). */
+b2r_status b2r_render_depth(b2r_solver* s, const double* verts_dev, int nv, const int32_t* tris_dev, int nt, const double* T16, double fx,
+                            double fy, double cx, double cy, int W, int H, double z_near, double z_far, float* depth_dev);
+/* RGBDImage.create_from_color_and_depth(depth_scale, depth_trunc) + PointCloud.create_from_rgbd_image on a FLOAT depth image
+ * (PoseEstimator.py:130-135, template_creation.py:230-233): points [M,3] f64 in row-major pixel order, pixel ids optional. */
+b2r_status b2r_backproject_depth32(b2r_solver* s, const float* depth_dev, int H, int W, double fx, double fy, double cx, double cy,
+                                   double depth_scale, double depth_trunc, double* points_dev, int32_t* pixel_ids_dev, int capacity,
+                                   int* count_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,8 +27,8 @@ _BUILD = os.path.join(_HERE, "_build")
 
 def build(force: bool = False) -> None:
     """Compile the oracle with the committed Makefile (g++ only, seconds)."""
-    libs = [os.path.join(_BUILD, n) for n in ("liboracle_teaser.so", "liboracle_presteps.so", "liboracle_refine.so")]
-    srcs = [os.path.join(_HERE, n) for n in ("teaser_oracle.cpp", "presteps_oracle.cpp", "refine_oracle.cpp")]
+    libs = [os.path.join(_BUILD, n) for n in ("liboracle_teaser.so", "liboracle_presteps.so", "liboracle_refine.so", "liboracle_raster.so")]
+    srcs = [os.path.join(_HERE, n) for n in ("teaser_oracle.cpp", "presteps_oracle.cpp", "refine_oracle.cpp", "raster_oracle.cpp")]
     stale = force or any(
         (not os.path.exists(l)) or os.path.getmtime(l) < os.path.getmtime(s) for l, s in zip(libs, srcs) if os.path.exists(s)
     )
