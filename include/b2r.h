@@ -273,6 +273,14 @@ b2r_status b2r_backproject_depth32(b2r_solver* s, const float* depth_dev, int H,
                                    double depth_scale, double depth_trunc, double* points_dev, int32_t* pixel_ids_dev, int capacity,
                                    int* count_out);
 
+/* LiDAR cloud -> image selection (main_seibersdorf.py:70-81,149-162): Xc = R p + t, keep z > z_min, project with K (row-major 3x3)
+ * and the OpenCV distortion D (4, 5 or 8 coefficients, else ignored) like cv2.projectPoints on float32 input, truncate to int32,
+ * keep pixels inside the W x H image whose mask byte is non-zero (mask_dev NULL: no mask).  idx_dev [<= n]: surviving point ids in
+ * ascending order, uv_dev [<= n, 2] their pixels (optional).  R9, t3, K9, D are HOST arrays. */
+b2r_status b2r_project_select(b2r_solver* s, const double* pts_dev, int n, const double* R9, const double* t3, const double* K9, const double* D,
+                              int nD, int W, int H, const uint8_t* mask_dev, double z_min, int32_t* idx_dev, int32_t* uv_dev, int* n_front_out,
+                              int* n_in_image_out, int* n_selected_out);
+
 #ifdef __cplusplus
 }
 #endif

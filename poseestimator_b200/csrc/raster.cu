@@ -124,6 +124,67 @@ __global__ void __launch_bounds__(256) backproject32_kernel(const float* __restr
   }
 }
 
+// LiDAR cloud -> image: the selection step of main_seibersdorf.project_and_colorize (main_seibersdorf.py:70-81,149-162):
+//   Xc = R p + t;  front = z > z_min;  uv = cv2.projectPoints(float32(Xc), 0, 0, K, D).astype(int32);  inside the image;  mask[v, u]
+// One thread per point, ordered compaction of the survivors (ascending point index, like the reference's index arrays).
+struct ProjArgs {
+  double R[9], t[3], fx, fy, cx, cy, k[8], z_min;
+  int nk, W, H;
+};
+__global__ void __launch_bounds__(256) project_select_kernel(const double* __restrict__ pts, int n, ProjArgs a, const unsigned char* __restrict__ mask,
+                                                             int* __restrict__ idx_out, int* __restrict__ uv_out, unsigned long long* ws,
+                                                             int* __restrict__ counts /* [0] selected [1] front [2] in image */) {
+  __shared__ int s_tile;
+  __shared__ unsigned s_warp[8];
+  __shared__ unsigned long long s_base;
+  const int tile = take_ticket(ws, &s_tile);
+  const int i = tile * 256 + threadIdx.x;
+  bool front = false, inimg = false, sel = false;
+  int u = 0, v = 0;
+  if (i < n) {
+    const double x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
+    const double X = ((a.R[0] * x + a.R[1] * y) + a.R[2] * z) + a.t[0];
+    const double Y = ((a.R[3] * x + a.R[4] * y) + a.R[5] * z) + a.t[1];
+    const double Z = ((a.R[6] * x + a.R[7] * y) + a.R[8] * z) + a.t[2];
+    front = Z > a.z_min;
+    if (front) {
+      // cv2.projectPoints on float32 input, identity pose: double arithmetic inside, float32 result, then astype(int32)
+      const double Xf = (double)(float)X, Yf = (double)(float)Y, Zf = (double)(float)Z;
+      const double iz = Zf != 0.0 ? 1.0 / Zf : 1.0;
+      const double xn = Xf * iz, yn = Yf * iz;
+      double xd = xn, yd = yn;
+      if (a.nk > 0) {
+        const double r2 = xn * xn + yn * yn, r4 = r2 * r2, r6 = r4 * r2;
+        const double a1 = 2 * xn * yn, a2 = r2 + 2 * xn * xn, a3 = r2 + 2 * yn * yn;
+        const double cdist = 1 + a.k[0] * r2 + a.k[1] * r4 + a.k[4] * r6;
+        const double icdist2 = 1.0 / (1 + a.k[5] * r2 + a.k[6] * r4 + a.k[7] * r6);
+        xd = xn * cdist * icdist2 + a.k[2] * a1 + a.k[3] * a2;
+        yd = yn * cdist * icdist2 + a.k[2] * a3 + a.k[3] * a1;
+      }
+      const float uf = (float)(xd * a.fx + a.cx), vf = (float)(yd * a.fy + a.cy);
+      // numpy float32 -> int32 truncates towards zero; out-of-range values are rejected by the image test anyway
+      u = (fabsf(uf) < 2.0e9f) ? (int)uf : -1;
+      v = (fabsf(vf) < 2.0e9f) ? (int)vf : -1;
+      inimg = u >= 0 && u < a.W && v >= 0 && v < a.H;
+      sel = inimg && (!mask || mask[(size_t)v * a.W + u] != 0);
+    }
+  }
+  const unsigned bf = __ballot_sync(FULL, front), bi = __ballot_sync(FULL, inimg);
+  if ((threadIdx.x & 31) == 0) { if (bf) atomicAdd(&counts[1], __popc(bf)); if (bi) atomicAdd(&counts[2], __popc(bi)); }
+  unsigned blk_total;
+  const unsigned local = block_scan_256(sel ? 1u : 0u, s_warp, &blk_total);
+  if (threadIdx.x == 0) {
+    s_base = lookback(ws, tile, blk_total);
+    if (tile == (int)gridDim.x - 1) counts[0] = (int)(s_base + blk_total);
+  }
+  __syncthreads();
+  if (sel) {
+    const size_t m = (size_t)s_base + local;
+    idx_out[m] = i;
+    if (uv_out) { uv_out[2 * m] = u; uv_out[2 * m + 1] = v; }
+  }
+}
+
 }  // namespace
 }  // namespace b2r
 
@@ -175,6 +236,36 @@ b2r_status b2r_backproject_depth32(b2r_solver* s, const float* depth_dev, int H,
   CK(cudaMemcpyAsync(count_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
   CK(cudaStreamSynchronize(s->stream));
   if (*count_out > capacity) *count_out = capacity;
+  return B2R_OK;
+}
+
+b2r_status b2r_project_select(b2r_solver* s, const double* pts_dev, int n, const double* R9, const double* t3, const double* K9, const double* D,
+                              int nD, int W, int H, const uint8_t* mask_dev, double z_min, int32_t* idx_dev, int32_t* uv_dev, int* n_front_out,
+                              int* n_in_image_out, int* n_selected_out) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!pts_dev || !R9 || !t3 || !K9 || !idx_dev || !n_selected_out || n < 0 || W < 1 || H < 1 || nD < 0 || (nD > 0 && !D))
+    return fail(s, B2R_ERR_INVALID_ARG, "project_select arguments");
+  CK(cudaSetDevice(s->device));
+  ProjArgs a;
+  for (int k = 0; k < 9; ++k) a.R[k] = R9[k];
+  for (int k = 0; k < 3; ++k) a.t[k] = t3[k];
+  a.fx = K9[0]; a.fy = K9[4]; a.cx = K9[2]; a.cy = K9[5]; a.z_min = z_min; a.W = W; a.H = H;
+  for (int k = 0; k < 8; ++k) a.k[k] = 0.0;
+  a.nk = (nD == 4 || nD == 5 || nD == 8) ? nD : 0;     // main_seibersdorf.py:78: D if D.size in (4, 5, 8) else None
+  for (int k = 0; k < a.nk; ++k) a.k[k] = D[k];
+  const int tiles = (n + 255) / 256 > 0 ? (n + 255) / 256 : 1;
+  CK(s->d_refine.ensure((size_t)(tiles + 4) * 8 + 4096));
+  unsigned long long* ws = (unsigned long long*)s->d_refine.p;
+  int* counts = (int*)(ws + tiles + 1);
+  CK(cudaMemsetAsync(ws, 0, (size_t)(tiles + 4) * 8, s->stream));
+  project_select_kernel<<<tiles, 256, 0, s->stream>>>(pts_dev, n, a, mask_dev, idx_dev, uv_dev, ws, counts);
+  s->launches += 1;
+  int h[3];
+  CK(cudaMemcpyAsync(h, counts, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  *n_selected_out = h[0];
+  if (n_front_out) *n_front_out = h[1];
+  if (n_in_image_out) *n_in_image_out = h[2];
   return B2R_OK;
 }
 
