@@ -281,6 +281,10 @@ b2r_status b2r_project_select(b2r_solver* s, const double* pts_dev, int n, const
                               int nD, int W, int H, const uint8_t* mask_dev, double z_min, int32_t* idx_dev, int32_t* uv_dev, int* n_front_out,
                               int* n_in_image_out, int* n_selected_out);
 
+/* uniform_downsample_farthest_point (registration_utils.py:98-128) started at first_index (the reference draws it with
+ * np.random.randint): idx_dev [target] point ids in selection order. */
+b2r_status b2r_farthest_point_sample(b2r_solver* s, const double* pts_dev, int n, int target, int first_index, int32_t* idx_dev);
+
 #ifdef __cplusplus
 }
 #endif

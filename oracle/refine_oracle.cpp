@@ -335,4 +335,25 @@ void orcr_pca_align(const double* src, int ns, const double* dst, int nd, double
   }
 }
 
+// uniform_downsample_farthest_point (registration_utils.py:98-128) from a given first index: distances start at +inf, every round
+// takes the minimum with the Euclidean distance to the last pick (np.linalg.norm: sqrt((x^2 + y^2) + z^2)), the next pick is the
+// first maximum, its distance is then set to 0.  idx_out: target indices in selection order.
+void orcr_fps(const double* pts, int n, int target, int first, int* idx_out) {
+  std::vector<double> dist(n, std::numeric_limits<double>::infinity());
+  int last = first;
+  idx_out[0] = first;
+  for (int i = 1; i < target; ++i) {
+    const double lx = pts[3 * last], ly = pts[3 * last + 1], lz = pts[3 * last + 2];
+    int best = 0; double bv = -1.0;
+    for (int j = 0; j < n; ++j) {
+      const double d = std::sqrt(sq3(pts[3 * j] - lx, pts[3 * j + 1] - ly, pts[3 * j + 2] - lz));
+      if (d < dist[j]) dist[j] = d;
+      if (dist[j] > bv) { bv = dist[j]; best = j; }
+    }
+    idx_out[i] = best;
+    dist[best] = 0.0;
+    last = best;
+  }
+}
+
 }  // extern "C"

@@ -64,7 +64,7 @@ EXPORTS = [
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
     "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
-    "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align", "b2r_render_depth", "b2r_backproject_depth32", "b2r_project_select",
+    "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align", "b2r_render_depth", "b2r_backproject_depth32", "b2r_project_select", "b2r_farthest_point_sample",
 ]
 
 IDX_MAX_CLIQUE, IDX_ROT_INLIERS, IDX_ROT_INLIERS_MAP, IDX_TRANS_INLIERS, IDX_TRANS_INLIERS_MAP, IDX_DEGREES = range(6)
@@ -134,6 +134,7 @@ def lib():
     L.b2r_pca_align.argtypes = [vp, vp, i32, vp, i32, vp]
     L.b2r_render_depth.argtypes = [vp, vp, i32, vp, i32, vp, d, d, d, d, i32, i32, d, d, vp]
     L.b2r_project_select.argtypes = [vp, vp, i32, vp, vp, vp, vp, i32, i32, i32, vp, d, vp, vp, ip, ip, ip]
+    L.b2r_farthest_point_sample.argtypes = [vp, vp, i32, i32, i32, vp]
     L.b2r_backproject_depth32.argtypes = [vp, vp, i32, i32, d, d, d, d, d, d, vp, vp, i32, ip]
     _lib = L
     return L

@@ -322,6 +322,48 @@ __global__ void __launch_bounds__(256) pca_kernel(PcaIn in, double* __restrict__
   }
 }
 
+// uniform_downsample_farthest_point (registration_utils.py:98-128) from a given first index: one persistent CTA, the running
+// minimum distances stay in global memory (L2), every round is one fused pass (distance to the last pick, running minimum,
+// arg-max with the lowest index on ties) + one block reduction.
+__global__ void __launch_bounds__(1024) fps_kernel(const double* __restrict__ pts, int n, int target, int first, double* __restrict__ dist,
+                                                   int* __restrict__ idx_out) {
+  __shared__ double s_val[32];
+  __shared__ int s_idx[32];
+  __shared__ int s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int j = tid; j < n; j += 1024) dist[j] = CUDART_INF;
+  if (tid == 0) { idx_out[0] = first; s_last = first; }
+  __syncthreads();
+  for (int i = 1; i < target; ++i) {
+    const int last = s_last;
+    const double lx = pts[3 * (size_t)last], ly = pts[3 * (size_t)last + 1], lz = pts[3 * (size_t)last + 2];
+    double bv = -1.0; int bj = 0x7fffffff;
+    for (int j = tid; j < n; j += 1024) {
+      const double d = __dsqrt_rn(sq3r(__dsub_rn(pts[3 * (size_t)j], lx), __dsub_rn(pts[3 * (size_t)j + 1], ly), __dsub_rn(pts[3 * (size_t)j + 2], lz)));
+      double m = dist[j];
+      if (d < m) { m = d; dist[j] = d; }
+      if (m > bv) { bv = m; bj = j; }          // ascending j per thread: the first maximum is kept
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      const double ov = __shfl_xor_sync(FULL, bv, o); const int oj = __shfl_xor_sync(FULL, bj, o);
+      if (ov > bv || (ov == bv && oj < bj)) { bv = ov; bj = oj; }
+    }
+    if (lane == 0) { s_val[warp] = bv; s_idx[warp] = bj; }
+    __syncthreads();
+    if (warp == 0) {
+      bv = s_val[lane]; bj = s_idx[lane];
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        const double ov = __shfl_xor_sync(FULL, bv, o); const int oj = __shfl_xor_sync(FULL, bj, o);
+        if (ov > bv || (ov == bv && oj < bj)) { bv = ov; bj = oj; }
+      }
+      if (lane == 0) { idx_out[i] = bj; dist[bj] = 0.0; s_last = bj; }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace
 }  // namespace b2r
 
@@ -606,6 +648,20 @@ b2r_status b2r_pca_align(b2r_solver* s, const double* src_dev, int ns, const dou
     for (int c = 0; c < 3; ++c) T16[4 * r3 + c] = Rd[3 * r3] * Ra[3 * c] + Rd[3 * r3 + 1] * Ra[3 * c + 1] + Rd[3 * r3 + 2] * Ra[3 * c + 2];
     T16[4 * r3 + 3] = cd[r3] - (T16[4 * r3] * cs[0] + T16[4 * r3 + 1] * cs[1] + T16[4 * r3 + 2] * cs[2]);
   }
+  return B2R_OK;
+}
+
+b2r_status b2r_farthest_point_sample(b2r_solver* s, const double* pts_dev, int n, int target, int first_index, int32_t* idx_dev) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!pts_dev || !idx_dev || n < 1 || target < 1 || target > n || first_index < 0 || first_index >= n)
+    return fail(s, B2R_ERR_INVALID_ARG, "farthest_point_sample arguments");
+  Ws w; b2r_status r = refine_ws(s, (size_t)n * 8 + 1024, &w);
+  if (r != B2R_OK) return r;
+  double* dist = w.take<double>(n);
+  fps_kernel<<<1, 1024, 0, s->stream>>>(pts_dev, n, target, first_index, dist, idx_dev);
+  s->launches += 1;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(s->stream));
   return B2R_OK;
 }
 

@@ -114,6 +114,51 @@ class Refiner(PreSteps):
         return T
 
 
+    # ---- the alternative down-sampling paths of row a-1b --------------------------------------------------------------------
+    def uniform_downsample_farthest_point(self, points, target_points=2000, first_index=None, rng=None, want_index=False):
+        """True farthest-point sampling (registration_utils.py:98-128).  The reference draws the first index with
+        np.random.randint; pass `first_index` or a seeded `rng` for a reproducible draw.  Clouds with <= target_points come back
+        unchanged.  -> points [target,3] CUDA tensor in selection order (and the indices)."""
+        torch = _torch()
+        p = self._pts(points)
+        n, target = p.shape[0], int(target_points)
+        if n <= target:
+            return (p, torch.arange(n, dtype=torch.int32, device=self._dev)) if want_index else p
+        if first_index is None:
+            first_index = int((rng or np.random).integers(n)) if hasattr(rng or np.random, "integers") else int(np.random.randint(n))
+        idx = self._empty((target,), torch.int32)
+        _lib.check(self._h, _lib.lib().b2r_farthest_point_sample(self._h, p.data_ptr(), n, target, int(first_index), idx.data_ptr()))
+        out = p[idx.long()]
+        return (out, idx) if want_index else out
+
+    def uniform_downsample_random(self, points, target_points=500, rng=None, want_index=False):
+        """HelpersRealtime.uniform_downsample_farthest_point (despite its name: np.random.choice without replacement, :47-54)."""
+        torch = _torch()
+        p = self._pts(points)
+        idx = (rng or np.random).choice(p.shape[0], size=int(target_points), replace=False)
+        it = torch.from_numpy(np.asarray(idx, np.int64)).to(self._dev)
+        return (p[it], it.to(torch.int32)) if want_index else p[it]
+
+    def preprocess_point_cloud_uniform(self, points, target_points=500, method="farthest_point", calc_fpfh=True, first_index=None, rng=None,
+                                       radius=0.05):
+        """registration_utils.preprocess_point_cloud_uniform (:133-174; HelpersRealtime's variant with method="random", :59-98):
+        down-sample, hybrid normals (radius, max_nn = min(30, n // 2)), FPFH (2.5 * radius, max_nn 100).
+        -> (points_down, fpfh [33,n] or None); (None, None) for empty / too small clouds, as the reference."""
+        p = self._pts(points)
+        if p.shape[0] == 0:
+            return None, None
+        if method == "random":
+            down = self.uniform_downsample_random(p, target_points, rng) if p.shape[0] >= target_points else p
+        else:
+            down = self.uniform_downsample_farthest_point(p, target_points, first_index, rng)
+        if down.shape[0] < 10:
+            return None, None
+        if not calc_fpfh:
+            return down, None
+        nrm = self.normals(down, radius, min(30, down.shape[0] // 2))
+        return down, self.fpfh(down, nrm, radius * 2.5, 100)
+
+
 def get_angular_error(R_exp, R_est) -> float:
     """registration_utils.py:21-23 (host arithmetic on two 3x3 matrices)."""
     return abs(np.arccos(min(max(((np.matmul(np.asarray(R_exp).T, np.asarray(R_est))).trace() - 1) / 2, -1.0), 1.0)))

@@ -4,6 +4,7 @@
 The scoring / Chamfer / resolution / PCA helpers of the reference are plain numpy + scipy:
     HelpersRealtime.py:100-130     nn_residuals, voxel_coverage, alignment_score
     registration_utils.py:21-23    get_angular_error
+    registration_utils.py:98-128   uniform_downsample_farthest_point (true FPS)
     registration_utils.py:229-240  cloud_resolution
     registration_utils.py:276-343  chamfer_distance, centroid_of, pca_axes, initial_align_centroid_pca
 (paths under /root/reference/src/pose_estimator/EstimHelpers/).  The modules themselves cannot be imported (they import open3d
@@ -40,6 +41,11 @@ class Cloud:
 
     def compute_point_cloud_distance(self, other):
         return cKDTree(other.points).query(self.points, k=1)[0]
+
+    def select_by_index(self, idx):
+        c = Cloud(self.points[np.asarray(idx)])
+        c.idx = np.asarray(idx)
+        return c
 
 
 class KDTreeFlann:
@@ -87,13 +93,17 @@ def main():
         raise SystemExit("the reference is not mounted here; the committed .npz files are the product of this script")
     hr = load_functions(os.path.join(REF, "HelpersRealtime.py"), ["nn_residuals", "voxel_coverage", "alignment_score"])
     ru = load_functions(os.path.join(REF, "registration_utils.py"),
-                        ["get_angular_error", "cloud_resolution", "chamfer_distance", "centroid_of", "pca_axes", "initial_align_centroid_pca"])
+                        ["get_angular_error", "cloud_resolution", "chamfer_distance", "centroid_of", "pca_axes", "initial_align_centroid_pca",
+                         "uniform_downsample_farthest_point"])
     for name, seed, ns, nd, noise, voxel in [("a", 1, 400, 500, 0.002, 0.02), ("b", 2, 257, 129, 0.0, 0.05), ("c", 3, 1200, 900, 0.004, 0.01)]:
         src, dst, R, t = clouds(seed, ns, nd, noise)
         src_aligned = src @ R.T + t
         with contextlib.redirect_stdout(io.StringIO()):     # nn_residuals prints a debugging line
             d = hr["nn_residuals"](Cloud(src_aligned), Cloud(dst))
             score = hr["alignment_score"](Cloud(src_aligned), Cloud(src), Cloud(dst), voxel)
+        np.random.seed(seed)                                   # the function draws its first index with np.random.randint
+        with contextlib.redirect_stdout(io.StringIO()):
+            fps = ru["uniform_downsample_farthest_point"](Cloud(src), target_points=min(100, ns // 2)).idx
         T0 = ru["initial_align_centroid_pca"](Cloud(src), Cloud(dst))
         Rs, ss = ru["pca_axes"](Cloud(src))
         out = dict(
@@ -103,7 +113,7 @@ def main():
             chamfer=ru["chamfer_distance"](Cloud(src_aligned), Cloud(dst)),
             resolution_src=ru["cloud_resolution"](Cloud(src)), resolution_dst=ru["cloud_resolution"](Cloud(dst), k=5),
             pca_T0=T0, pca_R_abs=np.abs(Rs), pca_s=ss, centroid_src=ru["centroid_of"](Cloud(src)),
-            angular_error=ru["get_angular_error"](R, T0[:3, :3]),
+            angular_error=ru["get_angular_error"](R, T0[:3, :3]), fps_idx=np.asarray(fps, np.int32),
         )
         np.savez_compressed(os.path.join(HERE, f"refine_{name}.npz"), **out)
         print(name, {k: (float(v) if np.ndim(v) == 0 else np.shape(v)) for k, v in out.items() if k not in ("src", "dst", "src_aligned")})

@@ -131,3 +131,34 @@ def test_transform_and_scores_against_oracle(rf, orc):
     neg = rng.uniform(-3, -1, (300, 3))                        # negative coordinates: floor, not truncation
     assert rf.voxel_coverage(neg, 0.1) == orc.voxel_coverage(neg, 0.1)
     assert rf.voxel_coverage(np.zeros((5, 3)), 0.1) == 1
+
+
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p) for p in GOLD])
+def test_farthest_point_sampling_matches_reference_golden(rf, orc, path):
+    g = np.load(path)
+    want = g["fps_idx"]
+    pts, idx = rf.uniform_downsample_farthest_point(g["src"], len(want), first_index=int(want[0]), want_index=True)
+    assert np.array_equal(idx.cpu().numpy(), want) and np.array_equal(pts.cpu().numpy(), g["src"][want])
+    rng = np.random.default_rng(5)
+    big = rng.uniform(-1, 1, (5000, 3)); big[100] = big[7]                 # a duplicate point: ties go to the lowest index
+    _, idx = rf.uniform_downsample_farthest_point(big, 300, first_index=4321, want_index=True)
+    assert np.array_equal(idx.cpu().numpy(), orc.farthest_point_sample(big, 300, 4321))
+    same = rf.uniform_downsample_farthest_point(big[:50], 80)              # fewer points than the target: unchanged
+    assert same.shape == (50, 3)
+
+
+def test_preprocess_point_cloud_uniform(rf):
+    from oracle import presteps as op
+    rng = np.random.default_rng(6)
+    u = rng.uniform(0, np.pi, 3000); v = rng.uniform(0, 2 * np.pi, 3000)
+    cloud = np.stack([0.3 * np.sin(u) * np.cos(v), 0.2 * np.sin(u) * np.sin(v), 0.1 * np.cos(u)], 1)
+    down, f = rf.preprocess_point_cloud_uniform(cloud, 400, first_index=11)
+    d = down.cpu().numpy()
+    assert d.shape == (400, 3) and f.shape == (33, 400)
+    nrm = op.normals(d, 0.05, 30)
+    ref = op.fpfh(d, nrm, 0.125, 100)
+    assert np.allclose(f.cpu().numpy(), ref, rtol=1e-9, atol=1e-9)
+    assert rf.preprocess_point_cloud_uniform(np.zeros((0, 3)), 100) == (None, None)
+    assert rf.preprocess_point_cloud_uniform(cloud[:5], 100) == (None, None)
+    r, none = rf.preprocess_point_cloud_uniform(cloud, 100, method="random", calc_fpfh=False, rng=np.random.default_rng(0))
+    assert r.shape == (100, 3) and none is None

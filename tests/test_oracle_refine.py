@@ -119,3 +119,11 @@ def test_umeyama_reflection_case(orc):
     dst = src.copy(); dst[:, 2] = [0.01, -0.01, -0.01, 0.01]
     T = orc.umeyama(src, dst, np.arange(4, dtype=np.int32))
     assert abs(np.linalg.det(T[:3, :3]) - 1) < 1e-12 and np.allclose(T[:3, :3] @ T[:3, :3].T, np.eye(3), atol=1e-12)
+
+
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p) for p in GOLD])
+def test_farthest_point_sampling_matches_reference_function(orc, path):
+    g = np.load(path)
+    want = g["fps_idx"]
+    assert np.array_equal(orc.farthest_point_sample(g["src"], len(want), int(want[0])), want)
+    assert len(set(want.tolist())) == len(want)
