@@ -142,6 +142,8 @@ int64_t b2r_launch_count(const b2r_solver* s);
 
 /* getSolution() and friends; `idx` selects the problem of the last batch (0 for b2r_solve). */
 b2r_status b2r_get_solution(b2r_solver* s, int idx, b2r_solution* out);
+/* the first `count` solutions of the last batch in one call (out: array of count b2r_solution) */
+b2r_status b2r_get_solutions(b2r_solver* s, b2r_solution* out, int count);
 b2r_status b2r_get_stats(b2r_solver* s, int idx, b2r_stats* out);
 /* out == NULL: only *count is written. */
 b2r_status b2r_get_indices(b2r_solver* s, int idx, b2r_index_kind kind, int32_t* out, int32_t* count);

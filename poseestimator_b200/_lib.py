@@ -59,13 +59,18 @@ class B2RStats(C.Structure):
 EXPORTS = [
     "b2r_default_params", "b2r_version", "b2r_device_count", "b2r_create", "b2r_destroy", "b2r_reset", "b2r_last_error",
     "b2r_solve", "b2r_solve_batch", "b2r_solve_batch_async", "b2r_sync", "b2r_batch_size", "b2r_launch_count",
-    "b2r_get_solution", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
+    "b2r_get_solution", "b2r_get_solutions", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
     "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
     "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
     "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align", "b2r_render_depth", "b2r_backproject_depth32", "b2r_project_select", "b2r_farthest_point_sample",
 ]
+
+# numpy view of an array of b2r_solution (112 bytes each)
+import numpy as _np  # noqa: E402
+SOLUTION_DTYPE = _np.dtype({"names": ["scale", "rotation", "translation", "valid"], "formats": ["<f8", ("<f8", (3, 3)), ("<f8", (3,)), "<i4"],
+                            "offsets": [0, 8, 80, 104], "itemsize": 112})
 
 IDX_MAX_CLIQUE, IDX_ROT_INLIERS, IDX_ROT_INLIERS_MAP, IDX_TRANS_INLIERS, IDX_TRANS_INLIERS_MAP, IDX_DEGREES = range(6)
 
@@ -101,6 +106,7 @@ def lib():
     L.b2r_launch_count.argtypes = [vp]
     L.b2r_launch_count.restype = i64
     L.b2r_get_solution.argtypes = [vp, i32, C.POINTER(B2RSolution)]
+    L.b2r_get_solutions.argtypes = [vp, vp, i32]
     L.b2r_get_stats.argtypes = [vp, i32, C.POINTER(B2RStats)]
     L.b2r_get_indices.argtypes = [vp, i32, i32, vp, C.POINTER(C.c_int32)]
     L.b2r_get_adjacency.argtypes = [vp, i32, vp, i32]

@@ -95,8 +95,15 @@ class BatchSolver:
         _lib.check(self._h, _lib.lib().b2r_get_solution(self._h, i, C.byref(sol)))
         return RegistrationSolution(sol.scale, np.array(sol.rotation[:]).reshape(3, 3), np.array(sol.translation[:]), sol.valid)
 
+    def solutions_array(self) -> np.ndarray:
+        """All solutions of the last batch in ONE C call: structured array (scale, rotation [3,3], translation [3], valid)."""
+        out = np.zeros(max(self._batch, 1), _lib.SOLUTION_DTYPE)
+        _lib.check(self._h, _lib.lib().b2r_get_solutions(self._h, C.c_void_p(out.ctypes.data), self._batch))
+        return out[: self._batch]
+
     def solutions(self):
-        return [self.solution(i) for i in range(self._batch)]
+        a = self.solutions_array()
+        return [RegistrationSolution(float(r["scale"]), r["rotation"], r["translation"], bool(r["valid"])) for r in a]
 
     def stats(self, i: int) -> dict:
         st = _lib.B2RStats()

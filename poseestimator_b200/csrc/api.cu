@@ -413,6 +413,14 @@ b2r_status b2r_get_solution(b2r_solver* s, int idx, b2r_solution* out) {
   return B2R_OK;
 }
 
+b2r_status b2r_get_solutions(b2r_solver* s, b2r_solution* out, int count) {
+  b2r_status r = check_index(s, 0);
+  if (r != B2R_OK) return r;
+  if (!out || count < 0 || count > s->batch) return fail(s, B2R_ERR_INVALID_ARG, "get_solutions: out / count");
+  for (int i = 0; i < count; ++i) { r = b2r_get_solution(s, i, out + i); if (r != B2R_OK) return r; }
+  return B2R_OK;
+}
+
 b2r_status b2r_get_stats(b2r_solver* s, int idx, b2r_stats* out) {
   b2r_status r = check_index(s, idx);
   if (r != B2R_OK) return r;

@@ -13,6 +13,7 @@
 //   5. canon_kernel       deterministic answer: the maximum clique whose sorted id list is lexicographically
 //                         smallest (upstream returns "a" maximum clique depending on thread timing, A.5-8).
 // All sizes stay on the device between the stages; the host never synchronises inside a solve.
+#include <stdio.h>
 #include "common.cuh"
 
 namespace b2r {
@@ -234,16 +235,24 @@ __global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const Prob
   constexpr int NW = kHeuThreads / 32;
   uint32_t* P = sh;                       // W
   uint32_t* U = sh + W;                   // W
-  int* scan = (int*)(sh + 2 * W);         // 40
+  uint32_t* Rm = sh + 2 * W;              // W: members to drop this round
+  int* scan = (int*)(sh + 3 * W);         // 40
   unsigned* s_best = (unsigned*)(scan + 40);
   int* s_nU = (int*)(scan + 41);
   int* s_lb = (int*)(scan + 42);
+  int* s_nR = (int*)(scan + 43);
   unsigned short* list = (unsigned short*)(scan + 48);  // n entries
   const uint32_t* row0 = d.adj + (size_t)v * d.pitch;
   for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] = row0[w];
   __syncthreads();
   int size = 1;
+#ifdef B2R_HEU_DEBUG
+  int rounds = 0; long long t0 = clock64();
+#endif
   for (;;) {
+#ifdef B2R_HEU_DEBUG
+    ++rounds;
+#endif
     // ascending member list + count
     __shared__ int sh_base2;
     if (threadIdx.x == 0) sh_base2 = 0;
@@ -274,8 +283,8 @@ __global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const Prob
     }
     const int cnt = sh_base2;
     if (cnt == 0) break;
-    if (threadIdx.x == 0) { *s_lb = *(volatile int*)&st->lb; *s_best = 0u; *s_nU = 0; }
-    for (int w = threadIdx.x; w < W; w += kHeuThreads) U[w] = 0u;
+    if (threadIdx.x == 0) { *s_lb = *(volatile int*)&st->lb; *s_best = 0u; *s_nU = 0; *s_nR = 0; }
+    for (int w = threadIdx.x; w < W; w += kHeuThreads) { U[w] = 0u; Rm[w] = 0u; }
     __syncthreads();
     if (size + cnt <= *s_lb) return;  // another seed already reached this size: cannot improve
     unsigned wbest = 0;
@@ -299,19 +308,25 @@ __global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const Prob
         const unsigned id = (unsigned)ids[q];
         wbest = max(wbest, ((unsigned)cq << 16) | (0xffffu - id));
         if (cq == cnt - 1 && lane == 0) atomicOr(&U[id >> 5], 1u << (id & 31));
+        if (2 * cq < cnt - 1 && lane == 0) atomicOr(&Rm[id >> 5], 1u << (id & 31));   // adjacent to less than half of the others
       }
     }
     if (lane == 0 && wbest) atomicMax(s_best, wbest);
     __syncthreads();
-    int nu = 0;
-    for (int w = threadIdx.x; w < Wb; w += kHeuThreads) nu += __popc(U[w]);
-    nu = __reduce_add_sync(FULL, nu);
+    int nu = 0, nr = 0;
+    for (int w = threadIdx.x; w < Wb; w += kHeuThreads) { nu += __popc(U[w]); nr += __popc(Rm[w]); }
+    nu = __reduce_add_sync(FULL, nu); nr = __reduce_add_sync(FULL, nr);
     if (lane == 0 && nu) atomicAdd(s_nU, nu);
+    if (lane == 0 && nr) atomicAdd(s_nR, nr);
     __syncthreads();
-    const int nU = *s_nU;
+    const int nU = *s_nU, nR = *s_nR;
     if (nU > 0) {
       size += nU;
       for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= ~U[w];
+    } else if (nR > 0 && nR < cnt) {
+      // bulk peel: a member adjacent to fewer than half of the candidates cannot be in a clique covering most of them; dropping
+      // all of those at once replaces the one-vertex-per-round elimination of sparse outliers (16-26 rounds -> 3 on config 3)
+      for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= ~Rm[w];
     } else {
       const unsigned u = 0xffffu - (*s_best & 0xffffu);
       size += 1;
@@ -320,6 +335,9 @@ __global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const Prob
     }
     __syncthreads();
   }
+#ifdef B2R_HEU_DEBUG
+  if (threadIdx.x == 0 && blockIdx.y < 2) printf("heu seed %d blk(%d,%d) rounds %d size %d cycles %lld\n", v, blockIdx.x, blockIdx.y, rounds, size, clock64() - t0);
+#endif
   if (threadIdx.x == 0) {
     atomicMax(&st->heu_key, ((unsigned long long)size << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
     atomicMax(&st->lb, size);
@@ -1031,7 +1049,7 @@ int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelPara
   if (all_seeds) {
     dispatch_wpl<HeuLaunch>(wpl, d_desc, gseed, 256, (size_t)8 * W * 4, 1, st);
   } else {
-    const size_t hs = (size_t)(2 * W + 64) * 4 + (size_t)2 * (n_max + 8);
+    const size_t hs = (size_t)(3 * W + 64) * 4 + (size_t)2 * (n_max + 8);
     heuristic_block_kernel<<<dim3(kHeuSeeds, batch), kHeuThreads, hs, st>>>(d_desc);
   }
   ++launches;

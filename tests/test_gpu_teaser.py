@@ -426,3 +426,17 @@ def test_non_unique_maximum_clique_is_canonical_and_fast(oracle_mod):
         n_multi += bs.stats(i)["n_pruned"] > bs.stats(i)["omega"]
     assert n_multi >= 1, "no problem of this batch has extra vertices in its (omega-1)-core; pick other seeds"
     assert tm["canonical"] < 5.0 and tm["exact_search"] < 5.0, tm
+
+
+def test_batched_solution_getter_equals_per_problem_getter():
+    from poseestimator_b200 import batch as b2batch
+    import teaserpp_python as tpp
+    pbs = [synth.make_problem(200 + 10 * i, 0.5, 40 + i) for i in range(5)]
+    bs = b2batch.BatchSolver(_params(tpp, pbs[0].noise_bound))
+    sols = bs.solve([(p.src, p.dst) for p in pbs])
+    arr = bs.solutions_array()
+    assert arr.shape == (5,) and arr["valid"].all()
+    for i, s in enumerate(sols):
+        one = bs.solution(i)
+        assert np.array_equal(arr["rotation"][i], one.rotation) and np.array_equal(arr["translation"][i], one.translation)
+        assert np.array_equal(s.rotation, one.rotation) and s.valid == one.valid and s.scale == one.scale
