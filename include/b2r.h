@@ -71,7 +71,7 @@ typedef struct b2r_params {
   double rotation_noise_bound;       /* GNC noise bound before the 2/scale factor; <=0 -> noise_bound.
                                         Lets the host mirror upstream's in-place compounding (A.6-2). */
   int32_t graph_exact_only;          /* 0: default (packed-fp32 sqrt-free filter, exact fp64 fallback); 1: always evaluate both
-                                        fp64 square roots; 2 / 3: the older fp64 filters v2 / v1 (A/B measurements, tests) */
+                                        fp64 square roots; 2 / 3: the older fp64 filters v2 / v1; 4: the packed-fp32 filter v3 (A/B measurements, tests) */
   double graph_filter_tau;           /* lower limit of the filter's ambiguity band relative to Sigma^2 (tests widen the band to
                                         force the exact path); <= 0: the band the error analysis needs */
 } b2r_params;

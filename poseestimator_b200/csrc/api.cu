@@ -54,11 +54,14 @@ void fill_kernel_params(b2r_solver* s) {
   k.exact_only = p.graph_exact_only == 1;
   k.filter_tau_min = p.graph_filter_tau > 0 ? p.graph_filter_tau : 0.0;
   {
-    // filter generation: params.graph_exact_only = 3 / 2 or B2R_GRAPH_V = 1 / 2 select the older fp64 filters (A/B runs, tests)
+    // filter generation: params.graph_exact_only = 3 / 2 / 4 or B2R_GRAPH_V = 1 / 2 / 3 select the older filters v1 / v2 (fp64) / v3 (A/B runs, tests)
     const char* gv = getenv("B2R_GRAPH_V");
-    const int v = p.graph_exact_only == 3 ? 1 : p.graph_exact_only == 2 ? 2 : (gv && gv[0] >= '1' && gv[0] <= '3') ? gv[0] - '0' : 3;
+    const int v = p.graph_exact_only == 3 ? 1 : p.graph_exact_only == 2 ? 2 : p.graph_exact_only == 4 ? 3 : p.graph_exact_only == 5 ? 4
+                  : (gv && gv[0] >= '1' && gv[0] <= '5') ? gv[0] - '0' : 5;
     k.graph_v1 = v == 1;
     k.graph_v2 = v == 2;
+    k.graph_v3 = v == 3;
+    k.graph_v4 = v == 4;
     // v2 band: |F| < 2^(max(2 e(H) - 1023, e(beta^4)) - 22 + shift), compared on the high words of H and F
     const double beta4 = beta2 * beta2;
     unsigned long long bits;
@@ -106,6 +109,8 @@ b2r_status ensure_workspace(b2r_solver* s, int batch, int n_max) {
   CK(s->d_pts.ensure(B * 6 * nc * sizeof(double)));
   CK(s->d_adj.ensure(B * nc * pc * sizeof(uint32_t)));
   CK(s->d_cadj.ensure(B * nc * pc * sizeof(uint32_t)));
+  CK(s->d_pts32.ensure(B * (size_t)(pc * 32) * 2 * sizeof(float4)));   // pc * 32 = n_cap rounded up to the tile edge
+  CK(s->d_amb.ensure(B * (size_t)kAmbCap * sizeof(uint32_t)));
   // ints per problem: deg, ids, clique (n each) + rot_inl (tim) + tls_id (4*tim)
   CK(s->d_int.ensure(B * (3 * (size_t)nc + 5 * (size_t)tc) * sizeof(int)));
   // doubles per problem: weights (tim), timx, timy, raw (3*tim each), tls_val (4*tim)
@@ -139,6 +144,10 @@ void build_desc(b2r_solver* s, int b, int n, const double* dsrc, const double* d
   unsigned char* ub = (unsigned char*)s->d_u8.p + (size_t)b * 2 * tc;
   d.rot_mask = ub; d.trans_mask = ub + tc;
   d.st = (ProbState*)s->d_state.p + b;
+  d.pts32 = (float4*)s->d_pts32.p + (size_t)b * pc * 32 * 2;
+  d.amb_list = (uint32_t*)s->d_amb.p + (size_t)b * kAmbCap;
+  d.amb_cap = kAmbCap;
+  d.pad2_ = 0;
   d.n = n;
   d.pitch = ext_adj ? ext_pitch : (int)pc;
   d.tim_cap = (int)tc;
@@ -246,7 +255,7 @@ b2r_status b2r_destroy(b2r_solver* s) {
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->stream);
   s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
-  s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release(); s->d_refine.release(); s->h_refine.release();
+  s->d_pts32.release(); s->d_amb.release(); s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release(); s->d_refine.release(); s->h_refine.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
   if (s->ev_ready) for (int i = 0; i < 12; ++i) cudaEventDestroy(s->ev[i]);
   if (s->own_stream) cudaStreamDestroy(s->stream);

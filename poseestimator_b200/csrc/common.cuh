@@ -46,6 +46,11 @@ struct ProbState {
   int use32;             // graph filter v3: 1 when the packed-fp32 filter may decide pairs of this problem (graph_prep_kernel)
   double ctr[6];         // centre of the bounding boxes of src (0..2) and dst (3..5): the fp32 copies are taken relative to it
   float f32c[8];         // v3 constants: -2 beta^2, beta^4, beta^2, a3, a2, a1, a0 (band polynomial), k (info)
+  // tensor-core filter (graph_tc.cu): band T(L) = tcc[1] + tcc[0] * L, tcc[2] = L above which both lengths may be below beta
+  float tcc[4];
+  double kappa;          // 1 / beta: the 22-bit copies are (x - ctr) * kappa
+  unsigned int amb_count;   // pairs appended to ProbDesc::amb_list (may exceed amb_cap: then tc_overflow is set)
+  int tc_overflow;       // 1: the list overflowed -> the whole problem is redone by the fp64 filter
 };
 
 // Per-problem pointers (device copies of host-built descriptors).
@@ -67,6 +72,10 @@ struct ProbDesc {
   int* tls_id;
   double* raw;           // 3 x tim_cap raw translations
   ProbState* st;
+  float4* pts32;         // tensor-core filter: 2 x float4 per point (22-bit centred scaled src xyz + p, dst xyz + mn), n_pad points
+  uint32_t* amb_list;    // tensor-core filter: (i << 16) | j of the pairs the exact kernel must decide
+  int amb_cap;
+  int pad2_;
   int n;
   int pitch;             // words per adjacency row (multiple of 4)
   int tim_cap;
@@ -90,12 +99,19 @@ struct KernelParams {
   int exact_only;
   int graph_v1;           // 1: the first filter kernel (one column per thread), kept for A/B measurements
   int graph_v2;           // 1: the fp64 filter with two columns per thread (v2) instead of the packed-fp32 filter (v3)
+  int graph_v3;           // 1: the packed-fp32 filter on coordinate differences (v3) instead of the norm-expansion filter (v4)
+  int graph_v4;           // 1: the packed-fp32 norm-expansion filter (v4) instead of the tensor-core filter (v5)
   double filter_tau_min;  // graph_filter_tau of the params (0 = none): lower limit of v3's band tau_G (tests widen it)
   unsigned band_k1, band_k2;  // high-word constants of the v2 ambiguity band (api.cu fill_kernel_params)
 };
 
 // launchers (each returns the number of kernels it enqueued)
 int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+// graph_tc.cu (v5): prep (boxes, constants, 22-bit records) + tcgen05 filter; graph.cu: exact fix-up of the listed pairs and the
+// fp64 filter for problems the fp32 path may not decide
+int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+int launch_graph_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+constexpr int kAmbCap = 1 << 15;      // listed pairs per problem
 int launch_tim_graph_rows(const double* src, const double* dst, int n, int row_begin, int row_end, uint32_t* adj,
                           int pitch, const KernelParams& kp, unsigned long long* slow_pairs, cudaStream_t st);
 int launch_degree(const ProbDesc* d_desc, int batch, int n_max, cudaStream_t st);

@@ -391,12 +391,16 @@ __global__ void __launch_bounds__(256) graph_prep_kernel(const ProbDesc* __restr
   if (threadIdx.x == 0) {
     ProbState* st = d.st;
     double M = 0.0;
+    double Mc[2] = {0.0, 0.0}, Pc[2] = {0.0, 0.0};   // per cloud: largest |centred coordinate|, bound of the largest squared norm
     for (int k = 0; k < 6; ++k) {
       double lo = s_mn[0][k], hi = s_mx[0][k];
       for (int w = 1; w < 8; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
       const double c = 0.5 * lo + 0.5 * hi;
       st->ctr[k] = c;
-      M = fmax(M, fmax(hi - c, c - lo));
+      const double h = fmax(hi - c, c - lo) * (1.0 + 1e-6);   // covers the fp32 rounding of the centred copy
+      M = fmax(M, h);
+      Mc[k / 3] = fmax(Mc[k / 3], h);
+      Pc[k / 3] += h * h;
     }
     const double u = 5.9604644775390625e-8;  // 2^-24
     const double beta = fabs(kp.beta), beta2 = beta * beta, beta4 = beta2 * beta2;
@@ -404,7 +408,11 @@ __global__ void __launch_bounds__(256) graph_prep_kernel(const ProbDesc* __restr
     const bool ok = !s_bad && n > 0 && M < 1e8 && beta >= 1e-6 && beta <= 1e8 && tmin < 0.015625;
     st->use32 = ok ? 1 : 0;
     if (ok) {
-      const double alpha = 8.5 * u, gamma = 7.0 * u * M * M;
+      // v3 (coordinate differences): alpha = 8.5 u, gamma = 7 u M^2.  v4 (norm expansion, see compute_tile4): the error of
+      // A~ and B~ together is below 4.47 u (A + B) + 3.47 u (Ms^2 + Md^2) + 12.004 u (Ps + Pd), P = largest squared norm of a
+      // centred point (bounded by the squared half-diagonal of the bounding box).
+      const double alpha = kp.graph_v3 ? 8.5 * u : 4.5 * u;
+      const double gamma = kp.graph_v3 ? 7.0 * u * M * M : 1.0001 * u * (3.47 * (Mc[0] * Mc[0] + Mc[1] * Mc[1]) + 12.004 * (Pc[0] + Pc[1]));
       const double s_typ = 2.0 * M * M;                         // a typical S1; only steers k
       double k = beta * sqrt(2.0 * s_typ) / (alpha * s_typ + gamma);
       if (!(k >= 8.0)) k = 8.0;                                 // a3 < 1/2
@@ -587,6 +595,281 @@ __global__ void __launch_bounds__(kTile, B2R_G3_MINB) tim_graph3_kernel(const Pr
   if (slow && (threadIdx.x & 31) == 0) atomicAdd(&d.st->slow_pairs, 2048ull * slow);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// v4 of the filter kernel (default): v3's packed-fp32 sign test with the squared lengths formed by NORM EXPANSION,
+//     A~ = fma(Z, -2 pz, fma(Y, -2 py, fma(X, -2 px, Hs_j + hs_i))),   Hs = fl32(|x^|^2) of the centred fp32 copy,
+// 4 packed instructions instead of 6 (B likewise), then Dm, S1, L, G, thr(S1) as in v3 and Q = S1 - beta^2 whose sign
+// replaces the S1 < beta^2 compare: 15 packed instructions per two pairs (v3: 18).  Per pair the integer pipe does
+// LOP3 (G | Q), one funnel shift that pushes the sign bit into the column's 32-row word, and one FSETP that ORs
+// !(|G| >= thr) into a per-chunk predicate (v3: ~10 integer-pipe instructions per two pairs more).
+//
+// Rigor.  x^ = fl32(x - c) per coordinate, |x^ - (x - c)| <= 1.0005 u M.  With A^ = |x^_j - x^_i|^2 (real arithmetic):
+//   |A^ - A| <= 3.4642 e a + 3 e^2,  e = 2.001 u M  (as v3);
+//   the computed chain returns A^ + (h_j - r_j) + (h_i - r_i) + eps0 + eps1 + eps2 + eps3  (r = |x^|^2, h = fl32(r) taken from
+//   an fp64 evaluation, eps_m = the rounding of step m); every exact partial sum is  sum_{k<=m} d^_k^2 + sum_{k>m} (x^_jk^2 + x^_ik^2)
+//   <= 2 (r_i + r_j), the last one is A^, so |A~ - A^| <= 6.002 u (r_i + r_j) + 1.0001 u A^ <= 12.004 u P + 1.0001 u A^.
+// Hence |A~ - A| + |B~ - B| <= 4.47 u (A + B) + 3.47 u (Ms^2 + Md^2) + 12.004 u (Ps + Pd) = alpha S1 + gamma with alpha = 4.5 u
+// (the slack pays for S1 -> S1~), and steps 3-5 of the v3 analysis (Dm, S1, L, G and the band polynomial) apply verbatim.
+// sign(fl(S1~ - beta^2~)) is exact (one rounded subtraction never changes the sign), so Q < 0 <=> S1~ < beta^2~ as in v3.
+//
+// Ambiguous pairs (about 30 per 12.5 M at config 3) are fixed ONE BY ONE: a 32-row chunk with any ambiguous pair replays
+// its rows (same instruction sequence, hence the same fp32 values), and only the flagged pairs are re-evaluated with the
+// reference's fp64 roundings and square roots (v3 redid all 2048 pairs of the chunk in fp64).
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef B2R_G4_UNROLL
+#define B2R_G4_UNROLL 16
+#endif
+#ifndef B2R_G4_MINB
+#define B2R_G4_MINB 5
+#endif
+
+constexpr int kG4Unroll = B2R_G4_UNROLL;
+
+struct TilePts4 {
+  float4 a[kTile];  // (-2 sx, -2 sy, -2 sz, |s|^2) of the centred fp32 copy of the row point
+  float4 b[kTile];  // (-2 dx, -2 dy, -2 dz, |d|^2)
+};
+
+struct Cols4 { float2 X, Y, Z, Hs, U, V, W, Hd; };
+struct Consts4 { float2 k1, k0, q2, q1, q0, nb2; };
+
+// centred fp32 copy of point i of both clouds and the fp32 roundings of its squared norms (evaluated in fp64: exact products,
+// sums rounded at 2^-53)
+__device__ __forceinline__ void load_point4(const double* __restrict__ src, const double* __restrict__ dst, size_t i, const double c[6],
+                                            float v[6], float& hs, float& hd) {
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    v[k] = __double2float_rn(src[3 * i + k] - c[k]);
+    v[3 + k] = __double2float_rn(dst[3 * i + k] - c[3 + k]);
+  }
+  const double x = v[0], y = v[1], z = v[2], p = v[3], q = v[4], r = v[5];
+  hs = __double2float_rn(fma(z, z, fma(y, y, x * x)));
+  hd = __double2float_rn(fma(r, r, fma(q, q, p * p)));
+}
+
+__device__ __forceinline__ void eval4(const Cols4& cl, const Consts4& cs, const float4 ra, const float4 rb, float2& G, float2& S1, float2& T) {
+  const float2 A = f2fma(cl.Z, f2bc(ra.z), f2fma(cl.Y, f2bc(ra.y), f2fma(cl.X, f2bc(ra.x), f2add(cl.Hs, f2bc(ra.w)))));
+  const float2 B = f2fma(cl.W, f2bc(rb.z), f2fma(cl.V, f2bc(rb.y), f2fma(cl.U, f2bc(rb.x), f2add(cl.Hd, f2bc(rb.w)))));
+  const float2 Dm = f2sub(A, B);
+  S1 = f2add(A, B);
+  G = f2fma(Dm, Dm, f2fma(cs.k1, S1, cs.k0));
+  T = f2fma(S1, f2fma(S1, cs.q2, cs.q1), cs.q0);
+}
+
+template <bool kInterior>
+__device__ __forceinline__ void compute_tile4(const double* __restrict__ src, const double* __restrict__ dst, int n, int i0, int j0,
+                                              const ProbState* __restrict__ st, const KernelParams& kp, TilePts4& sp,
+                                              uint32_t (*dirT)[kTile], uint32_t tw[8], unsigned& slow) {
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  double ctr[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) ctr[k] = st->ctr[k];
+  {
+    const int i = i0 + t;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (kInterior || i < n) {
+      float v[6], hs, hd;
+      load_point4(src, dst, (size_t)i, ctr, v, hs, hd);
+      a = make_float4(-2.f * v[0], -2.f * v[1], -2.f * v[2], hs);
+      b = make_float4(-2.f * v[3], -2.f * v[4], -2.f * v[5], hd);
+    }
+    sp.a[t] = a;
+    sp.b[t] = b;
+  }
+  const int ja = j0 + t, jb = j0 + kTile + t;
+  const bool oka = kInterior || ja < n, okb = kInterior || jb < n;
+  Cols4 cl;
+  cl.X = cl.Y = cl.Z = cl.Hs = cl.U = cl.V = cl.W = cl.Hd = f2bc(0.f);
+  if (oka) {
+    float v[6], hs, hd;
+    load_point4(src, dst, (size_t)ja, ctr, v, hs, hd);
+    cl.X.x = v[0]; cl.Y.x = v[1]; cl.Z.x = v[2]; cl.U.x = v[3]; cl.V.x = v[4]; cl.W.x = v[5]; cl.Hs.x = hs; cl.Hd.x = hd;
+  }
+  if (okb) {
+    float v[6], hs, hd;
+    load_point4(src, dst, (size_t)jb, ctr, v, hs, hd);
+    cl.X.y = v[0]; cl.Y.y = v[1]; cl.Z.y = v[2]; cl.U.y = v[3]; cl.V.y = v[4]; cl.W.y = v[5]; cl.Hs.y = hs; cl.Hd.y = hd;
+  }
+  Consts4 cs;
+  cs.k1 = f2bc(st->f32c[0]); cs.k0 = f2bc(st->f32c[1]); cs.nb2 = f2bc(-st->f32c[2]);
+  cs.q2 = f2bc(st->f32c[3]); cs.q1 = f2bc(st->f32c[4]); cs.q0 = f2bc(st->f32c[5]);
+  __syncthreads();
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t worda = 0, wordb = 0;
+    bool any_amb = false;
+#pragma unroll kG4Unroll
+    for (int k = 0; k < 32; ++k) {
+      const int il = 32 * c + k;
+      float2 G, S1, T;
+      eval4(cl, cs, sp.a[il], sp.b[il], G, S1, T);
+      const float2 Q = f2add(S1, cs.nb2);
+      // row k lands in bit 31 - k: word = (word << 1) | sign(G | Q)
+      worda = __funnelshift_l(__float_as_uint(G.x) | __float_as_uint(Q.x), worda, 1);
+      wordb = __funnelshift_l(__float_as_uint(G.y) | __float_as_uint(Q.y), wordb, 1);
+      any_amb |= !(fabsf(G.x) >= T.x) | !(fabsf(G.y) >= T.y);
+    }
+    worda = __brev(worda);
+    wordb = __brev(wordb);
+    if (__any_sync(0xffffffffu, any_amb)) {
+      // rare: replay the chunk and re-evaluate only the flagged pairs with the reference's fp64 roundings and square roots
+#pragma unroll 1
+      for (int k = 0; k < 32; ++k) {
+        const int il = 32 * c + k;
+        float2 G, S1, T;
+        eval4(cl, cs, sp.a[il], sp.b[il], G, S1, T);
+        const bool amba = !(fabsf(G.x) >= T.x), ambb = !(fabsf(G.y) >= T.y);
+        if (amba | ambb) {
+          const int i = i0 + il;
+          const size_t ii = (kInterior || i < n) ? (size_t)i : 0;
+          const double px = src[3 * ii], py = src[3 * ii + 1], pz = src[3 * ii + 2];
+          const double qx = dst[3 * ii], qy = dst[3 * ii + 1], qz = dst[3 * ii + 2];
+          if (amba) {
+            const size_t jj = oka ? (size_t)ja : 0;
+            const double A = sq3_ref(__dsub_rn(src[3 * jj], px), __dsub_rn(src[3 * jj + 1], py), __dsub_rn(src[3 * jj + 2], pz));
+            const double B = sq3_ref(__dsub_rn(dst[3 * jj], qx), __dsub_rn(dst[3 * jj + 1], qy), __dsub_rn(dst[3 * jj + 2], qz));
+            worda = (worda & ~(1u << k)) | ((verdict_exact(A, B, kp.beta) ? 1u : 0u) << k);
+            ++slow;
+          }
+          if (ambb) {
+            const size_t jj = okb ? (size_t)jb : 0;
+            const double A = sq3_ref(__dsub_rn(src[3 * jj], px), __dsub_rn(src[3 * jj + 1], py), __dsub_rn(src[3 * jj + 2], pz));
+            const double B = sq3_ref(__dsub_rn(dst[3 * jj], qx), __dsub_rn(dst[3 * jj + 1], qy), __dsub_rn(dst[3 * jj + 2], qz));
+            wordb = (wordb & ~(1u << k)) | ((verdict_exact(A, B, kp.beta) ? 1u : 0u) << k);
+            ++slow;
+          }
+        }
+      }
+    }
+    if (!kInterior) {  // rows past n, the diagonal and columns past n carry no pair
+      const int r0 = i0 + 32 * c;
+      const uint32_t rows = n - r0 >= 32 ? 0xffffffffu : (n - r0 <= 0 ? 0u : ((1u << (n - r0)) - 1u));
+      uint32_t maska = oka ? rows : 0u, maskb = okb ? rows : 0u;
+      if (ja >= r0 && ja < r0 + 32) maska &= ~(1u << (ja - r0));
+      if (jb >= r0 && jb < r0 + 32) maskb &= ~(1u << (jb - r0));
+      worda &= maska; wordb &= maskb;
+    }
+    dirT[warp][32 * c + lane] = warp_transpose32(worda, lane);
+    dirT[4 + warp][32 * c + lane] = warp_transpose32(wordb, lane);
+    tw[0] = c == 0 ? worda : tw[0]; tw[1] = c == 1 ? worda : tw[1]; tw[2] = c == 2 ? worda : tw[2]; tw[3] = c == 3 ? worda : tw[3];
+    tw[4] = c == 0 ? wordb : tw[4]; tw[5] = c == 1 ? wordb : tw[5]; tw[6] = c == 2 ? wordb : tw[6]; tw[7] = c == 3 ? wordb : tw[7];
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kTile, B2R_G4_MINB) tim_graph4_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  const int n = d.n;
+  const int T = (n + kTile - 1) / kTile;
+  int p = blockIdx.x;
+  int bi = 0, rowlen = (T + 1) / 2;
+  while (bi < T && p >= rowlen) { p -= rowlen; ++bi; rowlen = (T - bi + 1) / 2; }
+  if (bi >= T) return;
+  const int bj = bi + 2 * p;
+  __shared__ union { TilePts p64; TilePts4 p32; } sp;
+  __shared__ __align__(16) union { uint32_t rows[kTile][8]; uint32_t cols[8][kTile]; } dir;
+  uint32_t tw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  unsigned slow = 0;
+  const int t = threadIdx.x;
+  uint4 lo, hi;
+  const bool use32 = d.st->use32 != 0;
+  if (use32) {
+    if (bj != bi && (bj + 2) * kTile <= n) compute_tile4<true>(d.src, d.dst, n, bi * kTile, bj * kTile, d.st, kp, sp.p32, dir.cols, tw, slow);
+    else compute_tile4<false>(d.src, d.dst, n, bi * kTile, bj * kTile, d.st, kp, sp.p32, dir.cols, tw, slow);
+    lo = make_uint4(dir.cols[0][t], dir.cols[1][t], dir.cols[2][t], dir.cols[3][t]);
+    hi = make_uint4(dir.cols[4][t], dir.cols[5][t], dir.cols[6][t], dir.cols[7][t]);
+  } else {
+    compute_tile2<false>(d.src, d.dst, n, bi * kTile, bj * kTile, kp, sp.p64, dir.rows, tw, slow);
+    lo = *reinterpret_cast<const uint4*>(&dir.rows[t][0]);
+    hi = *reinterpret_cast<const uint4*>(&dir.rows[t][4]);
+  }
+  const int i = bi * kTile + t;
+  if (i < n) {
+    uint32_t* row = d.adj + (size_t)i * d.pitch + 4 * bj;
+    *reinterpret_cast<uint4*>(row) = lo;
+    if (bj + 1 < T) *reinterpret_cast<uint4*>(row + 4) = hi;
+  }
+  if (bj != bi) {
+    const int j = bj * kTile + t;
+    if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[0], tw[1], tw[2], tw[3]);
+  }
+  if (bj + 1 < T) {
+    const int j = (bj + 1) * kTile + t;
+    if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[4], tw[5], tw[6], tw[7]);
+  }
+  // v4 counts re-evaluated pairs one by one; the fp64 filter (use32 == 0) counts 2048-pair chunks per warp
+  if (slow) {
+    if (use32) atomicAdd(&d.st->slow_pairs, (unsigned long long)slow);
+    else if ((threadIdx.x & 31) == 0) atomicAdd(&d.st->slow_pairs, 2048ull * slow);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Companion of the tensor-core filter (graph_tc.cu): (a) the pairs it listed as ambiguous are decided here, one thread per
+// pair, with the reference's fp64 roundings and square roots, and both symmetric bits are set or cleared atomically;
+// (b) problems the fp32 path may not decide (use32 == 0: non-finite input, extreme extents) or whose list overflowed run the
+// fp64 filter (v2 tiles) over all their work items.  grid = (x, batch), 128 threads.
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTile) graph_fix_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  ProbState* st = d.st;
+  const int n = d.n;
+  const int t = threadIdx.x;
+  if (st->use32 && !st->tc_overflow) {
+    const unsigned cnt = min(st->amb_count, (unsigned)d.amb_cap);
+    for (unsigned idx = blockIdx.x * kTile + t; idx < cnt; idx += gridDim.x * kTile) {
+      const uint32_t e = d.amb_list[idx];
+      const size_t i = e >> 16, j = e & 0xffffu;
+      const double A = sq3_ref(__dsub_rn(d.src[3 * j], d.src[3 * i]), __dsub_rn(d.src[3 * j + 1], d.src[3 * i + 1]), __dsub_rn(d.src[3 * j + 2], d.src[3 * i + 2]));
+      const double B = sq3_ref(__dsub_rn(d.dst[3 * j], d.dst[3 * i]), __dsub_rn(d.dst[3 * j + 1], d.dst[3 * i + 1]), __dsub_rn(d.dst[3 * j + 2], d.dst[3 * i + 2]));
+      uint32_t* wij = d.adj + i * d.pitch + (j >> 5);
+      uint32_t* wji = d.adj + j * d.pitch + (i >> 5);
+      if (verdict_exact(A, B, kp.beta)) { atomicOr(wij, 1u << (j & 31)); atomicOr(wji, 1u << (i & 31)); }
+      else { atomicAnd(wij, ~(1u << (j & 31))); atomicAnd(wji, ~(1u << (i & 31))); }
+    }
+    if (blockIdx.x == 0 && t == 0) st->slow_pairs = cnt;
+    return;
+  }
+  const int T = (n + kTile - 1) / kTile;
+  __shared__ TilePts sp;
+  __shared__ __align__(16) uint32_t dir[kTile][8];
+  const int items = graph2_items(T);
+  unsigned slow = 0;
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    int p = item, bi = 0, rowlen = (T + 1) / 2;
+    while (bi < T && p >= rowlen) { p -= rowlen; ++bi; rowlen = (T - bi + 1) / 2; }
+    const int bj = bi + 2 * p;
+    uint32_t tw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    compute_tile2<false>(d.src, d.dst, n, bi * kTile, bj * kTile, kp, sp, dir, tw, slow);
+    const int i = bi * kTile + t;
+    if (i < n) {
+      uint32_t* row = d.adj + (size_t)i * d.pitch + 4 * bj;
+      *reinterpret_cast<uint4*>(row) = *reinterpret_cast<const uint4*>(&dir[t][0]);
+      if (bj + 1 < T) *reinterpret_cast<uint4*>(row + 4) = *reinterpret_cast<const uint4*>(&dir[t][4]);
+    }
+    if (bj != bi) {
+      const int j = bj * kTile + t;
+      if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[0], tw[1], tw[2], tw[3]);
+    }
+    if (bj + 1 < T) {
+      const int j = (bj + 1) * kTile + t;
+      if (j < n) *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + 4 * bi) = make_uint4(tw[4], tw[5], tw[6], tw[7]);
+    }
+    __syncthreads();
+  }
+  if (slow && (threadIdx.x & 31) == 0) atomicAdd(&st->slow_pairs, 2048ull * slow);
+}
+
+int launch_graph_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
+  const int T = (n_max + kTile - 1) / kTile;
+  int x = 1184 / (batch > 0 ? batch : 1);
+  if (x < 8) x = 8;
+  if (x > graph2_items(T)) x = graph2_items(T);
+  if (x < 1) x = 1;
+  graph_fix_kernel<<<dim3(x, batch), kTile, 0, st>>>(d_desc, kp);
+  return 1;
+}
+
 // Batched, symmetric: grid = (T(T+1)/2 for the largest problem, batch).
 template <int kMode>
 __global__ void __launch_bounds__(kTile) tim_graph_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
@@ -685,9 +968,11 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
   else if (kp.exact_only) tim_graph_kernel<1><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.graph_v1) tim_graph_kernel<0><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.graph_v2) tim_graph2_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
+  else if (!kp.graph_v3 && !kp.graph_v4) return launch_tim_graph_tc(d_desc, batch, n_max, kp, st);
   else {
     graph_prep_kernel<<<batch, 256, 0, st>>>(d_desc, kp);
-    tim_graph3_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
+    if (kp.graph_v3) tim_graph3_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
+    else tim_graph4_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
     return 2;
   }
   return 1;

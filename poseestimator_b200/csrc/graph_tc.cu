@@ -1,0 +1,490 @@
+// TIM pairwise-consistency graph, filter v5: the pair test on the 5th-generation tensor cores.
+//
+// Same contract as graph.cu (the bit of pair (i, j) equals the reference's fp64 verdict | ||src_j - src_i|| - ||dst_j - dst_i|| | <= beta,
+// upstream computeTIMs x2 + the addEdge loop behind `solver.solve`, HelpersRealtime.py:166 / registration_utils.py:261).
+//
+// Work in units of beta: x' = (x - centre) / beta, A' = |s'_j - s'_i|^2, B' = |d'_j - d'_i|^2.  With Dm = A' - B', L = 1 - 2 (A' + B'),
+//     G = Dm^2 + L = ((a' - b')^2 - 1) ((a' + b')^2 - 1),           edge  <=>  G <= 0   whenever A' + B' > 1.
+// Dm and L are BILINEAR in per-point quantities (r = squared norm):
+//     L_ij  = p_i + p_j + 4 s_i.s_j + 4 d_i.d_j,       p  = 1/2 - 2 (r_s + r_d)
+//     Dm_ij = m_i + m_j - 2 s_i.s_j + 2 d_i.d_j,       m  = r_s - r_d
+// so one tcgen05.mma (kind::tf32, M = 128 rows, N = 64 columns, K = 32) per output produces a 128 x 64 block of each in TMEM.
+// Every operand entry is an exact TF32 value: coordinates are rounded ONCE to 22 significant bits (hi + lo, both TF32) and the
+// products hi.hi + hi.lo + lo.hi are laid along K (3xTF32, the lo.lo term is bounded); the fp32 scalars p and m are split into
+// three TF32 pieces (exact).  The epilogue (4 warps, thread = row, tcgen05.ld 32 columns at a time) is per pair:
+//     G = fma(Dm, Dm, L),  T = fma(L, -t1, t0)  (packed f32x2),  sign(G) funnel-shifted into the adjacency word of the row,
+//     one FSETP each for  !(|G| >= T)  and  L > Lcut  ORed into a per-chunk "ambiguous" predicate.
+// Ambiguous pairs (|G| inside the error band, or both lengths possibly below beta) are appended to a per-problem list and
+// decided afterwards, one thread per pair, with the reference's fp64 roundings and square roots (graph_fix_kernel in graph.cu).
+//
+// Error budget (w = 2^-22, u = 2^-24, Pi = Ps + Pd = bounds of the largest squared norms, all in beta units), DESIGN.md
+// "graph filter v5":  geometry (22-bit copies) 17.34 w Pi on A' + B';  scalars u (1 + 4 Pi) resp. 2 u Pi;  dropped lo.lo 4 w Pi;
+// tensor-core accumulation ASSUMED within 2^-20 of the sum of |products| (measured on B200: below 2^-23, tests/test_gpu_teaser.py);
+//     E_L = w (71.8 Pi + 4.3),   E_D = 45.9 w Pi,
+//     |G~ - G| <= u |G~| + 2 E_D |Dm~| + E_D^2 + E_L + E_scale,     2 E_D |Dm~| <= Dm~^2 / k + k E_D^2,  Dm~^2 <= (|G~| + |L~|)(1 + 2u)
+// and T is twice that bound plus the 4e-15 (A' + B' + 1)^2 inside which the reference's own roundings could flip the verdict,
+// written as a linear function of L~ (|L~| <= 2.001 + 2 E_L - L~).
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace b2r {
+
+namespace {
+
+constexpr int kTcRowTile = 128;     // rows per CTA (TMEM lanes)
+constexpr int kTcUnit = 64;         // columns per MMA / TMEM stage
+constexpr int kTcUnitsPerItem = 16; // column units one CTA walks (8 column tiles)
+constexpr int kTcThreads = 160;     // warps 0-3 epilogue, warp 4 producer + MMA issuer
+constexpr uint32_t kTcTmemCols = 256;  // 2 stages x (Dm 64 + L 64)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile, 128-byte swizzle: row r at r * 128 B, its 16-byte chunk c at position c ^ (r & 7); 8-row groups 1024 B apart.
+// Same encodings as nn_gemm.cu (verified on B200): start >> 4, LBO = 1, SBO = 1024 >> 4, version 1, layout 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__device__ __forceinline__ constexpr uint32_t umma_idesc_tf32(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float2 f2fma(float2 a, float2 b, float2 c) {
+  float2 r;
+  asm("{.reg .b64 ra, rb, rc, rd; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mov.b64 rc, {%6,%7}; fma.rn.f32x2 rd, ra, rb, rc; "
+      "mov.b64 {%0,%1}, rd;}"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return r;
+}
+
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const uint32_t m = s == 16 ? 0x0000ffffu : s == 8 ? 0x00ff00ffu : s == 4 ? 0x0f0f0f0fu : s == 2 ? 0x33333333u : 0x55555555u;
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s);
+    x = (lane & s) ? ((x & ~m) | ((y & ~m) >> s)) : ((x & m) | ((y & m) << s));
+  }
+  return x;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// prep: one CTA per problem.  Pass 1: bounding boxes -> centres, extents, band constants (ProbState).  Pass 2: the 22-bit
+// records (2 x float4 per point, zero-filled up to the tile edge).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.x];
+  const int n = d.n;
+  const int t = threadIdx.x;
+  double mn[6], mx[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { mn[k] = CUDART_INF; mx[k] = -CUDART_INF; }
+  bool bad = false;
+  for (int i = t; i < n; i += 1024) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double a = d.src[3 * (size_t)i + k], b = d.dst[3 * (size_t)i + k];
+      bad |= !(fabs(a) <= 1.79e308) | !(fabs(b) <= 1.79e308);
+      mn[k] = fmin(mn[k], a); mx[k] = fmax(mx[k], a);
+      mn[3 + k] = fmin(mn[3 + k], b); mx[3 + k] = fmax(mx[3 + k], b);
+    }
+  }
+  __shared__ double s_mn[32][6], s_mx[32][6];
+  __shared__ double s_ctr[6];
+  __shared__ double s_kappa;
+  __shared__ int s_bad, s_ok;
+  if (t == 0) s_bad = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+      mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+    }
+  }
+  if ((t & 31) == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { s_mn[t >> 5][k] = mn[k]; s_mx[t >> 5][k] = mx[k]; }
+  }
+  if (bad) atomicOr(&s_bad, 1);
+  __syncthreads();
+  if (t == 0) {
+    ProbState* st = d.st;
+    const double beta = fabs(kp.beta);
+    const double kappa = 1.0 / beta;
+    double Pi = 0.0, Mmax = 0.0;
+    for (int k = 0; k < 6; ++k) {
+      double lo = s_mn[0][k], hi = s_mx[0][k];
+      for (int w = 1; w < 32; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
+      const double c = 0.5 * lo + 0.5 * hi;
+      st->ctr[k] = c;
+      s_ctr[k] = c;
+      const double h = fmax(hi - c, c - lo) * kappa * (1.0 + 1e-6);   // covers the roundings of the 22-bit copy
+      Mmax = fmax(Mmax, h);
+      Pi += h * h;
+    }
+    const double w22 = 2.384185791015625e-7, u = 5.9604644775390625e-8;   // 2^-22, 2^-24
+    const double E_L = w22 * (71.8 * Pi + 4.3), E_D = 45.9 * w22 * Pi;
+    const double tmin = kp.filter_tau_min;                                   // tests widen the band with it
+    // the fp32 path decides only well-conditioned problems; everything else goes to the fp64 filter (graph_fix_kernel)
+    const bool ok = !s_bad && n > 0 && beta >= 1e-300 && kappa <= 1e300 && Mmax < 1e12 && Pi > 1e-20 && E_L < 1e3 && tmin < 0.015625;
+    st->use32 = ok ? 1 : 0;
+    st->kappa = kappa;
+    s_kappa = kappa;
+    s_ok = ok ? 1 : 0;
+    if (ok) {
+      double k = sqrt(2.0 * Pi) / E_D;
+      if (!(k >= 8.0)) k = 8.0;
+      if (k > 1e12) k = 1e12;
+      const double E_scale = 2e-15 * (1.0 + 8.0 * Pi), refc = 4e-15 * (1.0 + 8.0 * Pi);
+      const double den = 1.0 - 2.0 * (1.0 + 2.0 * u) / k;
+      const double pad = 1.0 + 1e-5;                                         // fp32 evaluation of T
+      // T(L) = t0 - t1 L;  tmin (tests) widens the band relative to (A' + B' + 1)^2 <= (1 + 8 Pi)(3.001 - L) / 2
+      const double t1 = (2.0 / k + refc + tmin * (1.0 + 8.0 * Pi)) / den * pad;
+      const double labs = 2.001 + 2.0 * E_L;                                 // |L~| <= labs - L~  (L~ <= 1 + E_L)
+      const double t0 = (labs * 2.0 / k + 2.0 * (k + 1.0) * E_D * E_D + 2.0 * E_L + 2.0 * E_scale + (labs + 1.0) * (refc + tmin * (1.0 + 8.0 * Pi))) / den * pad;
+      st->tcc[0] = -__double2float_ru(t1);
+      st->tcc[1] = __double2float_ru(t0);
+      st->tcc[2] = -__double2float_ru(1.001 + 1.01 * E_L);                   // L~ <= this  =>  A' + B' > 1
+      st->tcc[3] = (float)k;
+    }
+  }
+  __syncthreads();
+  if (!s_ok) return;
+  const double kappa = s_kappa;
+  const int n_pad = (n + kTile - 1) / kTile * kTile;
+  for (int i = t; i < n_pad; i += 1024) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (i < n) {
+      float v[6];
+      double r[2] = {0.0, 0.0};
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        const double x = ((k < 3 ? d.src[3 * (size_t)i + k] : d.dst[3 * (size_t)i + k - 3]) - s_ctr[k]) * kappa;
+        const float x32 = __double2float_rn(x);
+        const float hi = to_tf32(x32);
+        const float lo = to_tf32(x32 - hi);
+        v[k] = hi + lo;                       // exact: 22 significant bits
+        r[k / 3] = fma((double)v[k], (double)v[k], r[k / 3]);
+      }
+      a = make_float4(v[0], v[1], v[2], __double2float_rn(0.5 - 2.0 * (r[0] + r[1])));
+      b = make_float4(v[3], v[4], v[5], __double2float_rn(r[0] - r[1]));
+    }
+    d.pts32[2 * (size_t)i] = a;
+    d.pts32[2 * (size_t)i + 1] = b;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// operand rows (K = 32 TF32 values = 128 bytes = 8 chunks of 16 bytes, chunk c of row r stored at c ^ (r & 7))
+//   k:      0-2     3-5     6-8     9-11    12-14   15-17   18-20    21-23    24-26    27-29   30-31
+//   column  s_hi    s_lo    s_hi    d_hi    d_lo    d_hi    p (3)    1 1 1    m (3)    1 1 1   0
+//   row L   4 s_hi  4 s_hi  4 s_lo  4 d_hi  4 d_hi  4 d_lo  1 1 1    p (3)    0        0       0
+//   row D  -2 s_hi -2 s_hi -2 s_lo  2 d_hi  2 d_hi  2 d_lo  0        0        1 1 1    m (3)   0
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct Split { float hi[6], lo[6], p[3], m[3]; };
+
+__device__ __forceinline__ Split split_record(const float4 a, const float4 b) {
+  Split s;
+  const float v[6] = {a.x, a.y, a.z, b.x, b.y, b.z};
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { s.hi[k] = to_tf32(v[k]); s.lo[k] = v[k] - s.hi[k]; }   // exact: v has 22 significant bits
+  s.p[0] = to_tf32(a.w); { const float r = a.w - s.p[0]; s.p[1] = to_tf32(r); s.p[2] = r - s.p[1]; }
+  s.m[0] = to_tf32(b.w); { const float r = b.w - s.m[0]; s.m[1] = to_tf32(r); s.m[2] = r - s.m[1]; }
+  return s;
+}
+
+__device__ __forceinline__ void store_row(unsigned char* tile, int r, const float (&v)[32]) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    *reinterpret_cast<float4*>(tile + r * 128 + ((c ^ (r & 7)) << 4)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+}
+
+__device__ __forceinline__ void store_col_row(unsigned char* tile, int r, const Split& s) {
+  float v[32];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    v[k] = s.hi[k]; v[3 + k] = s.lo[k]; v[6 + k] = s.hi[k];
+    v[9 + k] = s.hi[3 + k]; v[12 + k] = s.lo[3 + k]; v[15 + k] = s.hi[3 + k];
+    v[18 + k] = s.p[k]; v[21 + k] = 1.f; v[24 + k] = s.m[k]; v[27 + k] = 1.f;
+  }
+  v[30] = 0.f; v[31] = 0.f;
+  store_row(tile, r, v);
+}
+
+__device__ __forceinline__ void store_row_rows(unsigned char* tile_l, unsigned char* tile_d, int r, const Split& s) {
+  float v[32];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    v[k] = 4.f * s.hi[k]; v[3 + k] = 4.f * s.hi[k]; v[6 + k] = 4.f * s.lo[k];
+    v[9 + k] = 4.f * s.hi[3 + k]; v[12 + k] = 4.f * s.hi[3 + k]; v[15 + k] = 4.f * s.lo[3 + k];
+    v[18 + k] = 1.f; v[21 + k] = s.p[k]; v[24 + k] = 0.f; v[27 + k] = 0.f;
+  }
+  v[30] = 0.f; v[31] = 0.f;
+  store_row(tile_l, r, v);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    v[k] = -2.f * s.hi[k]; v[3 + k] = -2.f * s.hi[k]; v[6 + k] = -2.f * s.lo[k];
+    v[9 + k] = 2.f * s.hi[3 + k]; v[12 + k] = 2.f * s.hi[3 + k]; v[15 + k] = 2.f * s.lo[3 + k];
+    v[18 + k] = 0.f; v[21 + k] = 0.f; v[24 + k] = 1.f; v[27 + k] = s.m[k];
+  }
+  store_row(tile_d, r, v);
+}
+
+struct TcSmemCtl {
+  uint64_t full[2], empty[2];
+  uint32_t tmem_base;
+};
+
+constexpr int kTcRowBytes = kTcRowTile * 128;   // 16 KB
+constexpr int kTcColBytes = kTcUnit * 128;      // 8 KB
+constexpr int kTcSmemBytes = 100 * 1024;        // 2 x 16 KB + 4 x 8 KB + control; asks for 100 KB so that exactly two CTAs share an SM (TMEM: 2 x 256 columns)
+
+}  // namespace
+
+// work items of one problem: row block bi walks its column units v = 0 .. 2 (T - bi) - 1 in chunks of kTcUnitsPerItem
+__host__ __device__ inline int tc_items(int T) {
+  int s = 0;
+  for (int bi = 0; bi < T; ++bi) s += (2 * (T - bi) + kTcUnitsPerItem - 1) / kTcUnitsPerItem;
+  return s;
+}
+
+__global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  const int n = d.n;
+  if (!d.st->use32) return;
+  const int T = (n + kTile - 1) / kTile;
+  int p = blockIdx.x, bi = 0;
+  int per = (2 * T + kTcUnitsPerItem - 1) / kTcUnitsPerItem;
+  while (bi < T && p >= per) { p -= per; ++bi; per = (2 * (T - bi) + kTcUnitsPerItem - 1) / kTcUnitsPerItem; }
+  if (bi >= T) return;
+  const int v0 = p * kTcUnitsPerItem;
+  const int nu = min(kTcUnitsPerItem, 2 * (T - bi) - v0);
+  const int i0 = bi * kTile;
+
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* sRowL = sm;
+  unsigned char* sRowD = sm + kTcRowBytes;
+  unsigned char* sCol = sm + 2 * kTcRowBytes;   // ring of 4 slots
+  TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sm + 2 * kTcRowBytes + 4 * kTcColBytes);
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+
+  if (t == 128) {
+    for (int s = 0; s < 2; ++s) { mbar_init(&g->full[s], 1); mbar_init(&g->empty[s], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(kTcTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  } else {
+    const float4 a = d.pts32[2 * (size_t)(i0 + t)], b = d.pts32[2 * (size_t)(i0 + t) + 1];
+    store_row_rows(sRowL, sRowD, t, split_record(a, b));
+    fence_proxy_async();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = g->tmem_base;
+
+  if (warp == 4) {
+    // ===== producer: column operands of unit u into stage u & 1, then the eight MMAs (4 k-steps x {Dm, L}) =====
+    constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
+    const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD);
+    // column operands are built one unit ahead into a ring of four 8 KB slots, so that the MMAs of unit u start the moment the
+    // epilogue releases its TMEM stage (slot (u + 1) & 3 was last read by the MMAs of unit u - 3, retired before empty[] of u - 1)
+    auto load_unit = [&](int u, float4 (&ra)[2], float4 (&rb)[2]) {
+      const int v = v0 + u;
+      const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) { ra[h] = d.pts32[2 * (size_t)(j0 + lane + 32 * h)]; rb[h] = d.pts32[2 * (size_t)(j0 + lane + 32 * h) + 1]; }
+    };
+    auto build_unit = [&](int u, const float4 (&ra)[2], const float4 (&rb)[2]) {
+      unsigned char* col = sCol + (u & 3) * kTcColBytes;
+      store_col_row(col, lane, split_record(ra[0], rb[0]));
+      store_col_row(col, lane + 32, split_record(ra[1], rb[1]));
+    };
+    float4 ra[2], rb[2];
+    load_unit(0, ra, rb);
+    build_unit(0, ra, rb);
+    if (nu > 1) load_unit(1, ra, rb);
+    for (int u = 0; u < nu; ++u) {
+      const int s = u & 1;
+      if (u + 1 < nu) {
+        build_unit(u + 1, ra, rb);
+        if (u + 2 < nu) load_unit(u + 2, ra, rb);
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_wait(&g->empty[s], ((u >> 1) & 1) ^ 1);   // epilogue done with the TMEM stage
+        tc_fence_after();
+        const uint32_t cb = smem_u32(sCol + (u & 3) * kTcColBytes);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128, umma_desc_sw128(rowd) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128 + 64, umma_desc_sw128(rowl) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+        tc_commit(&g->full[s]);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===== epilogue: warp q owns TMEM lanes 32 q .. 32 q + 31 = rows i0 + 32 q + lane =====
+    const int q = warp;
+    const int i = i0 + 32 * q + lane;
+    const float2 nt1 = make_float2(d.st->tcc[0], d.st->tcc[0]), t0 = make_float2(d.st->tcc[1], d.st->tcc[1]);
+    const float lcut = d.st->tcc[2];
+    const bool rows_in = i0 + kTile <= n;
+    for (int u = 0; u < nu; ++u) {
+      const int s = u & 1;
+      const int v = v0 + u;
+      const int bj = bi + (v >> 1);
+      const int j0 = bj * kTile + (v & 1) * kTcUnit;
+      const bool interior = rows_in && (j0 + kTcUnit <= n) && (bj != bi);
+      mbar_wait(&g->full[s], (u >> 1) & 1);
+      tc_fence_after();
+      uint32_t words[2] = {0u, 0u};
+#pragma unroll 1
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t dm[32], lv[32];
+        const uint32_t ta = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * 128 + ch * 32);
+        tc_ld_32x32(ta, dm);
+        tc_ld_32x32(ta + 64, lv);
+        tc_wait_ld();
+        // four independent 8-column accumulators (one funnel-shift / predicate chain of 64 would be latency-bound);
+        // within an accumulator the higher column goes first, so column c of the chunk ends in bit c & 7
+        uint32_t wq[4] = {0u, 0u, 0u, 0u};
+        bool aq[4] = {false, false, false, false};
+#pragma unroll
+        for (int c = 6; c >= 0; c -= 2) {
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int cc = 8 * h + c;
+            const float2 D = make_float2(__uint_as_float(dm[cc]), __uint_as_float(dm[cc + 1]));
+            const float2 L = make_float2(__uint_as_float(lv[cc]), __uint_as_float(lv[cc + 1]));
+            const float2 G = f2fma(D, D, L);
+            const float2 Tb = f2fma(L, nt1, t0);
+            wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
+            wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
+            aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y) | (L.x > lcut) | (L.y > lcut);
+          }
+        }
+        uint32_t word = wq[0] + (wq[1] << 8) + (wq[2] << 16) + (wq[3] << 24);
+        const bool amb = aq[0] | aq[1] | aq[2] | aq[3];
+        const int jc = j0 + 32 * ch;
+        uint32_t mask = 0xffffffffu;
+        if (!interior) {
+          const int nc = n - jc;
+          mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
+          if (i >= n) mask = 0u;
+          if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
+          word &= mask;
+        }
+        if (amb) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
+          uint32_t aw = 0;
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const float Dv = __uint_as_float(dm[c]), Lv = __uint_as_float(lv[c]);
+            const float G = fmaf(Dv, Dv, Lv), Tb = fmaf(Lv, nt1.x, t0.x);
+            aw |= (!(fabsf(G) >= Tb) | (Lv > lcut)) ? (1u << c) : 0u;
+          }
+          aw &= mask;
+          if (aw) {
+            unsigned base = atomicAdd(&d.st->amb_count, (unsigned)__popc(aw));
+            while (aw) {
+              const int c = __ffs(aw) - 1;
+              aw &= aw - 1;
+              if (base < (unsigned)d.amb_cap) d.amb_list[base] = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+              else d.st->tc_overflow = 1;
+              ++base;
+            }
+          }
+        }
+        words[0] = ch == 0 ? word : words[0]; words[1] = ch == 1 ? word : words[1];
+        if (bj != bi) {  // transposed block: lane c receives the 32 row bits of column jc + c
+          const uint32_t tw = warp_transpose32(word, lane);
+          if (jc + lane < n) d.adj[(size_t)(jc + lane) * d.pitch + (i0 >> 5) + q] = tw;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&g->empty[s]);
+      if (i < n) *reinterpret_cast<uint2*>(d.adj + (size_t)i * d.pitch + (j0 >> 5)) = make_uint2(words[0], words[1]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTcTmemCols) : "memory");
+  }
+}
+
+int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(tim_graph5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    attr_set = true;
+  }
+  const int T = (n_max + kTile - 1) / kTile;
+  graph_tc_prep_kernel<<<batch, 1024, 0, st>>>(d_desc, kp);
+  tim_graph5_kernel<<<dim3(tc_items(T), batch), kTcThreads, kTcSmemBytes, st>>>(d_desc, kp);
+  return 2 + launch_graph_fix(d_desc, batch, n_max, kp, st);
+}
+
+}  // namespace b2r

@@ -48,7 +48,7 @@ struct b2r_solver {
   // workspace capacity
   int batch_cap = 0, n_cap = 0, pitch = 0;
   long long tim_cap = 0;
-  b2r::DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena, d_scale, d_pre, d_nn, d_grid, d_refine;
+  b2r::DevBuf d_pts, d_adj, d_cadj, d_int, d_dbl, d_u8, d_state, d_desc, d_arena, d_scale, d_pre, d_nn, d_grid, d_refine, d_pts32, d_amb;
   b2r::HostBuf h_state, h_desc, h_pts, h_refine;
   size_t arena_words_per_warp = 64 * 1024;
   int bnb_blocks = 1;

@@ -93,10 +93,10 @@ def test_graph_filter_equals_exact_kernel(oracle_mod, tau):
         assert b.stats()["graph_slow_pairs"] > 0
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5])
 @pytest.mark.parametrize("n,ratio,seed", [(300, 0.5, 31), (1111, 0.8, 32)])
 def test_every_filter_generation_matches_oracle(oracle_mod, mode, n, ratio, seed):
-    """graph_exact_only = 0 (packed-fp32 filter v3), 1 (two square roots), 2 / 3 (fp64 filters v2 / v1): same bits."""
+    """graph_exact_only = 0 (packed-fp32 norm-expansion filter v4), 1 (two square roots), 2 / 3 (fp64 filters v2 / v1), 4 (packed-fp32 filter v3): same bits."""
     import teaserpp_python as tpp
     pb = synth.make_problem(n, ratio, seed)
     ref = oracle_mod.tim_graph(pb.src, pb.dst, pb.noise_bound)
@@ -157,7 +157,7 @@ def test_borderline_pairs_follow_reference_rounding(oracle_mod):
         target = L + beta * (1 + (j % 5 - 2) * 2.2e-16)
         dst[:, j] = dst[:, 0] + v / L * target
     ref = oracle_mod.tim_graph(src, dst, nb)
-    for kw in (dict(graph_exact_only=True), dict(), dict(graph_exact_only=2), dict(graph_exact_only=3)):
+    for kw in (dict(graph_exact_only=True), dict(), dict(graph_exact_only=2), dict(graph_exact_only=3), dict(graph_exact_only=4), dict(graph_exact_only=5)):
         s = tpp.RobustRegistrationSolver(_params(tpp, nb, **kw))
         s.solve(src, dst)
         assert np.array_equal(s._adjacency_bits(), ref)
