@@ -109,7 +109,7 @@ b2r_status ensure_workspace(b2r_solver* s, int batch, int n_max) {
   CK(s->d_pts.ensure(B * 6 * nc * sizeof(double)));
   CK(s->d_adj.ensure(B * nc * pc * sizeof(uint32_t)));
   CK(s->d_cadj.ensure(B * nc * pc * sizeof(uint32_t)));
-  CK(s->d_pts32.ensure(B * (size_t)(pc * 32) * 2 * sizeof(float4)));   // pc * 32 = n_cap rounded up to the tile edge
+  CK(s->d_pts32.ensure(B * (size_t)(pc * 32) * 128));   // tensor-core filter: one 128-byte operand row per point, pc * 32 = n_cap rounded up to the tile edge
   CK(s->d_amb.ensure(B * (size_t)kAmbCap * sizeof(uint32_t)));
   // ints per problem: deg, ids, clique (n each) + rot_inl (tim) + tls_id (4*tim)
   CK(s->d_int.ensure(B * (3 * (size_t)nc + 5 * (size_t)tc) * sizeof(int)));
@@ -144,7 +144,7 @@ void build_desc(b2r_solver* s, int b, int n, const double* dsrc, const double* d
   unsigned char* ub = (unsigned char*)s->d_u8.p + (size_t)b * 2 * tc;
   d.rot_mask = ub; d.trans_mask = ub + tc;
   d.st = (ProbState*)s->d_state.p + b;
-  d.pts32 = (float4*)s->d_pts32.p + (size_t)b * pc * 32 * 2;
+  d.pts32 = (float4*)((unsigned char*)s->d_pts32.p + (size_t)b * pc * 32 * 128);
   d.amb_list = (uint32_t*)s->d_amb.p + (size_t)b * kAmbCap;
   d.amb_cap = kAmbCap;
   d.pad2_ = 0;

@@ -72,7 +72,7 @@ struct ProbDesc {
   int* tls_id;
   double* raw;           // 3 x tim_cap raw translations
   ProbState* st;
-  float4* pts32;         // tensor-core filter: 2 x float4 per point (22-bit centred scaled src xyz + p, dst xyz + mn), n_pad points
+  float4* pts32;         // tensor-core filter: pre-swizzled operand rows (column, row-L, row-D: 3 x n_pad x 128 B), graph_tc.cu
   uint32_t* amb_list;    // tensor-core filter: (i << 16) | j of the pairs the exact kernel must decide
   int amb_cap;
   int pad2_;

@@ -34,8 +34,12 @@ namespace {
 
 constexpr int kTcRowTile = 128;     // rows per CTA (TMEM lanes)
 constexpr int kTcUnit = 64;         // columns per MMA / TMEM stage
-constexpr int kTcUnitsPerItem = 16; // column units one CTA walks (8 column tiles)
-constexpr int kTcThreads = 160;     // warps 0-3 epilogue, warp 4 producer + MMA issuer
+#ifndef B2R_TC_UPI
+#define B2R_TC_UPI 16
+#endif
+constexpr int kTcUnitsPerItem = B2R_TC_UPI; // column units one CTA walks (16 = 8 column tiles)
+constexpr int kTcEpiWarps = 8;      // epilogue warps: lane quarter w & 3, 32-column half w >> 2 of every unit
+constexpr int kTcThreads = 32 * (kTcEpiWarps + 1);   // + one producer / MMA-issuer warp
 constexpr uint32_t kTcTmemCols = 256;  // 2 stages x (Dm 64 + L 64)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -53,6 +57,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "@p bra DONE_%=;\n\t"
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// the single waiting lane of the producer warp backs off between polls: its spin loop otherwise takes a quarter of the
+// SM sub-partition's issue slots from the epilogue warps
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(100);
+  }
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -121,8 +138,8 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------------
-// prep: one CTA per problem.  Pass 1: bounding boxes -> centres, extents, band constants (ProbState).  Pass 2: the 22-bit
-// records (2 x float4 per point, zero-filled up to the tile edge).
+// prep: one CTA per problem: bounding boxes -> centres, extents, band constants (ProbState).  graph_tc_ops_kernel then writes
+// the operand rows of every point (zero-filled up to the tile edge).
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
   const ProbDesc d = descs[blockIdx.x];
@@ -142,9 +159,7 @@ __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __r
     }
   }
   __shared__ double s_mn[32][6], s_mx[32][6];
-  __shared__ double s_ctr[6];
-  __shared__ double s_kappa;
-  __shared__ int s_bad, s_ok;
+  __shared__ int s_bad;
   if (t == 0) s_bad = 0;
   __syncthreads();
 #pragma unroll
@@ -171,7 +186,6 @@ __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __r
       for (int w = 1; w < 32; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
       const double c = 0.5 * lo + 0.5 * hi;
       st->ctr[k] = c;
-      s_ctr[k] = c;
       const double h = fmax(hi - c, c - lo) * kappa * (1.0 + 1e-6);   // covers the roundings of the 22-bit copy
       Mmax = fmax(Mmax, h);
       Pi += h * h;
@@ -183,8 +197,6 @@ __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __r
     const bool ok = !s_bad && n > 0 && beta >= 1e-300 && kappa <= 1e300 && Mmax < 1e12 && Pi > 1e-20 && E_L < 1e3 && tmin < 0.015625;
     st->use32 = ok ? 1 : 0;
     st->kappa = kappa;
-    s_kappa = kappa;
-    s_ok = ok ? 1 : 0;
     if (ok) {
       double k = sqrt(2.0 * Pi) / E_D;
       if (!(k >= 8.0)) k = 8.0;
@@ -201,30 +213,6 @@ __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __r
       st->tcc[2] = -__double2float_ru(1.001 + 1.01 * E_L);                   // L~ <= this  =>  A' + B' > 1
       st->tcc[3] = (float)k;
     }
-  }
-  __syncthreads();
-  if (!s_ok) return;
-  const double kappa = s_kappa;
-  const int n_pad = (n + kTile - 1) / kTile * kTile;
-  for (int i = t; i < n_pad; i += 1024) {
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-    if (i < n) {
-      float v[6];
-      double r[2] = {0.0, 0.0};
-#pragma unroll
-      for (int k = 0; k < 6; ++k) {
-        const double x = ((k < 3 ? d.src[3 * (size_t)i + k] : d.dst[3 * (size_t)i + k - 3]) - s_ctr[k]) * kappa;
-        const float x32 = __double2float_rn(x);
-        const float hi = to_tf32(x32);
-        const float lo = to_tf32(x32 - hi);
-        v[k] = hi + lo;                       // exact: 22 significant bits
-        r[k / 3] = fma((double)v[k], (double)v[k], r[k / 3]);
-      }
-      a = make_float4(v[0], v[1], v[2], __double2float_rn(0.5 - 2.0 * (r[0] + r[1])));
-      b = make_float4(v[3], v[4], v[5], __double2float_rn(r[0] - r[1]));
-    }
-    d.pts32[2 * (size_t)i] = a;
-    d.pts32[2 * (size_t)i + 1] = b;
   }
 }
 
@@ -267,35 +255,85 @@ __device__ __forceinline__ void store_col_row(unsigned char* tile, int r, const 
   store_row(tile, r, v);
 }
 
-__device__ __forceinline__ void store_row_rows(unsigned char* tile_l, unsigned char* tile_d, int r, const Split& s) {
+// row-L and row-D operand rows of point r from its column row (all scalings are powers of two: exact)
+__device__ __forceinline__ void rows_from_col_row(const unsigned char* stage, unsigned char* tile_l, unsigned char* tile_d, int r) {
+  float c[32];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float4 q = *reinterpret_cast<const float4*>(stage + r * 128 + ((k ^ (r & 7)) << 4));
+    c[4 * k] = q.x; c[4 * k + 1] = q.y; c[4 * k + 2] = q.z; c[4 * k + 3] = q.w;
+  }
   float v[32];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    v[k] = 4.f * s.hi[k]; v[3 + k] = 4.f * s.hi[k]; v[6 + k] = 4.f * s.lo[k];
-    v[9 + k] = 4.f * s.hi[3 + k]; v[12 + k] = 4.f * s.hi[3 + k]; v[15 + k] = 4.f * s.lo[3 + k];
-    v[18 + k] = 1.f; v[21 + k] = s.p[k]; v[24 + k] = 0.f; v[27 + k] = 0.f;
+    v[k] = 4.f * c[k]; v[3 + k] = 4.f * c[k]; v[6 + k] = 4.f * c[3 + k];
+    v[9 + k] = 4.f * c[9 + k]; v[12 + k] = 4.f * c[9 + k]; v[15 + k] = 4.f * c[12 + k];
+    v[18 + k] = 1.f; v[21 + k] = c[18 + k]; v[24 + k] = 0.f; v[27 + k] = 0.f;
   }
   v[30] = 0.f; v[31] = 0.f;
   store_row(tile_l, r, v);
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    v[k] = -2.f * s.hi[k]; v[3 + k] = -2.f * s.hi[k]; v[6 + k] = -2.f * s.lo[k];
-    v[9 + k] = 2.f * s.hi[3 + k]; v[12 + k] = 2.f * s.hi[3 + k]; v[15 + k] = 2.f * s.lo[3 + k];
-    v[18 + k] = 0.f; v[21 + k] = 0.f; v[24 + k] = 1.f; v[27 + k] = s.m[k];
+    v[k] = -2.f * c[k]; v[3 + k] = -2.f * c[k]; v[6 + k] = -2.f * c[3 + k];
+    v[9 + k] = 2.f * c[9 + k]; v[12 + k] = 2.f * c[9 + k]; v[15 + k] = 2.f * c[12 + k];
+    v[18 + k] = 0.f; v[21 + k] = 0.f; v[24 + k] = 1.f; v[27 + k] = c[24 + k];
   }
   store_row(tile_d, r, v);
 }
 
 struct TcSmemCtl {
-  uint64_t full[2], empty[2];
+  uint64_t rowfull, colfull[4], full[2], empty[2];
   uint32_t tmem_base;
 };
 
 constexpr int kTcRowBytes = kTcRowTile * 128;   // 16 KB
 constexpr int kTcColBytes = kTcUnit * 128;      // 8 KB
-constexpr int kTcSmemBytes = 100 * 1024;        // 2 x 16 KB + 4 x 8 KB + control; asks for 100 KB so that exactly two CTAs share an SM (TMEM: 2 x 256 columns)
+constexpr int kTcSmemBytes = 100 * 1024;        // 2 x 16 KB + 4 x 8 KB + control + 16 KB staging; asks for 100 KB so that exactly two CTAs share an SM (TMEM: 2 x 256 columns)
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// 1-D bulk copy global -> shared through the async proxy (the operand rows are stored pre-swizzled, so no tensor map is needed)
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes),
+               "r"(smem_u32(bar))
+               : "memory");
+}
 
 }  // namespace
+
+// Column-operand row of every point (128 bytes), already in the 128-byte-swizzled order the MMA reads (row j of a 64- or
+// 128-row tile uses j & 7, and tiles start at multiples of 64).  The row-L / row-D operands of a CTA's 128 rows are derived
+// from these rows in shared memory (rows_from_col_row).  grid = (n_pad / 128, batch).
+__global__ void __launch_bounds__(kTile) graph_tc_ops_kernel(const ProbDesc* __restrict__ descs) {
+  const ProbDesc d = descs[blockIdx.y];
+  const ProbState* st = d.st;
+  if (!st->use32) return;
+  const int n = d.n;
+  const int n_pad = (n + kTile - 1) / kTile * kTile;
+  const int i = blockIdx.x * kTile + threadIdx.x;
+  if (i >= n_pad) return;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+  if (i < n) {
+    const double kappa = st->kappa;
+    float v[6];
+    double r[2] = {0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double x = ((k < 3 ? d.src[3 * (size_t)i + k] : d.dst[3 * (size_t)i + k - 3]) - st->ctr[k]) * kappa;
+      const float x32 = __double2float_rn(x);
+      const float hi = to_tf32(x32);
+      const float lo = to_tf32(x32 - hi);
+      v[k] = hi + lo;                       // exact: 22 significant bits
+      r[k / 3] = fma((double)v[k], (double)v[k], r[k / 3]);
+    }
+    a = make_float4(v[0], v[1], v[2], __double2float_rn(0.5 - 2.0 * (r[0] + r[1])));
+    b = make_float4(v[3], v[4], v[5], __double2float_rn(r[0] - r[1]));
+  }
+  const Split sp = split_record(a, b);
+  unsigned char* base = reinterpret_cast<unsigned char*>(d.pts32);
+  store_col_row(base, i, sp);
+}
 
 // work items of one problem: row block bi walks its column units v = 0 .. 2 (T - bi) - 1 in chunks of kTcUnitsPerItem
 __host__ __device__ inline int tc_items(int T) {
@@ -324,17 +362,25 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
   unsigned char* sCol = sm + 2 * kTcRowBytes;   // ring of 4 slots
   TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sm + 2 * kTcRowBytes + 4 * kTcColBytes);
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const unsigned char* ops = reinterpret_cast<const unsigned char*>(d.pts32);
+  const unsigned char* ops_col = ops;
+  unsigned char* sStage = sm + 2 * kTcRowBytes + 4 * kTcColBytes + 1024;   // column rows of the CTA's own 128 points (16 KB)
 
-  if (t == 128) {
-    for (int s = 0; s < 2; ++s) { mbar_init(&g->full[s], 1); mbar_init(&g->empty[s], 4); }
+  if (t == 32 * kTcEpiWarps) {
+    mbar_init(&g->rowfull, 1);
+    for (int s = 0; s < 4; ++s) mbar_init(&g->colfull[s], 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&g->full[s], 1); mbar_init(&g->empty[s], kTcEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(&g->rowfull, kTcRowBytes);
+    bulk_g2s(sStage, ops_col + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
   }
-  if (warp == 4) {
+  __syncthreads();
+  if (warp == kTcEpiWarps) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(kTcTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  } else {
-    const float4 a = d.pts32[2 * (size_t)(i0 + t)], b = d.pts32[2 * (size_t)(i0 + t) + 1];
-    store_row_rows(sRowL, sRowD, t, split_record(a, b));
+  } else if (t < kTcRowTile) {
+    mbar_wait(&g->rowfull, 0);
+    rows_from_col_row(sStage, sRowL, sRowD, t);
     fence_proxy_async();
   }
   tc_fence_before();
@@ -342,36 +388,22 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
   tc_fence_after();
   const uint32_t tmem = g->tmem_base;
 
-  if (warp == 4) {
-    // ===== producer: column operands of unit u into stage u & 1, then the eight MMAs (4 k-steps x {Dm, L}) =====
-    constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
-    const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD);
-    // column operands are built one unit ahead into a ring of four 8 KB slots, so that the MMAs of unit u start the moment the
-    // epilogue releases its TMEM stage (slot (u + 1) & 3 was last read by the MMAs of unit u - 3, retired before empty[] of u - 1)
-    auto load_unit = [&](int u, float4 (&ra)[2], float4 (&rb)[2]) {
-      const int v = v0 + u;
-      const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) { ra[h] = d.pts32[2 * (size_t)(j0 + lane + 32 * h)]; rb[h] = d.pts32[2 * (size_t)(j0 + lane + 32 * h) + 1]; }
-    };
-    auto build_unit = [&](int u, const float4 (&ra)[2], const float4 (&rb)[2]) {
-      unsigned char* col = sCol + (u & 3) * kTcColBytes;
-      store_col_row(col, lane, split_record(ra[0], rb[0]));
-      store_col_row(col, lane + 32, split_record(ra[1], rb[1]));
-    };
-    float4 ra[2], rb[2];
-    load_unit(0, ra, rb);
-    build_unit(0, ra, rb);
-    if (nu > 1) load_unit(1, ra, rb);
-    for (int u = 0; u < nu; ++u) {
-      const int s = u & 1;
-      if (u + 1 < nu) {
-        build_unit(u + 1, ra, rb);
-        if (u + 2 < nu) load_unit(u + 2, ra, rb);
-      }
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) {
+  if (warp == kTcEpiWarps) {
+    // ===== producer (one lane): bulk copies of the pre-swizzled operand rows, then the eight MMAs (4 k-steps x {Dm, L}) per unit.
+    // Column units travel through a ring of four 8 KB slots, three units ahead of the MMAs. =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
+      const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD);
+      auto copy_unit = [&](int u) {
+        const int v = v0 + u;
+        const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
+        mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
+        bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
+      };
+      for (int u = 0; u < 3 && u < nu; ++u) copy_unit(u);
+      for (int u = 0; u < nu; ++u) {
+        const int s = u & 1;
+        mbar_wait(&g->colfull[u & 3], (u >> 2) & 1);
         mbar_wait(&g->empty[s], ((u >> 1) & 1) ^ 1);   // epilogue done with the TMEM stage
         tc_fence_after();
         const uint32_t cb = smem_u32(sCol + (u & 3) * kTcColBytes);
@@ -380,15 +412,20 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128 + 64, umma_desc_sw128(rowl) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
         tc_commit(&g->full[s]);
+        if (u + 3 < nu) {  // slot (u + 3) & 3 held unit u - 1: its MMAs must have retired before the slot is overwritten
+          if (u >= 1) mbar_wait(&g->full[(u - 1) & 1], ((u - 1) >> 1) & 1);
+          copy_unit(u + 3);
+        }
       }
-      __syncwarp();
     }
+    __syncwarp();
   } else {
-    // ===== epilogue: warp q owns TMEM lanes 32 q .. 32 q + 31 = rows i0 + 32 q + lane =====
-    const int q = warp;
+    // ===== epilogue: warp w owns TMEM lanes 32 (w & 3) .. + 31 = rows i0 + 32 (w & 3) + lane, columns 32 (w >> 2) .. + 31 of each unit =====
+    const int q = warp & 3, ch = warp >> 2;
     const int i = i0 + 32 * q + lane;
     const float2 nt1 = make_float2(d.st->tcc[0], d.st->tcc[0]), t0 = make_float2(d.st->tcc[1], d.st->tcc[1]);
     const float lcut = d.st->tcc[2];
+    const uint32_t lcut_bits = __float_as_uint(lcut);   // lcut < 0:  L > lcut  <=>  bits(L) < bits(lcut) as unsigned
     const bool rows_in = i0 + kTile <= n;
     for (int u = 0; u < nu; ++u) {
       const int s = u & 1;
@@ -398,78 +435,75 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
       const bool interior = rows_in && (j0 + kTcUnit <= n) && (bj != bi);
       mbar_wait(&g->full[s], (u >> 1) & 1);
       tc_fence_after();
-      uint32_t words[2] = {0u, 0u};
-#pragma unroll 1
-      for (int ch = 0; ch < 2; ++ch) {
-        uint32_t dm[32], lv[32];
-        const uint32_t ta = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * 128 + ch * 32);
-        tc_ld_32x32(ta, dm);
-        tc_ld_32x32(ta + 64, lv);
-        tc_wait_ld();
-        // four independent 8-column accumulators (one funnel-shift / predicate chain of 64 would be latency-bound);
-        // within an accumulator the higher column goes first, so column c of the chunk ends in bit c & 7
-        uint32_t wq[4] = {0u, 0u, 0u, 0u};
-        bool aq[4] = {false, false, false, false};
-#pragma unroll
-        for (int c = 6; c >= 0; c -= 2) {
-#pragma unroll
-          for (int h = 0; h < 4; ++h) {
-            const int cc = 8 * h + c;
-            const float2 D = make_float2(__uint_as_float(dm[cc]), __uint_as_float(dm[cc + 1]));
-            const float2 L = make_float2(__uint_as_float(lv[cc]), __uint_as_float(lv[cc + 1]));
-            const float2 G = f2fma(D, D, L);
-            const float2 Tb = f2fma(L, nt1, t0);
-            wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
-            wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
-            aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y) | (L.x > lcut) | (L.y > lcut);
-          }
-        }
-        uint32_t word = wq[0] + (wq[1] << 8) + (wq[2] << 16) + (wq[3] << 24);
-        const bool amb = aq[0] | aq[1] | aq[2] | aq[3];
-        const int jc = j0 + 32 * ch;
-        uint32_t mask = 0xffffffffu;
-        if (!interior) {
-          const int nc = n - jc;
-          mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
-          if (i >= n) mask = 0u;
-          if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
-          word &= mask;
-        }
-        if (amb) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
-          uint32_t aw = 0;
-#pragma unroll
-          for (int c = 0; c < 32; ++c) {
-            const float Dv = __uint_as_float(dm[c]), Lv = __uint_as_float(lv[c]);
-            const float G = fmaf(Dv, Dv, Lv), Tb = fmaf(Lv, nt1.x, t0.x);
-            aw |= (!(fabsf(G) >= Tb) | (Lv > lcut)) ? (1u << c) : 0u;
-          }
-          aw &= mask;
-          if (aw) {
-            unsigned base = atomicAdd(&d.st->amb_count, (unsigned)__popc(aw));
-            while (aw) {
-              const int c = __ffs(aw) - 1;
-              aw &= aw - 1;
-              if (base < (unsigned)d.amb_cap) d.amb_list[base] = ((uint32_t)i << 16) | (uint32_t)(jc + c);
-              else d.st->tc_overflow = 1;
-              ++base;
-            }
-          }
-        }
-        words[0] = ch == 0 ? word : words[0]; words[1] = ch == 1 ? word : words[1];
-        if (bj != bi) {  // transposed block: lane c receives the 32 row bits of column jc + c
-          const uint32_t tw = warp_transpose32(word, lane);
-          if (jc + lane < n) d.adj[(size_t)(jc + lane) * d.pitch + (i0 >> 5) + q] = tw;
-        }
-      }
+      uint32_t dm[32], lv[32];
+      const uint32_t ta = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * 128 + ch * 32);
+      tc_ld_32x32(ta, dm);
+      tc_ld_32x32(ta + 64, lv);
+      tc_wait_ld();
+      // the accumulators are in registers: release the TMEM stage right away
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&g->empty[s]);
-      if (i < n) *reinterpret_cast<uint2*>(d.adj + (size_t)i * d.pitch + (j0 >> 5)) = make_uint2(words[0], words[1]);
+      // four independent 8-column accumulators (one funnel-shift / predicate chain of 64 would be latency-bound);
+      // within an accumulator the higher column goes first, so column c of the chunk ends in bit c & 7
+      uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      bool aq[4] = {false, false, false, false};
+#pragma unroll
+      for (int c = 6; c >= 0; c -= 2) {
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const int cc = 8 * h + c;
+          const float2 D = make_float2(__uint_as_float(dm[cc]), __uint_as_float(dm[cc + 1]));
+          const float2 L = make_float2(__uint_as_float(lv[cc]), __uint_as_float(lv[cc + 1]));
+          const float2 G = f2fma(D, D, L);
+          const float2 Tb = f2fma(L, nt1, t0);
+          wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
+          wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
+          aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
+          lmin[h] = __vimin3_u32(lmin[h], lv[cc], lv[cc + 1]);
+        }
+      }
+      uint32_t word = wq[0] + (wq[1] << 8) + (wq[2] << 16) + (wq[3] << 24);
+      const bool amb = aq[0] | aq[1] | aq[2] | aq[3] | (min(min(lmin[0], lmin[1]), min(lmin[2], lmin[3])) < lcut_bits);
+      const int jc = j0 + 32 * ch;
+      uint32_t mask = 0xffffffffu;
+      if (!interior) {
+        const int nc = n - jc;
+        mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
+        if (i >= n) mask = 0u;
+        if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
+        word &= mask;
+      }
+      if (amb) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
+        uint32_t aw = 0;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const float Dv = __uint_as_float(dm[c]), Lv = __uint_as_float(lv[c]);
+          const float G = fmaf(Dv, Dv, Lv), Tb = fmaf(Lv, nt1.x, t0.x);
+          aw |= (!(fabsf(G) >= Tb) | (lv[c] < lcut_bits)) ? (1u << c) : 0u;
+        }
+        aw &= mask;
+        if (aw) {
+          unsigned base = atomicAdd(&d.st->amb_count, (unsigned)__popc(aw));
+          while (aw) {
+            const int c = __ffs(aw) - 1;
+            aw &= aw - 1;
+            if (base < (unsigned)d.amb_cap) d.amb_list[base] = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+            else d.st->tc_overflow = 1;
+            ++base;
+          }
+        }
+      }
+      if (bj != bi) {  // transposed block: lane c receives the 32 row bits of column jc + c
+        const uint32_t tw = warp_transpose32(word, lane);
+        if (jc + lane < n) d.adj[(size_t)(jc + lane) * d.pitch + (i0 >> 5) + q] = tw;
+      }
+      if (i < n) d.adj[(size_t)i * d.pitch + (jc >> 5)] = word;
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kTcEpiWarps) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTcTmemCols) : "memory");
   }
@@ -483,8 +517,9 @@ int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const Kern
   }
   const int T = (n_max + kTile - 1) / kTile;
   graph_tc_prep_kernel<<<batch, 1024, 0, st>>>(d_desc, kp);
+  graph_tc_ops_kernel<<<dim3(T, batch), kTile, 0, st>>>(d_desc);
   tim_graph5_kernel<<<dim3(tc_items(T), batch), kTcThreads, kTcSmemBytes, st>>>(d_desc, kp);
-  return 2 + launch_graph_fix(d_desc, batch, n_max, kp, st);
+  return 3 + launch_graph_fix(d_desc, batch, n_max, kp, st);
 }
 
 }  // namespace b2r
