@@ -6,8 +6,8 @@ consistency graph -> max clique -> GNC-TLS rotation -> adaptive-voting translati
 
   value     device-timed (CUDA events on the library's stream), inputs resident in HBM, L2 flushed between steps
   e2e       the same work through the public host API (numpy in, solutions out): H2D + kernels + D2H per step
-  roofline  the dominant kernel (tim_graph3_kernel): algorithmic bytes / measured launch time vs measured HBM peak,
-            plus its fraction of the packed-fp32 issue rate (the pipe that actually bounds it -- DESIGN.md)
+  roofline  the dominant stage (tensor-core graph filter, tim_graph5_kernel + its three helper kernels): algorithmic bytes /
+            measured stage time vs measured HBM peak, plus pair tests per second (the kernel is issue-bound -- DESIGN.md)
   cpu_baseline / --impl reference   the oracle (CPU port of the reference's TEASER++ path) on the host cores
 
 N>1: one process per GPU (torchrun), detections sharded with no collective on the data path; value = all ranks' work
@@ -41,14 +41,13 @@ def algorithmic_graph_bytes(n: int) -> int:
 
 
 GRAPH_FP64_OPS_PER_PAIR = 19  # 6 sub, 6 mul, 4 add, 1 sub, 1 abs, 1 cmp (+2 DSQRT, counted separately)
-GRAPH_F32X2_PER_PAIR = 9      # filter v3: 18 packed-fp32 instructions per two pairs (csrc/graph.cu)
-F32X2_PEAK_TINST = 18.3       # measured on this pool's B200 (profiles/r01_fp32x2_peak.jsonl, tools/peaks/fp32x2_peak.cu)
+GRAPH_EPILOGUE_SLOTS_PER_PAIR = 3.5   # filter v5 epilogue: per two pairs 2 FFMA2 + 2 SHF + 2 FSETP + 1 VIMNMX3 (csrc/graph_tc.cu)
 
 
-def graph_items(n: int) -> int:
-    """128 x 256 tiles one problem's graph kernel evaluates (graph.cu graph2_items)."""
+def graph_units(n: int) -> int:
+    """128 x 64 units one problem's tensor-core graph kernel evaluates (graph_tc.cu): 2 per 128 x 128 tile of the upper triangle."""
     t = (n + 127) // 128
-    return (t // 2) * (t // 2 + 1) + ((t + 1) // 2 if t & 1 else 0)
+    return t * (t + 1)
 
 
 class ClockSampler(threading.Thread):
@@ -308,9 +307,9 @@ def main():
         alg_bytes = algorithmic_graph_bytes(N_CORR) * B
         achieved = alg_bytes / (g_ms * 1e-3) / 1e9
         pairs = N_CORR * (N_CORR - 1) // 2 * B
-        evaluated = graph_items(N_CORR) * 128 * 256 * B
+        evaluated = graph_units(N_CORR) * 128 * 64 * B
         traffic = None
-        tp = os.path.join(ROOT, "profiles", "r01_graph3_ncu.json")
+        tp = os.path.join(ROOT, "profiles", "r01_graph5_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             if tj.get("batch") == B and tj.get("n") == N_CORR:
@@ -322,17 +321,18 @@ def main():
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "n": N_CORR, "outlier_ratio": OUTLIER_RATIO,
                        "l2": "flushed between steps (256 MiB write outside the timed events)",
                        "sharding": "independent registrations per rank, no collective"},
-            "roofline": {"bound": "hbm", "kernel": "tim_graph3_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "tim_graph5_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_note,
-                         "note": "compute-bound by design (O(N^2) pair tests, O(N^2/32) bytes out): the binding unit is the fp32 FMA "
-                                 "pipe (packed f32x2 issue rate), see fp32x2_* fields; stage time includes the 1-CTA-per-problem prep kernel",
+                         "note": "O(N^2) pair tests for O(N^2/32) bytes out: far from the HBM roof by construction.  Dm and L of every "
+                                 "pair come from tcgen05.mma (TF32) into TMEM; the kernel is bound by the issue slots of its epilogue "
+                                 "(sign + band test, 3.5 instructions per pair), see pair_tests_per_s; ms_per_launch is the whole graph "
+                                 "stage (prep + operand rows + tcgen05 kernel + exact fix-up of the listed pairs)",
                          "ms_per_launch": g_ms, "pairs_per_launch": pairs, "pairs_evaluated_per_launch": evaluated,
-                         "fp32x2_tinst_per_s": evaluated * GRAPH_F32X2_PER_PAIR / (g_ms * 1e-3) / 1e12,
-                         "fp32x2_peak_tinst_per_s": F32X2_PEAK_TINST,
-                         "fp32x2_frac": evaluated * GRAPH_F32X2_PER_PAIR / (g_ms * 1e-3) / 1e12 / F32X2_PEAK_TINST,
+                         "pair_tests_per_s": evaluated / (g_ms * 1e-3),
+                         "epilogue_tinst_per_s": evaluated * GRAPH_EPILOGUE_SLOTS_PER_PAIR / (g_ms * 1e-3) / 1e12,
                          "fp64_gops_algorithmic": pairs * GRAPH_FP64_OPS_PER_PAIR / (g_ms * 1e-3) / 1e9},
             "e2e": {"value": e2e_value, "unit": "registrations/s", "h2d_bytes_per_step": 48 * N_CORR * B,
-                    "d2h_bytes_per_step": int(B * 312 + B * (104 + 4 * st0["clique_size"]))},
+                    "d2h_bytes_per_step": int(B * 400 + B * (104 + 4 * st0["clique_size"]))},
             "latency_ms_p50": lat_max,
             "gpu_launches": int(launches),
             "stage_ms_per_step": {k: round(v, 4) for k, v in stage_ms.items()},

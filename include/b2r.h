@@ -165,6 +165,11 @@ b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* ds
 /* Continue a solve from a complete device adjacency (after the all-gather of row shards). */
 b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const double* dst_dev, int n,
                                     const uint32_t* adj_dev, int pitch_words);
+/* Test hook of the tensor-core graph filter: after a solve on this handle, recompute the raw fp32 values Dm~ and L~ (DESIGN.md
+ * "graph filter v5") of rows [128 row_block, +128) x the 64 columns of unit `unit` of that row block for problem idx, as the
+ * tcgen05.mma leaves them in TMEM.  dm_out / l_out: host, 128 x 64 floats row-major.  consts_out (host, 12 doubles): kappa,
+ * centres (6), t1, t0, lcut, k, use32. */
+b2r_status b2r_debug_tc_values(b2r_solver* s, int idx, int row_block, int unit, float* dm_out, float* l_out, double* consts_out);
 /* words per adjacency row the library uses for n vertices (multiple of 4) */
 int b2r_pitch_words(int n);
 

@@ -60,7 +60,7 @@ EXPORTS = [
     "b2r_default_params", "b2r_version", "b2r_device_count", "b2r_create", "b2r_destroy", "b2r_reset", "b2r_last_error",
     "b2r_solve", "b2r_solve_batch", "b2r_solve_batch_async", "b2r_sync", "b2r_batch_size", "b2r_launch_count",
     "b2r_get_solution", "b2r_get_solutions", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
-    "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
+    "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words", "b2r_debug_tc_values",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
     "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
@@ -115,6 +115,7 @@ def lib():
     L.b2r_get_timings.argtypes = [vp, vp]
     L.b2r_graph_rows.argtypes = [vp, vp, vp, i32, i32, i32, vp, i32]
     L.b2r_solve_from_adjacency.argtypes = [vp, vp, vp, i32, vp, i32]
+    L.b2r_debug_tc_values.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     L.b2r_pitch_words.argtypes = [i32]
     L.b2r_pitch_words.restype = i32
     d, ip = C.c_double, C.POINTER(C.c_int)

@@ -555,6 +555,31 @@ b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* ds
   return B2R_OK;
 }
 
+b2r_status b2r_debug_tc_values(b2r_solver* s, int idx, int row_block, int unit, float* dm_out, float* l_out, double* consts_out) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  if (!dm_out || !l_out || !consts_out) return fail(s, B2R_ERR_INVALID_ARG, "debug_tc_values arguments");
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  const int n = s->n[idx];
+  const int T = (n + kTile - 1) / kTile;
+  if (row_block < 0 || row_block >= T || unit < 0 || unit >= 2 * (T - row_block)) return fail(s, B2R_ERR_INVALID_ARG, "debug_tc_values: block / unit out of range");
+  consts_out[0] = st.kappa;
+  for (int k = 0; k < 6; ++k) consts_out[1 + k] = st.ctr[k];
+  consts_out[7] = -(double)st.tcc[0]; consts_out[8] = st.tcc[1]; consts_out[9] = st.tcc[2]; consts_out[10] = st.tcc[3];
+  consts_out[11] = st.use32;
+  if (!st.use32) return fail(s, B2R_ERR_STATE, "the tensor-core filter did not run on this problem (use32 == 0)");
+  CK(cudaSetDevice(s->device));
+  float* dbuf = nullptr;
+  CK(cudaMalloc(&dbuf, 2 * 128 * 64 * sizeof(float)));
+  s->launches += launch_graph_tc_debug((const ProbDesc*)s->d_desc.p, idx, row_block, unit, dbuf, dbuf + 128 * 64, s->stream);
+  cudaError_t e = cudaStreamSynchronize(s->stream);
+  if (e == cudaSuccess) e = cudaMemcpy(dm_out, dbuf, 128 * 64 * sizeof(float), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(l_out, dbuf + 128 * 64, 128 * 64 * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(dbuf);
+  CK(e);
+  return B2R_OK;
+}
+
 b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const double* dst_dev, int n, const uint32_t* adj_dev,
                                     int pitch_words) {
   if (!s) return B2R_ERR_INVALID_ARG;

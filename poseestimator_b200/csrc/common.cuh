@@ -110,6 +110,7 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
 // graph_tc.cu (v5): prep (boxes, constants, 22-bit records) + tcgen05 filter; graph.cu: exact fix-up of the listed pairs and the
 // fp64 filter for problems the fp32 path may not decide
 int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+int launch_graph_tc_debug(const ProbDesc* d_desc, int prob, int bi, int v, float* out_dm, float* out_l, cudaStream_t st);
 int launch_graph_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
 constexpr int kAmbCap = 1 << 15;      // listed pairs per problem
 int launch_tim_graph_rows(const double* src, const double* dst, int n, int row_begin, int row_end, uint32_t* adj,

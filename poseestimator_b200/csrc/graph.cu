@@ -933,20 +933,32 @@ __global__ void __launch_bounds__(256) degree_kernel(const ProbDesc* __restrict_
   if (threadIdx.x < 8) s_key[threadIdx.x] = 0ull;
   if (threadIdx.x == 8) s_sum = 0ull;
   __syncthreads();
-  const int W = 4 * ((d.n + kTile - 1) / kTile);
+  const int W4 = (d.n + kTile - 1) / kTile;   // 16-byte groups per row
   unsigned long long wsum = 0;
-#pragma unroll 2
-  for (int k = 0; k < 8; ++k) {
-    const int v = v0 + warp * 8 + k;
-    if (v >= d.n) break;
-    const uint32_t* row = d.adj + (size_t)v * d.pitch;
-    int c = 0;
-    for (int w = lane; w < W; w += 32) c += __popc(row[w]);
-    c = __reduce_add_sync(0xffffffffu, c);
-    if (lane == 0) {
-      d.deg[v] = c;
-      wsum += (unsigned long long)c;
-      atomicMax(&s_key[v & 7], ((unsigned long long)c << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
+  // four rows in flight per warp (16-byte loads, all issued before the reductions): the kernel is a pure HBM / L2 stream
+#pragma unroll 1
+  for (int k0 = 0; k0 < 8; k0 += 4) {
+    int c[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int v = v0 + warp * 8 + k0 + r;
+      if (v < d.n) {
+        const uint4* row = reinterpret_cast<const uint4*>(d.adj + (size_t)v * d.pitch);
+        for (int w = lane; w < W4; w += 32) {
+          const uint4 q = row[w];
+          c[r] += __popc(q.x) + __popc(q.y) + __popc(q.z) + __popc(q.w);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int v = v0 + warp * 8 + k0 + r;
+      const int cr = __reduce_add_sync(0xffffffffu, c[r]);
+      if (lane == 0 && v < d.n) {
+        d.deg[v] = cr;
+        wsum += (unsigned long long)cr;
+        atomicMax(&s_key[v & 7], ((unsigned long long)cr << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
+      }
     }
   }
   if (lane == 0) atomicAdd(&s_sum, wsum);

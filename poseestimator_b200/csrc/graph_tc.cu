@@ -58,19 +58,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-// the single waiting lane of the producer warp backs off between polls: its spin loop otherwise takes a quarter of the
-// SM sub-partition's issue slots from the epilogue warps
-__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
-  uint32_t done = 0;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    if (done) break;
-    __nanosleep(100);
-  }
-}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -520,6 +507,90 @@ int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const Kern
   graph_tc_ops_kernel<<<dim3(T, batch), kTile, 0, st>>>(d_desc);
   tim_graph5_kernel<<<dim3(tc_items(T), batch), kTcThreads, kTcSmemBytes, st>>>(d_desc, kp);
   return 3 + launch_graph_fix(d_desc, batch, n_max, kp, st);
+}
+
+}  // namespace b2r
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Test hook (b2r_debug_tc_values): the raw Dm~ and L~ of one 128 x 64 unit, exactly as the filter kernel's tcgen05.mma
+// leaves them in TMEM, so that tests can measure the tensor-core error against the bound the band assumes.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace b2r {
+
+__global__ void __launch_bounds__(128, 1) graph_tc_debug_kernel(const ProbDesc* __restrict__ descs, int prob, int bi, int v, float* __restrict__ out_dm,
+                                                                  float* __restrict__ out_l) {
+  const ProbDesc d = descs[prob];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* sRowL = sm;
+  unsigned char* sRowD = sm + kTcRowBytes;
+  unsigned char* sCol = sm + 2 * kTcRowBytes;
+  unsigned char* sStage = sCol + kTcColBytes;
+  TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sStage + kTcRowBytes);
+  const int t = threadIdx.x, warp = t >> 5;
+  const unsigned char* ops = reinterpret_cast<const unsigned char*>(d.pts32);
+  const int i0 = bi * kTile;
+  const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
+  if (t == 0) {
+    mbar_init(&g->rowfull, 1);
+    mbar_init(&g->full[0], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(&g->rowfull, kTcRowBytes + kTcColBytes);
+    bulk_g2s(sStage, ops + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
+    bulk_g2s(sCol, ops + (size_t)j0 * 128, kTcColBytes, &g->rowfull);
+  }
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  mbar_wait(&g->rowfull, 0);
+  rows_from_col_row(sStage, sRowL, sRowD, t);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = g->tmem_base;
+  if (t == 0) {
+    constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
+    const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD), cb = smem_u32(sCol);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem, umma_desc_sw128(rowd) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + 64, umma_desc_sw128(rowl) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+    tc_commit(&g->full[0]);
+  }
+  mbar_wait(&g->full[0], 0);
+  tc_fence_after();
+#pragma unroll 1
+  for (int ch = 0; ch < 2; ++ch) {
+    uint32_t dm[32], lv[32];
+    const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)(ch * 32);
+    tc_ld_32x32(ta, dm);
+    tc_ld_32x32(ta + 64, lv);
+    tc_wait_ld();
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      out_dm[t * kTcUnit + ch * 32 + c] = __uint_as_float(dm[c]);
+      out_l[t * kTcUnit + ch * 32 + c] = __uint_as_float(lv[c]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+  }
+}
+
+int launch_graph_tc_debug(const ProbDesc* d_desc, int prob, int bi, int v, float* out_dm, float* out_l, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(graph_tc_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    attr_set = true;
+  }
+  graph_tc_debug_kernel<<<1, 128, 64 * 1024, st>>>(d_desc, prob, bi, v, out_dm, out_l);
+  return 1;
 }
 
 }  // namespace b2r

@@ -294,6 +294,16 @@ class RobustRegistrationSolver:
             self._cache["adj"] = out
         return self._cache["adj"]
 
+    def _tc_values(self, row_block: int, unit: int):
+        """Test hook: raw Dm~ / L~ (128 x 64 fp32 each) of one unit of the tensor-core graph filter and its constants."""
+        self._require()
+        dm = np.zeros((128, 64), np.float32)
+        lv = np.zeros((128, 64), np.float32)
+        c = np.zeros(12, np.float64)
+        _lib.check(self._h, _lib.lib().b2r_debug_tc_values(self._h, 0, row_block, unit, C.c_void_p(dm.ctypes.data), C.c_void_p(lv.ctypes.data),
+                                                            C.c_void_p(c.ctypes.data)))
+        return dm, lv, dict(kappa=c[0], ctr=c[1:7].copy(), t1=c[7], t0=c[8], lcut=c[9], k=c[10], use32=int(c[11]))
+
     def _adjacency_dense(self) -> np.ndarray:
         bits = self._adjacency_bits()
         return np.unpackbits(bits.view(np.uint8), axis=1, bitorder="little")[:, : self._n].astype(bool)

@@ -440,3 +440,71 @@ def test_batched_solution_getter_equals_per_problem_getter():
         one = bs.solution(i)
         assert np.array_equal(arr["rotation"][i], one.rotation) and np.array_equal(arr["translation"][i], one.translation)
         assert np.array_equal(s.rotation, one.rotation) and s.valid == one.valid and s.scale == one.scale
+
+
+def _tf32_rna(x32):
+    """cvt.rna.tf32.f32: round to 10 explicit mantissa bits, ties away from zero."""
+    b = x32.astype(np.float32).view(np.uint32).astype(np.uint64)
+    b = (b + 0x1000) & 0xFFFFE000
+    return b.astype(np.uint32).view(np.float32)
+
+
+@pytest.mark.parametrize("n,ratio,seed,blocks", [(1000, 0.5, 41, ((0, 0), (0, 5), (3, 2), (7, 0))), (5000, 0.95, 5000, ((0, 0), (5, 33), (39, 0)))])
+def test_tensor_core_values_within_assumed_error(n, ratio, seed, blocks):
+    """The band of the tensor-core filter ASSUMES |tcgen05 result - exact sum of products| <= 2^-20 * sum |products| and bounds the
+    total error of Dm~ / L~ by E_D / E_L (graph_tc.cu).  Measure both on the device."""
+    import teaserpp_python as tpp
+    pb = synth.make_problem(n, ratio, seed)
+    s = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound))
+    s.solve(pb.src, pb.dst)
+    worst_tc = worst_d = worst_l = 0.0
+    for bi, unit in blocks:
+        dm, lv, c = s._tc_values(bi, unit)
+        assert c["use32"] == 1
+        kappa, ctr = c["kappa"], c["ctr"]
+        i0 = 128 * bi
+        j0 = 128 * (bi + unit // 2) + 64 * (unit % 2)
+        ri = np.arange(i0, min(i0 + 128, n)); cj = np.arange(j0, min(j0 + 64, n))
+        # exact (fp64) scaled quantities
+        S = (pb.src - ctr[:3, None]) * kappa; D = (pb.dst - ctr[3:, None]) * kappa
+        A = ((S[:, ri, None] - S[:, None, cj]) ** 2).sum(0); B = ((D[:, ri, None] - D[:, None, cj]) ** 2).sum(0)
+        Dm, L = A - B, 1.0 - 2.0 * (A + B)
+        # the bounds the kernel uses
+        he = np.concatenate([np.max(np.abs(pb.src - ctr[:3, None]), 1), np.max(np.abs(pb.dst - ctr[3:, None]), 1)]) * kappa * (1 + 1e-6)
+        Pi = float((he ** 2).sum()); w = 2.0 ** -22
+        E_L, E_D = w * (71.8 * Pi + 4.3), 45.9 * w * Pi
+        worst_d = max(worst_d, float(np.abs(dm[: len(ri), : len(cj)] - Dm).max()) / E_D)
+        worst_l = max(worst_l, float(np.abs(lv[: len(ri), : len(cj)] - L).max()) / E_L)
+        # the tensor-core accumulation alone: operands as the device builds them (22-bit copies, 3xTF32 split), products summed in fp64
+        def split(X):
+            x32 = X.astype(np.float32); hi = _tf32_rna(x32); lo = _tf32_rna(x32 - hi)
+            v = (hi + lo).astype(np.float32); h2 = _tf32_rna(v)
+            return v.astype(np.float64), h2.astype(np.float64), (v - h2).astype(np.float64)
+        sv, sh, sl = split(S); dv, dh, dl = split(D)
+        rs, rd = (sv ** 2).sum(0), (dv ** 2).sum(0)
+        p = (0.5 - 2.0 * (rs + rd)).astype(np.float32).astype(np.float64); m = (rs - rd).astype(np.float32).astype(np.float64)
+        def tri(h1, l1, h2, l2):  # hi.hi + hi.lo + lo.hi summed over the three coordinates, and the sum of |products|
+            t = h1[:, ri, None] * h2[:, None, cj] + h1[:, ri, None] * l2[:, None, cj] + l1[:, ri, None] * h2[:, None, cj]
+            a = np.abs(h1[:, ri, None] * h2[:, None, cj]) + np.abs(h1[:, ri, None] * l2[:, None, cj]) + np.abs(l1[:, ri, None] * h2[:, None, cj])
+            return t.sum(0), a.sum(0)
+        ts, as_ = tri(sh, sl, sh, sl); td, ad = tri(dh, dl, dh, dl)
+        L_ops = p[ri, None] + p[None, cj] + 4 * ts + 4 * td
+        D_ops = m[ri, None] + m[None, cj] - 2 * ts + 2 * td
+        L_abs = np.abs(p[ri, None]) + np.abs(p[None, cj]) + 4 * as_ + 4 * ad
+        D_abs = np.abs(m[ri, None]) + np.abs(m[None, cj]) + 2 * as_ + 2 * ad
+        worst_tc = max(worst_tc, float((np.abs(lv[: len(ri), : len(cj)] - L_ops) / L_abs).max()), float((np.abs(dm[: len(ri), : len(cj)] - D_ops) / D_abs).max()))
+    print(f"tensor-core accumulation error / sum|products|: 2^{np.log2(max(worst_tc, 1e-30)):.2f} (assumed 2^-20); "
+          f"|Dm~-Dm| / E_D = {worst_d:.3f}, |L~-L| / E_L = {worst_l:.3f}")
+    assert worst_tc <= 2.0 ** -21, "tcgen05 accumulation error exceeds half of the assumed bound"
+    assert worst_d <= 0.5 and worst_l <= 0.5
+
+
+def test_tensor_core_filter_list_overflow_falls_back(oracle_mod):
+    """A band so wide that the ambiguous-pair list overflows: the problem is redone by the fp64 filter, bits unchanged."""
+    import teaserpp_python as tpp
+    pb = synth.make_problem(1500, 0.7, 43)
+    ref = oracle_mod.tim_graph(pb.src, pb.dst, pb.noise_bound)
+    s = tpp.RobustRegistrationSolver(_params(tpp, pb.noise_bound, graph_filter_tau=1e-2))
+    s.solve(pb.src, pb.dst)
+    assert np.array_equal(s._adjacency_bits(), ref)
+    assert s.stats()["graph_slow_pairs"] > 32768
