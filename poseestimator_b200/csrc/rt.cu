@@ -204,11 +204,15 @@ __device__ __forceinline__ bool ep_less(double va, int ia, double vb, int ib) {
   return abs(ia) < abs(ib);
 }
 
-__device__ void bitonic_sort(double* val, int* id, int Epad) {
+// The three axes of the translation vote run concurrently: thread group g = threadIdx.x / kRtThreads owns axis g and
+// synchronises on its own named barrier (1 + g); tid is the index inside the group.
+__device__ __forceinline__ void grp_sync(int bar) { asm volatile("bar.sync %0, %1;" ::"r"(bar), "n"(kRtThreads) : "memory"); }
+
+__device__ void bitonic_sort(double* val, int* id, int Epad, int tid, int bar) {
   for (int k = 2; k <= Epad; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      __syncthreads();
-      for (int i = threadIdx.x; i < Epad; i += blockDim.x) {
+      grp_sync(bar);
+      for (int i = tid; i < Epad; i += kRtThreads) {
         const int l = i ^ j;
         if (l > i) {
           const double vi = val[i], vl = val[l];
@@ -220,12 +224,41 @@ __device__ void bitonic_sort(double* val, int* id, int Epad) {
       }
     }
   }
-  __syncthreads();
+  grp_sync(bar);
 }
 
-// One TLS estimate over X[0..M) with a constant range r.  Returns the estimate in every thread.
-__device__ double tls_estimate_const_range(const double* X, int M, double r, double* val, int* id, double* sm /*6*kRtThreads+8*/) {
-  const int tid = threadIdx.x;
+// exclusive prefix over the group's kRtThreads per-thread partials of K quantities (warp shuffles + one pass over the warp
+// totals); sm: K * kRtWarps doubles
+template <int K>
+__device__ __forceinline__ void grp_exclusive_scan(double (&v)[K], double* sm, int tid, int bar) {
+  const int lane = tid & 31, warp = tid >> 5;
+  double inc[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double x = v[k];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const double y = __shfl_up_sync(FULL, x, o);
+      if (lane >= o) x += y;
+    }
+    inc[k] = x;
+  }
+  grp_sync(bar);
+  if (lane == 31)
+#pragma unroll
+    for (int k = 0; k < K; ++k) sm[k * kRtWarps + warp] = inc[k];
+  grp_sync(bar);
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double base = 0.0;
+    for (int w = 0; w < warp; ++w) base += sm[k * kRtWarps + w];
+    v[k] = base + (inc[k] - v[k]);
+  }
+  grp_sync(bar);
+}
+
+// One TLS estimate over X[0..M) with a constant range r.  Returns the estimate in every thread of the group.
+__device__ double tls_estimate_const_range(const double* X, int M, double r, double* val, int* id, double* sm /*3*kRtThreads*/, int tid, int bar) {
   const int E = 2 * M;
   int Epad = 2;
   while (Epad < E) Epad <<= 1;
@@ -236,30 +269,21 @@ __device__ double tls_estimate_const_range(const double* X, int M, double r, dou
       else { val[e] = X[i] - r; id[e] = i + 1; }
     } else { val[e] = CUDART_INF; id[e] = 0x7fffffff; }
   }
-  bitonic_sort(val, id, Epad);
+  bitonic_sort(val, id, Epad, tid, bar);
   const double w = 1.0 / (r * r);
   const int chunk = (E + kRtThreads - 1) / kRtThreads;
   const int e0 = min(tid * chunk, E), e1 = min(e0 + chunk, E);
-  double s_w = 0, s_xw = 0, s_r = 0, s_x = 0, s_xx = 0, s_c = 0;
+  double pre[6] = {0, 0, 0, 0, 0, 0};   // card, w, xw, r, x, xx
   for (int e = e0; e < e1; ++e) {
     const int idx = abs(id[e]) - 1;
     const double eps = id[e] > 0 ? 1.0 : -1.0;
     const double x = X[idx];
-    s_c += eps; s_w += eps * w; s_xw += eps * w * x; s_r += eps * r; s_x += eps * x; s_xx += eps * x * x;
+    pre[0] += eps; pre[1] += eps * w; pre[2] += eps * w * x; pre[3] += eps * r; pre[4] += eps * x; pre[5] += eps * x * x;
   }
-  __syncthreads();
-  sm[0 * kRtThreads + tid] = s_c; sm[1 * kRtThreads + tid] = s_w; sm[2 * kRtThreads + tid] = s_xw;
-  sm[3 * kRtThreads + tid] = s_r; sm[4 * kRtThreads + tid] = s_x; sm[5 * kRtThreads + tid] = s_xx;
-  __syncthreads();
-  if (tid < 6) {  // exclusive scan of one quantity per thread
-    double run = 0;
-    double* a = sm + tid * kRtThreads;
-    for (int i = 0; i < kRtThreads; ++i) { const double t = a[i]; a[i] = run; run += t; }
-  }
-  __syncthreads();
-  double card = sm[0 * kRtThreads + tid], dw = sm[1 * kRtThreads + tid], dxw = sm[2 * kRtThreads + tid];
-  double rsum = (double)M * r - sm[3 * kRtThreads + tid];
-  double sx = sm[4 * kRtThreads + tid], sxx = sm[5 * kRtThreads + tid];
+  grp_exclusive_scan<6>(pre, sm, tid, bar);
+  double card = pre[0], dw = pre[1], dxw = pre[2];
+  double rsum = (double)M * r - pre[3];
+  double sx = pre[4], sxx = pre[5];
   double best_cost = CUDART_INF, best_x = 0.0;
   int best_e = 0x7fffffff;
   for (int e = e0; e < e1; ++e) {
@@ -272,27 +296,31 @@ __device__ double tls_estimate_const_range(const double* X, int M, double r, dou
     if (cost < best_cost) { best_cost = cost; best_x = xh; best_e = e; }
   }
   // argmin over threads: lowest cost, ties -> lowest endpoint position (first minimum)
-  __syncthreads();
+  grp_sync(bar);
   sm[tid] = best_cost; sm[kRtThreads + tid] = best_x; sm[2 * kRtThreads + tid] = (double)best_e;
-  __syncthreads();
-  for (int s = kRtThreads / 2; s > 0; s >>= 1) {
-    if (tid < s) {
-      const double ca = sm[tid], cb = sm[tid + s];
-      const double ea = sm[2 * kRtThreads + tid], eb = sm[2 * kRtThreads + tid + s];
-      if (cb < ca || (cb == ca && eb < ea)) { sm[tid] = cb; sm[kRtThreads + tid] = sm[kRtThreads + tid + s]; sm[2 * kRtThreads + tid] = eb; }
+  grp_sync(bar);
+  for (int s2 = kRtThreads / 2; s2 > 0; s2 >>= 1) {
+    if (tid < s2) {
+      const double ca = sm[tid], cb = sm[tid + s2];
+      const double ea = sm[2 * kRtThreads + tid], eb = sm[2 * kRtThreads + tid + s2];
+      if (cb < ca || (cb == ca && eb < ea)) { sm[tid] = cb; sm[kRtThreads + tid] = sm[kRtThreads + tid + s2]; sm[2 * kRtThreads + tid] = eb; }
     }
-    __syncthreads();
+    grp_sync(bar);
   }
   const double est = (sm[2 * kRtThreads] < 2.0e9) ? sm[kRtThreads] : CUDART_NAN;
-  __syncthreads();
+  grp_sync(bar);
   return est;
 }
 
-__global__ void __launch_bounds__(kRtThreads) translation_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
-  extern __shared__ double shd[];  // [6*kRtThreads + 8] scan scratch, then optional endpoint staging
+constexpr int kTrEndpoints = 2048;                                        // endpoints per axis that fit in shared memory
+constexpr size_t kTrGroupDoubles = 3 * kRtThreads + kTrEndpoints + kTrEndpoints / 2;   // scratch + val + id (ints)
+
+__global__ void __launch_bounds__(3 * kRtThreads) translation_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  extern __shared__ double shd[];  // per axis group: [3*kRtThreads] scratch, [2048] endpoint values, [2048] endpoint ids
   const ProbDesc d = descs[blockIdx.x];
   ProbState* st = d.st;
-  const int tid = threadIdx.x;
+  const int gtid = threadIdx.x;
+  const int grp = gtid / kRtThreads, tid = gtid % kRtThreads;
   const int C = st->clique_size;
   if (C <= 1) return;
   const int M = st->n_rot_inl;
@@ -301,7 +329,7 @@ __global__ void __launch_bounds__(kRtThreads) translation_kernel(const ProbDesc*
 #pragma unroll
   for (int i = 0; i < 9; ++i) R[i] = st->R[i];
   double* raw = d.raw;  // 3 x M (row r at raw + r*M)
-  for (int i = tid; i < M; i += kRtThreads) {
+  for (int i = gtid; i < M; i += 3 * kRtThreads) {
     const int pt = d.clique[d.rot_inl[i] % C];  // upstream indexes max_clique_ by TIM position (A.8)
     const double x0 = d.src[3 * (size_t)pt], x1 = d.src[3 * (size_t)pt + 1], x2 = d.src[3 * (size_t)pt + 2];
 #pragma unroll
@@ -309,40 +337,43 @@ __global__ void __launch_bounds__(kRtThreads) translation_kernel(const ProbDesc*
       raw[(size_t)r * M + i] = d.dst[3 * (size_t)pt + r] - scale * ((R[3 * r] * x0 + R[3 * r + 1] * x1) + R[3 * r + 2] * x2);
     d.trans_mask[i] = 1;
   }
+  __shared__ double s_t[3];
+  __shared__ int sh_c;
+  if (gtid == 0) sh_c = 0;
   __syncthreads();
-  double t[3] = {0, 0, 0};
   if (M >= 2) {
     const double r = kp.noise_bound * sqrt(kp.cbar2);  // A.7-4: 1x, not 2x
     int Epad = 2;
     while (Epad < 2 * M) Epad <<= 1;
-    double* sm = shd;
-    double* val = d.tls_val; int* id = d.tls_id;
-    if (Epad <= 2048) {  // endpoints fit in shared memory (24 KB)
-      val = shd + 6 * kRtThreads + 8;
-      id = (int*)(val + 2048);
+    double* sm = shd + (size_t)grp * kTrGroupDoubles;
+    double* val = sm + 3 * kRtThreads;
+    int* id = (int*)(val + kTrEndpoints);
+    if (Epad <= kTrEndpoints) {
+      const double est = tls_estimate_const_range(raw + (size_t)grp * M, M, r, val, id, sm, tid, 1 + grp);
+      if (tid == 0) s_t[grp] = est;
+    } else if (grp == 0) {  // large cliques: endpoints in the global scratch (4 * tim_cap entries), one axis after the other
+      for (int ax = 0; ax < 3; ++ax) {
+        const double est = tls_estimate_const_range(raw + (size_t)ax * M, M, r, d.tls_val, d.tls_id, sm, tid, 1);
+        if (tid == 0) s_t[ax] = est;
+      }
     }
-    for (int ax = 0; ax < 3; ++ax) {
-      const double* X = raw + (size_t)ax * M;
-      const double est = tls_estimate_const_range(X, M, r, val, id, sm);
-      t[ax] = est;
-      for (int i = tid; i < M; i += kRtThreads)
-        if (!(fabs(X[i] - est) <= r)) d.trans_mask[i] = 0;
-      __syncthreads();
+    __syncthreads();
+    for (int i = gtid; i < M; i += 3 * kRtThreads) {
+      const bool in = (fabs(raw[i] - s_t[0]) <= r) && (fabs(raw[(size_t)M + i] - s_t[1]) <= r) && (fabs(raw[2 * (size_t)M + i] - s_t[2]) <= r);
+      if (!in) d.trans_mask[i] = 0;
     }
   } else if (M == 1) {
-    t[0] = raw[0]; t[1] = raw[1]; t[2] = raw[2];
+    if (gtid < 3) s_t[gtid] = raw[gtid];
   }
+  __syncthreads();
   // count translation inliers
-  __shared__ int sh_c;
-  if (tid == 0) sh_c = 0;
-  __syncthreads();
   int c = 0;
-  for (int i = tid; i < M; i += kRtThreads) c += d.trans_mask[i];
+  for (int i = gtid; i < M; i += 3 * kRtThreads) c += d.trans_mask[i];
   c = __reduce_add_sync(FULL, c);
-  if ((tid & 31) == 0) atomicAdd(&sh_c, c);
+  if ((gtid & 31) == 0) atomicAdd(&sh_c, c);
   __syncthreads();
-  if (tid == 0) {
-    st->t[0] = t[0]; st->t[1] = t[1]; st->t[2] = t[2];
+  if (gtid == 0) {
+    st->t[0] = s_t[0]; st->t[1] = s_t[1]; st->t[2] = s_t[2];
     st->n_trans_inl = sh_c;
     st->valid = 1;
   }
@@ -351,11 +382,11 @@ __global__ void __launch_bounds__(kRtThreads) translation_kernel(const ProbDesc*
 int launch_rotation_translation(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st,
                                 cudaEvent_t* ev) {
   static bool attr = false;
-  const size_t tsmem = (6 * kRtThreads + 8) * sizeof(double) + 2048 * (sizeof(double) + sizeof(int));
+  const size_t tsmem = 3 * kTrGroupDoubles * sizeof(double);
   if (!attr) { cudaFuncSetAttribute(translation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem); attr = true; }
   rotation_kernel<<<batch, kRtThreads, 0, st>>>(d_desc, kp);
   if (ev) cudaEventRecord(ev[0], st);
-  translation_kernel<<<batch, kRtThreads, tsmem, st>>>(d_desc, kp);
+  translation_kernel<<<batch, 3 * kRtThreads, tsmem, st>>>(d_desc, kp);
   (void)n_max;
   return 2;
 }
