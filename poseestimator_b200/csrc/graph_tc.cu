@@ -360,6 +360,12 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     mbar_expect_tx(&g->rowfull, kTcRowBytes);
     bulk_g2s(sStage, ops_col + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
+    for (int u = 0; u < 3 && u < nu; ++u) {  // the first column units start travelling before the set-up barrier
+      const int v = v0 + u;
+      const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
+      mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
+      bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
+    }
   }
   __syncthreads();
   if (warp == kTcEpiWarps) {
@@ -387,7 +393,6 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
         mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
         bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
       };
-      for (int u = 0; u < 3 && u < nu; ++u) copy_unit(u);
       for (int u = 0; u < nu; ++u) {
         const int s = u & 1;
         mbar_wait(&g->colfull[u & 3], (u >> 2) & 1);
