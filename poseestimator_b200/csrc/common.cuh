@@ -51,6 +51,8 @@ struct ProbState {
   double kappa;          // 1 / beta: the 22-bit copies are (x - ctr) * kappa
   unsigned int amb_count;   // pairs appended to ProbDesc::amb_list (may exceed amb_cap: then tc_overflow is set)
   int tc_overflow;       // 1: the list overflowed -> the whole problem is redone by the fp64 filter
+  int deg_ready;         // 1: deg[] was accumulated by the tensor-core filter and its fix-up (degree_kernel skips the popcount)
+  int pad3_;
 };
 
 // Per-problem pointers (device copies of host-built descriptors).

@@ -824,10 +824,17 @@ __global__ void __launch_bounds__(kTile) graph_fix_kernel(const ProbDesc* __rest
       const double B = sq3_ref(__dsub_rn(d.dst[3 * j], d.dst[3 * i]), __dsub_rn(d.dst[3 * j + 1], d.dst[3 * i + 1]), __dsub_rn(d.dst[3 * j + 2], d.dst[3 * i + 2]));
       uint32_t* wij = d.adj + i * d.pitch + (j >> 5);
       uint32_t* wji = d.adj + j * d.pitch + (i >> 5);
-      if (verdict_exact(A, B, kp.beta)) { atomicOr(wij, 1u << (j & 31)); atomicOr(wji, 1u << (i & 31)); }
-      else { atomicAnd(wij, ~(1u << (j & 31))); atomicAnd(wji, ~(1u << (i & 31))); }
+      // the filter kernel counted the placeholder bits into the degrees: every bit that actually flips corrects its row's degree
+      const uint32_t bj_ = 1u << (j & 31), bi_ = 1u << (i & 31);
+      if (verdict_exact(A, B, kp.beta)) {
+        if (!(atomicOr(wij, bj_) & bj_)) atomicAdd(&d.deg[i], 1);
+        if (!(atomicOr(wji, bi_) & bi_)) atomicAdd(&d.deg[j], 1);
+      } else {
+        if (atomicAnd(wij, ~bj_) & bj_) atomicSub(&d.deg[i], 1);
+        if (atomicAnd(wji, ~bi_) & bi_) atomicSub(&d.deg[j], 1);
+      }
     }
-    if (blockIdx.x == 0 && t == 0) st->slow_pairs = cnt;
+    if (blockIdx.x == 0 && t == 0) { st->slow_pairs = cnt; st->deg_ready = 1; }
     return;
   }
   const int T = (n + kTile - 1) / kTile;
@@ -935,6 +942,19 @@ __global__ void __launch_bounds__(256) degree_kernel(const ProbDesc* __restrict_
   __syncthreads();
   const int W4 = (d.n + kTile - 1) / kTile;   // 16-byte groups per row
   unsigned long long wsum = 0;
+  if (d.st->deg_ready) {
+    // the tensor-core filter already left the degrees in deg[] (popcounts of the words it wrote, corrected by the fix-up):
+    // only the per-problem maxima and the seed keys remain
+    if (threadIdx.x < kDegRowsPerBlock) {
+      const int v = v0 + threadIdx.x;
+      if (v < d.n) {
+        const int cr = d.deg[v];
+        wsum = (unsigned long long)cr;
+        atomicMax(&s_key[v & 7], ((unsigned long long)cr << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
+      }
+    }
+    wsum = __reduce_add_sync(0xffffffffu, (unsigned)wsum);
+  } else {
   // four rows in flight per warp (16-byte loads, all issued before the reductions): the kernel is a pure HBM / L2 stream
 #pragma unroll 1
   for (int k0 = 0; k0 < 8; k0 += 4) {
@@ -960,6 +980,7 @@ __global__ void __launch_bounds__(256) degree_kernel(const ProbDesc* __restrict_
         atomicMax(&s_key[v & 7], ((unsigned long long)cr << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
       }
     }
+  }
   }
   if (lane == 0) atomicAdd(&s_sum, wsum);
   __syncthreads();

@@ -302,6 +302,7 @@ __global__ void __launch_bounds__(kTile) graph_tc_ops_kernel(const ProbDesc* __r
   if (i >= n_pad) return;
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
   if (i < n) {
+    d.deg[i] = 0;   // the filter kernel accumulates the vertex degrees (popcounts of the words it writes)
     const double kappa = st->kappa;
     float v[6];
     double r[2] = {0.0, 0.0};
@@ -419,6 +420,7 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
     const float lcut = d.st->tcc[2];
     const uint32_t lcut_bits = __float_as_uint(lcut);   // lcut < 0:  L > lcut  <=>  bits(L) < bits(lcut) as unsigned
     const bool rows_in = i0 + kTile <= n;
+    int rowdeg = 0;
     for (int u = 0; u < nu; ++u) {
       const int s = u & 1;
       const int v = v0 + u;
@@ -488,10 +490,15 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
       }
       if (bj != bi) {  // transposed block: lane c receives the 32 row bits of column jc + c
         const uint32_t tw = warp_transpose32(word, lane);
-        if (jc + lane < n) d.adj[(size_t)(jc + lane) * d.pitch + (i0 >> 5) + q] = tw;
+        if (jc + lane < n) {
+          d.adj[(size_t)(jc + lane) * d.pitch + (i0 >> 5) + q] = tw;
+          if (tw) atomicAdd(&d.deg[jc + lane], __popc(tw));
+        }
       }
       if (i < n) d.adj[(size_t)i * d.pitch + (jc >> 5)] = word;
+      rowdeg += __popc(word);
     }
+    if (i < n && rowdeg) atomicAdd(&d.deg[i], rowdeg);
   }
   tc_fence_before();
   __syncthreads();
