@@ -268,9 +268,12 @@ __device__ __forceinline__ void rows_from_col_row(const unsigned char* stage, un
   store_row(tile_d, r, v);
 }
 
+constexpr int kTcAmbBuf = 64;   // ambiguous pairs a warp collects in shared memory before it touches the global list
 struct TcSmemCtl {
   uint64_t rowfull, colfull[4], full[2], empty[2];
   uint32_t tmem_base;
+  int amb_cnt[8];
+  uint32_t amb_buf[8][kTcAmbBuf];
 };
 
 constexpr int kTcRowBytes = kTcRowTile * 128;   // 16 KB
@@ -358,6 +361,7 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
     mbar_init(&g->rowfull, 1);
     for (int s = 0; s < 4; ++s) mbar_init(&g->colfull[s], 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&g->full[s], 1); mbar_init(&g->empty[s], kTcEpiWarps); }
+    for (int w = 0; w < kTcEpiWarps; ++w) g->amb_cnt[w] = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     mbar_expect_tx(&g->rowfull, kTcRowBytes);
     bulk_g2s(sStage, ops_col + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
@@ -477,14 +481,18 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
           aw |= (!(fabsf(G) >= Tb) | (lv[c] < lcut_bits)) ? (1u << c) : 0u;
         }
         aw &= mask;
-        if (aw) {
-          unsigned base = atomicAdd(&d.st->amb_count, (unsigned)__popc(aw));
-          while (aw) {
-            const int c = __ffs(aw) - 1;
-            aw &= aw - 1;
-            if (base < (unsigned)d.amb_cap) d.amb_list[base] = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+        // into the warp's shared-memory buffer (flushed once per item): a global atomic with its L2 round trip here would make
+        // this warp lag a whole unit behind the others, and they share the TMEM stages
+        while (aw) {
+          const int c = __ffs(aw) - 1;
+          aw &= aw - 1;
+          const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+          const int pos = atomicAdd(&g->amb_cnt[warp], 1);
+          if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
+          else {  // buffer full (wide test bands): straight to the global list
+            const unsigned base = atomicAdd(&d.st->amb_count, 1u);
+            if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
             else d.st->tc_overflow = 1;
-            ++base;
           }
         }
       }
@@ -499,6 +507,17 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
       rowdeg += __popc(word);
     }
     if (i < n && rowdeg) atomicAdd(&d.deg[i], rowdeg);
+    __syncwarp();
+    const int cnt = min(g->amb_cnt[warp], kTcAmbBuf);
+    if (cnt > 0) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&d.st->amb_count, (unsigned)cnt);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      for (int k = lane; k < cnt; k += 32) {
+        if (base + k < (unsigned)d.amb_cap) d.amb_list[base + k] = g->amb_buf[warp][k];
+        else d.st->tc_overflow = 1;
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
