@@ -204,6 +204,11 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
   if (prof) CK(cudaEventRecord(s->ev[1], st));
   if (!skip_graph) s->launches += launch_tim_graph(dd, batch, n_max, s->kp, st);
   if (prof) CK(cudaEventRecord(s->ev[2], st));
+  if (s->stream_hi) {  // the tail continues on the high-priority stream
+    CK(cudaEventRecord(s->ev_graph, st));
+    st = s->stream_hi;
+    CK(cudaStreamWaitEvent(st, s->ev_graph, 0));
+  }
   s->launches += launch_degree(dd, batch, n_max, st);
   if (prof) CK(cudaEventRecord(s->ev[3], st));
   s->launches += launch_clique(dd, batch, n_max, s->kp, (uint32_t*)s->d_arena.p, s->arena_words_per_warp, s->bnb_blocks, st,
@@ -211,6 +216,10 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
   s->launches += launch_rotation_translation(dd, batch, n_max, s->kp, st, prof ? &s->ev[8] : nullptr);
   if (prof) CK(cudaEventRecord(s->ev[9], st));
   CK(cudaMemcpyAsync(s->h_state.p, s->d_state.p, (size_t)batch * sizeof(ProbState), cudaMemcpyDeviceToHost, st));
+  if (s->stream_hi) {  // the handle's stream (what callers synchronise on) waits for the tail
+    CK(cudaEventRecord(s->ev_tail, st));
+    CK(cudaStreamWaitEvent(s->stream, s->ev_tail, 0));
+  }
   CK(cudaGetLastError());
   s->pending = true;
   s->have_result = false;
@@ -268,7 +277,22 @@ b2r_status b2r_create(const b2r_params* params, int device, void* stream, b2r_so
   else {
     if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { delete s; return B2R_ERR_CUDA; }
     s->own_stream = true;
+
   }
+  {
+  int lo = 0, hi = 0;
+  const char* nohi = getenv("B2R_NO_HI_STREAM");
+  if (!(nohi && nohi[0] == '1') && cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess && hi < lo) {
+    if (cudaStreamCreateWithPriority(&s->stream_hi, cudaStreamNonBlocking, hi) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_graph, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_tail, cudaEventDisableTiming) != cudaSuccess) {
+      cudaGetLastError();
+      if (s->stream_hi) cudaStreamDestroy(s->stream_hi);
+      s->stream_hi = nullptr;
+    }
+  }
+  }
+
   s->params = *params;
   fill_kernel_params(s);
   *out = s;
@@ -283,6 +307,7 @@ b2r_status b2r_destroy(b2r_solver* s) {
   s->d_pts32.release(); s->d_amb.release(); s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release(); s->d_refine.release(); s->h_refine.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
   if (s->ev_ready) for (int i = 0; i < 12; ++i) cudaEventDestroy(s->ev[i]);
+  if (s->stream_hi) { cudaStreamDestroy(s->stream_hi); if (s->ev_graph) cudaEventDestroy(s->ev_graph); if (s->ev_tail) cudaEventDestroy(s->ev_tail); }
   if (s->own_stream) cudaStreamDestroy(s->stream);
   delete s;
   return B2R_OK;

@@ -40,6 +40,10 @@ struct b2r_solver {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
+  // latency-bound tail of a batch (degrees, clique, rotation, translation: 64 small CTAs per kernel) on a HIGH-priority stream, so that
+  // with several handles in flight it is not starved by another handle's graph kernel, which fills every SM
+  cudaStream_t stream_hi = nullptr;
+  cudaEvent_t ev_graph = nullptr, ev_tail = nullptr;
   b2r_params params;
   b2r::KernelParams kp;
   std::string err;
