@@ -135,7 +135,7 @@ b2r_status ensure_workspace(b2r_solver* s, int batch, int n_max) {
   CK(s->d_adj.ensure(B * nc * pc * sizeof(uint32_t)));
   CK(s->d_cadj.ensure(B * nc * pc * sizeof(uint32_t)));
   CK(s->d_pts32.ensure(B * (size_t)(pc * 32) * 128));   // tensor-core filter: one 128-byte operand row per point, pc * 32 = n_cap rounded up to the tile edge
-  CK(s->d_amb.ensure(B * (size_t)kAmbCap * sizeof(uint32_t)));
+  CK(s->d_amb.ensure(B * amb_cap_for(nc) * sizeof(uint32_t)));
   // ints per problem: deg, ids, clique (n each) + rot_inl (tim) + tls_id (4*tim)
   CK(s->d_int.ensure(B * (3 * (size_t)nc + 5 * (size_t)tc) * sizeof(int)));
   // doubles per problem: weights (tim), timx, timy, raw (3*tim each), tls_val (4*tim)
@@ -170,8 +170,8 @@ void build_desc(b2r_solver* s, int b, int n, const double* dsrc, const double* d
   d.rot_mask = ub; d.trans_mask = ub + tc;
   d.st = (ProbState*)s->d_state.p + b;
   d.pts32 = (float4*)((unsigned char*)s->d_pts32.p + (size_t)b * pc * 32 * 128);
-  d.amb_list = (uint32_t*)s->d_amb.p + (size_t)b * kAmbCap;
-  d.amb_cap = kAmbCap;
+  d.amb_list = (uint32_t*)s->d_amb.p + (size_t)b * amb_cap_for(nc);
+  d.amb_cap = (int)amb_cap_for(nc);
   d.pad2_ = 0;
   d.n = n;
   d.pitch = ext_adj ? ext_pitch : (int)pc;

@@ -114,7 +114,8 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
 int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
 int launch_graph_tc_debug(const ProbDesc* d_desc, int prob, int bi, int v, float* out_dm, float* out_l, cudaStream_t st);
 int launch_graph_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
-constexpr int kAmbCap = 1 << 15;      // listed pairs per problem
+// listed pairs per problem: about 1.4e-4 of the pairs are ambiguous at config 3; room for eight times that, at least 32768
+inline size_t amb_cap_for(size_t n_cap) { const size_t c = n_cap * n_cap / 1024; return c < ((size_t)1 << 15) ? ((size_t)1 << 15) : c; }
 int launch_tim_graph_rows(const double* src, const double* dst, int n, int row_begin, int row_end, uint32_t* adj,
                           int pitch, const KernelParams& kp, unsigned long long* slow_pairs, cudaStream_t st);
 int launch_degree(const ProbDesc* d_desc, int batch, int n_max, cudaStream_t st);

@@ -508,3 +508,22 @@ def test_tensor_core_filter_list_overflow_falls_back(oracle_mod):
     s.solve(pb.src, pb.dst)
     assert np.array_equal(s._adjacency_bits(), ref)
     assert s.stats()["graph_slow_pairs"] > 32768
+
+
+@pytest.mark.parametrize("n", [2, 3, 63, 64, 65, 127, 128, 129, 191, 192, 193, 257, 640, 1153])
+def test_tensor_core_filter_tile_edges_and_fused_degrees(oracle_mod, n):
+    """Sizes around the 64-column unit and 128-row tile edges: bits equal the oracle's, and the degrees the filter kernel
+    accumulates on the fly (corrected by the fix-up of the listed pairs) equal the popcounts of the final rows."""
+    import teaserpp_python as tpp
+    rng = np.random.default_rng(1000 + n)
+    src = rng.uniform(-1, 1, (3, n))
+    dst = synth.random_rotation(rng) @ src + rng.uniform(-1, 1, (3, 1)) + rng.normal(0, 0.01, (3, n))
+    k = n // 2
+    dst[:, :k] = rng.uniform(-2, 2, (3, k))
+    nb = 0.05
+    ref = oracle_mod.tim_graph(src, dst, nb)
+    s = tpp.RobustRegistrationSolver(_params(tpp, nb, inlier_selection_mode=tpp.RobustRegistrationSolver.INLIER_SELECTION_MODE.NONE))
+    s.solve(src, dst)
+    bits = s._adjacency_bits()
+    assert np.array_equal(bits, ref)
+    assert s.stats()["n_edges"] == int(np.unpackbits(ref.view(np.uint8)).sum()) // 2
