@@ -375,6 +375,10 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
     };
     unsigned nthr = std::thread::hardware_concurrency();
     if (nthr > 8) nthr = 8;
+    if (const char* pt = getenv("B2R_PACK_THREADS")) {  // several ranks on one host: cores / ranks, not 8 each
+      const int v = atoi(pt);
+      if (v >= 1 && v <= 64) nthr = (unsigned)v;
+    }
     if ((unsigned)batch < nthr) nthr = (unsigned)batch;
     if (total * sizeof(double) * 2 < (1u << 20) || nthr <= 1) pack(0, batch);
     else {
