@@ -29,6 +29,7 @@
 #ifndef B2R_H_
 #define B2R_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -130,12 +131,22 @@ b2r_status b2r_solve(b2r_solver* s, const double* src, const double* dst, int n,
                      int64_t row_stride, int64_t col_stride, int on_device);
 
 /* Batch of independent registrations (detections / templates / frames).  Each operand is packed 3 x n[b]
- * column-major.  _async only enqueues on the handle's stream (inputs must stay valid until b2r_sync). */
+ * column-major.  _async only enqueues on the handle's stream (inputs must stay valid until b2r_sync).
+ * on_device: 0 = ordinary host memory (copied through the handle's page-locked staging block), 1 = device pointers,
+ * 2 = page-locked host memory (cudaHostAlloc / cudaHostRegister / b2r_alloc_pinned): the copy engine reads the
+ * caller's buffers directly, operands adjacent in memory are merged into one copy. */
 b2r_status b2r_solve_batch(b2r_solver* s, int batch, const int* n, const double* const* src,
                            const double* const* dst, int on_device);
 b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const double* const* src,
                                  const double* const* dst, int on_device);
 b2r_status b2r_sync(b2r_solver* s);
+/* page-locked host memory for on_device == 2 callers that do not link the CUDA runtime themselves */
+b2r_status b2r_alloc_pinned(size_t bytes, void** out);
+b2r_status b2r_free_pinned(void* p);
+/* Fill page-locked memory with streaming stores (no CUDA call).  On the B200 hosts the copy engine reads lines that
+ * are still dirty in CPU caches 4x slower than lines in DRAM (profiles/r01_h2d_pack.jsonl): producers that write
+ * their correspondences into a pinned block should do it through this (or their own non-temporal stores). */
+b2r_status b2r_copy_to_pinned(void* dst, const void* src, size_t bytes);
 int b2r_batch_size(const b2r_solver* s);
 /* number of kernels this handle has launched since creation (bench.py's gpu_launches claim) */
 int64_t b2r_launch_count(const b2r_solver* s);

@@ -58,7 +58,7 @@ class B2RStats(C.Structure):
 # every symbol include/b2r.h declares (tests check the library exports all of them)
 EXPORTS = [
     "b2r_default_params", "b2r_version", "b2r_device_count", "b2r_create", "b2r_destroy", "b2r_reset", "b2r_last_error",
-    "b2r_solve", "b2r_solve_batch", "b2r_solve_batch_async", "b2r_sync", "b2r_batch_size", "b2r_launch_count",
+    "b2r_solve", "b2r_solve_batch", "b2r_solve_batch_async", "b2r_sync", "b2r_alloc_pinned", "b2r_free_pinned", "b2r_copy_to_pinned", "b2r_batch_size", "b2r_launch_count",
     "b2r_get_solution", "b2r_get_solutions", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
     "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words", "b2r_debug_tc_values",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
@@ -102,6 +102,9 @@ def lib():
     L.b2r_solve_batch.argtypes = [vp, i32, vp, vp, vp, i32]
     L.b2r_solve_batch_async.argtypes = [vp, i32, vp, vp, vp, i32]
     L.b2r_sync.argtypes = [vp]
+    L.b2r_alloc_pinned.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    L.b2r_free_pinned.argtypes = [C.c_void_p]
+    L.b2r_copy_to_pinned.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
     L.b2r_batch_size.argtypes = [vp]
     L.b2r_launch_count.argtypes = [vp]
     L.b2r_launch_count.restype = i64

@@ -26,6 +26,52 @@ def _pack(a) -> np.ndarray:
     return np.ascontiguousarray(a.T)
 
 
+class PinnedBuffer:
+    """Page-locked host memory from b2r_alloc_pinned, viewed as numpy arrays (for BatchSolver.solve_pinned_async)."""
+
+    def __init__(self, nbytes: int):
+        self._p = C.c_void_p()
+        st = _lib.lib().b2r_alloc_pinned(int(nbytes), C.byref(self._p))
+        if st != 0 or not self._p.value:
+            raise MemoryError(f"poseestimator_b200: b2r_alloc_pinned({nbytes}) failed ({_lib.STATUS_NAMES.get(st, st)})")
+        self.nbytes = int(nbytes)
+        self._raw = (C.c_char * self.nbytes).from_address(self._p.value)
+        self._raw._owner = self  # views reach the block through their .base chain; the memory lives as long as any view
+
+    def array(self, shape, dtype=np.float64, offset: int = 0) -> np.ndarray:
+        """A numpy view of the block (keeps the block alive through its .base chain)."""
+        count = int(np.prod(shape))
+        a = np.frombuffer(self._raw, dtype=dtype, count=count, offset=offset).reshape(shape)
+        return a
+
+    @staticmethod
+    def fill(dst: np.ndarray, src: np.ndarray) -> None:
+        """dst[...] = src with streaming stores (b2r_copy_to_pinned): the lines end up in DRAM, where the copy engine reads
+        them at full rate, instead of dirty in the CPU caches."""
+        src = np.ascontiguousarray(src, dtype=dst.dtype)
+        if not dst.flags.c_contiguous or dst.nbytes != src.nbytes:
+            raise ValueError("fill needs a C-contiguous destination of the source's size")
+        st = _lib.lib().b2r_copy_to_pinned(C.c_void_p(dst.ctypes.data), C.c_void_p(src.ctypes.data), src.nbytes)
+        if st != 0:
+            raise RuntimeError("b2r_copy_to_pinned failed")
+
+    def __del__(self):
+        p = getattr(self, "_p", None)
+        if p is not None and p.value:
+            try:
+                _lib.lib().b2r_free_pinned(p)
+            except Exception:  # noqa: BLE001
+                pass
+            self._p = C.c_void_p()
+
+
+def pinned_problem_block(batch: int, n: int):
+    """(src, dst): two page-locked (batch, n, 3) float64 arrays, each contiguous, so that a whole batch uploads in two copies."""
+    nb = batch * n * 3 * 8
+    buf = PinnedBuffer(2 * nb)
+    return buf.array((batch, n, 3)), buf.array((batch, n, 3), offset=nb)
+
+
 class BatchSolver:
     """Many registrations per call through b2r_solve_batch (one handle = one device + one stream)."""
 
@@ -69,6 +115,17 @@ class BatchSolver:
         self._keep = (packed, n, sp, dp)
         self._batch = B
         _lib.check(self._h, _lib.lib().b2r_solve_batch_async(self._h, B, n, sp, dp, 0))
+
+    def solve_pinned_async(self, packed):
+        """Like solve_packed_async for arrays that live in page-locked memory (PinnedBuffer, torch pin_memory, ...): no
+        staging pass on the host, the copy engine reads them directly; they must stay untouched until sync()."""
+        B = len(packed)
+        n = (C.c_int * B)(*[p[0].shape[0] for p in packed])
+        sp = (C.c_void_p * B)(*[p[0].ctypes.data for p in packed])
+        dp = (C.c_void_p * B)(*[p[1].ctypes.data for p in packed])
+        self._keep = (packed, n, sp, dp)
+        self._batch = B
+        _lib.check(self._h, _lib.lib().b2r_solve_batch_async(self._h, B, n, sp, dp, 2))
 
     # ---- device inputs (zero copy) ----------------------------------------------------------------------
     def solve_device_async(self, n_list, src_ptrs, dst_ptrs, keep_alive=None):

@@ -347,12 +347,37 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
     return fail(s, B2R_ERR_LIMIT, "estimate_scaling=True: the 2P-endpoint vote for this N needs more than 96 GB of workspace");
   b2r_status r = ensure_workspace(s, batch, n_max);
   if (r != B2R_OK) return r;
-  if (s->profiling) { r = ensure_events(s); if (r != B2R_OK) return r; if (on_device) CK(cudaEventRecord(s->ev[0], s->stream)); }
+  if (s->profiling) { r = ensure_events(s); if (r != B2R_OK) return r; if (on_device == 1) CK(cudaEventRecord(s->ev[0], s->stream)); }
   s->batch = batch;
   s->n.assign(n, n + batch);
   s->ext_adj = nullptr;
-  if (on_device) {
+  if (on_device < 0 || on_device > 2) return fail(s, B2R_ERR_INVALID_ARG, "on_device must be 0 (host), 1 (device) or 2 (page-locked host)");
+  if (on_device == 1) {
     for (int b = 0; b < batch; ++b) build_desc(s, b, n[b], src[b], dst[b], nullptr, 0);
+  } else if (on_device == 2) {
+    // page-locked host operands: the copy engine reads the caller's memory directly (no staging pass over the input on the
+    // host); operands that follow each other in memory go in one copy
+    double* ds = (double*)s->d_pts.p;
+    double* dd = ds + total;
+    std::vector<size_t> offs((size_t)batch + 1);
+    size_t off = 0;
+    for (int b = 0; b < batch; ++b) {
+      offs[b] = off;
+      build_desc(s, b, n[b], ds + off, dd + off, nullptr, 0);
+      off += (size_t)3 * n[b];
+    }
+    offs[batch] = off;
+    if (s->profiling) CK(cudaEventRecord(s->ev[0], s->stream));
+    for (int op = 0; op < 2; ++op) {
+      const double* const* hp = op ? dst : src;
+      double* dbase = op ? dd : ds;
+      for (int b0 = 0; b0 < batch;) {
+        int b1 = b0 + 1;
+        while (b1 < batch && hp[b1] == hp[b1 - 1] + (size_t)3 * n[b1 - 1]) ++b1;
+        CK(cudaMemcpyAsync(dbase + offs[b0], hp[b0], sizeof(double) * (offs[b1] - offs[b0]), cudaMemcpyHostToDevice, s->stream));
+        b0 = b1;
+      }
+    }
   } else {
     // pack all problems into one pinned staging block -> one H2D copy per operand
     double* hs = (double*)s->h_pts.p;
@@ -391,6 +416,21 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
     CK(cudaMemcpyAsync(ds, hs, sizeof(double) * 2 * total, cudaMemcpyHostToDevice, s->stream));
   }
   return enqueue_pipeline(s, batch, n_max, false);
+}
+
+b2r_status b2r_alloc_pinned(size_t bytes, void** out) {
+  if (!out || bytes == 0) return B2R_ERR_INVALID_ARG;
+  *out = nullptr;
+  return cudaHostAlloc(out, bytes, cudaHostAllocPortable) == cudaSuccess ? B2R_OK : B2R_ERR_CUDA;
+}
+b2r_status b2r_copy_to_pinned(void* dst, const void* src, size_t bytes) {
+  if ((!dst || !src) && bytes) return B2R_ERR_INVALID_ARG;
+  nt_memcpy(dst, src, bytes);
+  return B2R_OK;
+}
+b2r_status b2r_free_pinned(void* p) {
+  if (!p) return B2R_OK;
+  return cudaFreeHost(p) == cudaSuccess ? B2R_OK : B2R_ERR_CUDA;
 }
 
 b2r_status b2r_sync(b2r_solver* s) {
@@ -435,7 +475,7 @@ b2r_status b2r_solve(b2r_solver* s, const double* src, const double* dst, int n,
   if (n > kMaxN) return fail(s, B2R_ERR_LIMIT, "N > 65535 correspondences is not supported");
   const bool packed = (row_stride == 1 && col_stride == 3);
   if (packed) return b2r_solve_batch(s, 1, &n, &src, &dst, on_device);
-  if (!on_device) {
+  if (on_device != 1) {
     std::vector<double> a((size_t)3 * n), b((size_t)3 * n);
     for (int c = 0; c < n; ++c)
       for (int r = 0; r < 3; ++r) {

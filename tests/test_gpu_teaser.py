@@ -442,6 +442,54 @@ def test_batched_solution_getter_equals_per_problem_getter():
         assert np.array_equal(s.rotation, one.rotation) and s.valid == one.valid and s.scale == one.scale
 
 
+def _same_solutions(a, b):
+    return len(a) == len(b) and all(
+        np.ascontiguousarray(a[f]).tobytes() == np.ascontiguousarray(b[f]).tobytes() for f in ("scale", "rotation", "translation", "valid"))
+
+
+def test_page_locked_inputs_equal_staged_inputs():
+    """on_device == 2 (the copy engine reads the caller's page-locked arrays): one merged copy per operand for a contiguous
+    block, one copy per problem for scattered arrays, mixed sizes, and the strided single-solve entry; same bits as staging."""
+    from poseestimator_b200 import batch as b2batch
+    import teaserpp_python as tpp
+    B, n = 6, 300
+    pbs = [synth.make_problem(n, 0.6, 70 + i) for i in range(B)]
+    nb = pbs[0].noise_bound
+    bs = b2batch.BatchSolver(_params(tpp, nb))
+    packed = [(np.ascontiguousarray(p.src.T), np.ascontiguousarray(p.dst.T)) for p in pbs]
+    bs.solve_packed_async(packed); bs.sync()
+    want = bs.solutions_array().copy()
+    # contiguous block
+    ps, pd = b2batch.pinned_problem_block(B, n)
+    for i, (a, b) in enumerate(packed):
+        ps[i] = a; pd[i] = b
+    bs.solve_pinned_async([(ps[i], pd[i]) for i in range(B)]); bs.sync()
+    got = bs.solutions_array()
+    assert _same_solutions(got, want) and bool(got["valid"].all())
+    # scattered: reversed order inside the block, so no two operands are adjacent in the upload order
+    bs.solve_pinned_async([(ps[i], pd[i]) for i in reversed(range(B))]); bs.sync()
+    got = bs.solutions_array()
+    assert _same_solutions(got[::-1], want)
+    # mixed sizes carved from one buffer
+    sizes = [50, 333, 128, 2]
+    mp = [synth.make_problem(max(m, 8), 0.3, 90 + i) for i, m in enumerate(sizes)]
+    mixed = [(np.ascontiguousarray(p.src.T[:m]), np.ascontiguousarray(p.dst.T[:m])) for p, m in zip(mp, sizes)]
+    bs2 = b2batch.BatchSolver(_params(tpp, mp[0].noise_bound))
+    bs2.solve_packed_async(mixed); bs2.sync()
+    want2 = bs2.solutions_array().copy()
+    buf = b2batch.PinnedBuffer(2 * 24 * sum(sizes))
+    off = 0
+    pinned = []
+    for a, b in mixed:
+        va = buf.array(a.shape, offset=off); off += a.nbytes
+        vb = buf.array(b.shape, offset=off); off += b.nbytes
+        b2batch.PinnedBuffer.fill(va, a); vb[...] = b
+        pinned.append((va, vb))
+    bs2.solve_pinned_async(pinned); bs2.sync()
+    assert _same_solutions(bs2.solutions_array(), want2)
+    del pinned, buf
+
+
 def _tf32_rna(x32):
     """cvt.rna.tf32.f32: round to 10 explicit mantissa bits, ties away from zero."""
     b = x32.astype(np.float32).view(np.uint32).astype(np.uint64)
