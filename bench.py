@@ -254,7 +254,7 @@ def main():
     # kernel of the next batch; the serial pass above exists for the per-stage times.  Every step reads one of NSETS device copies
     # of the inputs in turn (NSETS x 15.4 MB > 126 MB of L2) and writes 205 MB of adjacency, so nothing survives in L2 from the
     # previous use of the same data.  Timed on the device: one start event, one end event per stream, the longest span counts.
-    NPIPE, NSETS = 3, 10
+    NPIPE, NSETS = int(os.environ.get("B2R_BENCH_NPIPE", "3")), 10
     sets = [(sp, dp)]
     keep = []
     for _ in range(NSETS - 1):

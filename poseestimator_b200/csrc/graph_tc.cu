@@ -278,7 +278,7 @@ struct TcSmemCtl {
 
 constexpr int kTcRowBytes = kTcRowTile * 128;   // 16 KB
 constexpr int kTcColBytes = kTcUnit * 128;      // 8 KB
-constexpr int kTcSmemBytes = 100 * 1024;        // 2 x 16 KB + 4 x 8 KB + control + 16 KB staging; asks for 100 KB so that exactly two CTAs share an SM (TMEM: 2 x 256 columns)
+constexpr int kTcSmemBytes = 83 * 1024;         // 2 x 16 KB + 4 x 8 KB + 1 KB control + 16 KB staging + alignment slack; two CTAs per SM by registers (2 x 288 x 96) and TMEM (2 x 256 columns)
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
