@@ -220,7 +220,12 @@ __global__ void __launch_bounds__(256) heuristic_kernel(const ProbDesc* __restri
 // warps with 4 independent row loads in flight per warp, so a round costs a few L2 round trips instead of |P| of them.
 // grid = (seeds per problem, batch); seed k = highest-degree vertex of id class k (degree_kernel).
 constexpr int kHeuThreads = 1024;
-constexpr int kHeuSeeds = 4;   // of the 8 id classes; the bound only has to be good, the exact search proves it
+// Seeds of the 8 id classes that get a CTA.  The bound only has to be good, the exact search proves it; every seed CTA (1024 threads)
+// takes the place of one resident graph CTA of another batch in flight: 4 seeds 100.2k reg/s, 2 seeds 102.6k, 1 seed 104.2k (config 3).
+#ifndef B2R_HEU_SEEDS
+#define B2R_HEU_SEEDS 2
+#endif
+constexpr int kHeuSeeds = B2R_HEU_SEEDS;
 __global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const ProbDesc* __restrict__ descs) {
   extern __shared__ uint32_t sh[];
   const ProbDesc d = descs[blockIdx.y];
