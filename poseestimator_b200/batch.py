@@ -72,6 +72,25 @@ def pinned_problem_block(batch: int, n: int):
     return buf.array((batch, n, 3)), buf.array((batch, n, 3), offset=nb)
 
 
+class HostBatch:
+    """Pointer tables (n, src, dst) of a batch of packed (N,3) float64 operands in host memory, built ONCE: a caller that rewrites
+    the same arrays every frame (a page-locked block, typically) submits with BatchSolver.solve_host_batch_async and pays no
+    per-step Python cost for the 2 x B pointers.  page_locked=True: the arrays live in page-locked memory (on_device = 2)."""
+
+    def __init__(self, packed, page_locked: bool = False):
+        B = len(packed)
+        for a, b in packed:
+            if a.dtype != np.float64 or b.dtype != np.float64 or not a.flags.c_contiguous or not b.flags.c_contiguous \
+                    or a.ndim != 2 or a.shape[1] != 3 or a.shape != b.shape:
+                raise TypeError("HostBatch needs C-contiguous (N, 3) float64 pairs of equal shape")
+        self.batch = B
+        self.n = (C.c_int * B)(*[p[0].shape[0] for p in packed])
+        self.sp = (C.c_void_p * B)(*[p[0].ctypes.data for p in packed])
+        self.dp = (C.c_void_p * B)(*[p[1].ctypes.data for p in packed])
+        self.mode = 2 if page_locked else 0
+        self._keep = packed
+
+
 class BatchSolver:
     """Many registrations per call through b2r_solve_batch (one handle = one device + one stream)."""
 
@@ -126,6 +145,12 @@ class BatchSolver:
         self._keep = (packed, n, sp, dp)
         self._batch = B
         _lib.check(self._h, _lib.lib().b2r_solve_batch_async(self._h, B, n, sp, dp, 2))
+
+    def solve_host_batch_async(self, hb: "HostBatch"):
+        """Submit a prepared HostBatch (pointer tables built once; the arrays' current contents are what gets uploaded)."""
+        self._keep = hb
+        self._batch = hb.batch
+        _lib.check(self._h, _lib.lib().b2r_solve_batch_async(self._h, hb.batch, hb.n, hb.sp, hb.dp, hb.mode))
 
     # ---- device inputs (zero copy) ----------------------------------------------------------------------
     def solve_device_async(self, n_list, src_ptrs, dst_ptrs, keep_alive=None):

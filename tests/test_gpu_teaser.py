@@ -466,6 +466,13 @@ def test_page_locked_inputs_equal_staged_inputs():
     bs.solve_pinned_async([(ps[i], pd[i]) for i in range(B)]); bs.sync()
     got = bs.solutions_array()
     assert _same_solutions(got, want) and bool(got["valid"].all())
+    hb = b2batch.HostBatch([(ps[i], pd[i]) for i in range(B)], page_locked=True)   # pointer tables built once, arrays rewritten in place
+    ps[...] = ps[::-1].copy(); pd[...] = pd[::-1].copy()
+    bs.solve_host_batch_async(hb); bs.sync()
+    assert _same_solutions(bs.solutions_array()[::-1], want)
+    ps[...] = ps[::-1].copy(); pd[...] = pd[::-1].copy()
+    bs.solve_host_batch_async(b2batch.HostBatch(packed)); bs.sync()
+    assert _same_solutions(bs.solutions_array(), want)
     # scattered: reversed order inside the block, so no two operands are adjacent in the upload order
     bs.solve_pinned_async([(ps[i], pd[i]) for i in reversed(range(B))]); bs.sync()
     got = bs.solutions_array()
