@@ -5,6 +5,7 @@
 D=gpurun_out/$1
 mkdir -p $D
 timeout 900 python -m pytest tests -m gpu -x -q > $D/pytest_gpu.log 2>&1; tail -2 $D/pytest_gpu.log
+timeout 300 python -c 'import __graft_entry__ as g; g.smoke(); print("smoke ok")' > $D/smoke.log 2>&1; tail -1 $D/smoke.log
 timeout 600 python bench.py > $D/bench.json 2> $D/bench.err || tail -5 $D/bench.err
 timeout 600 python bench.py --impl reference > $D/bench_ref.json 2> $D/bench_ref.err || tail -5 $D/bench_ref.err
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/bench_short.json 2> $D/bench_short.err && \
