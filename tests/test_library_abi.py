@@ -50,3 +50,34 @@ def test_product_never_imports_the_oracle():
     for f in os.listdir(os.path.join(ROOT, "teaserpp_python")):
         if f.endswith(".py"):
             assert "oracle" not in open(os.path.join(ROOT, "teaserpp_python", f)).read()
+
+
+def test_header_is_plain_c_and_struct_layouts_match_the_binding(tmp_path):
+    """include/b2r.h compiles as C99 and as C++ with nothing but the standard headers, a C program links against libb2r.so, and
+    the ctypes mirrors in _lib.py have the sizes the C compiler gives the structs (the stub INTEGRATION.md shows relies on it)."""
+    import ctypes as C
+    import subprocess
+    src = tmp_path / "abi.c"
+    src.write_text(
+        '#include "b2r.h"\n#include <stdio.h>\n'
+        "int main(void) {\n"
+        '  printf("%zu %zu %zu %zu %zu %d\\n", sizeof(b2r_params), sizeof(b2r_solution), sizeof(b2r_stats), sizeof(b2r_camera),\n'
+        "         sizeof(b2r_icp_result), b2r_version());\n"
+        "  b2r_params p; b2r_default_params(&p);\n"
+        '  printf("%.17g %.17g %d\\n", p.noise_bound, p.cbar2, (int)p.estimate_scaling);\n'
+        "  return 0;\n}\n")
+    inc = os.path.join(ROOT, "include")
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    exe = tmp_path / "abi"
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", inc, str(src), "-o", str(exe), "-L", libdir, "-lb2r",
+                    f"-Wl,-rpath,{libdir}"], check=True, capture_output=True)
+    subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-x", "c++", "-I", inc, str(src)], check=True, capture_output=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    sizes = [int(x) for x in out[:5]]
+    assert sizes == [C.sizeof(_lib.B2RParams), C.sizeof(_lib.B2RSolution), C.sizeof(_lib.B2RStats), C.sizeof(_lib.B2RCamera),
+                     C.sizeof(_lib.B2RIcpResult)]
+    assert int(out[5]) == _lib.lib().b2r_version()
+    assert C.sizeof(_lib.B2RSolution) == _lib.SOLUTION_DTYPE.itemsize
+    p = _lib.B2RParams()
+    _lib.lib().b2r_default_params(C.byref(p))
+    assert float(out[6]) == p.noise_bound and float(out[7]) == p.cbar2 and int(out[8]) == p.estimate_scaling
