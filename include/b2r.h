@@ -24,7 +24,9 @@
  *   - a handle is bound to one CUDA device and one stream; thread-compatible per handle,
  *     thread-safe across handles;
  *   - point sets are 3xN float64, column-major (x,y,z of point i at 3*i..3*i+2) unless strides are given;
- *   - there is NO CPU fallback: every entry point fails with B2R_ERR_CUDA when no device is usable.
+ *   - there is NO CPU fallback: every entry point fails with B2R_ERR_CUDA when no device is usable;
+ *   - on_device = 1 pointers must live on the handle's device (the library cannot check a raw pointer's device cheaply;
+ *     the Python host raises TypeError for tensors of another device).
  */
 #ifndef B2R_H_
 #define B2R_H_
@@ -36,7 +38,7 @@
 extern "C" {
 #endif
 
-#define B2R_VERSION 100 /* 0.1.0 */
+#define B2R_VERSION 200 /* 0.2.0 */
 
 typedef struct b2r_solver b2r_solver; /* opaque */
 
@@ -71,10 +73,8 @@ typedef struct b2r_params {
   /* --- extensions (0 = default behaviour) --- */
   double rotation_noise_bound;       /* GNC noise bound before the 2/scale factor; <=0 -> noise_bound.
                                         Lets the host mirror upstream's in-place compounding (A.6-2). */
-  int32_t graph_exact_only;          /* 0: default (packed-fp32 sqrt-free filter, exact fp64 fallback); 1: always evaluate both
-                                        fp64 square roots; 2 / 3: the older fp64 filters v2 / v1; 4: the packed-fp32 filter v3 (A/B measurements, tests) */
-  double graph_filter_tau;           /* lower limit of the filter's ambiguity band relative to Sigma^2 (tests widen the band to
-                                        force the exact path); <= 0: the band the error analysis needs */
+  int32_t reserved0;                 /* must be 0 (test hooks live in b2r_debug.h: b2r_debug_set_graph_filter) */
+  double reserved1;                  /* must be 0 */
 } b2r_params;
 
 typedef struct b2r_solution {
@@ -101,6 +101,9 @@ typedef struct b2r_stats {
   int64_t graph_slow_pairs;  /* pairs the sqrt-free filter sent to the exact fp64 path */
   int32_t exact_proven;      /* 1 unless the time limit stopped the exact search */
   int32_t flags;             /* internal error bits, 0 when ok */
+  int32_t fused_tail;        /* 1: everything after the graph ran in the fused tail kernel; 0: multi-kernel path (other inlier
+                                modes, or handed over: exact search needed / graph redone in fp64) */
+  int32_t pad_;
 } b2r_stats;
 
 typedef enum b2r_index_kind {
@@ -164,7 +167,9 @@ b2r_status b2r_get_adjacency(b2r_solver* s, int idx, uint32_t* out, int words_pe
 b2r_status b2r_get_gnc_weights(b2r_solver* s, int idx, double* out);
 /* per-stage device times of the last batch in ms (needs b2r_set_profiling(s,1)):
  * [0] upload [1] graph [2] degree [3] heuristic [4] prune+compact [5] exact search [6] canonical clique
- * [7] rotation [8] translation [9] total [10] scale vote (estimate_scaling=True only) [11] reserved */
+ * [7] rotation [8] translation [9] total [10] scale vote (estimate_scaling=True only)
+ * [11] fused tail: on the default PMC_EXACT path everything after the graph is ONE kernel (exact fix-up of the listed pairs,
+ *      degrees, greedy bound, core pruning, rotation, translation); [2] .. [8] are then 0 */
 b2r_status b2r_set_profiling(b2r_solver* s, int on);
 b2r_status b2r_get_timings(b2r_solver* s, float* ms12);
 
@@ -176,11 +181,6 @@ b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* ds
 /* Continue a solve from a complete device adjacency (after the all-gather of row shards). */
 b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const double* dst_dev, int n,
                                     const uint32_t* adj_dev, int pitch_words);
-/* Test hook of the tensor-core graph filter: after a solve on this handle, recompute the raw fp32 values Dm~ and L~ (DESIGN.md
- * "graph filter v5") of rows [128 row_block, +128) x the 64 columns of unit `unit` of that row block for problem idx, as the
- * tcgen05.mma leaves them in TMEM.  dm_out / l_out: host, 128 x 64 floats row-major.  consts_out (host, 12 doubles): kappa,
- * centres (6), t1, t0, lcut, k, use32. */
-b2r_status b2r_debug_tc_values(b2r_solver* s, int idx, int row_block, int unit, float* dm_out, float* l_out, double* consts_out);
 /* words per adjacency row the library uses for n vertices (multiple of 4) */
 int b2r_pitch_words(int n);
 

@@ -1,0 +1,41 @@
+/*
+ * b2r_debug.h -- test hooks and A/B knobs of libb2r.so.  NOT part of the drop-in boundary (include/b2r.h): nothing a caller of the
+ * reference's teaserpp_python path needs is declared here.  tests/ and tools/ use these to force the fallback paths of the
+ * consistency-graph filters and to measure the tensor-core arithmetic the exactness argument relies on.
+ */
+#ifndef B2R_DEBUG_H_
+#define B2R_DEBUG_H_
+
+#include "b2r.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Graph filter generation and band of this handle (takes effect at the next solve):
+ *   filter 0: default (tcgen05 filter v6, exact fp64 fix-up of the listed pairs); 1: always evaluate both fp64 square roots;
+ *          2 / 3: the fp64 sign-test filters v2 / v1; 4 / 5: the packed-fp32 filters v3 / v4 (A/B measurements, parity tests);
+ *   tau:   lower limit of the filter's ambiguity band relative to Sigma^2 (tests widen the band to force the exact path);
+ *          <= 0: the band the error analysis needs. */
+b2r_status b2r_debug_set_graph_filter(b2r_solver* s, int filter, double tau);
+
+/* After a solve on this handle: recompute the raw fp32 values Dm~ and L~ (DESIGN.md "graph filter v5") of rows
+ * [128 row_block, +128) x the 64 columns of unit `unit` of that row block for problem idx, as the tcgen05.mma leaves them in TMEM.
+ * dm_out / l_out: host, 128 x 64 floats row-major.  consts_out (host, 12 doubles): kappa, centres (6), t1, t0, lcut, k, use32. */
+b2r_status b2r_debug_tc_values(b2r_solver* s, int idx, int row_block, int unit, float* dm_out, float* l_out, double* consts_out);
+
+/* After a solve: EVERY 128 x 64 unit of problem idx is recomputed on the tensor cores and compared on the device with (a) the
+ * exact fp64 sum of the same operand products and (b) the fp64 value from the unrounded coordinates.  out8 (host):
+ *   [0] max |tc - sum of products| / sum |products|  over Dm~ and L~   (the band assumes <= 2^-20)
+ *   [1] max |Dm~ - Dm| / E_D      [2] max |L~ - L| / E_L               (the band assumes <= 1)
+ *   [3] pairs checked             [4] Pi   [5] E_D   [6] E_L   [7] 1 if the tensor-core filter decided this problem, else 0 */
+b2r_status b2r_debug_tc_sweep(b2r_solver* s, int idx, double* out8);
+
+/* SM cycles the fused tail kernel spent on problem idx of the last batch up to the end of each stage:
+ * [0] fix-up of listed pairs [1] degrees [2] greedy bound [3] core pruning [4] clique [5] rotation [6] translation [7] 0 */
+b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2R_DEBUG_H_ */

@@ -237,3 +237,12 @@ def gnc_tls(X, Y, noise_bound, factor=1.4, max_iter=100, thr=1e-6):
 
 def num_threads() -> int:
     return lib().orc_num_threads()
+
+
+def set_num_threads(n: int) -> int:
+    """OpenMP threads of the oracle (torchrun sets OMP_NUM_THREADS=1 for its ranks); returns the count now in force."""
+    L = lib()
+    L.orc_set_num_threads.restype = None
+    L.orc_set_num_threads.argtypes = [C.c_int]
+    L.orc_set_num_threads(int(n))
+    return L.orc_num_threads()

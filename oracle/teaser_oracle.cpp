@@ -835,5 +835,7 @@ void orc_tim_graph(const double* src, const double* dst, int n, double noise_bou
   }
 }
 int orc_num_threads() { return omp_get_max_threads(); }
+// torchrun exports OMP_NUM_THREADS=1 to every rank: the timed CPU arm sets its own thread count (bench.py)
+void orc_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 }  // extern "C"

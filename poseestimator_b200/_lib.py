@@ -23,8 +23,8 @@ class B2RParams(C.Structure):
         ("max_clique_time_limit", C.c_double),
         ("max_clique_num_threads", C.c_int32),
         ("rotation_noise_bound", C.c_double),
-        ("graph_exact_only", C.c_int32),
-        ("graph_filter_tau", C.c_double),
+        ("reserved0", C.c_int32),
+        ("reserved1", C.c_double),
     ]
 
 
@@ -48,7 +48,7 @@ class B2RStats(C.Structure):
         ("n_pruned", C.c_int32), ("omega", C.c_int32), ("clique_size", C.c_int32), ("n_rot_tims", C.c_int32),
         ("n_rot_inliers", C.c_int32), ("n_trans_inliers", C.c_int32), ("gnc_iterations", C.c_int32),
         ("gnc_cost", C.c_double), ("bnb_nodes", C.c_int64), ("graph_slow_pairs", C.c_int64),
-        ("exact_proven", C.c_int32), ("flags", C.c_int32),
+        ("exact_proven", C.c_int32), ("flags", C.c_int32), ("fused_tail", C.c_int32), ("pad_", C.c_int32),
     ]
 
     def as_dict(self):
@@ -60,12 +60,15 @@ EXPORTS = [
     "b2r_default_params", "b2r_version", "b2r_device_count", "b2r_create", "b2r_destroy", "b2r_reset", "b2r_last_error",
     "b2r_solve", "b2r_solve_batch", "b2r_solve_batch_async", "b2r_sync", "b2r_alloc_pinned", "b2r_free_pinned", "b2r_copy_to_pinned", "b2r_batch_size", "b2r_launch_count",
     "b2r_get_solution", "b2r_get_solutions", "b2r_get_stats", "b2r_get_indices", "b2r_get_adjacency", "b2r_get_gnc_weights",
-    "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words", "b2r_debug_tc_values",
+    "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
     "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
     "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align", "b2r_render_depth", "b2r_backproject_depth32", "b2r_project_select", "b2r_farthest_point_sample",
 ]
+
+# include/b2r_debug.h: test hooks, not part of the drop-in boundary
+DEBUG_EXPORTS = ["b2r_debug_set_graph_filter", "b2r_debug_tc_values", "b2r_debug_tc_sweep", "b2r_debug_tail_cycles"]
 
 # numpy view of an array of b2r_solution (112 bytes each)
 import numpy as _np  # noqa: E402
@@ -119,6 +122,9 @@ def lib():
     L.b2r_graph_rows.argtypes = [vp, vp, vp, i32, i32, i32, vp, i32]
     L.b2r_solve_from_adjacency.argtypes = [vp, vp, vp, i32, vp, i32]
     L.b2r_debug_tc_values.argtypes = [vp, i32, i32, i32, vp, vp, vp]
+    L.b2r_debug_set_graph_filter.argtypes = [vp, i32, C.c_double]
+    L.b2r_debug_tc_sweep.argtypes = [vp, i32, vp]
+    L.b2r_debug_tail_cycles.argtypes = [vp, i32, vp]
     L.b2r_pitch_words.argtypes = [i32]
     L.b2r_pitch_words.restype = i32
     d, ip = C.c_double, C.POINTER(C.c_int)

@@ -104,6 +104,7 @@ class BatchSolver:
         st = L.b2r_create(C.byref(cp), int(device), C.c_void_p(int(stream) if stream else None), C.byref(self._h))
         if st != 0:
             raise RuntimeError(f"poseestimator_b200: b2r_create failed ({_lib.STATUS_NAMES.get(st, st)})")
+        self._params._apply_debug(self._h)
         if profiling:
             L.b2r_set_profiling(self._h, 1)
         self.device = int(device)
@@ -154,7 +155,13 @@ class BatchSolver:
 
     # ---- device inputs (zero copy) ----------------------------------------------------------------------
     def solve_device_async(self, n_list, src_ptrs, dst_ptrs, keep_alive=None):
-        """Device pointers to packed 3xN column-major float64 operands (e.g. torch tensors' data_ptr())."""
+        """Device pointers to packed 3xN column-major float64 operands (e.g. torch tensors' data_ptr()) ON THIS HANDLE'S DEVICE;
+        pass the tensors as keep_alive and their device is checked (raw pointers cannot be)."""
+        if keep_alive is not None:
+            for t in (keep_alive if isinstance(keep_alive, (tuple, list)) else (keep_alive,)):
+                dev = getattr(t, "device", None)
+                if dev is not None and getattr(dev, "type", "") == "cuda" and dev.index is not None and dev.index != self.device:
+                    raise TypeError(f"tensor lives on {dev} but this solver is bound to cuda:{self.device}")
         B = len(n_list)
         n = (C.c_int * B)(*[int(x) for x in n_list])
         sp = (C.c_void_p * B)(*[int(x) for x in src_ptrs])
@@ -219,11 +226,25 @@ class BatchSolver:
         t = (C.c_float * 12)()
         _lib.check(self._h, _lib.lib().b2r_get_timings(self._h, t))
         names = ("upload", "graph", "degree", "heuristic", "prune_compact", "exact_search", "canonical", "rotation",
-                 "translation", "total", "scale_vote")
+                 "translation", "total", "scale_vote", "tail_fused")
         return dict(zip(names, [float(x) for x in t]))
 
     def launch_count(self) -> int:
         return int(_lib.lib().b2r_launch_count(self._h))
+
+    def tail_cycles(self, i: int) -> dict:
+        """Test hook (b2r_debug.h): SM cycles of the fused tail kernel at the end of each of its stages, problem i."""
+        out = (C.c_uint32 * 8)()
+        _lib.check(self._h, _lib.lib().b2r_debug_tail_cycles(self._h, int(i), out))
+        names = ("fix", "degrees", "heuristic", "prune", "clique", "rotation", "translation")
+        return dict(zip(names, [int(x) for x in out]))
+
+    def tc_sweep(self, i: int) -> dict:
+        """Test hook (b2r_debug.h): every unit of problem i recomputed on the tensor cores and compared with fp64 on the device."""
+        out = (C.c_double * 8)()
+        _lib.check(self._h, _lib.lib().b2r_debug_tc_sweep(self._h, int(i), out))
+        names = ("tc_accum_ratio", "dm_over_ED", "l_over_EL", "pairs", "Pi", "E_D", "E_L", "use32")
+        return dict(zip(names, [float(x) for x in out]))
 
     # ---- row-sharded large problem (config 5) -----------------------------------------------------------
     def graph_rows(self, src_ptr, dst_ptr, n, row_begin, row_end, out_ptr, pitch_words):

@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "../../include/b2r_debug.h"
 
 using namespace b2r;
 
@@ -63,7 +64,7 @@ void fill_kernel_params(b2r_solver* s) {
     k.e_beta2 = (int)((bits >> 52) & 0x7ff);
     // default band: |F| < 2^-24..2^-28 of Sigma^2; graph_filter_tau widens it (tests force the exact path with it)
     int shift = 0;
-    if (p.graph_filter_tau > 0) { shift = (int)ceil(log2(p.graph_filter_tau) + 28.0); if (shift < 0) shift = 0; if (shift > 64) shift = 64; }
+    if (p.reserved1 > 0) { shift = (int)ceil(log2(p.reserved1) + 28.0); if (shift < 0) shift = 0; if (shift > 64) shift = 64; }
     k.filter_shift = shift;
   }
   k.noise_bound = p.noise_bound; k.cbar2 = p.cbar2;
@@ -76,12 +77,12 @@ void fill_kernel_params(b2r_solver* s) {
   k.kcore_threshold = p.kcore_heuristic_threshold;
   const double lim = p.max_clique_time_limit;
   k.time_limit_ns = (lim > 0 && lim < 1e9) ? (unsigned long long)(lim * 1e9) : 0ull;
-  k.exact_only = p.graph_exact_only == 1;
-  k.filter_tau_min = p.graph_filter_tau > 0 ? p.graph_filter_tau : 0.0;
+  k.exact_only = p.reserved0 == 1;
+  k.filter_tau_min = p.reserved1 > 0 ? p.reserved1 : 0.0;
   {
-    // filter generation: params.graph_exact_only = 3 / 2 / 4 or B2R_GRAPH_V = 1 / 2 / 3 select the older filters v1 / v2 (fp64) / v3 (A/B runs, tests)
+    // filter generation: b2r_debug_set_graph_filter(3 / 2 / 4 / 5) or B2R_GRAPH_V = 1 / 2 / 3 / 4 select the older filters v1 / v2 (fp64) / v3 / v4 (A/B runs, tests)
     const char* gv = getenv("B2R_GRAPH_V");
-    const int v = p.graph_exact_only == 3 ? 1 : p.graph_exact_only == 2 ? 2 : p.graph_exact_only == 4 ? 3 : p.graph_exact_only == 5 ? 4
+    const int v = p.reserved0 == 3 ? 1 : p.reserved0 == 2 ? 2 : p.reserved0 == 4 ? 3 : p.reserved0 == 5 ? 4
                   : (gv && gv[0] >= '1' && gv[0] <= '5') ? gv[0] - '0' : 5;
     k.graph_v1 = v == 1;
     k.graph_v2 = v == 2;
@@ -110,6 +111,7 @@ b2r_status check_params(b2r_solver* s, const b2r_params* p) {
     return fail(s, B2R_ERR_INVALID_ARG, "only GNC_TLS rotation estimation is implemented (FGR is not on the reference's path)");
   if (p->inlier_selection_mode < 0 || p->inlier_selection_mode > 3) return fail(s, B2R_ERR_INVALID_ARG, "bad inlier_selection_mode");
   if (p->rotation_tim_graph < 0 || p->rotation_tim_graph > 1) return fail(s, B2R_ERR_INVALID_ARG, "bad rotation_tim_graph");
+  if (p->reserved0 != 0 || p->reserved1 != 0) return fail(s, B2R_ERR_INVALID_ARG, "reserved fields of b2r_params must be 0");
   return B2R_OK;
 }
 
@@ -131,27 +133,46 @@ b2r_status ensure_workspace(b2r_solver* s, int batch, int n_max) {
   (void)pitch;
   CK(cudaStreamSynchronize(s->stream));
   const size_t B = (size_t)bc;
-  CK(s->d_pts.ensure(B * 6 * nc * sizeof(double)));
-  CK(s->d_adj.ensure(B * nc * pc * sizeof(uint32_t)));
-  CK(s->d_cadj.ensure(B * nc * pc * sizeof(uint32_t)));
-  CK(s->d_pts32.ensure(B * (size_t)(pc * 32) * 128));   // tensor-core filter: one 128-byte operand row per point, pc * 32 = n_cap rounded up to the tile edge
-  CK(s->d_amb.ensure(B * amb_cap_for(nc) * sizeof(uint32_t)));
-  // ints per problem: deg, ids, clique (n each) + rot_inl (tim) + tls_id (4*tim)
-  CK(s->d_int.ensure(B * (3 * (size_t)nc + 5 * (size_t)tc) * sizeof(int)));
-  // doubles per problem: weights (tim), timx, timy, raw (3*tim each), tls_val (4*tim)
-  CK(s->d_dbl.ensure(B * (14 * (size_t)tc) * sizeof(double)));
-  CK(s->d_u8.ensure(B * 2 * (size_t)tc));
-  CK(s->d_state.ensure(B * sizeof(ProbState)));
-  CK(s->d_desc.ensure(B * sizeof(ProbDesc)));
-  CK(s->h_state.ensure(B * sizeof(ProbState)));
-  CK(s->h_desc.ensure(B * sizeof(ProbDesc)));
-  CK(s->h_pts.ensure(B * 6 * nc * sizeof(double)));
   s->bnb_blocks = (int)(296 / B);
   if (s->bnb_blocks < 1) s->bnb_blocks = 1;
   if (s->bnb_blocks > 37) s->bnb_blocks = 37;
   const char* ak = getenv("B2R_ARENA_KB");
   if (ak && atoi(ak) > 0) s->arena_words_per_warp = (size_t)atoi(ak) * 256;
-  CK(s->d_arena.ensure(B * s->bnb_blocks * kBnbWarpsPerBlock * s->arena_words_per_warp * sizeof(uint32_t)));
+  // Not failure-atomic buffer by buffer (DevBuf::ensure frees before it allocates), so a failure anywhere drops the WHOLE
+  // workspace and its recorded capacity: the next call re-allocates from scratch instead of trusting half-grown buffers.
+  auto grow = [&]() -> cudaError_t {
+    cudaError_t e;
+#define B2R_TRY(x) if ((e = (x)) != cudaSuccess) return e
+    B2R_TRY(s->d_pts.ensure(B * 6 * nc * sizeof(double)));
+    B2R_TRY(s->d_adj.ensure(B * nc * pc * sizeof(uint32_t)));
+    B2R_TRY(s->d_cadj.ensure(B * nc * pc * sizeof(uint32_t)));
+    B2R_TRY(s->d_pts32.ensure(B * (size_t)(pc * 32) * 128));   // tensor-core filter: one 128-byte operand row per point, pc * 32 = n_cap rounded up to the tile edge
+    B2R_TRY(s->d_amb.ensure(B * amb_cap_for(nc) * sizeof(uint32_t)));
+    // ints per problem: deg, ids, clique (n each) + rot_inl (tim) + tls_id (4*tim)
+    B2R_TRY(s->d_int.ensure(B * (3 * (size_t)nc + 5 * (size_t)tc) * sizeof(int)));
+    // doubles per problem: weights (tim), timx, timy, raw (3*tim each), tls_val (4*tim)
+    B2R_TRY(s->d_dbl.ensure(B * (14 * (size_t)tc) * sizeof(double)));
+    B2R_TRY(s->d_u8.ensure(B * 2 * (size_t)tc));
+    B2R_TRY(s->d_state.ensure(B * sizeof(ProbState)));
+    B2R_TRY(s->d_desc.ensure(B * sizeof(ProbDesc)));
+    B2R_TRY(s->h_state.ensure(B * sizeof(ProbState)));
+    B2R_TRY(s->h_desc.ensure(B * sizeof(ProbDesc)));
+    B2R_TRY(s->h_pts.ensure(B * 6 * nc * sizeof(double)));
+    B2R_TRY(s->d_arena.ensure(B * s->bnb_blocks * kBnbWarpsPerBlock * s->arena_words_per_warp * sizeof(uint32_t)));
+#undef B2R_TRY
+    return cudaSuccess;
+  };
+  const cudaError_t ge = grow();
+  if (ge != cudaSuccess) {
+    cudaGetLastError();   // the failed cudaMalloc must not surface in a later cudaGetLastError()
+    s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_pts32.release(); s->d_amb.release(); s->d_int.release();
+    s->d_dbl.release(); s->d_u8.release(); s->d_state.release(); s->d_desc.release(); s->d_arena.release();
+    s->h_state.release(); s->h_desc.release(); s->h_pts.release();
+    s->batch_cap = 0; s->n_cap = 0; s->pitch = 0; s->tim_cap = 0;
+    s->have_result = false; s->batch = 0;
+    s->err = std::string("workspace allocation: ") + cudaGetErrorString(ge);
+    return ge == cudaErrorMemoryAllocation ? B2R_ERR_OOM : B2R_ERR_CUDA;
+  }
   s->batch_cap = bc; s->n_cap = nc; s->pitch = pc; s->tim_cap = tc;
   return B2R_OK;
 }
@@ -186,6 +207,22 @@ b2r_status ensure_events(b2r_solver* s) {
   return B2R_OK;
 }
 
+// The multi-kernel clique / rotation / translation chain (one launch per stage).  Every kernel skips problems the fused tail
+// finished (ProbState::tail_done), so the same chain serves as the whole tail and as the hand-over path.
+b2r_status enqueue_chain(b2r_solver* s, const ProbDesc* dd, int batch, int n_max, cudaStream_t st, bool prof) {
+  s->launches += launch_degree(dd, batch, n_max, st);
+  if (prof) CK(cudaEventRecord(s->ev[3], st));
+  s->launches += launch_clique(dd, batch, n_max, s->kp, (uint32_t*)s->d_arena.p, s->arena_words_per_warp, s->bnb_blocks, st,
+                               prof ? &s->ev[4] : nullptr);
+  s->launches += launch_rotation_translation(dd, batch, n_max, s->kp, st, prof ? &s->ev[8] : nullptr);
+  return B2R_OK;
+}
+
+bool fused_tail_enabled(const b2r_solver* s) {
+  static const bool off = [] { const char* e = getenv("B2R_NO_FUSED_TAIL"); return e && e[0] == '1'; }();
+  return !off && s->kp.inlier_mode == B2R_INLIER_PMC_EXACT;
+}
+
 // enqueue stages 1.. on descriptors already in h_desc
 b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph) {
   cudaStream_t st = s->stream;
@@ -201,19 +238,31 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
       s->launches += launch_scale_estimate(hd[b].src, hd[b].dst, hd[b].n, s->kp.beta, hd[b].st, s->d_scale.p, st);
     if (prof) CK(cudaEventRecord(s->ev[11], st));
   }
+  const bool fused = fused_tail_enabled(s);
+  // does the graph come from the tensor-core filter (pair list + degrees accumulated on the fly)?
+  const bool tc = !skip_graph && !s->kp.estimate_scaling && !s->kp.exact_only && !s->kp.graph_v1 && !s->kp.graph_v2 && !s->kp.graph_v3 &&
+                  !s->kp.graph_v4;
   if (prof) CK(cudaEventRecord(s->ev[1], st));
-  if (!skip_graph) s->launches += launch_tim_graph(dd, batch, n_max, s->kp, st);
+  if (!skip_graph) {
+    if (tc && fused) s->launches += launch_tim_graph_tc(dd, batch, n_max, s->kp, st);   // the tail decides the listed pairs itself
+    else s->launches += launch_tim_graph(dd, batch, n_max, s->kp, st);
+  }
   if (prof) CK(cudaEventRecord(s->ev[2], st));
   if (s->stream_hi) {  // the tail continues on the high-priority stream
     CK(cudaEventRecord(s->ev_graph, st));
     st = s->stream_hi;
     CK(cudaStreamWaitEvent(st, s->ev_graph, 0));
   }
-  s->launches += launch_degree(dd, batch, n_max, st);
-  if (prof) CK(cudaEventRecord(s->ev[3], st));
-  s->launches += launch_clique(dd, batch, n_max, s->kp, (uint32_t*)s->d_arena.p, s->arena_words_per_warp, s->bnb_blocks, st,
-                               prof ? &s->ev[4] : nullptr);
-  s->launches += launch_rotation_translation(dd, batch, n_max, s->kp, st, prof ? &s->ev[8] : nullptr);
+  s->fused = fused;
+  s->handed_over = 0;
+  s->n_max = n_max;
+  if (fused) {
+    if (!tc) s->launches += launch_degree(dd, batch, n_max, st);
+    s->launches += launch_tail(dd, batch, n_max, s->kp, tc ? 0 : 1, st);
+  } else {
+    b2r_status r = enqueue_chain(s, dd, batch, n_max, st, prof);
+    if (r != B2R_OK) return r;
+  }
   if (prof) CK(cudaEventRecord(s->ev[9], st));
   CK(cudaMemcpyAsync(s->h_state.p, s->d_state.p, (size_t)batch * sizeof(ProbState), cudaMemcpyDeviceToHost, st));
   if (s->stream_hi) {  // the handle's stream (what callers synchronise on) waits for the tail
@@ -223,6 +272,27 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
   CK(cudaGetLastError());
   s->pending = true;
   s->have_result = false;
+  return B2R_OK;
+}
+
+// Problems the fused tail handed over (ProbState::tail_done == 0 after the batch): the fp64 graph filter where the graph is not
+// final, then the multi-kernel chain, which skips every finished problem.  Called from b2r_sync with the stream idle.
+b2r_status run_handed_over(b2r_solver* s) {
+  const ProbState* hs = (const ProbState*)s->h_state.p;
+  int todo = 0, regraph = 0;
+  for (int b = 0; b < s->batch; ++b) {
+    if (!hs[b].tail_done) { ++todo; if (hs[b].tail_why != 2) ++regraph; }
+  }
+  s->handed_over = todo;
+  if (!todo) return B2R_OK;
+  const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
+  cudaStream_t st = s->stream;
+  if (regraph) s->launches += launch_graph_fix(dd, s->batch, s->n_max, s->kp, st);
+  b2r_status r = enqueue_chain(s, dd, s->batch, s->n_max, st, false);
+  if (r != B2R_OK) return r;
+  CK(cudaMemcpyAsync(s->h_state.p, s->d_state.p, (size_t)s->batch * sizeof(ProbState), cudaMemcpyDeviceToHost, st));
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
   return B2R_OK;
 }
 
@@ -318,7 +388,10 @@ b2r_status b2r_reset(b2r_solver* s, const b2r_params* params) {
   b2r_status r = check_params(s, params);
   if (r != B2R_OK) return r;
   if (s->pending) { r = b2r_sync(s); if (r != B2R_OK) return r; }
+  const int32_t dbg_filter = s->params.reserved0;   // b2r_debug_set_graph_filter survives reset(params)
+  const double dbg_tau = s->params.reserved1;
   s->params = *params;
+  s->params.reserved0 = dbg_filter; s->params.reserved1 = dbg_tau;
   fill_kernel_params(s);
   s->have_result = false; s->batch = 0;
   return B2R_OK;
@@ -440,13 +513,25 @@ b2r_status b2r_sync(b2r_solver* s) {
   if (!s->pending) return B2R_OK;
   s->pending = false;
   if (s->profiling && s->ev_ready) {
-    for (int i = 0; i < 9; ++i) cudaEventElapsedTime(&s->timings[i], s->ev[i], s->ev[i + 1]);
+    if (s->fused) {   // one launch after the graph: [2] .. [8] have no events of their own, [11] is the fused tail
+      cudaEventElapsedTime(&s->timings[0], s->ev[0], s->ev[1]);
+      cudaEventElapsedTime(&s->timings[1], s->ev[1], s->ev[2]);
+      for (int i = 2; i < 9; ++i) s->timings[i] = 0.f;
+      cudaEventElapsedTime(&s->timings[11], s->ev[2], s->ev[9]);
+    } else {
+      for (int i = 0; i < 9; ++i) cudaEventElapsedTime(&s->timings[i], s->ev[i], s->ev[i + 1]);
+      s->timings[11] = 0.f;
+    }
     cudaEventElapsedTime(&s->timings[9], s->ev[0], s->ev[9]);
     s->timings[10] = 0.f;
     if (s->kp.estimate_scaling) {
       cudaEventElapsedTime(&s->timings[10], s->ev[10], s->ev[11]);
       s->timings[0] -= s->timings[10];  // the scale vote sits between the upload and graph events
     }
+  }
+  if (s->fused) {
+    b2r_status r = run_handed_over(s);
+    if (r != B2R_OK) return r;
   }
   s->have_result = true;
   const ProbState* hs = (const ProbState*)s->h_state.p;
@@ -547,6 +632,7 @@ b2r_status b2r_get_stats(b2r_solver* s, int idx, b2r_stats* out) {
   out->graph_slow_pairs = (int64_t)st.slow_pairs;
   out->exact_proven = (st.flags & FLAG_TIME_LIMIT) ? 0 : 1;
   out->flags = (int32_t)st.flags;
+  out->fused_tail = (s->fused && st.tail_why == 0 && st.tail_done) ? 1 : 0;
   return B2R_OK;
 }
 
@@ -647,6 +733,48 @@ b2r_status b2r_graph_rows(b2r_solver* s, const double* src_dev, const double* ds
   CK(cudaSetDevice(s->device));
   s->launches += launch_tim_graph_rows(src_dev, dst_dev, n, row_begin, row_end, adj_out_dev, pitch_words, s->kp, nullptr, s->stream);
   CK(cudaGetLastError());
+  return B2R_OK;
+}
+
+b2r_status b2r_debug_set_graph_filter(b2r_solver* s, int filter, double tau) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (filter < 0 || filter > 5) return fail(s, B2R_ERR_INVALID_ARG, "graph filter must be 0 .. 5");
+  if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
+  s->params.reserved0 = filter;
+  s->params.reserved1 = tau > 0 ? tau : 0.0;
+  fill_kernel_params(s);
+  return B2R_OK;
+}
+
+b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out8) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  if (!out8) return B2R_ERR_INVALID_ARG;
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  for (int k = 0; k < 8; ++k) out8[k] = st.tail_clk[k];
+  return B2R_OK;
+}
+
+b2r_status b2r_debug_tc_sweep(b2r_solver* s, int idx, double* out8) {
+  b2r_status r = check_index(s, idx);
+  if (r != B2R_OK) return r;
+  if (!out8) return B2R_ERR_INVALID_ARG;
+  const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
+  for (int k = 0; k < 8; ++k) out8[k] = 0.0;
+  out8[7] = st.use32;
+  if (!st.use32) return B2R_OK;
+  CK(cudaSetDevice(s->device));
+  double* dbuf = nullptr;
+  CK(cudaMalloc(&dbuf, 8 * sizeof(double)));
+  cudaError_t e = cudaMemsetAsync(dbuf, 0, 8 * sizeof(double), s->stream);
+  if (e == cudaSuccess) {
+    s->launches += launch_graph_tc_sweep((const ProbDesc*)s->d_desc.p, idx, s->n[idx], s->kp, dbuf, s->stream);
+    e = cudaStreamSynchronize(s->stream);
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out8, dbuf, 7 * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(dbuf);
+  CK(e);
+  out8[7] = 1.0;
   return B2R_OK;
 }
 

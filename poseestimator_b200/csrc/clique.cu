@@ -15,6 +15,7 @@
 // All sizes stay on the device between the stages; the host never synchronises inside a solve.
 #include <stdio.h>
 #include "common.cuh"
+#include "clique_dev.cuh"
 
 namespace b2r {
 
@@ -27,7 +28,6 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
-__device__ __forceinline__ int words_for(int n) { return 4 * ((n + kTile - 1) / kTile); }
 
 // ---------------------------------------------------------------------------------------------------------
 // warp-distributed bitsets: word w lives in lane (w & 31), slot (w >> 5)
@@ -230,120 +230,12 @@ __global__ void __launch_bounds__(kHeuThreads) heuristic_block_kernel(const Prob
   extern __shared__ uint32_t sh[];
   const ProbDesc d = descs[blockIdx.y];
   ProbState* st = d.st;
+  if (st->tail_done) return;   // the fused tail (tail.cu) finished this problem
   const unsigned long long skey = st->seed_key[blockIdx.x];
   if (skey == 0ull) return;
   const int v = (int)(0xffffffffu - (unsigned)(skey & 0xffffffffu));
-  const int n = d.n;
-  const int W = words_for(n);
-  const int Wb = (n + 31) >> 5;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int NW = kHeuThreads / 32;
-  uint32_t* P = sh;                       // W
-  uint32_t* U = sh + W;                   // W
-  uint32_t* Rm = sh + 2 * W;              // W: members to drop this round
-  int* scan = (int*)(sh + 3 * W);         // 40
-  unsigned* s_best = (unsigned*)(scan + 40);
-  int* s_nU = (int*)(scan + 41);
-  int* s_lb = (int*)(scan + 42);
-  int* s_nR = (int*)(scan + 43);
-  unsigned short* list = (unsigned short*)(scan + 48);  // n entries
-  const uint32_t* row0 = d.adj + (size_t)v * d.pitch;
-  for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] = row0[w];
-  __syncthreads();
-  int size = 1;
-#ifdef B2R_HEU_DEBUG
-  int rounds = 0; long long t0 = clock64();
-#endif
-  for (;;) {
-#ifdef B2R_HEU_DEBUG
-    ++rounds;
-#endif
-    // ascending member list + count
-    __shared__ int sh_base2;
-    if (threadIdx.x == 0) sh_base2 = 0;
-    __syncthreads();
-    for (int w0 = 0; w0 < Wb; w0 += kHeuThreads) {
-      const int w = w0 + threadIdx.x;
-      const uint32_t word = (w < Wb) ? P[w] : 0u;
-      const int c = __popc(word);
-      int incl = c;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
-      if (lane == 31) scan[warp] = incl;
-      __syncthreads();
-      if (warp == 0) {
-        int x = scan[lane], xi = x;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, xi, o); if (lane >= o) xi += t; }
-        scan[lane] = xi - x;
-        if (lane == 31) scan[32] = xi;
-      }
-      __syncthreads();
-      int pos = sh_base2 + scan[warp] + incl - c;
-      uint32_t bits = word;
-      while (bits) { list[pos++] = (unsigned short)(32 * w + (__ffs(bits) - 1)); bits &= bits - 1; }
-      __syncthreads();
-      if (threadIdx.x == 0) sh_base2 += scan[32];
-      __syncthreads();
-    }
-    const int cnt = sh_base2;
-    if (cnt == 0) break;
-    if (threadIdx.x == 0) { *s_lb = *(volatile int*)&st->lb; *s_best = 0u; *s_nU = 0; *s_nR = 0; }
-    for (int w = threadIdx.x; w < W; w += kHeuThreads) { U[w] = 0u; Rm[w] = 0u; }
-    __syncthreads();
-    if (size + cnt <= *s_lb) return;  // another seed already reached this size: cannot improve
-    unsigned wbest = 0;
-    for (int m0 = warp; m0 < cnt; m0 += 4 * NW) {
-      int c[4];
-      int ids[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int m = m0 + q * NW;
-        ids[q] = m < cnt ? (int)list[m] : -1;
-        c[q] = 0;
-        if (ids[q] >= 0) {
-          const uint32_t* row = d.adj + (size_t)ids[q] * d.pitch;
-          for (int w = lane; w < W; w += 32) c[q] += __popc(__ldg(row + w) & P[w]);
-        }
-      }
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (ids[q] < 0) continue;
-        const int cq = __reduce_add_sync(FULL, c[q]);
-        const unsigned id = (unsigned)ids[q];
-        wbest = max(wbest, ((unsigned)cq << 16) | (0xffffu - id));
-        if (cq == cnt - 1 && lane == 0) atomicOr(&U[id >> 5], 1u << (id & 31));
-        if (2 * cq < cnt - 1 && lane == 0) atomicOr(&Rm[id >> 5], 1u << (id & 31));   // adjacent to less than half of the others
-      }
-    }
-    if (lane == 0 && wbest) atomicMax(s_best, wbest);
-    __syncthreads();
-    int nu = 0, nr = 0;
-    for (int w = threadIdx.x; w < Wb; w += kHeuThreads) { nu += __popc(U[w]); nr += __popc(Rm[w]); }
-    nu = __reduce_add_sync(FULL, nu); nr = __reduce_add_sync(FULL, nr);
-    if (lane == 0 && nu) atomicAdd(s_nU, nu);
-    if (lane == 0 && nr) atomicAdd(s_nR, nr);
-    __syncthreads();
-    const int nU = *s_nU, nR = *s_nR;
-    if (nU > 0) {
-      size += nU;
-      for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= ~U[w];
-    } else if (nR > 0 && nR < cnt) {
-      // bulk peel: a member adjacent to fewer than half of the candidates cannot be in a clique covering most of them; dropping
-      // all of those at once replaces the one-vertex-per-round elimination of sparse outliers (16-26 rounds -> 3 on config 3)
-      for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= ~Rm[w];
-    } else {
-      const unsigned u = 0xffffu - (*s_best & 0xffffu);
-      size += 1;
-      const uint32_t* row = d.adj + (size_t)u * d.pitch;
-      for (int w = threadIdx.x; w < W; w += kHeuThreads) P[w] &= row[w];
-    }
-    __syncthreads();
-  }
-#ifdef B2R_HEU_DEBUG
-  if (threadIdx.x == 0 && blockIdx.y < 2) printf("heu seed %d blk(%d,%d) rounds %d size %d cycles %lld\n", v, blockIdx.x, blockIdx.y, rounds, size, clock64() - t0);
-#endif
-  if (threadIdx.x == 0) {
+  const int size = heuristic_seed_cta<kHeuThreads, false>(d, v, sh, &st->lb);
+  if (size > 0 && threadIdx.x == 0) {
     atomicMax(&st->heu_key, ((unsigned long long)size << 32) | (unsigned long long)(0xffffffffu - (unsigned)v));
     atomicMax(&st->lb, size);
   }
@@ -449,6 +341,7 @@ __global__ void __launch_bounds__(1024) prune_kernel(const ProbDesc* __restrict_
   extern __shared__ uint32_t sh[];
   const ProbDesc d = descs[blockIdx.x];
   ProbState* st = d.st;
+  if (st->tail_done) return;
   const int n = d.n;
   const int W = words_for(n);
   const int Wb = (n + 31) >> 5;
@@ -486,6 +379,7 @@ __global__ void __launch_bounds__(1024) prune_kernel(const ProbDesc* __restrict_
 __global__ void __launch_bounds__(256) compact_kernel(const ProbDesc* __restrict__ descs) {
   const ProbDesc d = descs[blockIdx.y];
   const ProbState* st = d.st;
+  if (st->tail_done) return;
   const int np = st->n_alive, Wc = st->Wc;
   if (st->flags & FLAG_COMPACT_TOO_LARGE) return;
   const int lane = threadIdx.x & 31;
@@ -703,6 +597,7 @@ __global__ void __launch_bounds__(kBnbWarpsPerBlock * 32) bnb_kernel(const ProbD
   extern __shared__ uint32_t sh[];
   const ProbDesc d = descs[blockIdx.y];
   ProbState* st = d.st;
+  if (st->tail_done) return;
   __shared__ int sh_hdr[4];
   if (threadIdx.x == 0) {  // omega / flags change under us (other CTAs of this problem): read them once per CTA
     sh_hdr[0] = st->n_alive; sh_hdr[1] = st->Wc; sh_hdr[2] = *(volatile int*)&st->omega; sh_hdr[3] = (int)*(volatile uint32_t*)&st->flags;
@@ -770,6 +665,7 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
   __shared__ CanonShared cs;
   const ProbDesc d = descs[blockIdx.x];
   ProbState* st = d.st;
+  if (st->tail_done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (st->flags & (FLAG_COMPACT_TOO_LARGE | FLAG_ARENA_OVERFLOW)) {
     if (threadIdx.x == 0) st->clique_size = 0;
@@ -1003,8 +899,8 @@ static void dispatch_wpl(int wpl, const ProbDesc* d_desc, dim3 grid, int block, 
 }
 template <int WPL> struct HeuLaunch {
   static void go(const ProbDesc* d, dim3 g, int b, size_t smem, int all_seeds, cudaStream_t s) {
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(heuristic_kernel<WPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024); attr = true; }
+    static PerDeviceOnce attr;
+    attr.run([] { return cudaFuncSetAttribute(heuristic_kernel<WPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024); });
     heuristic_kernel<WPL><<<g, b, smem, s>>>(d, all_seeds);
   }
 };
@@ -1012,21 +908,23 @@ template <int WPL> struct ReplayLaunch {
   static void go(const ProbDesc* d, dim3 g, int b, size_t smem, int, cudaStream_t s) { heuristic_replay_kernel<WPL><<<g, b, smem, s>>>(d); }
 };
 
-static size_t g_smem_optin = 0;
+// opt-in shared memory of the current device; the kernels' attributes are set once PER DEVICE before the value is used
 static size_t smem_optin_bytes() {
-  if (!g_smem_optin) {
-    int dev = 0, v = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    g_smem_optin = (size_t)v;
-    const size_t dyn = g_smem_optin - 2048;
-    cudaFuncSetAttribute(bnb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-    cudaFuncSetAttribute(canon_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-    cudaFuncSetAttribute(prune_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    cudaFuncSetAttribute(kcore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    cudaFuncSetAttribute(heuristic_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-  }
-  return g_smem_optin;
+  static PerDeviceOnce attr;
+  int dev = 0, v = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  const size_t optin = (size_t)v;
+  attr.run([&] {
+    const size_t dyn = optin - 2048;
+    cudaError_t e = cudaFuncSetAttribute(bnb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(canon_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(prune_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kcore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(heuristic_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    return e;
+  });
+  return optin;
 }
 
 int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, uint32_t* arena,

@@ -3,9 +3,29 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "../../include/b2r.h"
 
 namespace b2r {
+
+// cudaFuncSetAttribute (dynamic shared memory opt-in) applies to the CURRENT device only: handles on several devices in one
+// process each need it once, and a second thread must not launch before the first one has finished setting it.
+struct PerDeviceOnce {
+  std::mutex m;
+  unsigned long long done = 0;   // bit d: set on device d
+  template <class F>
+  cudaError_t run(F&& f) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> g(m);
+    if ((done >> (dev & 63)) & 1ull) return cudaSuccess;
+    e = f();
+    if (e == cudaSuccess) done |= 1ull << (dev & 63);
+    return e;
+  }
+};
 
 constexpr int kTile = 128;            // consistency-graph tile edge (rows and columns per CTA)
 constexpr int kMaxN = 65535;          // degree / id packing in the clique kernels (16 + 16 bits)
@@ -52,7 +72,11 @@ struct ProbState {
   unsigned int amb_count;   // pairs appended to ProbDesc::amb_list (may exceed amb_cap: then tc_overflow is set)
   int tc_overflow;       // 1: the list overflowed -> the whole problem is redone by the fp64 filter
   int deg_ready;         // 1: deg[] was accumulated by the tensor-core filter and its fix-up (degree_kernel skips the popcount)
-  int pad3_;
+  float tc_pi;           // tensor-core filter: upper bound of |s'|^2 + |d'|^2 over the problem's points (beta units), for the per-row band
+  // fused tail (tail.cu)
+  int tail_done;         // 1: the fused tail kernel finished this problem (the multi-kernel clique / rotation / translation path skips it)
+  int tail_why;          // why the fused tail handed the problem to the multi-kernel path (0 = it did not)
+  unsigned int tail_clk[8];  // SM cycles the fused tail spent up to the end of: fix-up, degrees, heuristic, prune, clique, rotation, translation
 };
 
 // Per-problem pointers (device copies of host-built descriptors).
@@ -112,13 +136,18 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
 // graph_tc.cu (v5): prep (boxes, constants, 22-bit records) + tcgen05 filter; graph.cu: exact fix-up of the listed pairs and the
 // fp64 filter for problems the fp32 path may not decide
 int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+int launch_tim_graph_tc_and_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
 int launch_graph_tc_debug(const ProbDesc* d_desc, int prob, int bi, int v, float* out_dm, float* out_l, cudaStream_t st);
+// every unit of one problem checked on the device against fp64 (b2r_debug_tc_sweep); out: 8 doubles, zeroed by the caller
+int launch_graph_tc_sweep(const ProbDesc* d_desc, int prob, int n, const KernelParams& kp, double* out, cudaStream_t st);
 int launch_graph_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
 // listed pairs per problem: about 1.4e-4 of the pairs are ambiguous at config 3; room for eight times that, at least 32768
 inline size_t amb_cap_for(size_t n_cap) { const size_t c = n_cap * n_cap / 1024; return c < ((size_t)1 << 15) ? ((size_t)1 << 15) : c; }
 int launch_tim_graph_rows(const double* src, const double* dst, int n, int row_begin, int row_end, uint32_t* adj,
                           int pitch, const KernelParams& kp, unsigned long long* slow_pairs, cudaStream_t st);
 int launch_degree(const ProbDesc* d_desc, int batch, int n_max, cudaStream_t st);
+// tail.cu: everything after the graph in one launch, one CTA per problem (mode 0: tensor-core graph of this batch, 1: final graph + degree_kernel)
+int launch_tail(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, int mode, cudaStream_t st);
 int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, uint32_t* arena,
                   size_t arena_words_per_warp, int bnb_blocks_per_problem, cudaStream_t st, cudaEvent_t* ev /*4 or null*/);
 int launch_rotation_translation(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st,

@@ -22,18 +22,9 @@
 #include <math_constants.h>
 
 #include "common.cuh"
+#include "exact.cuh"
 
 namespace b2r {
-
-__device__ __forceinline__ double sq3_ref(double dx, double dy, double dz) {
-  // (dx*dx + dy*dy) + dz*dz, each operation rounded separately (reference order, no FMA)
-  return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-}
-
-__device__ __forceinline__ bool verdict_exact(double A, double B, double beta) {
-  const double a = __dsqrt_rn(A), b = __dsqrt_rn(B);
-  return fabs(__dsub_rn(a, b)) <= beta;
-}
 
 // estimate_scaling=True (A.4-5 + A.7-3): the edge set is the scale-inlier mask |b/a - s| <= beta * (1/a),
 // s = the adaptive-voting estimate (scale.cu), every operation rounded as the reference's doubles are.
@@ -813,26 +804,13 @@ __global__ void __launch_bounds__(kTile, B2R_G4_MINB) tim_graph4_kernel(const Pr
 __global__ void __launch_bounds__(kTile) graph_fix_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
   const ProbDesc d = descs[blockIdx.y];
   ProbState* st = d.st;
+  if (st->tail_done || st->tail_why == 2) return;   // the fused tail (tail.cu) already fixed this problem's listed pairs
   const int n = d.n;
   const int t = threadIdx.x;
   if (st->use32 && !st->tc_overflow) {
     const unsigned cnt = min(st->amb_count, (unsigned)d.amb_cap);
     for (unsigned idx = blockIdx.x * kTile + t; idx < cnt; idx += gridDim.x * kTile) {
-      const uint32_t e = d.amb_list[idx];
-      const size_t i = e >> 16, j = e & 0xffffu;
-      const double A = sq3_ref(__dsub_rn(d.src[3 * j], d.src[3 * i]), __dsub_rn(d.src[3 * j + 1], d.src[3 * i + 1]), __dsub_rn(d.src[3 * j + 2], d.src[3 * i + 2]));
-      const double B = sq3_ref(__dsub_rn(d.dst[3 * j], d.dst[3 * i]), __dsub_rn(d.dst[3 * j + 1], d.dst[3 * i + 1]), __dsub_rn(d.dst[3 * j + 2], d.dst[3 * i + 2]));
-      uint32_t* wij = d.adj + i * d.pitch + (j >> 5);
-      uint32_t* wji = d.adj + j * d.pitch + (i >> 5);
-      // the filter kernel counted the placeholder bits into the degrees: every bit that actually flips corrects its row's degree
-      const uint32_t bj_ = 1u << (j & 31), bi_ = 1u << (i & 31);
-      if (verdict_exact(A, B, kp.beta)) {
-        if (!(atomicOr(wij, bj_) & bj_)) atomicAdd(&d.deg[i], 1);
-        if (!(atomicOr(wji, bi_) & bi_)) atomicAdd(&d.deg[j], 1);
-      } else {
-        if (atomicAnd(wij, ~bj_) & bj_) atomicSub(&d.deg[i], 1);
-        if (atomicAnd(wji, ~bi_) & bi_) atomicSub(&d.deg[j], 1);
-      }
+      fix_listed_pair(d.src, d.dst, d.adj, d.pitch, d.deg, d.amb_list[idx], kp.beta);
     }
     if (blockIdx.x == 0 && t == 0) { st->slow_pairs = cnt; st->deg_ready = 1; }
     return;
@@ -937,6 +915,7 @@ __global__ void __launch_bounds__(256) degree_kernel(const ProbDesc* __restrict_
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int v0 = blockIdx.x * kDegRowsPerBlock;
   if (v0 >= d.n) return;
+  if (d.st->tail_done || d.st->tail_why == 2) return;   // the fused tail (tail.cu) already reduced this problem's degrees
   if (threadIdx.x < 8) s_key[threadIdx.x] = 0ull;
   if (threadIdx.x == 8) s_sum = 0ull;
   __syncthreads();
@@ -1001,7 +980,7 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
   else if (kp.exact_only) tim_graph_kernel<1><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.graph_v1) tim_graph_kernel<0><<<grid, kTile, 0, st>>>(d_desc, kp);
   else if (kp.graph_v2) tim_graph2_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);
-  else if (!kp.graph_v3 && !kp.graph_v4) return launch_tim_graph_tc(d_desc, batch, n_max, kp, st);
+  else if (!kp.graph_v3 && !kp.graph_v4) return launch_tim_graph_tc_and_fix(d_desc, batch, n_max, kp, st);
   else {
     graph_prep_kernel<<<batch, 256, 0, st>>>(d_desc, kp);
     if (kp.graph_v3) tim_graph3_kernel<<<dim3(graph2_items(T), batch), kTile, 0, st>>>(d_desc, kp);

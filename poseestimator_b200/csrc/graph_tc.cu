@@ -25,6 +25,7 @@
 // and T is twice that bound plus the 4e-15 (A' + B' + 1)^2 inside which the reference's own roundings could flip the verdict,
 // written as a linear function of L~ (|L~| <= 2.001 + 2 E_L - L~).
 #include <math_constants.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -58,6 +59,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar_addr, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar_addr), "r"(parity) : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -80,6 +93,15 @@ __device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
         "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
         "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
         "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr)
       : "memory");
 }
@@ -122,12 +144,91 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
   return x;
 }
 
+// The same 32 x 32 bit transpose in 13 instructions instead of ~50: the two byte-granular steps are one PRMT each (per-lane
+// selector), the three sub-byte steps one rotate (per-lane amount) + one LOP3 bit-select (per-lane mask) each.
+struct TposeConst { uint32_t sel16, sel8, km4, km2, km1; int sh4, sh2, sh1; };
+__device__ __forceinline__ TposeConst tpose_const(int lane) {
+  TposeConst k;
+  k.sel16 = (lane & 16) ? 0x3276u : 0x5410u;
+  k.sel8 = (lane & 8) ? 0x3715u : 0x6240u;
+  k.km4 = (lane & 4) ? 0xf0f0f0f0u : 0x0f0f0f0fu;  k.sh4 = (lane & 4) ? 28 : 4;
+  k.km2 = (lane & 2) ? 0xccccccccu : 0x33333333u;  k.sh2 = (lane & 2) ? 30 : 2;
+  k.km1 = (lane & 1) ? 0xaaaaaaaau : 0x55555555u;  k.sh1 = (lane & 1) ? 31 : 1;
+  // opaque to the compiler: otherwise it re-derives all eight from the lane id (R2P + SEL + MOV, ~16 instructions) at every use
+  asm volatile("" : "+r"(k.sel16), "+r"(k.sel8), "+r"(k.km4), "+r"(k.km2), "+r"(k.km1), "+r"(k.sh4), "+r"(k.sh2), "+r"(k.sh1));
+  return k;
+}
+__device__ __forceinline__ uint32_t warp_transpose32_fast(uint32_t x, const TposeConst& k) {
+  uint32_t y = __shfl_xor_sync(0xffffffffu, x, 16);
+  x = __byte_perm(x, y, k.sel16);
+  y = __shfl_xor_sync(0xffffffffu, x, 8);
+  x = __byte_perm(x, y, k.sel8);
+  y = __shfl_xor_sync(0xffffffffu, x, 4);
+  y = __funnelshift_l(y, y, k.sh4);
+  x = (x & k.km4) | (y & ~k.km4);
+  y = __shfl_xor_sync(0xffffffffu, x, 2);
+  y = __funnelshift_l(y, y, k.sh2);
+  x = (x & k.km2) | (y & ~k.km2);
+  y = __shfl_xor_sync(0xffffffffu, x, 1);
+  y = __funnelshift_l(y, y, k.sh1);
+  x = (x & k.km1) | (y & ~k.km1);
+  return x;
+}
+__device__ __forceinline__ float2 f2mul(float2 a, float2 b) {
+  float2 r;
+  asm("{.reg .b64 ra, rb, rd; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mul.rn.f32x2 rd, ra, rb; mov.b64 {%0,%1}, rd;}"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return r;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------------
 // prep: one CTA per problem: bounding boxes -> centres, extents, band constants (ProbState).  graph_tc_ops_kernel then writes
 // the operand rows of every point (zero-filled up to the tile edge).
 // ---------------------------------------------------------------------------------------------------------------------
+// band constants of one problem from the bounding boxes of its two clouds (one thread); st == nullptr: only the decision
+// "the fp32 path may decide this problem" is returned (the other slices of graph_tc_setup_kernel)
+__device__ bool tc_write_constants(ProbState* st, const double (&lo6)[6], const double (&hi6)[6], bool bad, int n, const KernelParams& kp) {
+  const double beta = fabs(kp.beta);
+  const double kappa = 1.0 / beta;
+  double Pi = 0.0, Mmax = 0.0;
+  for (int k = 0; k < 6; ++k) {
+    const double lo = lo6[k], hi = hi6[k];
+    const double c = 0.5 * lo + 0.5 * hi;
+    if (st) st->ctr[k] = c;
+    const double h = fmax(hi - c, c - lo) * kappa * (1.0 + 1e-6);   // covers the roundings of the 22-bit copy
+    Mmax = fmax(Mmax, h);
+    Pi += h * h;
+  }
+  const double w22 = 2.384185791015625e-7, u = 5.9604644775390625e-8;   // 2^-22, 2^-24
+  const double E_L = w22 * (71.8 * Pi + 4.3), E_D = 45.9 * w22 * Pi;
+  const double tmin = kp.filter_tau_min;                                   // tests widen the band with it
+  // the fp32 path decides only well-conditioned problems; everything else goes to the fp64 filter (graph_fix_kernel)
+  const bool ok = !bad && n > 0 && beta >= 1e-300 && kappa <= 1e300 && Mmax < 1e12 && Pi > 1e-20 && E_L < 1e3 && tmin < 0.015625;
+  if (!st) return ok;
+  st->use32 = ok ? 1 : 0;
+  st->kappa = kappa;
+  if (ok) {
+    double k = sqrt(2.0 * Pi) / E_D;
+    if (!(k >= 8.0)) k = 8.0;
+    if (k > 1e12) k = 1e12;
+    const double E_scale = 2e-15 * (1.0 + 8.0 * Pi), refc = 4e-15 * (1.0 + 8.0 * Pi);
+    const double den = 1.0 - 2.0 * (1.0 + 2.0 * u) / k;
+    const double pad = 1.0 + 1e-5;                                         // fp32 evaluation of T
+    // T(L) = t0 - t1 L;  tmin (tests) widens the band relative to (A' + B' + 1)^2 <= (1 + 8 Pi)(3.001 - L) / 2
+    const double t1 = (2.0 / k + refc + tmin * (1.0 + 8.0 * Pi)) / den * pad;
+    const double labs = 2.001 + 2.0 * E_L;                                 // |L~| <= labs - L~  (L~ <= 1 + E_L)
+    const double t0 = (labs * 2.0 / k + 2.0 * (k + 1.0) * E_D * E_D + 2.0 * E_L + 2.0 * E_scale + (labs + 1.0) * (refc + tmin * (1.0 + 8.0 * Pi))) / den * pad;
+    st->tcc[0] = -__double2float_ru(t1);
+    st->tcc[1] = __double2float_ru(t0);
+    st->tcc[2] = -__double2float_ru(1.001 + 1.01 * E_L);                   // L~ <= this  =>  A' + B' > 1
+    st->tcc[3] = (float)k;
+    st->tc_pi = __double2float_ru(Pi);
+  }
+  return ok;
+}
+
 __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
   const ProbDesc d = descs[blockIdx.x];
   const int n = d.n;
@@ -164,42 +265,13 @@ __global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __r
   if (bad) atomicOr(&s_bad, 1);
   __syncthreads();
   if (t == 0) {
-    ProbState* st = d.st;
-    const double beta = fabs(kp.beta);
-    const double kappa = 1.0 / beta;
-    double Pi = 0.0, Mmax = 0.0;
+    double lo6[6], hi6[6];
     for (int k = 0; k < 6; ++k) {
       double lo = s_mn[0][k], hi = s_mx[0][k];
       for (int w = 1; w < 32; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
-      const double c = 0.5 * lo + 0.5 * hi;
-      st->ctr[k] = c;
-      const double h = fmax(hi - c, c - lo) * kappa * (1.0 + 1e-6);   // covers the roundings of the 22-bit copy
-      Mmax = fmax(Mmax, h);
-      Pi += h * h;
+      lo6[k] = lo; hi6[k] = hi;
     }
-    const double w22 = 2.384185791015625e-7, u = 5.9604644775390625e-8;   // 2^-22, 2^-24
-    const double E_L = w22 * (71.8 * Pi + 4.3), E_D = 45.9 * w22 * Pi;
-    const double tmin = kp.filter_tau_min;                                   // tests widen the band with it
-    // the fp32 path decides only well-conditioned problems; everything else goes to the fp64 filter (graph_fix_kernel)
-    const bool ok = !s_bad && n > 0 && beta >= 1e-300 && kappa <= 1e300 && Mmax < 1e12 && Pi > 1e-20 && E_L < 1e3 && tmin < 0.015625;
-    st->use32 = ok ? 1 : 0;
-    st->kappa = kappa;
-    if (ok) {
-      double k = sqrt(2.0 * Pi) / E_D;
-      if (!(k >= 8.0)) k = 8.0;
-      if (k > 1e12) k = 1e12;
-      const double E_scale = 2e-15 * (1.0 + 8.0 * Pi), refc = 4e-15 * (1.0 + 8.0 * Pi);
-      const double den = 1.0 - 2.0 * (1.0 + 2.0 * u) / k;
-      const double pad = 1.0 + 1e-5;                                         // fp32 evaluation of T
-      // T(L) = t0 - t1 L;  tmin (tests) widens the band relative to (A' + B' + 1)^2 <= (1 + 8 Pi)(3.001 - L) / 2
-      const double t1 = (2.0 / k + refc + tmin * (1.0 + 8.0 * Pi)) / den * pad;
-      const double labs = 2.001 + 2.0 * E_L;                                 // |L~| <= labs - L~  (L~ <= 1 + E_L)
-      const double t0 = (labs * 2.0 / k + 2.0 * (k + 1.0) * E_D * E_D + 2.0 * E_L + 2.0 * E_scale + (labs + 1.0) * (refc + tmin * (1.0 + 8.0 * Pi))) / den * pad;
-      st->tcc[0] = -__double2float_ru(t1);
-      st->tcc[1] = __double2float_ru(t0);
-      st->tcc[2] = -__double2float_ru(1.001 + 1.01 * E_L);                   // L~ <= this  =>  A' + B' > 1
-      st->tcc[3] = (float)k;
-    }
+    tc_write_constants(d.st, lo6, hi6, s_bad != 0, n, kp);
   }
 }
 
@@ -295,23 +367,15 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 // Column-operand row of every point (128 bytes), already in the 128-byte-swizzled order the MMA reads (row j of a 64- or
 // 128-row tile uses j & 7, and tiles start at multiples of 64).  The row-L / row-D operands of a CTA's 128 rows are derived
 // from these rows in shared memory (rows_from_col_row).  grid = (n_pad / 128, batch).
-__global__ void __launch_bounds__(kTile) graph_tc_ops_kernel(const ProbDesc* __restrict__ descs) {
-  const ProbDesc d = descs[blockIdx.y];
-  const ProbState* st = d.st;
-  if (!st->use32) return;
-  const int n = d.n;
-  const int n_pad = (n + kTile - 1) / kTile * kTile;
-  const int i = blockIdx.x * kTile + threadIdx.x;
-  if (i >= n_pad) return;
+__device__ __forceinline__ void tc_store_operand_row(const ProbDesc& d, const double (&ctr)[6], double kappa, int i, int n) {
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
   if (i < n) {
     d.deg[i] = 0;   // the filter kernel accumulates the vertex degrees (popcounts of the words it writes)
-    const double kappa = st->kappa;
     float v[6];
     double r[2] = {0.0, 0.0};
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
-      const double x = ((k < 3 ? d.src[3 * (size_t)i + k] : d.dst[3 * (size_t)i + k - 3]) - st->ctr[k]) * kappa;
+      const double x = ((k < 3 ? d.src[3 * (size_t)i + k] : d.dst[3 * (size_t)i + k - 3]) - ctr[k]) * kappa;
       const float x32 = __double2float_rn(x);
       const float hi = to_tf32(x32);
       const float lo = to_tf32(x32 - hi);
@@ -322,8 +386,84 @@ __global__ void __launch_bounds__(kTile) graph_tc_ops_kernel(const ProbDesc* __r
     b = make_float4(v[3], v[4], v[5], __double2float_rn(r[0] - r[1]));
   }
   const Split sp = split_record(a, b);
-  unsigned char* base = reinterpret_cast<unsigned char*>(d.pts32);
-  store_col_row(base, i, sp);
+  store_col_row(reinterpret_cast<unsigned char*>(d.pts32), i, sp);
+}
+
+__global__ void __launch_bounds__(kTile) graph_tc_ops_kernel(const ProbDesc* __restrict__ descs) {
+  const ProbDesc d = descs[blockIdx.y];
+  const ProbState* st = d.st;
+  if (!st->use32) return;
+  const int n = d.n;
+  const int n_pad = (n + kTile - 1) / kTile * kTile;
+  const int i = blockIdx.x * kTile + threadIdx.x;
+  if (i >= n_pad) return;
+  double ctr[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) ctr[k] = st->ctr[k];
+  tc_store_operand_row(d, ctr, st->kappa, i, n);
+}
+
+// prep + operand rows in ONE launch: grid = (slices, batch).  Every CTA of a problem reduces the bounding boxes of the whole
+// problem itself (48 n bytes out of L2; min / max are exact, so all slices agree bit for bit), slice 0 writes the constants, and
+// each slice writes the operand rows of its share of the points.  No grid-wide synchronisation is needed.
+__global__ void __launch_bounds__(1024) graph_tc_setup_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  const int n = d.n;
+  const int t = threadIdx.x;
+  double mn[6], mx[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { mn[k] = CUDART_INF; mx[k] = -CUDART_INF; }
+  bool bad = false;
+  for (int i = t; i < n; i += 1024) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double a = d.src[3 * (size_t)i + k], b = d.dst[3 * (size_t)i + k];
+      bad |= !(fabs(a) <= 1.79e308) | !(fabs(b) <= 1.79e308);
+      mn[k] = fmin(mn[k], a); mx[k] = fmax(mx[k], a);
+      mn[3 + k] = fmin(mn[3 + k], b); mx[3 + k] = fmax(mx[3 + k], b);
+    }
+  }
+  __shared__ double s_mn[32][6], s_mx[32][6];
+  __shared__ double s_ctr[6], s_kappa;
+  __shared__ int s_bad, s_use32;
+  if (t == 0) s_bad = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+      mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+    }
+  }
+  if ((t & 31) == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { s_mn[t >> 5][k] = mn[k]; s_mx[t >> 5][k] = mx[k]; }
+  }
+  if (bad) atomicOr(&s_bad, 1);
+  __syncthreads();
+  if (t == 0) {
+    double lo6[6], hi6[6];
+    for (int k = 0; k < 6; ++k) {
+      double lo = s_mn[0][k], hi = s_mx[0][k];
+      for (int w = 1; w < 32; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
+      lo6[k] = lo; hi6[k] = hi;
+      s_ctr[k] = 0.5 * lo + 0.5 * hi;    // the same expression tc_write_constants stores
+    }
+    // slice 0 writes the state; the others take the same decision without touching it
+    s_use32 = tc_write_constants(blockIdx.x == 0 ? d.st : nullptr, lo6, hi6, s_bad != 0, n, kp) ? 1 : 0;
+    s_kappa = 1.0 / fabs(kp.beta);
+  }
+  __syncthreads();
+  if (!s_use32) return;
+  double ctr[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) ctr[k] = s_ctr[k];
+  const double kappa = s_kappa;
+  const int n_pad = (n + kTile - 1) / kTile * kTile;
+  const int per = ((n_pad / kTile + gridDim.x - 1) / gridDim.x) * kTile;   // whole 128-row blocks per slice
+  const int i_begin = blockIdx.x * per, i_end = min(i_begin + per, n_pad);
+  for (int i = i_begin + t; i < i_end; i += 1024) tc_store_operand_row(d, ctr, kappa, i, n);
 }
 
 // work items of one problem: row block bi walks its column units v = 0 .. 2 (T - bi) - 1 in chunks of kTcUnitsPerItem
@@ -527,17 +667,431 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDes
   }
 }
 
-int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(tim_graph5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-    attr_set = true;
+// ---------------------------------------------------------------------------------------------------------------------
+// Filter v6: the same tensor-core formulation, producer warp, TMEM staging and exactness argument as tim_graph5_kernel; the
+// epilogue is rebuilt around its instruction count (ncu of v5, profiles/r01_graph_kernel_ncu_full.md: 308 warp instructions per
+// 32 x 32 chunk, 113 of them the decision core):
+//   * the mirrored block's 32 x 32 bit transpose is 13 instructions (PRMT / rotate + bit-select with per-lane constants), not ~50;
+//   * running pointers instead of per-unit index arithmetic, the TMEM stage a compile-time constant (units unrolled by two);
+//   * edge units (diagonal tile, last column tile, partial row block) take a separate masked path, interior units none of it;
+//   * an ambiguous chunk replays only the flagged 8-column groups, not all 32 columns;
+//   * VAR 1 / 2: the band is a per-ROW constant T_i = T(L_min,i) >= T(L_ij) (L_ij >= 1 - 4 (r_i + Pi)), which removes the packed
+//     FMA that evaluated T(L) per pair; VAR 1 tests G^2 < T_i^2 with one packed multiply and one 3-input integer minimum per
+//     two pairs (bit patterns of non-negative floats order like the floats), VAR 2 keeps the two compares.
+//     A wider band only sends more pairs to the exact fix-up (graph_fix_kernel / tail): never a wrong bit.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int S_> struct StageC { static constexpr int value = S_; };
+
+template <int VAR, bool LD16>
+__global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[blockIdx.y];
+  const int n = d.n;
+  if (!d.st->use32) return;
+  const int T = (n + kTile - 1) / kTile;
+  int p = blockIdx.x, bi = 0;
+  int per = (2 * T + kTcUnitsPerItem - 1) / kTcUnitsPerItem;
+  while (bi < T && p >= per) { p -= per; ++bi; per = (2 * (T - bi) + kTcUnitsPerItem - 1) / kTcUnitsPerItem; }
+  if (bi >= T) return;
+  const int v0 = p * kTcUnitsPerItem;
+  const int nu = min(kTcUnitsPerItem, 2 * (T - bi) - v0);
+  const int i0 = bi * kTile;
+
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* sRowL = sm;
+  unsigned char* sRowD = sm + kTcRowBytes;
+  unsigned char* sCol = sm + 2 * kTcRowBytes;   // ring of 4 slots
+  TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sm + 2 * kTcRowBytes + 4 * kTcColBytes);
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const unsigned char* ops_col = reinterpret_cast<const unsigned char*>(d.pts32);
+  unsigned char* sStage = sm + 2 * kTcRowBytes + 4 * kTcColBytes + 1024;   // column rows of the CTA's own 128 points (16 KB)
+
+  if (t == 32 * kTcEpiWarps) {
+    mbar_init(&g->rowfull, 1);
+    for (int s = 0; s < 4; ++s) mbar_init(&g->colfull[s], 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&g->full[s], 1); mbar_init(&g->empty[s], kTcEpiWarps); }
+    for (int w = 0; w < kTcEpiWarps; ++w) g->amb_cnt[w] = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(&g->rowfull, kTcRowBytes);
+    bulk_g2s(sStage, ops_col + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
+    for (int u = 0; u < 3 && u < nu; ++u) {  // the first column units start travelling before the set-up barrier
+      const int j0 = i0 + (v0 + u) * kTcUnit;
+      mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
+      bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
+    }
   }
+  __syncthreads();
+  if (warp == kTcEpiWarps) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(kTcTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  } else {
+    mbar_wait(&g->rowfull, 0);   // every epilogue thread observes the bulk copy itself (VAR 1 / 2 read their row's norms from it)
+    if (t < kTcRowTile) {
+      rows_from_col_row(sStage, sRowL, sRowD, t);
+      fence_proxy_async();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = g->tmem_base;
+
+  if (warp == kTcEpiWarps) {
+    // ===== producer (one lane): identical to v5 =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
+      const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD);
+      auto copy_unit = [&](int u) {
+        const int j0 = i0 + (v0 + u) * kTcUnit;
+        mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
+        bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
+      };
+      for (int u = 0; u < nu; ++u) {
+        const int s = u & 1;
+        mbar_wait(&g->colfull[u & 3], (u >> 2) & 1);
+        mbar_wait(&g->empty[s], ((u >> 1) & 1) ^ 1);   // epilogue done with the TMEM stage
+        tc_fence_after();
+        const uint32_t cb = smem_u32(sCol + (u & 3) * kTcColBytes);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128, umma_desc_sw128(rowd) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128 + 64, umma_desc_sw128(rowl) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+        tc_commit(&g->full[s]);
+        if (u + 3 < nu) {  // slot (u + 3) & 3 held unit u - 1: its MMAs must have retired before the slot is overwritten
+          if (u >= 1) mbar_wait(&g->full[(u - 1) & 1], ((u - 1) >> 1) & 1);
+          copy_unit(u + 3);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue: warp w owns TMEM lanes 32 (w & 3) .. + 31 = rows i0 + 32 (w & 3) + lane, columns 32 (w >> 2) .. + 31 of each unit =====
+    const int q = warp & 3, ch = warp >> 2;
+    const int r = 32 * q + lane;
+    const int i = i0 + r;
+    const ProbState* stp = d.st;
+    const float nt1s = stp->tcc[0], t0s = stp->tcc[1];
+    const float2 nt1 = make_float2(nt1s, nt1s), t0 = make_float2(t0s, t0s);
+    const uint32_t lcut_bits = __float_as_uint(stp->tcc[2]);   // lcut < 0:  L > lcut  <=>  bits(L) < bits(lcut) as unsigned
+    float Ti = 0.f;
+    uint32_t t2_bits = 0u;
+    if (VAR != 0) {
+      // p_i = 1/2 - 2 (r_s + r_d) of this row sits at K positions 18..20 of its operand row (three exact TF32 pieces)
+      const float4 c4 = *reinterpret_cast<const float4*>(sStage + r * 128 + ((4 ^ (r & 7)) << 4));
+      const float4 c5 = *reinterpret_cast<const float4*>(sStage + r * 128 + ((5 ^ (r & 7)) << 4));
+      const float pr = (c4.z + c4.w) + c5.x;
+      const float ri = fmaxf(0.25f - 0.5f * pr, 0.f) * 1.000001f;            // r_s + r_d, rounded up
+      const float Lb = -(4.f * (ri + stp->tc_pi) * 1.0001f + 1.f);            // <= every L~_ij of the row (error E_L included)
+      Ti = fmaf(Lb, nt1s, t0s) * 1.00001f;                                    // T(Lb) >= T(L~_ij): T decreases with L
+      t2_bits = __float_as_uint(Ti * Ti * 1.00001f);
+    }
+    const TposeConst tk = tpose_const(lane);
+    const bool rows_in = i0 + kTile <= n;
+    // units [ub, ue) of this item are interior: off the diagonal tile, all 64 columns and all 128 rows inside the problem
+    const int ub = v0 == 0 ? 2 : 0;
+    const int ue = rows_in ? max(0, min(nu, (n - i0) / kTcUnit - v0)) : 0;
+    int jc = i0 + v0 * kTcUnit + 32 * ch;                                     // first column of this warp's chunk in unit 0
+    uint32_t* rowp = d.adj + (size_t)min(i, n - 1) * d.pitch + (jc >> 5);     // += 2 words per unit
+    uint32_t* colp = d.adj + (size_t)(jc + lane) * d.pitch + (i0 >> 5) + q;   // += 64 rows per unit (dereferenced only inside the problem)
+    int* degp = d.deg + jc + lane;
+    const size_t colstep = (size_t)kTcUnit * d.pitch;
+    uint32_t tbase = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(ch * 32);
+    asm volatile("" : "+r"(tbase));   // keep it in a register (re-derived from the thread id per unit otherwise)
+    int rowdeg = 0;
+    uint32_t ph = 0;
+
+    uint32_t bar_full = smem_u32(&g->full[0]);          // full[S] at + 8 S, empty[S] at + 16 + 8 S
+    asm volatile("" : "+r"(bar_full));                  // kept in a register (re-derived from the CTA's shared window per unit otherwise)
+
+    auto unit32 = [&](auto stage_c, const int u) {
+      constexpr int S = decltype(stage_c)::value;
+      mbar_wait_a(bar_full + 8 * S, ph);
+      tc_fence_after();
+      uint32_t dm[32], lv[32];
+      tc_ld_32x32(tbase + S * 128, dm);
+      tc_ld_32x32(tbase + S * 128 + 64, lv);
+      tc_wait_ld();
+      // the accumulators are in registers: release the TMEM stage right away
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(bar_full + 16 + 8 * S);
+      // four independent 8-column accumulators; within one the higher column goes first, so column c ends in bit c & 7
+      uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      uint32_t gmin[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      bool aq[4] = {false, false, false, false};
+#pragma unroll
+      for (int c = 6; c >= 0; c -= 2) {
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const int cc = 8 * h + c;
+          const float2 D = make_float2(__uint_as_float(dm[cc]), __uint_as_float(dm[cc + 1]));
+          const float2 L = make_float2(__uint_as_float(lv[cc]), __uint_as_float(lv[cc + 1]));
+          const float2 G = f2fma(D, D, L);
+          wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
+          wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
+          lmin[h] = __vimin3_u32(lmin[h], lv[cc], lv[cc + 1]);
+          if (VAR == 0) {
+            const float2 Tb = f2fma(L, nt1, t0);
+            aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
+          } else if (VAR == 1) {
+            const float2 Q = f2mul(G, G);
+            gmin[h] = __vimin3_u32(gmin[h], __float_as_uint(Q.x), __float_as_uint(Q.y));
+          } else {
+            aq[h] |= !(fabsf(G.x) >= Ti) | !(fabsf(G.y) >= Ti);
+          }
+        }
+      }
+      uint32_t word = wq[0] + (wq[1] << 8) + (wq[2] << 16) + (wq[3] << 24);
+      bool fl[4];
+#pragma unroll
+      for (int h = 0; h < 4; ++h) fl[h] = (VAR == 1 ? (gmin[h] < t2_bits) : aq[h]) | (lmin[h] < lcut_bits);
+      const bool interior = (u >= ub) & (u < ue);
+      uint32_t mask = 0xffffffffu;
+      if (!interior) {
+        const int nc = n - jc;
+        mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
+        if (i >= n) mask = 0u;
+        if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
+        word &= mask;
+      }
+      if (fl[0] | fl[1] | fl[2] | fl[3]) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
+        uint32_t aw = 0;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          if (fl[h]) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const int cc = 8 * h + c;
+              const float Dv = __uint_as_float(dm[cc]), Lv = __uint_as_float(lv[cc]);
+              const float G = fmaf(Dv, Dv, Lv);
+              bool a;
+              if (VAR == 0) a = !(fabsf(G) >= fmaf(Lv, nt1s, t0s));
+              else if (VAR == 1) a = __float_as_uint(__fmul_rn(G, G)) < t2_bits;
+              else a = !(fabsf(G) >= Ti);
+              aw |= (a | (lv[cc] < lcut_bits)) ? (1u << cc) : 0u;
+            }
+          }
+        }
+        aw &= mask;
+        // into the warp's shared-memory buffer (flushed once per item): a global atomic with its L2 round trip here would make
+        // this warp lag a whole unit behind the others, and they share the TMEM stages
+        while (aw) {
+          const int c = __ffs(aw) - 1;
+          aw &= aw - 1;
+          const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+          const int pos = atomicAdd(&g->amb_cnt[warp], 1);
+          if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
+          else {  // buffer full (wide test bands): straight to the global list
+            const unsigned base = atomicAdd(&d.st->amb_count, 1u);
+            if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
+            else d.st->tc_overflow = 1;
+          }
+        }
+      }
+      if (interior) {
+        // off the diagonal tile, fully inside the problem: lane c receives the 32 row bits of column jc + c
+        const uint32_t tw = warp_transpose32_fast(word, tk);
+        *colp = tw;
+        if (tw) atomicAdd(degp, __popc(tw));
+        *rowp = word;
+      } else {
+        if (u >= ub) {
+          const uint32_t tw = warp_transpose32_fast(word, tk);
+          if (jc + lane < n) {
+            *colp = tw;
+            if (tw) atomicAdd(degp, __popc(tw));
+          }
+        }
+        if (i < n) *rowp = word;
+      }
+      rowdeg += __popc(word);
+      rowp += 2; colp += colstep; degp += kTcUnit; jc += kTcUnit;
+    };
+
+    // The same unit with the accumulators fetched 16 columns at a time (32 live registers instead of 64: the whole loop state
+    // fits the 96 registers two resident CTAs leave each thread) and four independent 4-column bit accumulators per half.
+    auto unit16 = [&](auto stage_c, const int u) {
+      constexpr int S = decltype(stage_c)::value;
+      mbar_wait_a(bar_full + 8 * S, ph);
+      tc_fence_after();
+      const bool interior = (u >= ub) & (u < ue);
+      uint32_t mask = 0xffffffffu;
+      if (!interior) {
+        const int nc = n - jc;
+        mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
+        if (i >= n) mask = 0u;
+        if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
+      }
+      uint32_t word = 0u, aw = 0u;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t dm[16], lv[16];
+        tc_ld_32x16(tbase + S * 128 + 16 * half, dm);
+        tc_ld_32x16(tbase + S * 128 + 64 + 16 * half, lv);
+        tc_wait_ld();
+        if (half == 1) {  // both halves are in registers: release the TMEM stage
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_a(bar_full + 16 + 8 * S);
+        }
+        uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4], gmin[4];
+        bool aq[4] = {false, false, false, false};
+#pragma unroll
+        for (int c = 2; c >= 0; c -= 2) {
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int cc = 4 * h + c;
+            const float2 D = make_float2(__uint_as_float(dm[cc]), __uint_as_float(dm[cc + 1]));
+            const float2 L = make_float2(__uint_as_float(lv[cc]), __uint_as_float(lv[cc + 1]));
+            const float2 G = f2fma(D, D, L);
+            wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
+            wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
+            lmin[h] = __vimin3_u32(c == 2 ? 0xffffffffu : lmin[h], lv[cc], lv[cc + 1]);
+            if (VAR == 0) {
+              const float2 Tb = f2fma(L, nt1, t0);
+              aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
+            } else if (VAR == 1) {
+              const float2 Q = f2mul(G, G);
+              gmin[h] = __vimin3_u32(c == 2 ? 0xffffffffu : gmin[h], __float_as_uint(Q.x), __float_as_uint(Q.y));
+            } else {
+              aq[h] |= !(fabsf(G.x) >= Ti) | !(fabsf(G.y) >= Ti);
+            }
+          }
+        }
+        word |= (wq[0] + (wq[1] << 4) + (wq[2] << 8) + (wq[3] << 12)) << (16 * half);
+        // first a combined test (one branch per half), per-group flags only on the rare path
+        const uint32_t lm = min(__vimin3_u32(lmin[0], lmin[1], lmin[2]), lmin[3]);
+        bool any = lm < lcut_bits;
+        if (VAR == 1) any |= min(__vimin3_u32(gmin[0], gmin[1], gmin[2]), gmin[3]) < t2_bits;
+        else any |= aq[0] | aq[1] | aq[2] | aq[3];
+        if (any) {
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const bool fl = (VAR == 1 ? (gmin[h] < t2_bits) : aq[h]) | (lmin[h] < lcut_bits);
+            if (fl) {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                const int cc = 4 * h + c;
+                const float Dv = __uint_as_float(dm[cc]), Lv = __uint_as_float(lv[cc]);
+                const float G = fmaf(Dv, Dv, Lv);
+                bool a;
+                if (VAR == 0) a = !(fabsf(G) >= fmaf(Lv, nt1s, t0s));
+                else if (VAR == 1) a = __float_as_uint(__fmul_rn(G, G)) < t2_bits;
+                else a = !(fabsf(G) >= Ti);
+                aw |= (a | (lv[cc] < lcut_bits)) ? (1u << (16 * half + cc)) : 0u;
+              }
+            }
+          }
+        }
+      }
+      word &= mask;
+      aw &= mask;
+      while (aw) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
+        const int c = __ffs(aw) - 1;
+        aw &= aw - 1;
+        const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+        const int pos = atomicAdd(&g->amb_cnt[warp], 1);
+        if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
+        else {  // buffer full (wide test bands): straight to the global list
+          const unsigned base = atomicAdd(&d.st->amb_count, 1u);
+          if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
+          else d.st->tc_overflow = 1;
+        }
+      }
+      if (interior) {
+        const uint32_t tw = warp_transpose32_fast(word, tk);
+        *colp = tw;
+        if (tw) atomicAdd(degp, __popc(tw));
+        *rowp = word;
+      } else {
+        if (u >= ub) {
+          const uint32_t tw = warp_transpose32_fast(word, tk);
+          if (jc + lane < n) {
+            *colp = tw;
+            if (tw) atomicAdd(degp, __popc(tw));
+          }
+        }
+        if (i < n) *rowp = word;
+      }
+      rowdeg += __popc(word);
+      rowp += 2; colp += colstep; degp += kTcUnit; jc += kTcUnit;
+    };
+
+#pragma unroll 1
+    for (int u = 0; u < nu; u += 2) {
+      if (LD16) {
+        unit16(StageC<0>{}, u);
+        if (u + 1 < nu) unit16(StageC<1>{}, u + 1);
+      } else {
+        unit32(StageC<0>{}, u);
+        if (u + 1 < nu) unit32(StageC<1>{}, u + 1);
+      }
+      ph ^= 1u;
+    }
+    if (i < n && rowdeg) atomicAdd(&d.deg[i], rowdeg);
+    __syncwarp();
+    const int cnt = min(g->amb_cnt[warp], kTcAmbBuf);
+    if (cnt > 0) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&d.st->amb_count, (unsigned)cnt);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      for (int k = lane; k < cnt; k += 32) {
+        if (base + k < (unsigned)d.amb_cap) d.amb_list[base + k] = g->amb_buf[warp][k];
+        else d.st->tc_overflow = 1;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kTcEpiWarps) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTcTmemCols) : "memory");
+  }
+}
+
+// B2R_G6 (A/B runs): 0 = v5 kernel; v6: 1 = T(L) band, 32-column loads; 2 = T(L) band, 16-column loads (default);
+// 3 = per-row band on G^2, 16-column loads; 4 = per-row band on G^2, 32-column loads; 5 = per-row band with compares, 16-column loads
+static int g6_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2R_G6");
+    v = (e && e[0] >= '0' && e[0] <= '5') ? e[0] - '0' : 2;
+  }
+  return v;
+}
+
+int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
+  static PerDeviceOnce attr;
+  attr.run([] {
+    cudaError_t e = cudaFuncSetAttribute(tim_graph5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    return e;
+  });
   const int T = (n_max + kTile - 1) / kTile;
-  graph_tc_prep_kernel<<<batch, 1024, 0, st>>>(d_desc, kp);
-  graph_tc_ops_kernel<<<dim3(T, batch), kTile, 0, st>>>(d_desc);
-  tim_graph5_kernel<<<dim3(tc_items(T), batch), kTcThreads, kTcSmemBytes, st>>>(d_desc, kp);
-  return 3 + launch_graph_fix(d_desc, batch, n_max, kp, st);
+  // prep + operand rows in one launch: about one CTA per SM (every slice re-reduces the problem's bounding boxes), never more
+  // slices than 128-row blocks
+  int slices = 148 / batch;
+  if (slices > T) slices = T;
+  if (slices < 1) slices = 1;
+  graph_tc_setup_kernel<<<dim3(slices, batch), 1024, 0, st>>>(d_desc, kp);
+  const dim3 grid(tc_items(T), batch);
+  switch (g6_variant()) {
+    case 0: tim_graph5_kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    case 1: tim_graph6_kernel<0, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    case 3: tim_graph6_kernel<1, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    case 4: tim_graph6_kernel<1, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    case 5: tim_graph6_kernel<2, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    default: tim_graph6_kernel<0, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+  }
+  return 2;
+}
+
+int launch_tim_graph_tc_and_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
+  return launch_tim_graph_tc(d_desc, batch, n_max, kp, st) + launch_graph_fix(d_desc, batch, n_max, kp, st);
 }
 
 }  // namespace b2r
@@ -615,12 +1169,146 @@ __global__ void __launch_bounds__(128, 1) graph_tc_debug_kernel(const ProbDesc* 
 }
 
 int launch_graph_tc_debug(const ProbDesc* d_desc, int prob, int bi, int v, float* out_dm, float* out_l, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(graph_tc_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    attr_set = true;
-  }
+  static PerDeviceOnce attr;
+  attr.run([] { return cudaFuncSetAttribute(graph_tc_debug_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); });
   graph_tc_debug_kernel<<<1, 128, 64 * 1024, st>>>(d_desc, prob, bi, v, out_dm, out_l);
+  return 1;
+}
+
+}  // namespace b2r
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Test hook (b2r_debug_tc_sweep): EVERY unit of one problem is recomputed on the tensor cores exactly as the filter kernel does and
+// compared on the device with fp64 -- (a) the exact sum of the same operand products (the accumulation error the band ASSUMES to be
+// below 2^-20 of the sum of |products|), (b) the values from the unrounded coordinates (the total error the band bounds by E_D, E_L).
+// grid = T (T + 1) units, 128 threads (thread = row).  out: [0] max accumulation ratio, [1] max |Dm~-Dm| / E_D, [2] max |L~-L| / E_L,
+// [3] pairs checked, [4] Pi, [5] E_D, [6] E_L.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace b2r {
+
+namespace {
+__device__ __forceinline__ float sw_elem(const unsigned char* tile, int r, int k) {
+  return *reinterpret_cast<const float*>(tile + r * 128 + ((((k >> 2) ^ (r & 7))) << 4) + (k & 3) * 4);
+}
+__device__ __forceinline__ void atomic_max_nonneg(double* addr, double v) {
+  atomicMax(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(v));
+}
+}  // namespace
+
+__global__ void __launch_bounds__(128, 1) graph_tc_sweep_kernel(const ProbDesc* __restrict__ descs, int prob, double* __restrict__ out) {
+  const ProbDesc d = descs[prob];
+  const ProbState* st = d.st;
+  const int n = d.n;
+  const int T = (n + kTile - 1) / kTile;
+  int p = blockIdx.x, bi = 0;
+  while (bi < T && p >= 2 * (T - bi)) { p -= 2 * (T - bi); ++bi; }
+  if (bi >= T) return;
+  const int v = p;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* sRowL = sm;
+  unsigned char* sRowD = sm + kTcRowBytes;
+  unsigned char* sCol = sm + 2 * kTcRowBytes;
+  unsigned char* sStage = sCol + kTcColBytes;
+  TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sStage + kTcRowBytes);
+  const int t = threadIdx.x, warp = t >> 5;
+  const unsigned char* ops = reinterpret_cast<const unsigned char*>(d.pts32);
+  const int i0 = bi * kTile;
+  const int j0 = i0 + v * kTcUnit;
+  if (t == 0) {
+    mbar_init(&g->rowfull, 1);
+    mbar_init(&g->full[0], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(&g->rowfull, kTcRowBytes + kTcColBytes);
+    bulk_g2s(sStage, ops + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
+    bulk_g2s(sCol, ops + (size_t)j0 * 128, kTcColBytes, &g->rowfull);
+  }
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  mbar_wait(&g->rowfull, 0);
+  rows_from_col_row(sStage, sRowL, sRowD, t);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = g->tmem_base;
+  if (t == 0) {
+    constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
+    const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD), cb = smem_u32(sCol);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem, umma_desc_sw128(rowd) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + 64, umma_desc_sw128(rowl) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
+    tc_commit(&g->full[0]);
+  }
+  mbar_wait(&g->full[0], 0);
+  tc_fence_after();
+  const int i = i0 + t;
+  const double kappa = st->kappa;
+  const double Pi = (double)st->tc_pi;
+  const double w22 = 2.384185791015625e-7;
+  const double E_L = w22 * (71.8 * Pi + 4.3), E_D = 45.9 * w22 * Pi;
+  double si[3] = {0, 0, 0}, di[3] = {0, 0, 0};
+  if (i < n) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { si[k] = (d.src[3 * (size_t)i + k] - st->ctr[k]) * kappa; di[k] = (d.dst[3 * (size_t)i + k] - st->ctr[3 + k]) * kappa; }
+  }
+  double worst_tc = 0.0, worst_d = 0.0, worst_l = 0.0;
+  unsigned checked = 0;
+#pragma unroll 1
+  for (int ch = 0; ch < 2; ++ch) {
+    uint32_t dm[32], lv[32];
+    const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)(ch * 32);
+    tc_ld_32x32(ta, dm);
+    tc_ld_32x32(ta + 64, lv);
+    tc_wait_ld();
+#pragma unroll 1
+    for (int c = 0; c < 32; ++c) {
+      const int cj = ch * 32 + c, j = j0 + cj;
+      if (i >= n || j >= n) continue;
+      double sd = 0.0, ad = 0.0, sl = 0.0, al = 0.0;
+      for (int k = 0; k < 32; ++k) {
+        const double col = (double)sw_elem(sCol, cj, k);
+        const double pd = (double)sw_elem(sRowD, t, k) * col, pl = (double)sw_elem(sRowL, t, k) * col;
+        sd += pd; ad += fabs(pd); sl += pl; al += fabs(pl);
+      }
+      const double tdm = (double)__uint_as_float(dm[c]), tl = (double)__uint_as_float(lv[c]);
+      if (ad > 0.0) worst_tc = fmax(worst_tc, fabs(tdm - sd) / ad);
+      if (al > 0.0) worst_tc = fmax(worst_tc, fabs(tl - sl) / al);
+      double A = 0.0, B = 0.0;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const double a = (d.src[3 * (size_t)j + k] - st->ctr[k]) * kappa - si[k];
+        const double b = (d.dst[3 * (size_t)j + k] - st->ctr[3 + k]) * kappa - di[k];
+        A += a * a; B += b * b;
+      }
+      worst_d = fmax(worst_d, fabs(tdm - (A - B)) / E_D);
+      worst_l = fmax(worst_l, fabs(tl - (1.0 - 2.0 * (A + B))) / E_L);
+      ++checked;
+    }
+  }
+  atomic_max_nonneg(out + 0, worst_tc);
+  atomic_max_nonneg(out + 1, worst_d);
+  atomic_max_nonneg(out + 2, worst_l);
+  if (checked) atomicAdd(out + 3, (double)checked);
+  if (blockIdx.x == 0 && t == 0) { out[4] = Pi; out[5] = E_D; out[6] = E_L; }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+  }
+}
+
+int launch_graph_tc_sweep(const ProbDesc* d_desc, int prob, int n, const KernelParams& kp, double* out, cudaStream_t st) {
+  static PerDeviceOnce attr;
+  attr.run([] { return cudaFuncSetAttribute(graph_tc_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); });
+  (void)kp;
+  const int T = (n + kTile - 1) / kTile;
+  graph_tc_sweep_kernel<<<T * (T + 1), 128, 64 * 1024, st>>>(d_desc, prob, out);
   return 1;
 }
 

@@ -33,7 +33,14 @@ constexpr int kMaxSplits = 16;
 constexpr int kGemmThreads = 192; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
 constexpr uint32_t kTileBytes = kBM * 128;                 // one k-block of one operand tile: 128 rows x 128 B
 constexpr uint32_t kOperandBytes = kKBlocks * kTileBytes;  // 64 KB
-constexpr double kEpsRel = 2.0e-5;  // |D~_ij - D_ij| <= kEpsRel * (|fq_i|^2 + |fr_j|^2), see DESIGN.md "NN error bound"
+// |D~_ij - D_ij| <= kEpsRel * (|fq_i - c|^2 + |fr_j - c|^2) for descriptors centred on c (nn_centre_kernel).  With u = 2^-24:
+//   fp32 copy of a centred coordinate x' = X (1 + d), |d| <= u;  3xTF32 split x' = hi + lo + r, |r| <= 2^-22 |x'|;
+//   dropped lo.lo and r terms: 3 * 2^-22 sum|x'y'|;  fp32 accumulation on the tensor core over K = 120: assumed within
+//   2^-18 of sum|products| (measured 2^-22 for K = 32 in the graph filter, tests/test_gpu_tc_sweep.py; 16x margin);
+//   with sum|x'y'| <= (nq + nr) / 2 and the factor 2 of -2 x.y:  (3 * 2^-22 + 2^-18 + 2u)(nq + nr) + norms and final fma (4u)
+//   = 4.9e-6 (nq + nr)  ->  6e-6.
+constexpr double kEpsRel = 6.0e-6;
+constexpr int kCentreRows = 4096;   // rows of the reference cloud whose mean is the common centre c
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -113,15 +120,36 @@ __device__ __forceinline__ float to_tf32(float x) {
 }
 
 // ---- prep -----------------------------------------------------------------------------------------------------------
+// Common centre of both descriptor sets: the mean of the first kCentreRows reference rows (one CTA, fixed summation order, so the
+// centre -- and with it every rounded operand -- is the same on every run).  Distances do not change under a common shift;
+// the error bound is relative to the CENTRED norms, which for FPFH histograms (every row sums to 300, norms ~ 1e4) are one to two
+// orders smaller than the raw ones.
+__global__ void __launch_bounds__(1024) nn_centre_kernel(const double* __restrict__ f, int n, int dim, double* __restrict__ centre) {
+  __shared__ double part[32][kKSeg];
+  const int rows = n < kCentreRows ? n : kCentreRows;
+  const int t = threadIdx.x % kKSeg, r0 = threadIdx.x / kKSeg;      // 1024 / 40 = 25 row lanes (threads 1000..1023 idle)
+  double s = 0.0;
+  if (r0 < 25 && t < dim)
+    for (int r = r0; r < rows; r += 25) s += f[(size_t)r * dim + t];
+  if (r0 < 25) part[r0][t] = s;
+  __syncthreads();
+  if (threadIdx.x < kKSeg) {
+    double a = 0.0;
+    for (int k = 0; k < 25; ++k) a += part[k][threadIdx.x];
+    centre[threadIdx.x] = (threadIdx.x < dim && rows > 0) ? a / rows : 0.0;
+  }
+}
+
 // out: [n_pad][128] floats.  role 0 (left operand): [hi | hi | lo | 0]; role 1 (right operand): [hi | lo | hi | 0].
-__global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__ f, int n, int dim, int n_pad, float* __restrict__ out_l,
-                                                      float* __restrict__ out_r, float* __restrict__ norm, unsigned int* __restrict__ norm_max) {
+__global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__ f, int n, int dim, int n_pad, const double* __restrict__ centre,
+                                                      float* __restrict__ out_l, float* __restrict__ out_r, float* __restrict__ norm,
+                                                      unsigned int* __restrict__ norm_max) {
   const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
   if (e >= (long long)n_pad * kKTot) return;
   const int row = (int)(e / kKTot), k = (int)(e % kKTot);
   const int seg = k / kKSeg, t = k % kKSeg;
   float x = 0.f;
-  if (row < n && t < dim && seg < 3) x = (float)f[(size_t)row * dim + t];
+  if (row < n && t < dim && seg < 3) x = (float)(f[(size_t)row * dim + t] - centre[t]);
   const float hi = to_tf32(x);
   const float lo = to_tf32(x - hi);
   out_l[e] = seg == 2 ? lo : hi;
@@ -130,8 +158,8 @@ __global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__
     float nv = CUDART_INF_F;
     if (row < n) {
       double s = 0;
-      for (int q = 0; q < dim; ++q) { const double v = f[(size_t)row * dim + q]; s += v * v; }
-      nv = (float)s;
+      for (int q = 0; q < dim; ++q) { const double v = f[(size_t)row * dim + q] - centre[q]; s += v * v; }
+      nv = __double2float_ru(s);                 // rounded up: the norms only enter error bounds and the approximate distance
       atomicMax(norm_max, __float_as_uint(nv));  // non-negative floats order like their bit patterns
     }
     norm[row] = nv;
@@ -337,8 +365,11 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 EncodeTiledFn encode_tiled() {
+  // process-wide (a driver entry point, not per-device state); guarded against two threads resolving it at once
   static EncodeTiledFn fn = nullptr;
   static bool tried = false;
+  static std::mutex mtx;
+  std::lock_guard<std::mutex> lock(mtx);
   if (!tried) {
     tried = true;
     void* p = nullptr;
@@ -399,10 +430,16 @@ size_t cand_bytes(int nq, int nr) {
   return 2 * pad256((size_t)rt * kBM * s * kTopK * 4) + 256;
 }
 
-b2r_status launch_prep(b2r_solver* s, const double* f, int dim, Prepped& p) {
+b2r_status launch_centre(b2r_solver* s, const double* f_ref, int n_ref, int dim, double* centre) {
+  nn_centre_kernel<<<1, 1024, 0, s->stream>>>(f_ref, n_ref, dim, centre);
+  ++s->launches;
+  return B2R_OK;
+}
+
+b2r_status launch_prep(b2r_solver* s, const double* f, int dim, const double* centre, Prepped& p) {
   CK(cudaMemsetAsync(p.norm_max, 0, 4, s->stream));
   const long long total = (long long)p.n_pad * kKTot;
-  nn_prep_kernel<<<(int)((total + 255) / 256), 256, 0, s->stream>>>(f, p.n, dim, p.n_pad, p.l, p.r, p.norm, p.norm_max);
+  nn_prep_kernel<<<(int)((total + 255) / 256), 256, 0, s->stream>>>(f, p.n, dim, p.n_pad, centre, p.l, p.r, p.norm, p.norm_max);
   ++s->launches;
   return B2R_OK;
 }
@@ -410,9 +447,9 @@ b2r_status launch_prep(b2r_solver* s, const double* f, int dim, Prepped& p) {
 // nn[i] = exact argmin_j |fq_i - fr_j|^2 via the tensor-core shortlist.  scratch: cand_bytes(nq, nr) bytes.
 b2r_status launch_direction(b2r_solver* s, const double* fq, const Prepped& q, const double* fr, const Prepped& r, int dim, char* scratch,
                             int* nn, double* dist, unsigned int* n_fallback) {
-  static bool attr = false;
+  static PerDeviceOnce attr;
   const size_t smem = 3 * (size_t)kOperandBytes + sizeof(GemmSmem) + 1024;
-  if (!attr) { CK(cudaFuncSetAttribute(nn_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+  CK(attr.run([&] { return cudaFuncSetAttribute(nn_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); }));
   const int rt = q.n_pad / kBM, ct = r.n_pad / kBN;
   const int splits = choose_splits(rt, ct);
   float* cand_v = (float*)scratch;
@@ -440,16 +477,19 @@ b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double
   if (nq == 0) return B2R_OK;
   if (dim > kKSeg || nr == 0) return b2r_nn_exact(s, fq_dev, nq, fr_dev, nr, dim, nn_dev, dist_dev);  // K = 3 x 40 TF32 columns at most
   CK(cudaSetDevice(s->device));
-  CK(s->d_nn.ensure(prepped_bytes(nq) + prepped_bytes(nr) + cand_bytes(nq, nr) + 1024));
+  CK(s->d_nn.ensure(prepped_bytes(nq) + prepped_bytes(nr) + cand_bytes(nq, nr) + 2048));
   char* p = (char*)s->d_nn.p;
   Prepped q, r;
   p = carve_prepped(p, nq, &q);
   p = carve_prepped(p, nr, &r);
   unsigned int* n_fb = (unsigned int*)p; p += 256;
+  double* centre = (double*)p; p += 512;
   CK(cudaMemsetAsync(n_fb, 0, 4, s->stream));
-  b2r_status st = launch_prep(s, fq_dev, dim, q);
+  b2r_status st = launch_centre(s, fr_dev, nr, dim, centre);
   if (st != B2R_OK) return st;
-  st = launch_prep(s, fr_dev, dim, r);
+  st = launch_prep(s, fq_dev, dim, centre, q);
+  if (st != B2R_OK) return st;
+  st = launch_prep(s, fr_dev, dim, centre, r);
   if (st != B2R_OK) return st;
   st = launch_direction(s, fq_dev, q, fr_dev, r, dim, p, nn_dev, dist_dev, n_fb);
   if (st != B2R_OK) return st;
@@ -479,16 +519,19 @@ b2r_status b2r_mutual_nn(b2r_solver* s, const double* fa_dev, int na, const doub
     return b2r_mutual_pairs(s, nn01_dev, na, nn10_dev, nb, pairs_dev, n_pairs_out);
   }
   const size_t cb = cand_bytes(na, nb) > cand_bytes(nb, na) ? cand_bytes(na, nb) : cand_bytes(nb, na);
-  CK(s->d_nn.ensure(prepped_bytes(na) + prepped_bytes(nb) + cb + 1024));
+  CK(s->d_nn.ensure(prepped_bytes(na) + prepped_bytes(nb) + cb + 2048));
   char* p = (char*)s->d_nn.p;
   Prepped a, b;
   p = carve_prepped(p, na, &a);
   p = carve_prepped(p, nb, &b);
   unsigned int* n_fb = (unsigned int*)p; p += 256;
+  double* centre = (double*)p; p += 512;
   CK(cudaMemsetAsync(n_fb, 0, 4, s->stream));
-  b2r_status st = launch_prep(s, fa_dev, dim, a);
+  b2r_status st = launch_centre(s, fb_dev, nb, dim, centre);   // one centre for both directions
   if (st != B2R_OK) return st;
-  st = launch_prep(s, fb_dev, dim, b);
+  st = launch_prep(s, fa_dev, dim, centre, a);
+  if (st != B2R_OK) return st;
+  st = launch_prep(s, fb_dev, dim, centre, b);
   if (st != B2R_OK) return st;
   st = launch_direction(s, fa_dev, a, fb_dev, b, dim, p, nn01_dev, nullptr, n_fb);   // same stream: scratch reuse is ordered
   if (st != B2R_OK) return st;

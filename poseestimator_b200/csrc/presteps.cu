@@ -954,8 +954,8 @@ constexpr int kKnnGridMinPoints = 4096;  // below this the brute-force kernel is
 
 static int launch_knn_brute(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
                             cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(knn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)knn_smem_bytes()); attr = true; }
+  static PerDeviceOnce attr;
+  attr.run([] { return cudaFuncSetAttribute(knn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)knn_smem_bytes()); });
   knn_kernel<<<(nq + kKnnWarps - 1) / kKnnWarps, kKnnWarps * 32, knn_smem_bytes(), st>>>(pts, n, queries, nq, K, radius, idx, d2, cnt);
   return 1;
 }
@@ -963,8 +963,8 @@ static int launch_knn_brute(const double* pts, int n, const double* queries, int
 // ws: knn_grid_ws_bytes(n) bytes of device scratch (256-byte aligned)
 static int launch_knn_grid(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
                            void* ws, cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(knn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)knn_grid_smem_bytes()); attr = true; }
+  static PerDeviceOnce attr;
+  attr.run([] { return cudaFuncSetAttribute(knn_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)knn_grid_smem_bytes()); });
   char* p = (char*)ws;
   auto take = [&](size_t bytes) { char* r = p; p += pad256_(bytes); return (void*)r; };
   unsigned long long* keys = (unsigned long long*)take((size_t)n * 8);

@@ -63,6 +63,9 @@ struct b2r_solver {
   bool pending = false;
   bool have_result = false;
   const uint32_t* ext_adj = nullptr;  // solve_from_adjacency
+  bool fused = false;                 // the last batch went through the fused tail kernel (tail.cu)
+  int handed_over = 0;                // problems of the last batch the fused tail handed to the multi-kernel path
+  int n_max = 0;
 
   bool profiling = false;
   cudaEvent_t ev[12] = {};

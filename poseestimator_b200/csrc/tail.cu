@@ -1,0 +1,232 @@
+// Fused tail: everything `solver.solve` (HelpersRealtime.py:166, registration_utils.py:261) does after the consistency graph, for one
+// registration per CTA, in ONE launch -- exact fix-up of the pairs the tensor-core filter listed, vertex-degree maxima and seeds,
+// greedy clique bound, (lb-1)-core pruning, and when the core IS the clique (the proof of maximality upstream's PMC reaches through
+// max_core + 1 == lb, A.5-4) the chain TIMs + GNC-TLS rotation (A.6) and the adaptive-voting translation (A.7).
+//
+// Why: the stages are tiny and strictly dependent (SURVEY 8a-4 .. a-6: "latency only -> batch across detections"); as eight
+// grid-wide launches of ~64 CTAs they cost 0.29 ms per 64 x 5000 batch, three quarters of it launch gaps and cold first touches.
+// Problems are independent, so a CTA carries one from the graph to the pose without any grid-wide synchronisation.
+//
+// A problem the fused path cannot finish is HANDED OVER untouched to the multi-kernel path (clique.cu / rt.cu), which b2r_sync
+// launches for the batch when it finds ProbState::tail_done == 0:
+//   tail_why 1  the graph itself is not final (fp32 path refused the problem or its pair list overflowed): fp64 filter first
+//   tail_why 2  the (lb-1)-core is larger than the greedy clique: the exact branch and bound has to decide
+// Results are identical on both paths: same heuristic rule, same peel, same rotation / translation bodies (rt.cuh).
+#include "clique_dev.cuh"
+#include "exact.cuh"
+#include "rt.cuh"
+
+namespace b2r {
+
+constexpr int kTailThreads = 3 * kRtThreads;   // 768: the translation stage needs exactly three groups of kRtThreads
+constexpr int kTailWarps = kTailThreads / 32;
+#ifndef B2R_HEU_SEEDS
+#define B2R_HEU_SEEDS 2
+#endif
+
+struct TailShared {
+  unsigned long long key[8];
+  unsigned long long deg_sum;
+  int lb, changed, cnt, base;
+  int scan[40];
+};
+
+// ascending list of the set bits of `bits` (Wb words) as 16-bit ids; returns the count (uniform)
+__device__ int tail_list_bits(const uint32_t* bits, int Wb, unsigned short* list, TailShared* ts) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (threadIdx.x == 0) ts->base = 0;
+  __syncthreads();
+  for (int w0 = 0; w0 < Wb; w0 += kTailThreads) {
+    const int w = w0 + threadIdx.x;
+    const uint32_t word = (w < Wb) ? bits[w] : 0u;
+    const int c = __popc(word);
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) ts->scan[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int x = lane < kTailWarps ? ts->scan[lane] : 0, xi = x;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, xi, o); if (lane >= o) xi += t; }
+      ts->scan[lane] = xi - x;
+      if (lane == 31) ts->scan[32] = xi;
+    }
+    __syncthreads();
+    int pos = ts->base + ts->scan[warp] + incl - c;
+    uint32_t b = word;
+    while (b) { list[pos++] = (unsigned short)(32 * w + (__ffs(b) - 1)); b &= b - 1; }
+    __syncthreads();
+    if (threadIdx.x == 0) ts->base += ts->scan[32];
+    __syncthreads();
+  }
+  return ts->base;
+}
+
+// mode 0: the graph comes from the tensor-core filter of this batch (pair list to fix, degrees accumulated by the filter);
+// mode 1: the graph is final and degree_kernel has run (other filters, estimate_scaling, b2r_solve_from_adjacency)
+__global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* __restrict__ descs, KernelParams kp, int mode) {
+  extern __shared__ __align__(16) unsigned char tsm[];
+  __shared__ TailShared ts;
+  const ProbDesc d = descs[blockIdx.x];
+  ProbState* st = d.st;
+  const int n = d.n;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int W = words_for(n), Wb = (n + 31) >> 5;
+  const long long clk0 = clock64();
+  auto stamp = [&](int k) { if (tid == 0) st->tail_clk[k] = (unsigned int)(clock64() - clk0); };
+
+  if (mode == 0) {
+    if (!st->use32 || st->tc_overflow) {   // uniform: the state was written by earlier kernels
+      if (tid == 0) st->tail_why = 1;
+      return;
+    }
+    // ---- 1. exact decision of the listed pairs (graph_fix_kernel's first half) ----
+    const unsigned cnt = min(st->amb_count, (unsigned)d.amb_cap);
+    for (unsigned idx = tid; idx < cnt; idx += kTailThreads) fix_listed_pair(d.src, d.dst, d.adj, d.pitch, d.deg, d.amb_list[idx], kp.beta);
+    if (tid < 8) ts.key[tid] = 0ull;
+    if (tid == 8) ts.deg_sum = 0ull;
+    __threadfence();
+    __syncthreads();
+    stamp(0);
+    // ---- 2. degree maxima, 2 * edges, seed of every id class (degree_kernel's fast path) ----
+    {
+      unsigned long long key = 0ull, sum = 0ull;   // kTailThreads % 8 == 0: a thread only ever sees vertices of class tid & 7
+      for (int v = tid; v < n; v += kTailThreads) {
+        const int c = __ldcg(d.deg + v);
+        sum += (unsigned long long)c;
+        const unsigned long long k = ((unsigned long long)c << 32) | (unsigned long long)(0xffffffffu - (unsigned)v);
+        key = k > key ? k : key;
+      }
+#pragma unroll
+      for (int o = 8; o <= 16; o <<= 1) {
+        const unsigned long long other = __shfl_xor_sync(FULL, key, o);
+        key = other > key ? other : key;
+      }
+      sum = (unsigned long long)__reduce_add_sync(FULL, (unsigned)sum);
+      if (lane < 8 && key) atomicMax(&ts.key[lane], key);
+      if (lane == 0) atomicAdd(&ts.deg_sum, sum);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      unsigned long long m = 0;
+      for (int k = 0; k < 8; ++k) { st->seed_key[k] = ts.key[k]; m = ts.key[k] > m ? ts.key[k] : m; }
+      st->max_deg = (int)(m >> 32);
+      st->deg_sum = ts.deg_sum;
+      st->slow_pairs = cnt;
+      st->deg_ready = 1;
+    }
+  } else {
+    if (tid < 8) ts.key[tid] = st->seed_key[tid];
+    __syncthreads();
+  }
+
+  stamp(1);
+  // ---- 3. greedy clique bound from the seeds of the first id classes, one after the other (heuristic_block_kernel) ----
+  uint32_t* sh = reinterpret_cast<uint32_t*>(tsm);
+  if (tid == 0) ts.lb = 0;
+  __syncthreads();
+  unsigned long long heu_key = 0ull;
+  for (int k = 0; k < B2R_HEU_SEEDS; ++k) {
+    const unsigned long long skey = ts.key[k];
+    if (skey == 0ull) continue;
+    const int v = (int)(0xffffffffu - (unsigned)(skey & 0xffffffffu));
+    const int size = heuristic_seed_cta<kTailThreads, true>(d, v, sh, &ts.lb);
+    __syncthreads();
+    if (size > 0) {
+      const unsigned long long hk = ((unsigned long long)size << 32) | (unsigned long long)(0xffffffffu - (unsigned)v);
+      heu_key = hk > heu_key ? hk : heu_key;
+      if (tid == 0 && size > ts.lb) ts.lb = size;
+    }
+    __syncthreads();
+  }
+  const int lb = ts.lb;
+  stamp(2);
+
+  // ---- 4. (lb-1)-core of the graph (prune_kernel): alive bitset + member list in shared memory, one warp per member ----
+  const int T = max(lb - 1, 0);
+  uint32_t* alive = sh;                                        // W words
+  unsigned short* list = reinterpret_cast<unsigned short*>(sh + W);   // n entries
+  for (int w = tid; w < W; w += kTailThreads) alive[w] = 0u;
+  __syncthreads();
+  for (int v0 = 0; v0 < n; v0 += kTailThreads) {
+    const int v = v0 + tid;
+    const bool a = v < n && __ldcg(d.deg + v) >= T;
+    const uint32_t bal = __ballot_sync(FULL, a);
+    if (lane == 0 && (v >> 5) < W) alive[v >> 5] = bal;
+  }
+  int n_alive = 0;
+  for (;;) {
+    n_alive = tail_list_bits(alive, Wb, list, &ts);
+    if (tid == 0) ts.changed = 0;
+    __syncthreads();
+    if (T > 0) {
+      for (int m0 = warp; m0 < n_alive; m0 += 4 * kTailWarps) {
+        int c[4], ids[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int m = m0 + q * kTailWarps;
+          ids[q] = m < n_alive ? (int)list[m] : -1;
+          c[q] = 0;
+          if (ids[q] >= 0) {
+            const uint32_t* row = d.adj + (size_t)ids[q] * d.pitch;
+            for (int w = lane; w < W; w += 32) c[q] += __popc(__ldcg(row + w) & alive[w]);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (ids[q] < 0) continue;
+          const int cq = __reduce_add_sync(FULL, c[q]);
+          if (cq < T && lane == 0) { atomicAnd(&alive[ids[q] >> 5], ~(1u << (ids[q] & 31))); ts.changed = 1; }
+        }
+      }
+    }
+    __syncthreads();
+    if (!ts.changed) break;
+  }
+  // Note: a vertex counted against neighbours that die in the same pass is caught by the next pass (the loop ends on a pass
+  // without removals), so the fixed point is the T-core whatever the order -- the same set prune_kernel leaves.
+  stamp(3);
+  const int Wc = (((n_alive + 31) >> 5) + 3) & ~3;
+  for (int m = tid; m < n_alive; m += kTailThreads) d.ids[m] = (int)list[m];
+  if (tid == 0) {
+    st->lb = lb; st->heu_key = heu_key;
+    st->T = T; st->n_alive = n_alive; st->Wc = Wc; st->omega = lb;
+    if (Wc > kMaxCompactWords) st->flags |= FLAG_COMPACT_TOO_LARGE;
+  }
+  if (n_alive != lb || lb <= 0) {   // the core is larger than the bound: the exact search decides (multi-kernel path)
+    if (tid == 0) st->tail_why = 2;
+    return;
+  }
+  // ---- 5. the (lb-1)-core has exactly lb vertices, each adjacent to the lb-1 others: it is the unique maximum clique ----
+  for (int m = tid; m < n_alive; m += kTailThreads) d.clique[m] = (int)list[m];
+  if (tid == 0) st->clique_size = lb;
+  __threadfence_block();
+  __syncthreads();
+  stamp(4);
+
+  // ---- 6. rotation on the first thread group, then the three translation axes on all three ----
+  if (tid < kRtThreads) rotation_body(d, kp, 4);
+  __syncthreads();
+  stamp(5);
+  translation_body(d, kp, reinterpret_cast<double*>(tsm));
+  __syncthreads();
+  stamp(6);
+  if (tid == 0) st->tail_done = 1;
+}
+
+size_t tail_smem_bytes(int n_max) {
+  const size_t tr = 3 * kTrGroupDoubles * sizeof(double);
+  const size_t he = heuristic_smem_bytes(n_max);
+  return (tr > he ? tr : he) + 16;
+}
+
+int launch_tail(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, int mode, cudaStream_t st) {
+  static PerDeviceOnce attr;
+  attr.run([] { return cudaFuncSetAttribute(tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tail_smem_bytes(kMaxN)); });
+  tail_kernel<<<batch, kTailThreads, tail_smem_bytes(n_max), st>>>(d_desc, kp, mode);
+  return 1;
+}
+
+}  // namespace b2r

@@ -60,6 +60,8 @@ class PreSteps:
             p = torch.from_numpy(np.ascontiguousarray(p, np.float64)).to(self._dev)
         if p.dtype != torch.float64 or p.ndim != 2:
             raise TypeError("expected a float64 [n, d] array")
+        if p.device != self._dev:   # a raw pointer of another device would fault inside the handle's kernels
+            raise TypeError(f"tensor lives on {p.device} but this handle is bound to {self._dev}")
         return p.contiguous()
 
     def _empty(self, shape, dtype):

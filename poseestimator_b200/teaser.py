@@ -69,7 +69,7 @@ class _Params:
         self.max_clique_exact_solution = True  # deprecated upstream: False -> PMC_HEU
         self.max_clique_time_limit = 3000.0
         self.max_clique_num_threads = 0
-        # extensions of this implementation (not in upstream)
+        # test hooks of this implementation (not in upstream, not in b2r_params: applied through include/b2r_debug.h)
         self.graph_exact_only = False
         self.graph_filter_tau = 0.0
 
@@ -92,9 +92,13 @@ class _Params:
             rotation_cost_threshold=float(self.rotation_cost_threshold), rotation_tim_graph=int(self.rotation_tim_graph),
             inlier_selection_mode=mode, kcore_heuristic_threshold=float(self.kcore_heuristic_threshold),
             max_clique_time_limit=float(self.max_clique_time_limit), max_clique_num_threads=int(self.max_clique_num_threads),
-            rotation_noise_bound=float(rotation_noise_bound), graph_exact_only=int(self.graph_exact_only),
-            graph_filter_tau=float(self.graph_filter_tau),
+            rotation_noise_bound=float(rotation_noise_bound),
         )
+
+    def _apply_debug(self, handle) -> None:
+        """graph_exact_only / graph_filter_tau are test hooks: b2r_debug_set_graph_filter (include/b2r_debug.h)."""
+        if int(self.graph_exact_only) or float(self.graph_filter_tau) > 0:
+            _lib.check(handle, _lib.lib().b2r_debug_set_graph_filter(handle, int(self.graph_exact_only), float(self.graph_filter_tau)))
 
     def __repr__(self):
         return "<Params " + " ".join(f"{k}={getattr(self, k)!r}" for k in self.__slots__) + ">"
@@ -150,6 +154,7 @@ class RobustRegistrationSolver:
         st = L.b2r_create(C.byref(cp), self._device, C.c_void_p(int(stream) if stream else None), C.byref(self._h))
         if st != 0:
             raise RuntimeError(f"poseestimator_b200: b2r_create failed ({_lib.STATUS_NAMES.get(st, st)})")
+        self._params._apply_debug(self._h)
         self._src = self._dst = None
         self._n = 0
         self._solved = False
@@ -175,6 +180,7 @@ class RobustRegistrationSolver:
         self._rot_nb = float(self._params.noise_bound)
         cp = self._params._to_c(self._rot_nb)
         _lib.check(self._h, _lib.lib().b2r_reset(self._h, C.byref(cp)))
+        _lib.check(self._h, _lib.lib().b2r_debug_set_graph_filter(self._h, int(self._params.graph_exact_only), float(self._params.graph_filter_tau)))
         self._solved = False
         self._solution = RegistrationSolution()
         self._pending_params = None
@@ -193,6 +199,8 @@ class RobustRegistrationSolver:
             if (src.dtype != torch.float64 or dst.dtype != torch.float64 or src.dim() != 2 or src.shape[0] != 3
                     or src.shape != dst.shape):
                 raise TypeError("solve(): CUDA tensors must be float64 of identical shape (3, N)")
+            if src.device.index != self._device or dst.device.index != self._device:
+                raise TypeError(f"solve(): tensors live on {src.device} / {dst.device} but this solver is bound to cuda:{self._device}")
             if src.stride() != dst.stride():  # bring both to the packed column-major layout
                 src, dst = src.T.contiguous().T, dst.T.contiguous().T
             torch.cuda.current_stream(src.device).synchronize()  # the library runs on its own stream

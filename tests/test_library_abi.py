@@ -8,8 +8,8 @@ from poseestimator_b200 import _lib
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared_symbols():
-    txt = open(os.path.join(ROOT, "include", "b2r.h")).read()
+def _declared_symbols(header="b2r.h"):
+    txt = open(os.path.join(ROOT, "include", header)).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     return sorted(set(re.findall(r"\b(b2r_[a-z0-9_]+)\s*\(", txt)))
 
@@ -21,6 +21,11 @@ def test_header_symbols_are_exported():
     missing = [n for n in names if not hasattr(L, n)]
     assert not missing, missing
     assert sorted(_lib.EXPORTS) == names, set(names) ^ set(_lib.EXPORTS)
+    # the test hooks live in their own header, outside the drop-in boundary
+    dbg = _declared_symbols("b2r_debug.h")
+    assert not [n for n in dbg if not hasattr(L, n)]
+    assert sorted(_lib.DEBUG_EXPORTS) == dbg, set(dbg) ^ set(_lib.DEBUG_EXPORTS)
+    assert not [n for n in names if n.startswith("b2r_debug")]
 
 
 def test_no_device_means_error_not_fallback():

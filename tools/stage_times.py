@@ -20,3 +20,6 @@ for it in range(R + 2):
         for k, v in bs.timings_ms().items(): acc[k] = acc.get(k, 0) + v / R
 print(f"B={B} N={N} ratio={ratio}", {k: round(v, 4) for k, v in acc.items()})
 print(" stats0", {k: v for k, v in bs.stats(0).items() if k in ("n_edges", "heuristic_lb", "n_pruned", "omega", "clique_size", "bnb_nodes", "graph_slow_pairs", "gnc_iterations")})
+if bs.stats(0).get("fused_tail"):
+    for i in (0, 1, B - 1):
+        print(" tail cycles", i, bs.tail_cycles(i))
