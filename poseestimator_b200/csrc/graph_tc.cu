@@ -134,16 +134,6 @@ __device__ __forceinline__ float2 f2fma(float2 a, float2 b, float2 c) {
   return r;
 }
 
-__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
-#pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) {
-    const uint32_t m = s == 16 ? 0x0000ffffu : s == 8 ? 0x00ff00ffu : s == 4 ? 0x0f0f0f0fu : s == 2 ? 0x33333333u : 0x55555555u;
-    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s);
-    x = (lane & s) ? ((x & ~m) | ((y & ~m) >> s)) : ((x & m) | ((y & m) << s));
-  }
-  return x;
-}
-
 // The same 32 x 32 bit transpose in 13 instructions instead of ~50: the two byte-granular steps are one PRMT each (per-lane
 // selector), the three sub-byte steps one rotate (per-lane amount) + one LOP3 bit-select (per-lane mask) each.
 struct TposeConst { uint32_t sel16, sel8, km4, km2, km1; int sh4, sh2, sh1; };
@@ -229,52 +219,6 @@ __device__ bool tc_write_constants(ProbState* st, const double (&lo6)[6], const 
   return ok;
 }
 
-__global__ void __launch_bounds__(1024) graph_tc_prep_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
-  const ProbDesc d = descs[blockIdx.x];
-  const int n = d.n;
-  const int t = threadIdx.x;
-  double mn[6], mx[6];
-#pragma unroll
-  for (int k = 0; k < 6; ++k) { mn[k] = CUDART_INF; mx[k] = -CUDART_INF; }
-  bool bad = false;
-  for (int i = t; i < n; i += 1024) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      const double a = d.src[3 * (size_t)i + k], b = d.dst[3 * (size_t)i + k];
-      bad |= !(fabs(a) <= 1.79e308) | !(fabs(b) <= 1.79e308);
-      mn[k] = fmin(mn[k], a); mx[k] = fmax(mx[k], a);
-      mn[3 + k] = fmin(mn[3 + k], b); mx[3 + k] = fmax(mx[3 + k], b);
-    }
-  }
-  __shared__ double s_mn[32][6], s_mx[32][6];
-  __shared__ int s_bad;
-  if (t == 0) s_bad = 0;
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < 6; ++k) {
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
-      mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
-      mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
-    }
-  }
-  if ((t & 31) == 0) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) { s_mn[t >> 5][k] = mn[k]; s_mx[t >> 5][k] = mx[k]; }
-  }
-  if (bad) atomicOr(&s_bad, 1);
-  __syncthreads();
-  if (t == 0) {
-    double lo6[6], hi6[6];
-    for (int k = 0; k < 6; ++k) {
-      double lo = s_mn[0][k], hi = s_mx[0][k];
-      for (int w = 1; w < 32; ++w) { lo = fmin(lo, s_mn[w][k]); hi = fmax(hi, s_mx[w][k]); }
-      lo6[k] = lo; hi6[k] = hi;
-    }
-    tc_write_constants(d.st, lo6, hi6, s_bad != 0, n, kp);
-  }
-}
-
 // ---------------------------------------------------------------------------------------------------------------------
 // operand rows (K = 32 TF32 values = 128 bytes = 8 chunks of 16 bytes, chunk c of row r stored at c ^ (r & 7))
 //   k:      0-2     3-5     6-8     9-11    12-14   15-17   18-20    21-23    24-26    27-29   30-31
@@ -350,7 +294,9 @@ struct TcSmemCtl {
 
 constexpr int kTcRowBytes = kTcRowTile * 128;   // 16 KB
 constexpr int kTcColBytes = kTcUnit * 128;      // 8 KB
-constexpr int kTcSmemBytes = 83 * 1024;         // 2 x 16 KB + 4 x 8 KB + 1 KB control + 16 KB staging + alignment slack; two CTAs per SM by registers (2 x 288 x 96) and TMEM (2 x 256 columns)
+constexpr int kTcCtlBytes = 3 * 1024;           // TcSmemCtl (barriers + the warps' pair buffers)
+static_assert(sizeof(TcSmemCtl) <= kTcCtlBytes, "control block overlaps the staging tile");
+constexpr int kTcSmemBytes = 2 * kTcRowBytes + 4 * kTcColBytes + kTcCtlBytes + kTcRowBytes + 1024;   // + alignment slack = 84 KB; two CTAs per SM by registers (2 x 288 x 96) and TMEM (2 x 256 columns)
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -387,20 +333,6 @@ __device__ __forceinline__ void tc_store_operand_row(const ProbDesc& d, const do
   }
   const Split sp = split_record(a, b);
   store_col_row(reinterpret_cast<unsigned char*>(d.pts32), i, sp);
-}
-
-__global__ void __launch_bounds__(kTile) graph_tc_ops_kernel(const ProbDesc* __restrict__ descs) {
-  const ProbDesc d = descs[blockIdx.y];
-  const ProbState* st = d.st;
-  if (!st->use32) return;
-  const int n = d.n;
-  const int n_pad = (n + kTile - 1) / kTile * kTile;
-  const int i = blockIdx.x * kTile + threadIdx.x;
-  if (i >= n_pad) return;
-  double ctr[6];
-#pragma unroll
-  for (int k = 0; k < 6; ++k) ctr[k] = st->ctr[k];
-  tc_store_operand_row(d, ctr, st->kappa, i, n);
 }
 
 // prep + operand rows in ONE launch: grid = (slices, batch).  Every CTA of a problem reduces the bounding boxes of the whole
@@ -473,216 +405,31 @@ __host__ __device__ inline int tc_items(int T) {
   return s;
 }
 
-__global__ void __launch_bounds__(kTcThreads, 2) tim_graph5_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
-  const ProbDesc d = descs[blockIdx.y];
-  const int n = d.n;
-  if (!d.st->use32) return;
-  const int T = (n + kTile - 1) / kTile;
-  int p = blockIdx.x, bi = 0;
-  int per = (2 * T + kTcUnitsPerItem - 1) / kTcUnitsPerItem;
-  while (bi < T && p >= per) { p -= per; ++bi; per = (2 * (T - bi) + kTcUnitsPerItem - 1) / kTcUnitsPerItem; }
-  if (bi >= T) return;
-  const int v0 = p * kTcUnitsPerItem;
-  const int nu = min(kTcUnitsPerItem, 2 * (T - bi) - v0);
-  const int i0 = bi * kTile;
-
-  extern __shared__ __align__(1024) unsigned char smem_raw[];
-  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  unsigned char* sRowL = sm;
-  unsigned char* sRowD = sm + kTcRowBytes;
-  unsigned char* sCol = sm + 2 * kTcRowBytes;   // ring of 4 slots
-  TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sm + 2 * kTcRowBytes + 4 * kTcColBytes);
-  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const unsigned char* ops = reinterpret_cast<const unsigned char*>(d.pts32);
-  const unsigned char* ops_col = ops;
-  unsigned char* sStage = sm + 2 * kTcRowBytes + 4 * kTcColBytes + 1024;   // column rows of the CTA's own 128 points (16 KB)
-
-  if (t == 32 * kTcEpiWarps) {
-    mbar_init(&g->rowfull, 1);
-    for (int s = 0; s < 4; ++s) mbar_init(&g->colfull[s], 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(&g->full[s], 1); mbar_init(&g->empty[s], kTcEpiWarps); }
-    for (int w = 0; w < kTcEpiWarps; ++w) g->amb_cnt[w] = 0;
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    mbar_expect_tx(&g->rowfull, kTcRowBytes);
-    bulk_g2s(sStage, ops_col + (size_t)i0 * 128, kTcRowBytes, &g->rowfull);
-    for (int u = 0; u < 3 && u < nu; ++u) {  // the first column units start travelling before the set-up barrier
-      const int v = v0 + u;
-      const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
-      mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
-      bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
-    }
-  }
-  __syncthreads();
-  if (warp == kTcEpiWarps) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(kTcTmemCols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  } else if (t < kTcRowTile) {
-    mbar_wait(&g->rowfull, 0);
-    rows_from_col_row(sStage, sRowL, sRowD, t);
-    fence_proxy_async();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = g->tmem_base;
-
-  if (warp == kTcEpiWarps) {
-    // ===== producer (one lane): bulk copies of the pre-swizzled operand rows, then the eight MMAs (4 k-steps x {Dm, L}) per unit.
-    // Column units travel through a ring of four 8 KB slots, three units ahead of the MMAs. =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
-      const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD);
-      auto copy_unit = [&](int u) {
-        const int v = v0 + u;
-        const int j0 = (bi + (v >> 1)) * kTile + (v & 1) * kTcUnit;
-        mbar_expect_tx(&g->colfull[u & 3], kTcColBytes);
-        bulk_g2s(sCol + (u & 3) * kTcColBytes, ops_col + (size_t)j0 * 128, kTcColBytes, &g->colfull[u & 3]);
-      };
-      for (int u = 0; u < nu; ++u) {
-        const int s = u & 1;
-        mbar_wait(&g->colfull[u & 3], (u >> 2) & 1);
-        mbar_wait(&g->empty[s], ((u >> 1) & 1) ^ 1);   // epilogue done with the TMEM stage
-        tc_fence_after();
-        const uint32_t cb = smem_u32(sCol + (u & 3) * kTcColBytes);
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128, umma_desc_sw128(rowd) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks) tc_mma_tf32(tmem + s * 128 + 64, umma_desc_sw128(rowl) + 2 * ks, umma_desc_sw128(cb) + 2 * ks, idesc, ks != 0 ? 1u : 0u);
-        tc_commit(&g->full[s]);
-        if (u + 3 < nu) {  // slot (u + 3) & 3 held unit u - 1: its MMAs must have retired before the slot is overwritten
-          if (u >= 1) mbar_wait(&g->full[(u - 1) & 1], ((u - 1) >> 1) & 1);
-          copy_unit(u + 3);
-        }
-      }
-    }
-    __syncwarp();
-  } else {
-    // ===== epilogue: warp w owns TMEM lanes 32 (w & 3) .. + 31 = rows i0 + 32 (w & 3) + lane, columns 32 (w >> 2) .. + 31 of each unit =====
-    const int q = warp & 3, ch = warp >> 2;
-    const int i = i0 + 32 * q + lane;
-    const float2 nt1 = make_float2(d.st->tcc[0], d.st->tcc[0]), t0 = make_float2(d.st->tcc[1], d.st->tcc[1]);
-    const float lcut = d.st->tcc[2];
-    const uint32_t lcut_bits = __float_as_uint(lcut);   // lcut < 0:  L > lcut  <=>  bits(L) < bits(lcut) as unsigned
-    const bool rows_in = i0 + kTile <= n;
-    int rowdeg = 0;
-    for (int u = 0; u < nu; ++u) {
-      const int s = u & 1;
-      const int v = v0 + u;
-      const int bj = bi + (v >> 1);
-      const int j0 = bj * kTile + (v & 1) * kTcUnit;
-      const bool interior = rows_in && (j0 + kTcUnit <= n) && (bj != bi);
-      mbar_wait(&g->full[s], (u >> 1) & 1);
-      tc_fence_after();
-      uint32_t dm[32], lv[32];
-      const uint32_t ta = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * 128 + ch * 32);
-      tc_ld_32x32(ta, dm);
-      tc_ld_32x32(ta + 64, lv);
-      tc_wait_ld();
-      // the accumulators are in registers: release the TMEM stage right away
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&g->empty[s]);
-      // four independent 8-column accumulators (one funnel-shift / predicate chain of 64 would be latency-bound);
-      // within an accumulator the higher column goes first, so column c of the chunk ends in bit c & 7
-      uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      bool aq[4] = {false, false, false, false};
-#pragma unroll
-      for (int c = 6; c >= 0; c -= 2) {
-#pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          const int cc = 8 * h + c;
-          const float2 D = make_float2(__uint_as_float(dm[cc]), __uint_as_float(dm[cc + 1]));
-          const float2 L = make_float2(__uint_as_float(lv[cc]), __uint_as_float(lv[cc + 1]));
-          const float2 G = f2fma(D, D, L);
-          const float2 Tb = f2fma(L, nt1, t0);
-          wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
-          wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
-          aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
-          lmin[h] = __vimin3_u32(lmin[h], lv[cc], lv[cc + 1]);
-        }
-      }
-      uint32_t word = wq[0] + (wq[1] << 8) + (wq[2] << 16) + (wq[3] << 24);
-      const bool amb = aq[0] | aq[1] | aq[2] | aq[3] | (min(min(lmin[0], lmin[1]), min(lmin[2], lmin[3])) < lcut_bits);
-      const int jc = j0 + 32 * ch;
-      uint32_t mask = 0xffffffffu;
-      if (!interior) {
-        const int nc = n - jc;
-        mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
-        if (i >= n) mask = 0u;
-        if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
-        word &= mask;
-      }
-      if (amb) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
-        uint32_t aw = 0;
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          const float Dv = __uint_as_float(dm[c]), Lv = __uint_as_float(lv[c]);
-          const float G = fmaf(Dv, Dv, Lv), Tb = fmaf(Lv, nt1.x, t0.x);
-          aw |= (!(fabsf(G) >= Tb) | (lv[c] < lcut_bits)) ? (1u << c) : 0u;
-        }
-        aw &= mask;
-        // into the warp's shared-memory buffer (flushed once per item): a global atomic with its L2 round trip here would make
-        // this warp lag a whole unit behind the others, and they share the TMEM stages
-        while (aw) {
-          const int c = __ffs(aw) - 1;
-          aw &= aw - 1;
-          const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
-          const int pos = atomicAdd(&g->amb_cnt[warp], 1);
-          if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
-          else {  // buffer full (wide test bands): straight to the global list
-            const unsigned base = atomicAdd(&d.st->amb_count, 1u);
-            if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
-            else d.st->tc_overflow = 1;
-          }
-        }
-      }
-      if (bj != bi) {  // transposed block: lane c receives the 32 row bits of column jc + c
-        const uint32_t tw = warp_transpose32(word, lane);
-        if (jc + lane < n) {
-          d.adj[(size_t)(jc + lane) * d.pitch + (i0 >> 5) + q] = tw;
-          if (tw) atomicAdd(&d.deg[jc + lane], __popc(tw));
-        }
-      }
-      if (i < n) d.adj[(size_t)i * d.pitch + (jc >> 5)] = word;
-      rowdeg += __popc(word);
-    }
-    if (i < n && rowdeg) atomicAdd(&d.deg[i], rowdeg);
-    __syncwarp();
-    const int cnt = min(g->amb_cnt[warp], kTcAmbBuf);
-    if (cnt > 0) {
-      unsigned base = 0;
-      if (lane == 0) base = atomicAdd(&d.st->amb_count, (unsigned)cnt);
-      base = __shfl_sync(0xffffffffu, base, 0);
-      for (int k = lane; k < cnt; k += 32) {
-        if (base + k < (unsigned)d.amb_cap) d.amb_list[base + k] = g->amb_buf[warp][k];
-        else d.st->tc_overflow = 1;
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == kTcEpiWarps) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTcTmemCols) : "memory");
-  }
-}
-
 // ---------------------------------------------------------------------------------------------------------------------
-// Filter v6: the same tensor-core formulation, producer warp, TMEM staging and exactness argument as tim_graph5_kernel; the
-// epilogue is rebuilt around its instruction count (ncu of v5, profiles/r01_graph_kernel_ncu_full.md: 308 warp instructions per
-// 32 x 32 chunk, 113 of them the decision core):
-//   * the mirrored block's 32 x 32 bit transpose is 13 instructions (PRMT / rotate + bit-select with per-lane constants), not ~50;
-//   * running pointers instead of per-unit index arithmetic, the TMEM stage a compile-time constant (units unrolled by two);
-//   * edge units (diagonal tile, last column tile, partial row block) take a separate masked path, interior units none of it;
-//   * an ambiguous chunk replays only the flagged 8-column groups, not all 32 columns;
-//   * VAR 1 / 2: the band is a per-ROW constant T_i = T(L_min,i) >= T(L_ij) (L_ij >= 1 - 4 (r_i + Pi)), which removes the packed
-//     FMA that evaluated T(L) per pair; VAR 1 tests G^2 < T_i^2 with one packed multiply and one 3-input integer minimum per
-//     two pairs (bit patterns of non-negative floats order like the floats), VAR 2 keeps the two compares.
-//     A wider band only sends more pairs to the exact fix-up (graph_fix_kernel / tail): never a wrong bit.
+// The filter kernel.  grid = (work items of the largest problem, batch); an item is a 128-row block and up to 16 column units of
+// 64 columns.  Warp 8 (one lane) feeds the tensor cores: operand rows by cp.async.bulk into a 4-slot ring, 2 x 4 tcgen05.mma per
+// unit into one of two TMEM stages (Dm: 64 columns, L: 64 columns), tcgen05.commit on the stage's `full` barrier.  Warps 0-7 are
+// the epilogue: warp w owns TMEM lanes 32 (w & 3) .. + 31 (rows) and columns 32 (w >> 2) .. + 31 of every unit.
+//
+// What the epilogue is built around (ncu of the earlier kernels, profiles/r01_graph_kernel_ncu_full.md and
+// profiles/r02_graph6_ncu.md: latency bound -- four epilogue warps per scheduler, issue slot busy 48 % -- with the LSU and
+// L1 -> L2 paths at ~50 % from 4-byte scattered adjacency stores, 5.3 sectors written per 32 useful bytes):
+//   * accumulators fetched 16 columns at a time (32 live registers: the loop state fits the 96 registers two resident CTAs
+//     leave a thread), four independent 4-column bit accumulators per fetch, the TMEM stage a compile-time constant;
+//   * edge units (diagonal tile, last column tile, partial row block) take a masked path, interior units none of it;
+//   * an ambiguous chunk replays only the flagged 4-column groups;
+//   * STAGED: the unit's adjacency word goes to shared memory (the 16 KB that staged the CTA's own operand rows; word k of row
+//     r at k ^ (r & 31), conflict free for every access pattern below) and NOTHING else happens per unit.  After the last unit
+//     the eight warps flush the item: rows as 128-byte coalesced stores, and the mirrored blocks as sixteen INDEPENDENT
+//     32 x 32 bit transposes per warp (13 instructions each, PRMT / rotate + bit-select with per-lane constants) whose four
+//     words per column leave as one 16-byte store and ONE degree atomic.  Per item: 1.5 k sectors written instead of 8 k, a
+//     quarter of the degree atomics, and the transposes' shuffle chains overlap each other instead of stalling the unit loop.
+// Bits of ambiguous pairs are written as 0 and are NOT counted in the degrees: the exact fix-up (graph_fix_kernel / tail_kernel)
+// only ever SETS bits and increments, without reading anything back.
 // ---------------------------------------------------------------------------------------------------------------------
 template <int S_> struct StageC { static constexpr int value = S_; };
 
-template <int VAR, bool LD16>
+template <bool LD16, bool STAGED>
 __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
   const ProbDesc d = descs[blockIdx.y];
   const int n = d.n;
@@ -704,7 +451,8 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
   TcSmemCtl* g = reinterpret_cast<TcSmemCtl*>(sm + 2 * kTcRowBytes + 4 * kTcColBytes);
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const unsigned char* ops_col = reinterpret_cast<const unsigned char*>(d.pts32);
-  unsigned char* sStage = sm + 2 * kTcRowBytes + 4 * kTcColBytes + 1024;   // column rows of the CTA's own 128 points (16 KB)
+  // column rows of the CTA's own 128 points (16 KB) during set-up; STAGED: the item's adjacency words (128 rows x 32) afterwards
+  unsigned char* sStage = sm + 2 * kTcRowBytes + 4 * kTcColBytes + kTcCtlBytes;
 
   if (t == 32 * kTcEpiWarps) {
     mbar_init(&g->rowfull, 1);
@@ -724,12 +472,10 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
   if (warp == kTcEpiWarps) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&g->tmem_base)), "r"(kTcTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  } else {
-    mbar_wait(&g->rowfull, 0);   // every epilogue thread observes the bulk copy itself (VAR 1 / 2 read their row's norms from it)
-    if (t < kTcRowTile) {
-      rows_from_col_row(sStage, sRowL, sRowD, t);
-      fence_proxy_async();
-    }
+  } else if (t < kTcRowTile) {
+    mbar_wait(&g->rowfull, 0);
+    rows_from_col_row(sStage, sRowL, sRowD, t);
+    fence_proxy_async();
   }
   tc_fence_before();
   __syncthreads();
@@ -737,7 +483,7 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
   const uint32_t tmem = g->tmem_base;
 
   if (warp == kTcEpiWarps) {
-    // ===== producer (one lane): identical to v5 =====
+    // ===== producer (one lane) =====
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_tf32(kTcRowTile, kTcUnit);
       const uint32_t rowl = smem_u32(sRowL), rowd = smem_u32(sRowD);
@@ -765,7 +511,7 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
     }
     __syncwarp();
   } else {
-    // ===== epilogue: warp w owns TMEM lanes 32 (w & 3) .. + 31 = rows i0 + 32 (w & 3) + lane, columns 32 (w >> 2) .. + 31 of each unit =====
+    // ===== epilogue =====
     const int q = warp & 3, ch = warp >> 2;
     const int r = 32 * q + lane;
     const int i = i0 + r;
@@ -773,36 +519,79 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
     const float nt1s = stp->tcc[0], t0s = stp->tcc[1];
     const float2 nt1 = make_float2(nt1s, nt1s), t0 = make_float2(t0s, t0s);
     const uint32_t lcut_bits = __float_as_uint(stp->tcc[2]);   // lcut < 0:  L > lcut  <=>  bits(L) < bits(lcut) as unsigned
-    float Ti = 0.f;
-    uint32_t t2_bits = 0u;
-    if (VAR != 0) {
-      // p_i = 1/2 - 2 (r_s + r_d) of this row sits at K positions 18..20 of its operand row (three exact TF32 pieces)
-      const float4 c4 = *reinterpret_cast<const float4*>(sStage + r * 128 + ((4 ^ (r & 7)) << 4));
-      const float4 c5 = *reinterpret_cast<const float4*>(sStage + r * 128 + ((5 ^ (r & 7)) << 4));
-      const float pr = (c4.z + c4.w) + c5.x;
-      const float ri = fmaxf(0.25f - 0.5f * pr, 0.f) * 1.000001f;            // r_s + r_d, rounded up
-      const float Lb = -(4.f * (ri + stp->tc_pi) * 1.0001f + 1.f);            // <= every L~_ij of the row (error E_L included)
-      Ti = fmaf(Lb, nt1s, t0s) * 1.00001f;                                    // T(Lb) >= T(L~_ij): T decreases with L
-      t2_bits = __float_as_uint(Ti * Ti * 1.00001f);
-    }
-    const TposeConst tk = tpose_const(lane);
     const bool rows_in = i0 + kTile <= n;
     // units [ub, ue) of this item are interior: off the diagonal tile, all 64 columns and all 128 rows inside the problem
     const int ub = v0 == 0 ? 2 : 0;
     const int ue = rows_in ? max(0, min(nu, (n - i0) / kTcUnit - v0)) : 0;
     int jc = i0 + v0 * kTcUnit + 32 * ch;                                     // first column of this warp's chunk in unit 0
+    uint32_t tbase = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(ch * 32);
+    asm volatile("" : "+r"(tbase));   // keep it in a register (re-derived from the thread id per unit otherwise)
+    uint32_t bar_full = smem_u32(&g->full[0]);          // full[S] at + 8 S, empty[S] at + 16 + 8 S
+    asm volatile("" : "+r"(bar_full));
+    int rowdeg = 0;
+    uint32_t ph = 0;
+    // STAGED: word k = 2 u + ch of row r lives at sStage + 128 r + 4 (k ^ (r & 31));  r & 31 == lane for the writer
+    uint32_t* const stage_w = reinterpret_cast<uint32_t*>(sStage);
+    uint32_t stage_row = smem_u32(sStage) + 128u * (uint32_t)r;
+    asm volatile("" : "+r"(stage_row));
+    // !STAGED: running pointers of the direct stores
+    TposeConst tk;
+    if (!STAGED) tk = tpose_const(lane);
     uint32_t* rowp = d.adj + (size_t)min(i, n - 1) * d.pitch + (jc >> 5);     // += 2 words per unit
     uint32_t* colp = d.adj + (size_t)(jc + lane) * d.pitch + (i0 >> 5) + q;   // += 64 rows per unit (dereferenced only inside the problem)
     int* degp = d.deg + jc + lane;
     const size_t colstep = (size_t)kTcUnit * d.pitch;
-    uint32_t tbase = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(ch * 32);
-    asm volatile("" : "+r"(tbase));   // keep it in a register (re-derived from the thread id per unit otherwise)
-    int rowdeg = 0;
-    uint32_t ph = 0;
 
-    uint32_t bar_full = smem_u32(&g->full[0]);          // full[S] at + 8 S, empty[S] at + 16 + 8 S
-    asm volatile("" : "+r"(bar_full));                  // kept in a register (re-derived from the CTA's shared window per unit otherwise)
+    // pair (i, jc + c) for every set bit c of aw goes to the warp's shared-memory buffer (flushed once per item: a global atomic
+    // with its L2 round trip here would make this warp lag a whole unit behind the others, and they share the TMEM stages)
+    auto list_pairs = [&](uint32_t aw) {
+      while (aw) {
+        const int c = __ffs(aw) - 1;
+        aw &= aw - 1;
+        const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
+        const int pos = atomicAdd(&g->amb_cnt[warp], 1);
+        if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
+        else {  // buffer full (wide test bands): straight to the global list
+          const unsigned base = atomicAdd(&d.st->amb_count, 1u);
+          if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
+          else d.st->tc_overflow = 1;
+        }
+      }
+    };
+    // the unit's finished word: into the staging tile, or straight to the row and (transposed) to the 32 mirrored rows
+    auto emit = [&](uint32_t word, const int u, const bool interior) {
+      rowdeg += __popc(word);
+      if (STAGED) {
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(stage_row + (uint32_t)(((2 * u + ch) ^ lane) << 2)), "r"(word) : "memory");
+      } else {
+        if (interior) {
+          const uint32_t tw = warp_transpose32_fast(word, tk);
+          *colp = tw;
+          if (tw) atomicAdd(degp, __popc(tw));
+          *rowp = word;
+        } else {
+          if (u >= ub) {
+            const uint32_t tw = warp_transpose32_fast(word, tk);
+            if (jc + lane < n) {
+              *colp = tw;
+              if (tw) atomicAdd(degp, __popc(tw));
+            }
+          }
+          if (i < n) *rowp = word;
+        }
+        rowp += 2; colp += colstep; degp += kTcUnit;
+      }
+      jc += kTcUnit;
+    };
+    auto edge_mask = [&]() -> uint32_t {
+      const int nc = n - jc;
+      uint32_t mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
+      if (i >= n) mask = 0u;
+      if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
+      return mask;
+    };
 
+    // 32 columns per fetch (64 live accumulator registers)
     auto unit32 = [&](auto stage_c, const int u) {
       constexpr int S = decltype(stage_c)::value;
       mbar_wait_a(bar_full + 8 * S, ph);
@@ -811,13 +600,11 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
       tc_ld_32x32(tbase + S * 128, dm);
       tc_ld_32x32(tbase + S * 128 + 64, lv);
       tc_wait_ld();
-      // the accumulators are in registers: release the TMEM stage right away
-      tc_fence_before();
+      tc_fence_before();   // the accumulators are in registers: release the TMEM stage right away
       __syncwarp();
       if (lane == 0) mbar_arrive_a(bar_full + 16 + 8 * S);
       // four independent 8-column accumulators; within one the higher column goes first, so column c ends in bit c & 7
       uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      uint32_t gmin[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
       bool aq[4] = {false, false, false, false};
 #pragma unroll
       for (int c = 6; c >= 0; c -= 2) {
@@ -830,31 +617,17 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
           wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
           wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
           lmin[h] = __vimin3_u32(lmin[h], lv[cc], lv[cc + 1]);
-          if (VAR == 0) {
-            const float2 Tb = f2fma(L, nt1, t0);
-            aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
-          } else if (VAR == 1) {
-            const float2 Q = f2mul(G, G);
-            gmin[h] = __vimin3_u32(gmin[h], __float_as_uint(Q.x), __float_as_uint(Q.y));
-          } else {
-            aq[h] |= !(fabsf(G.x) >= Ti) | !(fabsf(G.y) >= Ti);
-          }
+          const float2 Tb = f2fma(L, nt1, t0);
+          aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
         }
       }
       uint32_t word = wq[0] + (wq[1] << 8) + (wq[2] << 16) + (wq[3] << 24);
       bool fl[4];
 #pragma unroll
-      for (int h = 0; h < 4; ++h) fl[h] = (VAR == 1 ? (gmin[h] < t2_bits) : aq[h]) | (lmin[h] < lcut_bits);
+      for (int h = 0; h < 4; ++h) fl[h] = aq[h] | (lmin[h] < lcut_bits);
       const bool interior = (u >= ub) & (u < ue);
-      uint32_t mask = 0xffffffffu;
-      if (!interior) {
-        const int nc = n - jc;
-        mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
-        if (i >= n) mask = 0u;
-        if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
-        word &= mask;
-      }
-      if (fl[0] | fl[1] | fl[2] | fl[3]) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
+      const uint32_t mask = interior ? 0xffffffffu : edge_mask();
+      if (fl[0] | fl[1] | fl[2] | fl[3]) {
         uint32_t aw = 0;
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
@@ -864,64 +637,23 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
               const int cc = 8 * h + c;
               const float Dv = __uint_as_float(dm[cc]), Lv = __uint_as_float(lv[cc]);
               const float G = fmaf(Dv, Dv, Lv);
-              bool a;
-              if (VAR == 0) a = !(fabsf(G) >= fmaf(Lv, nt1s, t0s));
-              else if (VAR == 1) a = __float_as_uint(__fmul_rn(G, G)) < t2_bits;
-              else a = !(fabsf(G) >= Ti);
+              const bool a = !(fabsf(G) >= fmaf(Lv, nt1s, t0s));
               aw |= (a | (lv[cc] < lcut_bits)) ? (1u << cc) : 0u;
             }
           }
         }
         aw &= mask;
-        // into the warp's shared-memory buffer (flushed once per item): a global atomic with its L2 round trip here would make
-        // this warp lag a whole unit behind the others, and they share the TMEM stages
-        while (aw) {
-          const int c = __ffs(aw) - 1;
-          aw &= aw - 1;
-          const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
-          const int pos = atomicAdd(&g->amb_cnt[warp], 1);
-          if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
-          else {  // buffer full (wide test bands): straight to the global list
-            const unsigned base = atomicAdd(&d.st->amb_count, 1u);
-            if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
-            else d.st->tc_overflow = 1;
-          }
-        }
+        word &= ~aw;
+        list_pairs(aw);
       }
-      if (interior) {
-        // off the diagonal tile, fully inside the problem: lane c receives the 32 row bits of column jc + c
-        const uint32_t tw = warp_transpose32_fast(word, tk);
-        *colp = tw;
-        if (tw) atomicAdd(degp, __popc(tw));
-        *rowp = word;
-      } else {
-        if (u >= ub) {
-          const uint32_t tw = warp_transpose32_fast(word, tk);
-          if (jc + lane < n) {
-            *colp = tw;
-            if (tw) atomicAdd(degp, __popc(tw));
-          }
-        }
-        if (i < n) *rowp = word;
-      }
-      rowdeg += __popc(word);
-      rowp += 2; colp += colstep; degp += kTcUnit; jc += kTcUnit;
+      emit(word & mask, u, interior);
     };
 
-    // The same unit with the accumulators fetched 16 columns at a time (32 live registers instead of 64: the whole loop state
-    // fits the 96 registers two resident CTAs leave each thread) and four independent 4-column bit accumulators per half.
+    // 16 columns per fetch
     auto unit16 = [&](auto stage_c, const int u) {
       constexpr int S = decltype(stage_c)::value;
       mbar_wait_a(bar_full + 8 * S, ph);
       tc_fence_after();
-      const bool interior = (u >= ub) & (u < ue);
-      uint32_t mask = 0xffffffffu;
-      if (!interior) {
-        const int nc = n - jc;
-        mask = nc >= 32 ? 0xffffffffu : (nc <= 0 ? 0u : ((1u << nc) - 1u));
-        if (i >= n) mask = 0u;
-        if (i >= jc && i < jc + 32) mask &= ~(1u << (i - jc));
-      }
       uint32_t word = 0u, aw = 0u;
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
@@ -934,7 +666,7 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
           __syncwarp();
           if (lane == 0) mbar_arrive_a(bar_full + 16 + 8 * S);
         }
-        uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4], gmin[4];
+        uint32_t wq[4] = {0u, 0u, 0u, 0u}, lmin[4];
         bool aq[4] = {false, false, false, false};
 #pragma unroll
         for (int c = 2; c >= 0; c -= 2) {
@@ -947,74 +679,37 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
             wq[h] = __funnelshift_l(__float_as_uint(G.y), wq[h], 1);
             wq[h] = __funnelshift_l(__float_as_uint(G.x), wq[h], 1);
             lmin[h] = __vimin3_u32(c == 2 ? 0xffffffffu : lmin[h], lv[cc], lv[cc + 1]);
-            if (VAR == 0) {
-              const float2 Tb = f2fma(L, nt1, t0);
-              aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
-            } else if (VAR == 1) {
-              const float2 Q = f2mul(G, G);
-              gmin[h] = __vimin3_u32(c == 2 ? 0xffffffffu : gmin[h], __float_as_uint(Q.x), __float_as_uint(Q.y));
-            } else {
-              aq[h] |= !(fabsf(G.x) >= Ti) | !(fabsf(G.y) >= Ti);
-            }
+            const float2 Tb = f2fma(L, nt1, t0);
+            aq[h] |= !(fabsf(G.x) >= Tb.x) | !(fabsf(G.y) >= Tb.y);
           }
         }
         word |= (wq[0] + (wq[1] << 4) + (wq[2] << 8) + (wq[3] << 12)) << (16 * half);
         // first a combined test (one branch per half), per-group flags only on the rare path
         const uint32_t lm = min(__vimin3_u32(lmin[0], lmin[1], lmin[2]), lmin[3]);
-        bool any = lm < lcut_bits;
-        if (VAR == 1) any |= min(__vimin3_u32(gmin[0], gmin[1], gmin[2]), gmin[3]) < t2_bits;
-        else any |= aq[0] | aq[1] | aq[2] | aq[3];
-        if (any) {
+        if ((lm < lcut_bits) | aq[0] | aq[1] | aq[2] | aq[3]) {
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
-            const bool fl = (VAR == 1 ? (gmin[h] < t2_bits) : aq[h]) | (lmin[h] < lcut_bits);
-            if (fl) {
+            if (aq[h] | (lmin[h] < lcut_bits)) {
 #pragma unroll
               for (int c = 0; c < 4; ++c) {
                 const int cc = 4 * h + c;
                 const float Dv = __uint_as_float(dm[cc]), Lv = __uint_as_float(lv[cc]);
                 const float G = fmaf(Dv, Dv, Lv);
-                bool a;
-                if (VAR == 0) a = !(fabsf(G) >= fmaf(Lv, nt1s, t0s));
-                else if (VAR == 1) a = __float_as_uint(__fmul_rn(G, G)) < t2_bits;
-                else a = !(fabsf(G) >= Ti);
+                const bool a = !(fabsf(G) >= fmaf(Lv, nt1s, t0s));
                 aw |= (a | (lv[cc] < lcut_bits)) ? (1u << (16 * half + cc)) : 0u;
               }
             }
           }
         }
       }
-      word &= mask;
-      aw &= mask;
-      while (aw) {  // list the pairs the exact kernel has to decide (their bits here are placeholders)
-        const int c = __ffs(aw) - 1;
-        aw &= aw - 1;
-        const uint32_t e = ((uint32_t)i << 16) | (uint32_t)(jc + c);
-        const int pos = atomicAdd(&g->amb_cnt[warp], 1);
-        if (pos < kTcAmbBuf) g->amb_buf[warp][pos] = e;
-        else {  // buffer full (wide test bands): straight to the global list
-          const unsigned base = atomicAdd(&d.st->amb_count, 1u);
-          if (base < (unsigned)d.amb_cap) d.amb_list[base] = e;
-          else d.st->tc_overflow = 1;
-        }
+      const bool interior = (u >= ub) & (u < ue);
+      const uint32_t mask = interior ? 0xffffffffu : edge_mask();
+      if (aw) {
+        aw &= mask;
+        word &= ~aw;
+        list_pairs(aw);
       }
-      if (interior) {
-        const uint32_t tw = warp_transpose32_fast(word, tk);
-        *colp = tw;
-        if (tw) atomicAdd(degp, __popc(tw));
-        *rowp = word;
-      } else {
-        if (u >= ub) {
-          const uint32_t tw = warp_transpose32_fast(word, tk);
-          if (jc + lane < n) {
-            *colp = tw;
-            if (tw) atomicAdd(degp, __popc(tw));
-          }
-        }
-        if (i < n) *rowp = word;
-      }
-      rowdeg += __popc(word);
-      rowp += 2; colp += colstep; degp += kTcUnit; jc += kTcUnit;
+      emit(word & mask, u, interior);
     };
 
 #pragma unroll 1
@@ -1040,6 +735,36 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
         else d.st->tc_overflow = 1;
       }
     }
+    if (STAGED) {
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kTcEpiWarps) : "memory");   // the eight epilogue warps: every word of the item is staged
+      tk = tpose_const(lane);
+      const int kw = 2 * nu;                          // words per row of this item
+      const int wbase = (i0 >> 5) + 2 * v0;           // its first word in the adjacency row
+      // rows: warp w flushes rows 16 w .. 16 w + 15, one 128-byte store each
+#pragma unroll 8
+      for (int rr = 0; rr < 16; ++rr) {
+        const int r2 = 16 * warp + rr, i2 = i0 + r2;
+        const uint32_t x = stage_w[32 * r2 + (lane ^ (r2 & 31))];
+        if (i2 < n && lane < kw) d.adj[(size_t)i2 * d.pitch + wbase + lane] = x;
+      }
+      // mirrored blocks: chunk k = 2 u + ch holds columns jk .. jk + 31; lane c of the transposes owns column jk + c
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const int k = warp + 8 * kk;
+        if (k >= kw || (k >> 1) < ub) continue;       // beyond the item / diagonal tile (its rows are their own mirror)
+        uint32_t x[4];
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) x[qq] = stage_w[32 * (32 * qq + lane) + (k ^ lane)];
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) x[qq] = warp_transpose32_fast(x[qq], tk);
+        const int j = i0 + v0 * kTcUnit + 32 * k + lane;
+        if (j < n) {
+          *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + (i0 >> 5)) = make_uint4(x[0], x[1], x[2], x[3]);
+          const int c = __popc(x[0]) + __popc(x[1]) + __popc(x[2]) + __popc(x[3]);
+          if (c) atomicAdd(d.deg + j, c);
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -1049,13 +774,13 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
   }
 }
 
-// B2R_G6 (A/B runs): 0 = v5 kernel; v6: 1 = T(L) band, 32-column loads; 2 = T(L) band, 16-column loads (default);
-// 3 = per-row band on G^2, 16-column loads; 4 = per-row band on G^2, 32-column loads; 5 = per-row band with compares, 16-column loads
+// B2R_G6 (A/B runs): 1 = direct stores, 16-column fetches; 2 = staged stores, 16-column fetches; 3 = staged stores, 32-column
+// fetches (default).  64 x 5000 graph stage on B200: 0.539 / 0.521 / 0.500 ms
 static int g6_variant() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B2R_G6");
-    v = (e && e[0] >= '0' && e[0] <= '5') ? e[0] - '0' : 2;
+    v = (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 3;
   }
   return v;
 }
@@ -1063,12 +788,9 @@ static int g6_variant() {
 int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {
   static PerDeviceOnce attr;
   attr.run([] {
-    cudaError_t e = cudaFuncSetAttribute(tim_graph5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(tim_graph6_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tim_graph6_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
     return e;
   });
   const int T = (n_max + kTile - 1) / kTile;
@@ -1080,12 +802,9 @@ int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const Kern
   graph_tc_setup_kernel<<<dim3(slices, batch), 1024, 0, st>>>(d_desc, kp);
   const dim3 grid(tc_items(T), batch);
   switch (g6_variant()) {
-    case 0: tim_graph5_kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
-    case 1: tim_graph6_kernel<0, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
-    case 3: tim_graph6_kernel<1, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
-    case 4: tim_graph6_kernel<1, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
-    case 5: tim_graph6_kernel<2, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
-    default: tim_graph6_kernel<0, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    case 1: tim_graph6_kernel<true, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    case 2: tim_graph6_kernel<true, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
+    default: tim_graph6_kernel<false, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
   }
   return 2;
 }

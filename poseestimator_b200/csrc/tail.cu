@@ -123,11 +123,17 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   }
 
   stamp(1);
-  // ---- 3. greedy clique bound from the seeds of the first id classes, one after the other (heuristic_block_kernel) ----
+  // ---- 3 + 4. greedy clique bound from the seed of an id class (heuristic_block_kernel), then the (lb-1)-core of the graph
+  // (prune_kernel: alive bitset + member list in shared memory, one warp per eight members).  When the core has exactly lb
+  // vertices the bound is proven and the seeds of the other classes are not needed; otherwise the next seed may raise the bound
+  // (the multi-kernel path always runs all seeds: the bound is the same whenever it matters).
   uint32_t* sh = reinterpret_cast<uint32_t*>(tsm);
+  uint32_t* alive = sh;                                               // W words
+  unsigned short* list = reinterpret_cast<unsigned short*>(sh + W);   // n entries
   if (tid == 0) ts.lb = 0;
   __syncthreads();
   unsigned long long heu_key = 0ull;
+  int lb = 0, T = 0, n_alive = 0;
   for (int k = 0; k < B2R_HEU_SEEDS; ++k) {
     const unsigned long long skey = ts.key[k];
     if (skey == 0ull) continue;
@@ -140,53 +146,46 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
       if (tid == 0 && size > ts.lb) ts.lb = size;
     }
     __syncthreads();
-  }
-  const int lb = ts.lb;
-  stamp(2);
-
-  // ---- 4. (lb-1)-core of the graph (prune_kernel): alive bitset + member list in shared memory, one warp per member ----
-  const int T = max(lb - 1, 0);
-  uint32_t* alive = sh;                                        // W words
-  unsigned short* list = reinterpret_cast<unsigned short*>(sh + W);   // n entries
-  for (int w = tid; w < W; w += kTailThreads) alive[w] = 0u;
-  __syncthreads();
-  for (int v0 = 0; v0 < n; v0 += kTailThreads) {
-    const int v = v0 + tid;
-    const bool a = v < n && __ldcg(d.deg + v) >= T;
-    const uint32_t bal = __ballot_sync(FULL, a);
-    if (lane == 0 && (v >> 5) < W) alive[v >> 5] = bal;
-  }
-  int n_alive = 0;
-  for (;;) {
-    n_alive = tail_list_bits(alive, Wb, list, &ts);
-    if (tid == 0) ts.changed = 0;
+    if (k > 0 && ts.lb == lb) continue;   // this seed did not raise the bound: the core is the one already computed
+    lb = ts.lb;
+    if (k == 0) stamp(2);
+    T = max(lb - 1, 0);
+    for (int w = tid; w < W; w += kTailThreads) alive[w] = 0u;
     __syncthreads();
-    if (T > 0) {
-      for (int m0 = warp; m0 < n_alive; m0 += 4 * kTailWarps) {
-        int c[4], ids[4];
+    for (int v0 = 0; v0 < n; v0 += kTailThreads) {
+      const int vv = v0 + tid;
+      const bool a = vv < n && __ldcg(d.deg + vv) >= T;
+      const uint32_t bal = __ballot_sync(FULL, a);
+      if (lane == 0 && (vv >> 5) < W) alive[vv >> 5] = bal;
+    }
+    for (;;) {
+      n_alive = tail_list_bits(alive, Wb, list, &ts);
+      if (tid == 0) ts.changed = 0;
+      __syncthreads();
+      if (T > 0) {
+        constexpr int R = 8;
+        for (int m0 = warp; m0 < n_alive; m0 += R * kTailWarps) {
+          int c[R], ids[R];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int m = m0 + q * kTailWarps;
-          ids[q] = m < n_alive ? (int)list[m] : -1;
-          c[q] = 0;
-          if (ids[q] >= 0) {
-            const uint32_t* row = d.adj + (size_t)ids[q] * d.pitch;
-            for (int w = lane; w < W; w += 32) c[q] += __popc(__ldcg(row + w) & alive[w]);
+          for (int q = 0; q < R; ++q) {
+            const int m = m0 + q * kTailWarps;
+            ids[q] = m < n_alive ? (int)list[m] : -1;
+          }
+          rows_and_count<R, true>(d.adj, d.pitch, ids, alive, W >> 2, lane, c);
+#pragma unroll
+          for (int q = 0; q < R; ++q) {
+            if (ids[q] < 0) continue;
+            if (c[q] < T && lane == 0) { atomicAnd(&alive[ids[q] >> 5], ~(1u << (ids[q] & 31))); ts.changed = 1; }
           }
         }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (ids[q] < 0) continue;
-          const int cq = __reduce_add_sync(FULL, c[q]);
-          if (cq < T && lane == 0) { atomicAnd(&alive[ids[q] >> 5], ~(1u << (ids[q] & 31))); ts.changed = 1; }
-        }
       }
+      __syncthreads();
+      if (!ts.changed) break;
     }
-    __syncthreads();
-    if (!ts.changed) break;
+    // Note: a vertex counted against neighbours that die in the same pass is caught by the next pass (the loop ends on a pass
+    // without removals), so the fixed point is the T-core whatever the order -- the same set prune_kernel leaves.
+    if (n_alive == lb) break;   // the core IS the clique: proven
   }
-  // Note: a vertex counted against neighbours that die in the same pass is caught by the next pass (the loop ends on a pass
-  // without removals), so the fixed point is the T-core whatever the order -- the same set prune_kernel leaves.
   stamp(3);
   const int Wc = (((n_alive + 31) >> 5) + 3) & ~3;
   for (int m = tid; m < n_alive; m += kTailThreads) d.ids[m] = (int)list[m];

@@ -312,6 +312,14 @@ class RobustRegistrationSolver:
                                                             C.c_void_p(c.ctypes.data)))
         return dm, lv, dict(kappa=c[0], ctr=c[1:7].copy(), t1=c[7], t0=c[8], lcut=c[9], k=c[10], use32=int(c[11]))
 
+    def _tc_sweep(self) -> dict:
+        """Test hook (b2r_debug.h): EVERY unit of the tensor-core graph filter recomputed and compared with fp64 on the device."""
+        self._require()
+        out = (C.c_double * 8)()
+        _lib.check(self._h, _lib.lib().b2r_debug_tc_sweep(self._h, 0, out))
+        names = ("tc_accum_ratio", "dm_over_ED", "l_over_EL", "pairs", "Pi", "E_D", "E_L", "use32")
+        return dict(zip(names, [float(x) for x in out]))
+
     def _adjacency_dense(self) -> np.ndarray:
         bits = self._adjacency_bits()
         return np.unpackbits(bits.view(np.uint8), axis=1, bitorder="little")[:, : self._n].astype(bool)

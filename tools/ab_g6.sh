@@ -3,10 +3,10 @@
 # (teaser GPU tests) and the per-stage times of a config-3 batch.
 D=gpurun_out/${1:-g6}
 mkdir -p $D
-for v in ${2:-0 1 2 3 4 5}; do
+for v in ${2:-1 2 3}; do
   echo "== B2R_G6=$v"
   B2R_G6=$v timeout 600 python -m pytest tests/test_gpu_teaser.py tests/test_gpu_full_size.py -x -q > $D/pytest_g6_$v.log 2>&1; tail -1 $D/pytest_g6_$v.log
-  for rep in 1 2; do B2R_G6=$v timeout 300 python tools/stage_times.py 64 5000 0.95 2>&1 | tail -2; done
+  for rep in 1 2; do B2R_G6=$v timeout 300 python tools/stage_times.py 64 5000 0.95 2>&1 | tail -5 | head -3; done
 done 2>&1 | tee $D/ab_g6.log
 echo "== no fused tail, default G6"
 B2R_NO_FUSED_TAIL=1 timeout 600 python -m pytest tests/test_gpu_teaser.py -x -q 2>&1 | tail -1
