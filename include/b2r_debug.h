@@ -32,8 +32,9 @@ b2r_status b2r_debug_tc_values(b2r_solver* s, int idx, int row_block, int unit, 
 b2r_status b2r_debug_tc_sweep(b2r_solver* s, int idx, double* out8);
 
 /* SM cycles the fused tail kernel spent on problem idx of the last batch up to the end of each stage:
- * [0] fix-up of listed pairs [1] degrees [2] greedy bound [3] core pruning [4] clique [5] rotation [6] translation [7] 0 */
-b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out8);
+ * [0] fix-up of listed pairs [1] degrees [2] greedy bound [3] core pruning [4] clique [5] rotation [6] translation
+ * [7] state loaded (start of the fix-up); [8..31] finer marks inside the stages (0 where a stage did not run), see tail.cu */
+b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out32);
 
 #ifdef __cplusplus
 }

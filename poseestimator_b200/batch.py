@@ -234,10 +234,12 @@ class BatchSolver:
 
     def tail_cycles(self, i: int) -> dict:
         """Test hook (b2r_debug.h): SM cycles of the fused tail kernel at the end of each of its stages, problem i."""
-        out = (C.c_uint32 * 8)()
+        out = (C.c_uint32 * 32)()
         _lib.check(self._h, _lib.lib().b2r_debug_tail_cycles(self._h, int(i), out))
-        names = ("fix", "degrees", "heuristic", "prune", "clique", "rotation", "translation")
-        return dict(zip(names, [int(x) for x in out]))
+        names = ("fix", "degrees", "heuristic", "prune", "clique", "rotation", "translation", "start")
+        r = dict(zip(names, [int(x) for x in out]))
+        r["marks"] = {k: int(out[k]) for k in range(8, 32) if out[k]}
+        return r
 
     def tc_sweep(self, i: int) -> dict:
         """Test hook (b2r_debug.h): every unit of problem i recomputed on the tensor cores and compared with fp64 on the device."""

@@ -746,12 +746,12 @@ b2r_status b2r_debug_set_graph_filter(b2r_solver* s, int filter, double tau) {
   return B2R_OK;
 }
 
-b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out8) {
+b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out32) {
   b2r_status r = check_index(s, idx);
   if (r != B2R_OK) return r;
-  if (!out8) return B2R_ERR_INVALID_ARG;
+  if (!out32) return B2R_ERR_INVALID_ARG;
   const ProbState& st = ((const ProbState*)s->h_state.p)[idx];
-  for (int k = 0; k < 8; ++k) out8[k] = st.tail_clk[k];
+  for (int k = 0; k < 32; ++k) out32[k] = st.tail_clk[k];
   return B2R_OK;
 }
 

@@ -12,30 +12,61 @@ __host__ __device__ inline size_t heuristic_smem_bytes(int n) {
   return (3 * W + 64) * 4 + (size_t)2 * (n + 8);
 }
 
-// |row_m & mask| for up to 8 adjacency rows at once, one warp: every lane issues its 16-byte loads of ALL rows before the first
-// popcount, so a sweep costs about one L2 round trip per 32 x 16 bytes of row instead of one per word (the scalar loop this
-// replaces was a chain of dependent loads: 20 round trips per four rows at N = 5000).  W4 = words per row / 4.
-template <int R, bool kCoherent>
-__device__ __forceinline__ void rows_and_count(const uint32_t* __restrict__ adj, int pitch, const int (&ids)[R], const uint32_t* mask, int W4, int lane,
-                                               int (&cnt)[R]) {
+// |row_q & mask| for up to R adjacency rows at once, one warp: every lane issues its 16-byte loads of ALL rows before the first
+// popcount, so a sweep costs about one memory round trip per 32 x 16 bytes of row instead of one per word.  rowp[q] may point to
+// global memory or to a row staged in shared memory (generic loads), nullptr = no row.  W4 = words per row / 4.
+template <int R>
+__device__ __forceinline__ void rows_and_count(const uint4* const (&rowp)[R], const uint32_t* mask, int W4, int lane, int (&cnt)[R]) {
 #pragma unroll
   for (int q = 0; q < R; ++q) cnt[q] = 0;
   for (int w = lane; w < W4; w += 32) {
     const uint4 m = reinterpret_cast<const uint4*>(mask)[w];
     uint4 x[R];
 #pragma unroll
-    for (int q = 0; q < R; ++q) {
-      x[q] = make_uint4(0u, 0u, 0u, 0u);
-      if (ids[q] >= 0) {
-        const uint4* row = reinterpret_cast<const uint4*>(adj + (size_t)ids[q] * pitch) + w;
-        x[q] = kCoherent ? __ldcg(row) : __ldg(row);
-      }
-    }
+    for (int q = 0; q < R; ++q) x[q] = rowp[q] ? rowp[q][w] : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
     for (int q = 0; q < R; ++q) cnt[q] += __popc(x[q].x & m.x) + __popc(x[q].y & m.y) + __popc(x[q].z & m.z) + __popc(x[q].w & m.w);
   }
 #pragma unroll
   for (int q = 0; q < R; ++q) cnt[q] = __reduce_add_sync(0xffffffffu, cnt[q]);
+}
+
+// Adjacency rows staged in shared memory (fused tail): the first round of the seed heuristic needs the rows of all |P| members,
+// later rounds and the core peel need subsets of them.  One cp.async.bulk per row brings them in with a single memory round trip
+// (the 2 x 4 dependent sweeps this replaces cost ~2.7 k cycles each out of DRAM); afterwards a row is found from its vertex id
+// through the bitset of requested vertices and its per-word prefix popcount.
+struct RowCache {
+  uint32_t* rows;        // cap rows of W words, 16-byte aligned
+  uint32_t* P1;          // W words: vertices whose rows were requested (ascending: the first n_cached of them are resident)
+  unsigned short* pre;   // per word of P1: set bits below it
+  uint64_t* mbar;
+  int cap, n_cached, W;
+};
+__device__ __forceinline__ const uint4* cached_row(const RowCache& rc, int id) {
+  if (rc.n_cached == 0) return nullptr;
+  const uint32_t w = rc.P1[id >> 5], b = 1u << (id & 31);
+  if (!(w & b)) return nullptr;
+  const int slot = (int)rc.pre[id >> 5] + __popc(w & (b - 1u));
+  return slot < rc.n_cached ? reinterpret_cast<const uint4*>(rc.rows + (size_t)slot * rc.W) : nullptr;
+}
+__device__ __forceinline__ void rc_mbar_init(uint64_t* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void rc_mbar_expect(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void rc_mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}" : "=r"(done) : "r"(a), "r"(parity) : "memory");
+  }
+}
+__device__ __forceinline__ void rc_bulk_row(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"((uint32_t)__cvta_generic_to_shared(dst)),
+               "l"(src), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(bar))
+               : "memory");
 }
 
 // Greedy clique from seed v inside P = N(v), one CTA of NT threads (the rule of the PMC_EXACT path; restated in
@@ -46,8 +77,9 @@ __device__ __forceinline__ void rows_and_count(const uint32_t* __restrict__ adj,
 //   * takes the member of largest degP (ties: lowest id) and intersects P with its row.
 // Returns the clique size, or 0 when the seed cannot beat *lb_now (another seed's result).  kCoherent: adjacency rows are read
 // with ld.global.cg (the fused tail modified them with atomics earlier in the same kernel), else through the read-only path.
-template <int NT, bool kCoherent>
-__device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const int* lb_now) {
+// kCache: the rows of the first round's members are staged in shared memory (RowCache) and every later row read looks there first.
+template <int NT, bool kCoherent, bool kCache = false>
+__device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const int* lb_now, RowCache* rc = nullptr, TailMarks tm = TailMarks()) {
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int NW = NT / 32;
   const int n = d.n;
@@ -70,8 +102,11 @@ __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const 
   for (int w = threadIdx.x; w < W; w += NT) P[w] = ld(row0 + w);
   __syncthreads();
   int size = 1;
-  for (;;) {
+  int round = 0;
+  tm.mark(8);    // seed row in shared memory
+  for (;; ++round) {
     // ascending member list + count
+    const bool fill = kCache && rc->n_cached == 0 && rc->cap > 0;   // uniform: n_cached changes between barriers only
     if (threadIdx.x == 0) *s_base = 0;
     __syncthreads();
     for (int w0 = 0; w0 < Wb; w0 += NT) {
@@ -92,6 +127,7 @@ __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const 
       }
       __syncthreads();
       int pos = *s_base + scan[warp] + incl - c;
+      if (kCache && fill && w < Wb) { rc->P1[w] = word; rc->pre[w] = (unsigned short)min(pos, 65535); }
       uint32_t bits = word;
       while (bits) { list[pos++] = (unsigned short)(32 * w + (__ffs(bits) - 1)); bits &= bits - 1; }
       __syncthreads();
@@ -99,21 +135,44 @@ __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const 
       __syncthreads();
     }
     const int cnt = *s_base;
+    if (round < 3) tm.mark(9 + 4 * round);    // member list
     if (cnt == 0) break;
     if (threadIdx.x == 0) { *s_lb = *(volatile const int*)lb_now; *s_best = 0u; *s_nU = 0; *s_nR = 0; }
     for (int w = threadIdx.x; w < W; w += NT) { U[w] = 0u; Rm[w] = 0u; }
     __syncthreads();
     if (size + cnt <= *s_lb) return 0;  // another seed already reached this size: cannot improve
+    if (kCache && fill) {
+      // one bulk copy per member row, all in flight together; the first min(cnt, cap) members of the ascending list become resident
+      const int nc = min(cnt, rc->cap);
+      const uint32_t row_bytes = (uint32_t)W * 4u;
+      if (threadIdx.x == 0) rc_mbar_expect(rc->mbar, (uint32_t)nc * row_bytes);
+      asm volatile("fence.proxy.async;" ::: "memory");   // the rows were modified through the generic proxy (fix-up atomics) earlier in this kernel
+      for (int m = threadIdx.x; m < nc; m += NT) rc_bulk_row(rc->rows + (size_t)m * W, d.adj + (size_t)list[m] * d.pitch, row_bytes, rc->mbar);
+      rc_mbar_wait(rc->mbar, 0);
+      __syncthreads();
+      if (threadIdx.x == 0) rc->n_cached = nc;
+      __syncthreads();
+    }
+    if (round < 3) tm.mark(10 + 4 * round);   // rows staged
+    if (kCache && tm.clk && threadIdx.x == 0 && round == 0) { tm.clk[30] = (unsigned)rc->n_cached; tm.clk[31] = (unsigned)rc->cap; }
     unsigned wbest = 0;
     constexpr int R = 8;
     for (int m0 = warp; m0 < cnt; m0 += R * NW) {
       int c[R], ids[R];
+      const uint4* rowp[R];
 #pragma unroll
       for (int q = 0; q < R; ++q) {
         const int m = m0 + q * NW;
         ids[q] = m < cnt ? (int)list[m] : -1;
+        rowp[q] = nullptr;
+        if (ids[q] >= 0) {
+          if (kCache) rowp[q] = cached_row(*rc, ids[q]);
+          if (!rowp[q]) rowp[q] = reinterpret_cast<const uint4*>(d.adj + (size_t)ids[q] * d.pitch);
+        }
       }
-      rows_and_count<R, kCoherent>(d.adj, d.pitch, ids, P, W >> 2, lane, c);
+      if (round == 0 && m0 == warp) tm.mark(26);
+      rows_and_count<R>(rowp, P, W >> 2, lane, c);
+      if (round == 0 && m0 == warp) tm.mark(27);
 #pragma unroll
       for (int q = 0; q < R; ++q) {
         if (ids[q] < 0) continue;
@@ -124,8 +183,10 @@ __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const 
         if (2 * cq < cnt - 1 && lane == 0) atomicOr(&Rm[id >> 5], 1u << (id & 31));   // adjacent to less than half of the others
       }
     }
+    if (round == 0) tm.mark(30);
     if (lane == 0 && wbest) atomicMax(s_best, wbest);
     __syncthreads();
+    if (round < 3) tm.mark(11 + 4 * round);   // degrees inside P counted
     int nu = 0, nr = 0;
     for (int w = threadIdx.x; w < Wb; w += NT) { nu += __popc(U[w]); nr += __popc(Rm[w]); }
     nu = __reduce_add_sync(kFull, nu); nr = __reduce_add_sync(kFull, nr);
@@ -145,6 +206,7 @@ __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const 
       for (int w = threadIdx.x; w < W; w += NT) P[w] &= ld(row + w);
     }
     __syncthreads();
+    if (round < 3) tm.mark(12 + 4 * round);   // P updated
   }
   return size;
 }

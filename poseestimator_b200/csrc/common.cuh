@@ -76,7 +76,15 @@ struct ProbState {
   // fused tail (tail.cu)
   int tail_done;         // 1: the fused tail kernel finished this problem (the multi-kernel clique / rotation / translation path skips it)
   int tail_why;          // why the fused tail handed the problem to the multi-kernel path (0 = it did not)
-  unsigned int tail_clk[8];  // SM cycles the fused tail spent up to the end of: fix-up, degrees, heuristic, prune, clique, rotation, translation
+  unsigned int tail_clk[32]; // SM cycles the fused tail spent up to the end of: fix-up, degrees, heuristic, prune, clique, rotation, translation, start;
+                             // [8..31]: finer marks inside the stages (b2r_debug_tail_cycles)
+};
+
+// cycle marks of the fused tail (test hook): thread 0 of the CTA stores clock64() - t0 into slot k
+struct TailMarks {
+  unsigned int* clk = nullptr;
+  long long t0 = 0;
+  __device__ __forceinline__ void mark(int k) const { if (clk && threadIdx.x == 0) clk[k] = (unsigned int)(clock64() - t0); }
 };
 
 // Per-problem pointers (device copies of host-built descriptors).

@@ -19,11 +19,18 @@ __device__ __forceinline__ bool verdict_exact(double A, double B, double beta) {
 // not count them, so the fix-up only SETS bits and increments degrees: reductions without a return value, nothing to wait for.
 // A pair of two different 128-row tiles is listed once (by the tile that owns row i) and owns both mirrored bits; inside a
 // diagonal tile both (i, j) and (j, i) are listed and each entry owns its own row's bit.
-__device__ __forceinline__ void fix_listed_pair(const double* __restrict__ src, const double* __restrict__ dst, uint32_t* adj, int pitch, int* deg,
-                                                uint32_t e, double beta) {
+struct FixPair { double s[6], t[6]; };   // src_i, src_j, dst_i, dst_j
+__device__ __forceinline__ FixPair load_listed_pair(const double* __restrict__ src, const double* __restrict__ dst, uint32_t e) {
   const size_t i = e >> 16, j = e & 0xffffu;
-  const double A = sq3_ref(__dsub_rn(src[3 * j], src[3 * i]), __dsub_rn(src[3 * j + 1], src[3 * i + 1]), __dsub_rn(src[3 * j + 2], src[3 * i + 2]));
-  const double B = sq3_ref(__dsub_rn(dst[3 * j], dst[3 * i]), __dsub_rn(dst[3 * j + 1], dst[3 * i + 1]), __dsub_rn(dst[3 * j + 2], dst[3 * i + 2]));
+  FixPair p;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { p.s[k] = src[3 * i + k]; p.s[3 + k] = src[3 * j + k]; p.t[k] = dst[3 * i + k]; p.t[3 + k] = dst[3 * j + k]; }
+  return p;
+}
+__device__ __forceinline__ void decide_listed_pair(const FixPair& p, uint32_t* adj, int pitch, int* deg, uint32_t e, double beta) {
+  const size_t i = e >> 16, j = e & 0xffffu;
+  const double A = sq3_ref(__dsub_rn(p.s[3], p.s[0]), __dsub_rn(p.s[4], p.s[1]), __dsub_rn(p.s[5], p.s[2]));
+  const double B = sq3_ref(__dsub_rn(p.t[3], p.t[0]), __dsub_rn(p.t[4], p.t[1]), __dsub_rn(p.t[5], p.t[2]));
   if (!verdict_exact(A, B, beta)) return;
   atomicOr(adj + i * pitch + (j >> 5), 1u << (j & 31));
   atomicAdd(&deg[i], 1);
@@ -31,6 +38,10 @@ __device__ __forceinline__ void fix_listed_pair(const double* __restrict__ src, 
     atomicOr(adj + j * pitch + (i >> 5), 1u << (i & 31));
     atomicAdd(&deg[j], 1);
   }
+}
+__device__ __forceinline__ void fix_listed_pair(const double* __restrict__ src, const double* __restrict__ dst, uint32_t* adj, int pitch, int* deg,
+                                                uint32_t e, double beta) {
+  decide_listed_pair(load_listed_pair(src, dst, e), adj, pitch, deg, e, beta);
 }
 
 }  // namespace b2r

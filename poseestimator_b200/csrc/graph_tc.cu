@@ -36,9 +36,9 @@ namespace {
 constexpr int kTcRowTile = 128;     // rows per CTA (TMEM lanes)
 constexpr int kTcUnit = 64;         // columns per MMA / TMEM stage
 #ifndef B2R_TC_UPI
-#define B2R_TC_UPI 16
+#define B2R_TC_UPI 32
 #endif
-constexpr int kTcUnitsPerItem = B2R_TC_UPI; // column units one CTA walks (16 = 8 column tiles)
+constexpr int kTcUnitsPerItem = B2R_TC_UPI; // column units one CTA walks (32 = 16 column tiles; 16: 0.490 ms, 32: 0.475 ms per 64 x 5000 stage)
 constexpr int kTcEpiWarps = 8;      // epilogue warps: lane quarter w & 3, 32-column half w >> 2 of every unit
 constexpr int kTcThreads = 32 * (kTcEpiWarps + 1);   // + one producer / MMA-issuer warp
 constexpr uint32_t kTcTmemCols = 256;  // 2 stages x (Dm 64 + L 64)
@@ -62,6 +62,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_arrive_a(uint32_t bar_addr) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
 }
+// (a suspend-time hint on this try_wait changes nothing measurable: 0.4755 vs 0.4751 ms per 64 x 5000 stage)
 __device__ __forceinline__ void mbar_wait_a(uint32_t bar_addr, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -296,7 +297,9 @@ constexpr int kTcRowBytes = kTcRowTile * 128;   // 16 KB
 constexpr int kTcColBytes = kTcUnit * 128;      // 8 KB
 constexpr int kTcCtlBytes = 3 * 1024;           // TcSmemCtl (barriers + the warps' pair buffers)
 static_assert(sizeof(TcSmemCtl) <= kTcCtlBytes, "control block overlaps the staging tile");
-constexpr int kTcSmemBytes = 2 * kTcRowBytes + 4 * kTcColBytes + kTcCtlBytes + kTcRowBytes + 1024;   // + alignment slack = 84 KB; two CTAs per SM by registers (2 x 288 x 96) and TMEM (2 x 256 columns)
+constexpr int kTcStageBytes = kTcRowTile * 2 * kTcUnitsPerItem * 4;   // the item's adjacency words: 128 rows x 2 words per unit (>= the 16 KB of operand rows staged there during set-up)
+static_assert(kTcStageBytes >= kTcRowBytes, "staging tile smaller than the operand rows it holds during set-up");
+constexpr int kTcSmemBytes = 2 * kTcRowBytes + 4 * kTcColBytes + kTcCtlBytes + kTcStageBytes + 1024;   // + alignment slack = 84 KB; two CTAs per SM by registers (2 x 288 x 96) and TMEM (2 x 256 columns)
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -435,11 +438,25 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
   const int n = d.n;
   if (!d.st->use32) return;
   const int T = (n + kTile - 1) / kTile;
-  int p = blockIdx.x, bi = 0;
-  int per = (2 * T + kTcUnitsPerItem - 1) / kTcUnitsPerItem;
-  while (bi < T && p >= per) { p -= per; ++bi; per = (2 * (T - bi) + kTcUnitsPerItem - 1) / kTcUnitsPerItem; }
-  if (bi >= T) return;
-  const int v0 = p * kTcUnitsPerItem;
+  // item -> (row block, first unit) in closed form (every warp of every CTA needs it before anything else; the loop over row
+  // blocks this replaces was a 14-iteration dependent chain on the uniform datapath).  Row block bi owns ceil(m / G) items,
+  // m = T - bi; counted from the END, S(m) = G q (q + 1) / 2 + r (q + 1) items belong to blocks of fewer than m + 1 rows (m = G q + r).
+  constexpr int G = kTcUnitsPerItem / 2;   // row blocks whose item count is the same: ceil(m / G)
+  int bi, v0;
+  {
+    const int qT = T / G, rT = T % G;
+    const int total = G * qT * (qT + 1) / 2 + rT * (qT + 1);
+    if ((int)blockIdx.x >= total) return;
+    const int pe = total - 1 - (int)blockIdx.x;
+    int q = (int)((sqrtf(1.0f + (8.0f / G) * (float)pe) - 1.0f) * 0.5f);
+    q += (G * (q + 1) * (q + 2) / 2 <= pe) ? 1 : 0;
+    q -= (G * q * (q + 1) / 2 > pe) ? 1 : 0;
+    const int rem = pe - G * q * (q + 1) / 2;
+    const int r = rem / (q + 1);
+    const int m = G * q + r + 1;
+    bi = T - m;
+    v0 = (q - (rem - r * (q + 1))) * kTcUnitsPerItem;
+  }
   const int nu = min(kTcUnitsPerItem, 2 * (T - bi) - v0);
   const int i0 = bi * kTile;
 
@@ -530,9 +547,10 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
     asm volatile("" : "+r"(bar_full));
     int rowdeg = 0;
     uint32_t ph = 0;
-    // STAGED: word k = 2 u + ch of row r lives at sStage + 128 r + 4 (k ^ (r & 31));  r & 31 == lane for the writer
+    // STAGED: word k = 2 u + ch of row r lives at sStage + 4 (kSW r + (k ^ (r & 31)));  r & 31 == lane for the writer
+    constexpr int kSW = 2 * kTcUnitsPerItem;   // staged words per row
     uint32_t* const stage_w = reinterpret_cast<uint32_t*>(sStage);
-    uint32_t stage_row = smem_u32(sStage) + 128u * (uint32_t)r;
+    uint32_t stage_row = smem_u32(sStage) + 4u * kSW * (uint32_t)r;
     asm volatile("" : "+r"(stage_row));
     // !STAGED: running pointers of the direct stores
     TposeConst tk;
@@ -740,21 +758,24 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
       tk = tpose_const(lane);
       const int kw = 2 * nu;                          // words per row of this item
       const int wbase = (i0 >> 5) + 2 * v0;           // its first word in the adjacency row
-      // rows: warp w flushes rows 16 w .. 16 w + 15, one 128-byte store each
-#pragma unroll 8
+      // rows: warp w flushes rows 16 w .. 16 w + 15, 128-byte stores
+#pragma unroll 4
       for (int rr = 0; rr < 16; ++rr) {
         const int r2 = 16 * warp + rr, i2 = i0 + r2;
-        const uint32_t x = stage_w[32 * r2 + (lane ^ (r2 & 31))];
-        if (i2 < n && lane < kw) d.adj[(size_t)i2 * d.pitch + wbase + lane] = x;
+#pragma unroll
+        for (int h = 0; h < kSW / 32; ++h) {
+          const uint32_t x = stage_w[kSW * r2 + 32 * h + (lane ^ (r2 & 31))];
+          if (i2 < n && 32 * h + lane < kw) d.adj[(size_t)i2 * d.pitch + wbase + 32 * h + lane] = x;
+        }
       }
       // mirrored blocks: chunk k = 2 u + ch holds columns jk .. jk + 31; lane c of the transposes owns column jk + c
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) {
+      for (int kk = 0; kk < kSW / 8; ++kk) {
         const int k = warp + 8 * kk;
         if (k >= kw || (k >> 1) < ub) continue;       // beyond the item / diagonal tile (its rows are their own mirror)
         uint32_t x[4];
 #pragma unroll
-        for (int qq = 0; qq < 4; ++qq) x[qq] = stage_w[32 * (32 * qq + lane) + (k ^ lane)];
+        for (int qq = 0; qq < 4; ++qq) x[qq] = stage_w[kSW * (32 * qq + lane) + (k ^ lane)];
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) x[qq] = warp_transpose32_fast(x[qq], tk);
         const int j = i0 + v0 * kTcUnit + 32 * k + lane;

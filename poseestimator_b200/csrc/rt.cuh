@@ -71,7 +71,7 @@ __device__ inline double block_max(double v, double* red, int bar) {
 
 // The rotation stage of one registration on threads 0 .. kRtThreads-1 of the CTA (named barrier `bar`).  Returns false when the
 // solution stays invalid (clique <= 1, COMPLETE TIM graph beyond the workspace).
-__device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, int bar) {
+__device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, int bar, TailMarks tm = TailMarks()) {
   ProbState* st = d.st;
   __shared__ double red[9 * kRtWarps];
   __shared__ double sR[9];
@@ -121,6 +121,7 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
     }
   }
   grp_sync(bar);
+  tm.mark(28);   // TIMs built
   // A.6-2/3 GNC-TLS
   const double nb_base = kp.rot_noise_bound > 0 ? kp.rot_noise_bound : kp.noise_bound;
   const double nb = nb_base * (2.0 / scale);
@@ -177,6 +178,7 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
     if (cost_diff < kp.cost_threshold) break;
   }
   grp_sync(bar);
+  tm.mark(29);   // GNC done
   // rotation inliers (w >= 0.5), ascending positions
   if (tid == 0) sh_cnt = 0;
   grp_sync(bar);
@@ -236,6 +238,89 @@ __device__ inline void bitonic_sort(double* val, int* id, int Epad, int tid, int
   grp_sync(bar);
 }
 
+// The same sort for Epad = kRtThreads * R endpoints in shared memory (R = 1, 2, 4, 8), elements in REGISTERS: thread t owns
+// e = t + kRtThreads * r.  Of the log2(Epad) (log2(Epad) + 1) / 2 compare-exchange stages only those with a partner in another
+// warp (strides 32 .. 128) go through shared memory and the group barrier; strides >= kRtThreads pair two registers of one
+// thread and strides <= 16 are warp shuffles -- at 512 endpoints 9 barrier stages instead of 45, every thread busy in all of them.
+// The stage is bound by instruction issue (3 axes x 512 endpoints x 45 stages on one SM), so the keys are integers: the value
+// as an order-preserving 64-bit pattern (-0 folded into +0 first, as `va != vb` does) and (exit before entry flag, |id|) as 32
+// bits -- a compare is 3 integer compares instead of two fp64 compares and two branches.  ep_less is a strict total order (ids
+// are unique), so the result is the one bitonic_sort leaves.
+struct EpKey { unsigned long long hi; unsigned lo; };
+__device__ __forceinline__ EpKey ep_key(double v, int id) {
+  const long long b = __double_as_longlong(v + 0.0);
+  EpKey k;
+  k.hi = (unsigned long long)b ^ ((unsigned long long)(b >> 63) | 0x8000000000000000ull);
+  k.lo = id > 0 ? (unsigned)id : (0x80000000u | (unsigned)(-id));
+  if (id == 0x7fffffff) { k.hi = ~0ull; k.lo = ~0u; }   // padding: behind every real endpoint, NaN values included
+  return k;
+}
+__device__ __forceinline__ bool key_less(const EpKey& a, const EpKey& b) { return (a.hi < b.hi) | ((a.hi == b.hi) & (a.lo < b.lo)); }
+
+template <int R>
+__device__ __forceinline__ void bitonic_sort_regs(double* val, int* id, int tid, int bar) {
+  constexpr int Epad = kRtThreads * R;
+  EpKey key[R];
+  grp_sync(bar);
+#pragma unroll
+  for (int r = 0; r < R; ++r) key[r] = ep_key(val[tid + kRtThreads * r], id[tid + kRtThreads * r]);
+  unsigned long long* kh = reinterpret_cast<unsigned long long*>(val);   // the exchange stages reuse the arrays for the keys
+  unsigned* kl = reinterpret_cast<unsigned*>(id);
+#pragma unroll 1
+  for (int k = 2; k <= Epad; k <<= 1) {
+#pragma unroll 1
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= kRtThreads) {  // partner in another register of this thread (register indices stay compile-time constants)
+#pragma unroll
+        for (int dr = R / 2; dr >= 1; dr >>= 1) {
+          if (j != dr * kRtThreads) continue;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            if ((r & dr) != 0) continue;
+            const int r2 = r | dr;
+            const bool up = ((tid + kRtThreads * r) & k) == 0;
+            // ascending: the lower register keeps the smaller element
+            const bool swap = key_less(key[r2], key[r]) == up;
+            const EpKey a = key[r], b = key[r2];
+            key[r].hi = swap ? b.hi : a.hi; key[r].lo = swap ? b.lo : a.lo;
+            key[r2].hi = swap ? a.hi : b.hi; key[r2].lo = swap ? a.lo : b.lo;
+          }
+        }
+      } else {
+        EpKey pk[R];
+        if (j >= 32) {        // partner in another warp: through shared memory
+#pragma unroll
+          for (int r = 0; r < R; ++r) { kh[tid + kRtThreads * r] = key[r].hi; kl[tid + kRtThreads * r] = key[r].lo; }
+          grp_sync(bar);
+#pragma unroll
+          for (int r = 0; r < R; ++r) { pk[r].hi = kh[(tid ^ j) + kRtThreads * r]; pk[r].lo = kl[(tid ^ j) + kRtThreads * r]; }
+          grp_sync(bar);
+        } else {              // partner in another lane
+#pragma unroll
+          for (int r = 0; r < R; ++r) { pk[r].hi = __shfl_xor_sync(FULL, key[r].hi, j); pk[r].lo = __shfl_xor_sync(FULL, key[r].lo, j); }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int e = tid + kRtThreads * r;
+          const bool keep_min = ((e & k) == 0) == ((e & j) == 0);
+          const bool take = key_less(pk[r], key[r]) == keep_min;   // keys are distinct: !less(p, k) <=> less(k, p); no divergent branch
+          key[r].hi = take ? pk[r].hi : key[r].hi;
+          key[r].lo = take ? pk[r].lo : key[r].lo;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const unsigned long long h = key[r].hi;
+    const long long b = (long long)((h >> 63) ? (h ^ 0x8000000000000000ull) : ~h);
+    const bool pad = key[r].lo == ~0u;
+    val[tid + kRtThreads * r] = pad ? CUDART_INF : __longlong_as_double(b);
+    id[tid + kRtThreads * r] = pad ? 0x7fffffff : ((key[r].lo & 0x80000000u) ? -(int)(key[r].lo & 0x7fffffffu) : (int)key[r].lo);
+  }
+  grp_sync(bar);
+}
+
 // exclusive prefix over the group's kRtThreads per-thread partials of K quantities (warp shuffles + one pass over the warp
 // totals); sm: K * kRtWarps doubles
 template <int K>
@@ -267,9 +352,10 @@ __device__ __forceinline__ void grp_exclusive_scan(double (&v)[K], double* sm, i
 }
 
 // One TLS estimate over X[0..M) with a constant range r.  Returns the estimate in every thread of the group.
-__device__ inline double tls_estimate_const_range(const double* X, int M, double r, double* val, int* id, double* sm /*3*kRtThreads*/, int tid, int bar) {
+__device__ inline double tls_estimate_const_range(const double* X, int M, double r, double* val, int* id, double* sm /*3*kRtThreads*/, int tid, int bar, bool fast,
+                                                  TailMarks tm = TailMarks()) {
   const int E = 2 * M;
-  int Epad = 2;
+  int Epad = fast ? kRtThreads : 2;   // fast: val / id are shared memory with room for kTrEndpoints entries
   while (Epad < E) Epad <<= 1;
   for (int e = tid; e < Epad; e += kRtThreads) {
     if (e < E) {
@@ -278,7 +364,13 @@ __device__ inline double tls_estimate_const_range(const double* X, int M, double
       else { val[e] = X[i] - r; id[e] = i + 1; }
     } else { val[e] = CUDART_INF; id[e] = 0x7fffffff; }
   }
-  bitonic_sort(val, id, Epad, tid, bar);
+  tm.mark(21);   // endpoints written
+  if (fast && Epad == kRtThreads) bitonic_sort_regs<1>(val, id, tid, bar);
+  else if (fast && Epad == 2 * kRtThreads) bitonic_sort_regs<2>(val, id, tid, bar);
+  else if (fast && Epad == 4 * kRtThreads) bitonic_sort_regs<4>(val, id, tid, bar);
+  else if (fast && Epad == 8 * kRtThreads) bitonic_sort_regs<8>(val, id, tid, bar);
+  else bitonic_sort(val, id, Epad, tid, bar);
+  tm.mark(22);   // sorted
   const double w = 1.0 / (r * r);
   const int chunk = (E + kRtThreads - 1) / kRtThreads;
   const int e0 = min(tid * chunk, E), e1 = min(e0 + chunk, E);
@@ -290,6 +382,7 @@ __device__ inline double tls_estimate_const_range(const double* X, int M, double
     pre[0] += eps; pre[1] += eps * w; pre[2] += eps * w * x; pre[3] += eps * r; pre[4] += eps * x; pre[5] += eps * x * x;
   }
   grp_exclusive_scan<6>(pre, sm, tid, bar);
+  tm.mark(23);   // prefix sums
   double card = pre[0], dw = pre[1], dxw = pre[2];
   double rsum = (double)M * r - pre[3];
   double sx = pre[4], sxx = pre[5];
@@ -306,6 +399,7 @@ __device__ inline double tls_estimate_const_range(const double* X, int M, double
   }
   // argmin over threads: lowest cost, ties -> lowest endpoint position (first minimum)
   grp_sync(bar);
+  tm.mark(24);   // costs evaluated
   sm[tid] = best_cost; sm[kRtThreads + tid] = best_x; sm[2 * kRtThreads + tid] = (double)best_e;
   grp_sync(bar);
   for (int s2 = kRtThreads / 2; s2 > 0; s2 >>= 1) {
@@ -326,7 +420,7 @@ constexpr size_t kTrGroupDoubles = 3 * kRtThreads + kTrEndpoints + kTrEndpoints 
 
 // The translation stage of one registration on a CTA of exactly 3 * kRtThreads threads; shd: 3 * kTrGroupDoubles doubles of shared
 // memory (per axis group: [3*kRtThreads] scratch, [2048] endpoint values, [2048] endpoint ids).
-__device__ inline void translation_body(const ProbDesc& d, const KernelParams& kp, double* shd) {
+__device__ inline void translation_body(const ProbDesc& d, const KernelParams& kp, double* shd, TailMarks tm = TailMarks()) {
   ProbState* st = d.st;
   const int gtid = threadIdx.x;
   const int grp = gtid / kRtThreads, tid = gtid % kRtThreads;
@@ -351,6 +445,7 @@ __device__ inline void translation_body(const ProbDesc& d, const KernelParams& k
   if (gtid == 0) sh_c = 0;
   if (gtid < 3) s_t[gtid] = 0.0;   // M == 0 (every GNC weight below 0.5, or the rotation stage bailed out): t = 0, valid = 0
   __syncthreads();
+  tm.mark(20);   // raw translations written
   if (M >= 2) {
     const double r = kp.noise_bound * sqrt(kp.cbar2);  // A.7-4: 1x, not 2x
     int Epad = 2;
@@ -359,15 +454,16 @@ __device__ inline void translation_body(const ProbDesc& d, const KernelParams& k
     double* val = sm + 3 * kRtThreads;
     int* id = (int*)(val + kTrEndpoints);
     if (Epad <= kTrEndpoints) {
-      const double est = tls_estimate_const_range(raw + (size_t)grp * M, M, r, val, id, sm, tid, 1 + grp);
+      const double est = tls_estimate_const_range(raw + (size_t)grp * M, M, r, val, id, sm, tid, 1 + grp, true, tm);
       if (tid == 0) s_t[grp] = est;
     } else if (grp == 0) {  // large cliques: endpoints in the global scratch (4 * tim_cap entries), one axis after the other
       for (int ax = 0; ax < 3; ++ax) {
-        const double est = tls_estimate_const_range(raw + (size_t)ax * M, M, r, d.tls_val, d.tls_id, sm, tid, 1);
+        const double est = tls_estimate_const_range(raw + (size_t)ax * M, M, r, d.tls_val, d.tls_id, sm, tid, 1, false);
         if (tid == 0) s_t[ax] = est;
       }
     }
     __syncthreads();
+    tm.mark(25);   // three estimates
     for (int i = gtid; i < M; i += 3 * kRtThreads) {
       const bool in = (fabs(raw[i] - s_t[0]) <= r) && (fabs(raw[(size_t)M + i] - s_t[1]) <= r) && (fabs(raw[2 * (size_t)M + i] - s_t[2]) <= r);
       if (!in) d.trans_mask[i] = 0;

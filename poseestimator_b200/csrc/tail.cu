@@ -12,6 +12,8 @@
 //   tail_why 1  the graph itself is not final (fp32 path refused the problem or its pair list overflowed): fp64 filter first
 //   tail_why 2  the (lb-1)-core is larger than the greedy clique: the exact branch and bound has to decide
 // Results are identical on both paths: same heuristic rule, same peel, same rotation / translation bodies (rt.cuh).
+#include <stdlib.h>
+
 #include "clique_dev.cuh"
 #include "exact.cuh"
 #include "rt.cuh"
@@ -66,9 +68,11 @@ __device__ int tail_list_bits(const uint32_t* bits, int Wb, unsigned short* list
 
 // mode 0: the graph comes from the tensor-core filter of this batch (pair list to fix, degrees accumulated by the filter);
 // mode 1: the graph is final and degree_kernel has run (other filters, estimate_scaling, b2r_solve_from_adjacency)
-__global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* __restrict__ descs, KernelParams kp, int mode) {
+__global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* __restrict__ descs, KernelParams kp, int mode, int dyn_smem_bytes) {
   extern __shared__ __align__(16) unsigned char tsm[];
   __shared__ TailShared ts;
+  __shared__ RowCache rcache;
+  __shared__ __align__(8) uint64_t rc_bar;
   const ProbDesc d = descs[blockIdx.x];
   ProbState* st = d.st;
   const int n = d.n;
@@ -76,6 +80,9 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   const int W = words_for(n), Wb = (n + 31) >> 5;
   const long long clk0 = clock64();
   auto stamp = [&](int k) { if (tid == 0) st->tail_clk[k] = (unsigned int)(clock64() - clk0); };
+  TailMarks tm;
+  tm.clk = st->tail_clk; tm.t0 = clk0;
+  if (tid < 24) st->tail_clk[8 + tid] = 0u;
 
   if (mode == 0) {
     if (!st->use32 || st->tc_overflow) {   // uniform: the state was written by earlier kernels
@@ -84,7 +91,19 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
     }
     // ---- 1. exact decision of the listed pairs (graph_fix_kernel's first half) ----
     const unsigned cnt = min(st->amb_count, (unsigned)d.amb_cap);
-    for (unsigned idx = tid; idx < cnt; idx += kTailThreads) fix_listed_pair(d.src, d.dst, d.adj, d.pitch, d.deg, d.amb_list[idx], kp.beta);
+    stamp(7);
+    // two pairs of a thread in flight together (registers): the list entries first, then their 24 coordinate loads, then the arithmetic
+    constexpr int FQ = 2;
+    for (unsigned i0 = tid; i0 < cnt; i0 += FQ * kTailThreads) {
+      uint32_t e[FQ];
+      FixPair fp[FQ];
+#pragma unroll
+      for (int q = 0; q < FQ; ++q) { const unsigned idx = i0 + q * kTailThreads; e[q] = idx < cnt ? d.amb_list[idx] : 0xffffffffu; }
+#pragma unroll
+      for (int q = 0; q < FQ; ++q) if (e[q] != 0xffffffffu) fp[q] = load_listed_pair(d.src, d.dst, e[q]);
+#pragma unroll
+      for (int q = 0; q < FQ; ++q) if (e[q] != 0xffffffffu) decide_listed_pair(fp[q], d.adj, d.pitch, d.deg, e[q], kp.beta);
+    }
     if (tid < 8) ts.key[tid] = 0ull;
     if (tid == 8) ts.deg_sum = 0ull;
     __threadfence();
@@ -130,7 +149,17 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   uint32_t* sh = reinterpret_cast<uint32_t*>(tsm);
   uint32_t* alive = sh;                                               // W words
   unsigned short* list = reinterpret_cast<unsigned short*>(sh + W);   // n entries
-  if (tid == 0) ts.lb = 0;
+  if (tid == 0) {
+    ts.lb = 0;
+    // row cache: whatever shared memory the launch got beyond the heuristic's own arrays (the translation scratch reuses all of it later)
+    size_t off = (heuristic_smem_bytes(n) + 15) & ~(size_t)15;
+    rcache.P1 = reinterpret_cast<uint32_t*>(tsm + off); off += (size_t)W * 4;
+    rcache.pre = reinterpret_cast<unsigned short*>(tsm + off); off += ((size_t)W * 2 + 15) & ~(size_t)15;
+    rcache.rows = reinterpret_cast<uint32_t*>(tsm + off);
+    rcache.cap = (size_t)dyn_smem_bytes > off ? (int)(((size_t)dyn_smem_bytes - off) / ((size_t)W * 4)) : 0;
+    rcache.n_cached = 0; rcache.W = W; rcache.mbar = &rc_bar;
+    rc_mbar_init(&rc_bar);
+  }
   __syncthreads();
   unsigned long long heu_key = 0ull;
   int lb = 0, T = 0, n_alive = 0;
@@ -138,7 +167,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
     const unsigned long long skey = ts.key[k];
     if (skey == 0ull) continue;
     const int v = (int)(0xffffffffu - (unsigned)(skey & 0xffffffffu));
-    const int size = heuristic_seed_cta<kTailThreads, true>(d, v, sh, &ts.lb);
+    const int size = heuristic_seed_cta<kTailThreads, true, true>(d, v, sh, &ts.lb, &rcache, k == 0 ? tm : TailMarks());
     __syncthreads();
     if (size > 0) {
       const unsigned long long hk = ((unsigned long long)size << 32) | (unsigned long long)(0xffffffffu - (unsigned)v);
@@ -162,16 +191,24 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
       n_alive = tail_list_bits(alive, Wb, list, &ts);
       if (tid == 0) ts.changed = 0;
       __syncthreads();
-      if (T > 0) {
+      // |alive| == lb: every member of the greedy clique has at least lb - 1 = T neighbours, so it is inside `alive`, and a set of
+      // lb vertices that contains a clique of size lb IS that clique -- all of it survives any further pass: nothing to peel
+      if (T > 0 && n_alive != lb) {
         constexpr int R = 8;
         for (int m0 = warp; m0 < n_alive; m0 += R * kTailWarps) {
           int c[R], ids[R];
+          const uint4* rowp[R];
 #pragma unroll
           for (int q = 0; q < R; ++q) {
             const int m = m0 + q * kTailWarps;
             ids[q] = m < n_alive ? (int)list[m] : -1;
+            rowp[q] = nullptr;
+            if (ids[q] >= 0) {
+              rowp[q] = cached_row(rcache, ids[q]);
+              if (!rowp[q]) rowp[q] = reinterpret_cast<const uint4*>(d.adj + (size_t)ids[q] * d.pitch);
+            }
           }
-          rows_and_count<R, true>(d.adj, d.pitch, ids, alive, W >> 2, lane, c);
+          rows_and_count<R>(rowp, alive, W >> 2, lane, c);
 #pragma unroll
           for (int q = 0; q < R; ++q) {
             if (ids[q] < 0) continue;
@@ -206,10 +243,10 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   stamp(4);
 
   // ---- 6. rotation on the first thread group, then the three translation axes on all three ----
-  if (tid < kRtThreads) rotation_body(d, kp, 4);
+  if (tid < kRtThreads) rotation_body(d, kp, 4, tm);
   __syncthreads();
   stamp(5);
-  translation_body(d, kp, reinterpret_cast<double*>(tsm));
+  translation_body(d, kp, reinterpret_cast<double*>(tsm), tm);
   __syncthreads();
   stamp(6);
   if (tid == 0) st->tail_done = 1;
@@ -221,10 +258,29 @@ size_t tail_smem_bytes(int n_max) {
   return (tr > he ? tr : he) + 16;
 }
 
+// The kernel always gets all the shared memory an SM can give one CTA (it runs one CTA per SM by its thread count anyway): what
+// the stages do not need themselves holds staged adjacency rows (RowCache).
 int launch_tail(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, int mode, cudaStream_t st) {
   static PerDeviceOnce attr;
-  attr.run([] { return cudaFuncSetAttribute(tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tail_smem_bytes(kMaxN)); });
-  tail_kernel<<<batch, kTailThreads, tail_smem_bytes(n_max), st>>>(d_desc, kp, mode);
+  static int dyn_max[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  attr.run([dev] {
+    int optin = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaFuncAttributes fa;
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, tail_kernel);
+    if (e != cudaSuccess) return e;
+    dyn_max[dev & 63] = optin - (int)fa.sharedSizeBytes;
+    return cudaFuncSetAttribute(tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max[dev & 63]);
+  });
+  int dyn = dyn_max[dev & 63];
+  // not the whole SM: with the maximum carve-out (227 KB) the first stage of the kernel ran 60 k cycles longer on B200 (0.183 vs
+  // 0.133 ms per batch) -- 160 KB holds 235 rows at N = 5000.  B2R_TAIL_SMEM_KB overrides (A/B runs).
+  static const int cap_kb = [] { const char* e = getenv("B2R_TAIL_SMEM_KB"); return e ? atoi(e) : 160; }();
+  if (cap_kb > 0 && dyn > cap_kb * 1024) dyn = cap_kb * 1024;
+  if (dyn < (int)tail_smem_bytes(n_max)) dyn = (int)tail_smem_bytes(n_max);   // (attribute query failed: the launch will report it)
+  tail_kernel<<<batch, kTailThreads, dyn, st>>>(d_desc, kp, mode, dyn);
   return 1;
 }
 

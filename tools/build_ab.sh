@@ -7,9 +7,9 @@ tag=$1; shift
 mkdir -p _ab/_obj_$tag
 ARCH="-gencode arch=compute_100a,code=sm_100a"
 objs=""
-for f in api clique rt radix scale presteps nn_gemm refine raster graph graph_tc; do
+for f in api clique tail rt radix scale presteps nn_gemm refine raster graph graph_tc; do
   case $f in
-    graph|graph_tc|rt|clique) nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -cudart static "$@" -c $f.cu -o _ab/_obj_$tag/$f.o & objs="$objs _ab/_obj_$tag/$f.o";;
+    graph|graph_tc|rt|clique|tail) nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -cudart static "$@" -c $f.cu -o _ab/_obj_$tag/$f.o & objs="$objs _ab/_obj_$tag/$f.o";;
     *) objs="$objs _obj/$f.o";;
   esac
 done
