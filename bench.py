@@ -8,7 +8,7 @@ consistency graph -> max clique -> GNC-TLS rotation -> adaptive-voting translati
             latency-bound tail of a batch overlaps the next batch's graph kernel; value_one_handle = the serial one-handle pass
             (L2 flushed between steps) that also yields the per-stage times
   e2e       the same work through the public host API (numpy in, solutions out): H2D + kernels + D2H per step
-  roofline  the dominant stage (tensor-core graph filter, tim_graph5_kernel + its three helper kernels): algorithmic bytes /
+  roofline  the dominant stage (tensor-core graph filter, tim_graph6_kernel + its set-up kernel): algorithmic bytes /
             measured stage time vs measured HBM peak, plus pair tests per second (the kernel is issue-bound -- DESIGN.md)
   cpu_baseline / --impl reference   the oracle (CPU port of the reference's TEASER++ path) on the host cores
 
@@ -368,7 +368,7 @@ def main():
         pairs = N_CORR * (N_CORR - 1) // 2 * B
         evaluated = graph_units(N_CORR) * 128 * 64 * B
         traffic = None
-        tp = os.path.join(ROOT, "profiles", "r01_graph5_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r02_graph6_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             if tj.get("batch") == B and tj.get("n") == N_CORR:
@@ -376,7 +376,7 @@ def main():
         # second reading of the same kernel: the stage is bound by warp-instruction issue, not HBM.  Instructions per launch from
         # the committed ncu capture (smsp__inst_executed.sum, same grid: 64 x 5000); peak = SMs x 4 schedulers x SM clock under load.
         issue = None
-        ip = os.path.join(ROOT, "profiles", "r01_graph5_full_ncu.json")
+        ip = os.path.join(ROOT, "profiles", "r02_graph6_full_ncu.json")
         if traffic is not None and os.path.exists(ip):
             winst = json.load(open(ip)).get("smsp__inst_executed.sum")
             clk = sampler.summary().get("sm_mhz") or 0.0
@@ -395,7 +395,7 @@ def main():
                        "l2": f"every step reads one of {NSETS} device copies of the inputs in turn ({NSETS} x 15.4 MB > 126 MB L2) and writes "
                              "205 MB of adjacency; the one-handle serial pass (value_one_handle, stage_ms_per_step) flushes L2 with a 256 MiB write between steps",
                        "sharding": "independent registrations per rank, no collective"},
-            "roofline": {"bound": "hbm", "kernel": "tim_graph5_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "tim_graph6_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_note,
                          "note": "O(N^2) pair tests for O(N^2/32) bytes out: far from the HBM roof by construction.  Dm and L of every "
                                  "pair come from tcgen05.mma (TF32) into TMEM; the kernel is bound by the issue slots of its epilogue "

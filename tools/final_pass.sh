@@ -11,7 +11,7 @@ timeout 600 python bench.py --impl reference > $D/bench_ref.json 2> $D/bench_ref
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/bench_short.json 2> $D/bench_short.err && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $D/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/ncu_list.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:tim_graph5 -s 3 -c 1 -o $D/graph5_full -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:tim_graph6 -s 3 -c 1 -o $D/graph6_full -f \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/ncu_full.log 2>&1
 ls -la $D | tail -12
 python - <<PY

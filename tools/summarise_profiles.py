@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 STAGE_OF = {
     "tim_graph": "graph", "graph_prep": "graph", "graph_tc": "graph", "graph_fix": "graph", "degree": "degree", "heuristic": "heuristic", "prune": "prune_compact",
     "compact": "prune_compact", "bnb": "exact_search", "canon": "canonical", "rotation": "rotation",
-    "translation": "translation", "gather": "rotation",
+    "translation": "translation", "gather": "rotation", "tail_kernel": "tail_fused",
 }
 
 NCU_KEYS = [
