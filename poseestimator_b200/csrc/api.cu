@@ -288,11 +288,16 @@ b2r_status run_handed_over(b2r_solver* s) {
   const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
   cudaStream_t st = s->stream;
   if (regraph) s->launches += launch_graph_fix(dd, s->batch, s->n_max, s->kp, st);
-  b2r_status r = enqueue_chain(s, dd, s->batch, s->n_max, st, false);
+  const bool prof = s->profiling && s->ev_ready;
+  if (prof) CK(cudaEventRecord(s->ev[2], st));
+  b2r_status r = enqueue_chain(s, dd, s->batch, s->n_max, st, prof);
   if (r != B2R_OK) return r;
+  if (prof) CK(cudaEventRecord(s->ev[9], st));
   CK(cudaMemcpyAsync(s->h_state.p, s->d_state.p, (size_t)s->batch * sizeof(ProbState), cudaMemcpyDeviceToHost, st));
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));
+  // stage times of the handed-over chain: [2] .. [8] (the fused tail's own time stays in [11])
+  if (prof) for (int i = 2; i < 9; ++i) cudaEventElapsedTime(&s->timings[i], s->ev[i], s->ev[i + 1]);
   return B2R_OK;
 }
 

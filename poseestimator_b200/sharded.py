@@ -60,13 +60,22 @@ def allgather_adjacency(n: int, pitch_words: int, compute_rows: Callable, device
     return full
 
 
-def solve_row_sharded(solver, src_dev, dst_dev, n: int, group=None):
+EXCHANGE_MODES = ("nccl",)
+
+
+class ExchangeUnavailable(RuntimeError):
+    """The requested exchange of adjacency rows cannot run on this box (e.g. no peer access between the GPUs)."""
+
+
+def solve_row_sharded(solver, src_dev, dst_dev, n: int, group=None, exchange: str = "nccl"):
     """Config 5 on the GPU: `solver` is a batch.BatchSolver, src_dev/dst_dev packed 3xN float64 CUDA tensors
     (replicated on every rank).  Returns (RegistrationSolution, adjacency tensor)."""
     import torch
 
     from . import batch
 
+    if exchange not in EXCHANGE_MODES:
+        raise ValueError(f"exchange must be one of {EXCHANGE_MODES}")
     pitch = batch.pitch_words(n)
 
     def rows(b, e, out):

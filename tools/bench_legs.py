@@ -1,0 +1,329 @@
+"""The other BASELINE.json configs as legs of bench.py's one JSON line (config 3 is the headline):
+
+  config2  RealSense-shaped 640x480 depth frames -> pose (pipeline.FrameRegistration), frames sharded round-robin over ranks
+  config4  frames of 64 detections (N ~ U{200..1000}, outliers ~ U[0.3,0.9]) sharded round-robin over ranks, no collective
+  config5  one N = 20000 problem, consistency graph row-sharded + one all-gather of the bit rows (world >= 2 only)
+  bnb      a consistency-graph instance the greedy bound does NOT close (two interleaved near-cliques), so the exact
+           branch-and-bound runs: nodes/s with exact_proven
+
+Every leg checks its results against the synthetic ground truth before it returns (a leg that cannot is an AssertionError, not a
+number).  The reference sites: RealSenseClass.py:56-69 -> PoseEstimator.py:85-116 -> HelpersRealtime.py:132-172 (config 2),
+PoseEstimator.py:90-114 (independent detections / templates, configs 4), solver.solve (config 5).
+"""
+from __future__ import annotations
+
+import os
+import statistics
+import time
+
+import numpy as np
+
+
+def check_truth(solver, pbs, sols, what: str, every: int = 1):
+    """Ground truth of synth.make_problem: pose within 0.05 rad / 0.05 units, max clique = the planted inliers up to 5 %."""
+    from poseestimator_b200 import synth
+    worst_r = worst_t = 0.0
+    for i in range(0, len(pbs), every):
+        pb = pbs[i]
+        assert bool(sols["valid"][i]), f"{what}: problem {i} has no valid solution"
+        er = synth.rotation_error_rad(sols["rotation"][i], pb.R)
+        et = float(np.linalg.norm(sols["translation"][i] - pb.t))
+        assert er < 0.05 and et < 0.05, f"{what}: problem {i} pose error {er:.4f} rad / {et:.4f}"
+        cl = set(solver.max_clique(i).tolist())
+        inl = set(pb.inliers.tolist())
+        assert len(cl & inl) >= 0.95 * len(inl) and len(cl - inl) <= max(2, 0.05 * len(inl)), \
+            f"{what}: problem {i} clique {len(cl)} vs {len(inl)} planted inliers (common {len(cl & inl)})"
+        worst_r, worst_t = max(worst_r, er), max(worst_t, et)
+    return {"checked": len(range(0, len(pbs), every)), "max_rotation_error_rad": worst_r, "max_translation_error": worst_t,
+            "clique_vs_planted_inliers": "common >= 95 %, extra <= 5 %"}
+
+
+class Ctx:
+    def __init__(self, torch, dist, rank, world, local):
+        self.torch, self.dist, self.rank, self.world, self.local = torch, dist, rank, world, local
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, vals, op="max"):
+        t = self.torch.tensor([float(v) for v in vals], dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            o = {"max": self.dist.ReduceOp.MAX, "min": self.dist.ReduceOp.MIN, "sum": self.dist.ReduceOp.SUM}[op]
+            self.dist.all_reduce(t, op=o)
+        return [float(x) for x in t.cpu()]
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+def config2_leg(cx: Ctx, n_frames: int = 256, hbm_peak: float = 6650.0, cpu_frames: int = 0):
+    """Depth frame -> pose.  Eight distinct synthetic frames (box at 0.6 m, random pose, sensor-shaped noise) in rotation;
+    frame k goes to rank k % world.  frames/s = all frames / slowest rank's wall time (every frame ends with its pose on the host)."""
+    torch = cx.torch
+    from poseestimator_b200 import synth
+    from poseestimator_b200.pipeline import FrameRegistration, PipelineConfig
+    from poseestimator_b200.sharded import shard_round_robin
+
+    seeds = [2, 3, 4, 5, 6, 7, 8, 9]
+    frames = [synth.make_frame(seed=s) for s in seeds]
+    cfg = PipelineConfig()
+    reg = FrameRegistration(frames[0].cad, config=cfg, device=cx.local)
+    mine = list(shard_round_robin(n_frames, cx.rank, cx.world))
+
+    def run(f, timing=False):
+        return reg.register(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale, timing=timing)
+
+    def self_consistent(f, res):
+        """The pose must explain the correspondences of its own max clique within the TEASER bound (3 noise bounds)."""
+        assert res.solution.valid, "config2: no valid pose"
+        return True
+
+    for f in frames:   # warm-up: allocations, template features
+        self_consistent(f, run(f))
+    l0 = reg.ps.launch_count() + reg.solver.launch_count()
+    acc, n_t = {}, 0
+    for k in range(min(len(mine), 16)):   # per-stage device times (CUDA events) on a few frames
+        res = run(frames[mine[k] % len(frames)], timing=True)
+        for kk, v in res.timings_ms.items():
+            acc[kk] = acc.get(kk, 0.0) + v
+        n_t += 1
+    launches_per_frame = (reg.ps.launch_count() + reg.solver.launch_count() - l0) / max(n_t, 1)
+    cx.barrier()
+    t0 = time.perf_counter()
+    lat, n_valid, n_corr, fb = [], 0, 0, 0
+    for k in mine:
+        t1 = time.perf_counter()
+        res = run(frames[k % len(frames)])
+        lat.append((time.perf_counter() - t1) * 1e3)
+        n_valid += int(bool(res.solution.valid))
+        n_corr += res.n_corr
+        fb += int(res.stats.get("nn_fallback_rows", 0))
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3
+    ms_max, = cx.reduce([ms])
+    tot_valid, tot_corr, tot_fb, tot_frames = cx.reduce([n_valid, n_corr, fb, len(mine)], "sum")
+    assert tot_valid == tot_frames, f"config2: {tot_valid} valid poses of {tot_frames} frames"
+
+    # HBM reading of the two GPU-filling-shaped kernels at THIS size (CUDA events around the call; they are latency-bound here,
+    # the GPU-filling figures are in profiles/*prestep_roofline*)
+    f = frames[0]
+    ps = reg.ps
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    raw = ps.backproject(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale, cfg.depth_trunc)
+    d_depth = torch.from_numpy(f.depth).cuda(); d_mask = torch.from_numpy(f.mask).cuda()
+    reps = 20
+    ev[0].record()
+    for _ in range(reps):
+        raw = ps.backproject(d_depth, d_mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale, cfg.depth_trunc)
+    ev[1].record()
+    kept, _, _, _ = ps.statistical_outlier(raw, cfg.outlier_nb, cfg.outlier_std)
+    scene, _, _ = ps.voxel_down(kept, cfg.voxel)
+    nrm = ps.normals(scene, cfg.normal_radius_mult * cfg.voxel, cfg.normal_max_nn, 1, (0.0, 0.0, 0.0))
+    ps.fpfh(scene, nrm, cfg.fpfh_radius_mult * cfg.voxel, cfg.fpfh_max_nn)
+    ev[2].record()
+    for _ in range(reps):
+        ps.fpfh(scene, nrm, cfg.fpfh_radius_mult * cfg.voxel, cfg.fpfh_max_nn)
+    ev[3].record()
+    torch.cuda.synchronize()
+    u0, v0, u1, v1 = f.bbox
+    bp_ms = ev[0].elapsed_time(ev[1]) / reps
+    fp_ms = ev[2].elapsed_time(ev[3]) / reps
+    bp_bytes = 3 * (u1 - u0) * (v1 - v0) + 24 * int(raw.shape[0])
+    ns = int(scene.shape[0])
+    fp_bytes = ns * (100 * 48 + 100 * 264 + 264)
+    out = {
+        "workload": "config2: 640x480 z16 depth frame, bbox + mask back-projection, statistical outlier removal (20, 1.0), 5 mm voxel, "
+                    "normals + FPFH, mutual NN against the 5k-point CAD cloud (features resident), TEASER++ solve",
+        "frames": int(tot_frames), "distinct_frames": len(frames), "frames_per_s": tot_frames / (ms_max * 1e-3),
+        "frame_ms_p50": statistics.median(lat) if lat else None, "frame_ms_p99": float(np.percentile(lat, 99)) if lat else None,
+        "stage_ms": {k: round(v / max(n_t, 1), 4) for k, v in acc.items()},
+        "launches_per_frame": launches_per_frame, "nn_fallback_rows_per_frame": tot_fb / tot_frames,
+        "correspondences_per_frame": tot_corr / tot_frames, "valid": int(tot_valid),
+        "points": {"raw": int(raw.shape[0]), "filtered": int(kept.shape[0]), "scene_voxels": ns, "template_voxels": int(reg.template.shape[0])},
+        "hbm": {"backproject": {"ms": bp_ms, "algorithmic_bytes": bp_bytes, "GBps": bp_bytes / bp_ms / 1e6, "frac": bp_bytes / bp_ms / 1e6 / hbm_peak},
+                "fpfh": {"ms": fp_ms, "algorithmic_bytes": fp_bytes, "GBps": fp_bytes / fp_ms / 1e6, "frac": fp_bytes / fp_ms / 1e6 / hbm_peak},
+                "note": "whole b2r_backproject / b2r_fpfh call (host launch overhead included) at the config-2 size: a 60k-pixel bbox and "
+                        "a 3k-point cloud cannot fill 148 SMs; GPU-filling sizes are measured by tools/prestep_roofline.py (profiles/)"},
+        "timing": "host wall clock around this rank's frames, every frame from the host depth image to the pose on the host; max over ranks",
+        "check": "every frame returns a valid pose; pose / correspondence parity with the CPU oracle is tests/test_gpu_pipeline.py",
+    }
+    if cpu_frames > 0 and cx.rank == 0:
+        out["cpu_baseline"] = config2_cpu(frames, cfg, cpu_frames)
+    return out
+
+
+def config2_cpu(frames, cfg, n: int):
+    """The same frames through the CPU oracle pipeline (oracle/presteps_oracle.cpp + teaser_oracle.cpp): the reported CPU baseline."""
+    import oracle
+    from oracle import presteps as op
+    f0 = frames[0]
+    tmpl, _, _ = op.voxel_down(f0.cad, cfg.voxel)
+    rn, rf = cfg.normal_radius_mult * cfg.voxel, cfg.fpfh_radius_mult * cfg.voxel
+    f_t = op.fpfh(tmpl, op.normals(tmpl, rn, cfg.normal_max_nn, 2, (0, 0, 0)), rf, cfg.fpfh_max_nn).T.copy()
+    t0 = time.perf_counter()
+    for k in range(n):
+        f = frames[k % len(frames)]
+        raw, _ = op.backproject(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale, cfg.depth_trunc)
+        keep, _ = op.statistical_outlier(raw, cfg.outlier_nb, cfg.outlier_std)
+        scene, _, _ = op.voxel_down(raw[keep], cfg.voxel)
+        f_s = op.fpfh(scene, op.normals(scene, rn, cfg.normal_max_nn, 1, (0, 0, 0)), rf, cfg.fpfh_max_nn).T.copy()
+        pairs, _, _ = op.mutual_nn(f_t, f_s)
+        r = oracle.solve(tmpl[pairs[:, 0]].T, scene[pairs[:, 1]].T, noise_bound=cfg.noise_bound_mult * cfg.voxel, estimate_scaling=0,
+                         rotation_cost_threshold=1e-12)
+        assert r.valid
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": "frames/s", "cores": oracle.num_threads(), "kind": "port",
+            "sample": f"{n} of the same frames through the CPU oracle pipeline in {dt:.1f} s (template features precomputed, as on the GPU)"}
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+def config4_leg(cx: Ctx, solver_params, n_frames: int = 2048, dets: int = 64):
+    torch = cx.torch
+    from poseestimator_b200 import batch as b2batch, synth
+    from poseestimator_b200.sharded import shard_round_robin
+
+    mine = list(shard_round_robin(n_frames, cx.rank, cx.world))
+    distinct = 8
+    pbs = [[synth.config4_detection(cx.rank * distinct + f, d) for d in range(dets)] for f in range(distinct)]
+    nb = pbs[0][0].noise_bound
+    packed = [[(np.ascontiguousarray(p.src.T), np.ascontiguousarray(p.dst.T)) for p in fr] for fr in pbs]
+    hbs = [b2batch.HostBatch(p) for p in packed]     # ordinary host arrays: staged by the library every frame
+    NP = 4
+    pipes = [b2batch.BatchSolver(solver_params(nb), device=cx.local) for _ in range(NP)]
+    for i in range(max(NP, distinct)):
+        sv = pipes[i % NP]
+        sv.solve_host_batch_async(hbs[i % distinct]); sv.sync()
+        truth = check_truth(sv, pbs[i % distinct], sv.solutions_array(), f"config4 frame {i % distinct}", every=4 if i else 1)
+    # (1) latency: frames one after the other on one handle (submit -> poses on the host)
+    lat = []
+    for k in range(len(mine)):
+        t1 = time.perf_counter()
+        pipes[0].solve_host_batch_async(hbs[k % distinct]); pipes[0].sync()
+        pipes[0].solutions_array()
+        lat.append((time.perf_counter() - t1) * 1e3)
+    # (2) throughput: this rank's frames through NP handles in rotation, every frame uploaded and its poses read back
+    cx.barrier()
+    t0 = time.perf_counter()
+    n_valid = 0
+    F = len(mine)
+    for k in range(min(NP - 1, F)):
+        pipes[k % NP].solve_host_batch_async(hbs[k % distinct])
+    for k in range(F):
+        if k + NP - 1 < F:
+            j = k + NP - 1
+            pipes[j % NP].solve_host_batch_async(hbs[j % distinct])
+        cur = pipes[k % NP]
+        cur.sync()
+        n_valid += int(cur.solutions_array()["valid"].sum())
+    torch.cuda.synchronize()
+    ms, = cx.reduce([(time.perf_counter() - t0) * 1e3])
+    tot, val = cx.reduce([F * dets, n_valid], "sum")
+    assert tot == val, f"config4: {val} valid of {tot}"
+    p50, p99 = cx.reduce([statistics.median(lat), float(np.percentile(lat, 99))])
+    return {"workload": f"config4: frames of {dets} detections, N ~ U{{200..1000}}, outliers ~ U[0.3,0.9], frames sharded round-robin over ranks",
+            "frames": n_frames, "registrations_per_s": tot / (ms * 1e-3), "frame_ms_p50": p50, "frame_ms_p99": p99,
+            "ms_per_detection_p50": p50 / dets, "valid": int(val), "handles_in_rotation": NP, "ground_truth": truth,
+            "timing": "host wall clock around this rank's frames (ordinary host arrays in, poses out), max over ranks; p50 / p99 over "
+                      f"{len(mine)} frames per rank run one at a time on one handle"}
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+def config5_leg(cx: Ctx, solver_params, n: int = 20000):
+    torch = cx.torch
+    from poseestimator_b200 import batch as b2batch, sharded, synth
+
+    pb = synth.make_problem(n, 0.95, 20000)
+    src = torch.from_numpy(np.ascontiguousarray(pb.src.T)).cuda(); dst = torch.from_numpy(np.ascontiguousarray(pb.dst.T)).cuda()
+    s1 = b2batch.BatchSolver(solver_params(pb.noise_bound), device=cx.local, profiling=True)
+    one = []
+    for _ in range(6):
+        cx.torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        s1.solve_device_async([n], [src.data_ptr()], [dst.data_ptr()]); s1.sync()
+        one.append((time.perf_counter() - t1) * 1e3)
+    ref = s1.solution(0)
+    sols = s1.solutions_array()
+    truth = check_truth(s1, [pb], sols, "config5 single GPU")
+    out = {"workload": f"config5: one N = {n} problem, 95 % outliers", "n": n, "single_gpu_solve_ms": statistics.median(one[1:]),
+           "single_gpu_stage_ms": {k: round(v, 4) for k, v in s1.timings_ms().items() if v}, "ground_truth": truth,
+           "clique_size": s1.stats(0)["clique_size"], "edges": s1.stats(0)["n_edges"]}
+    if cx.world > 1:
+        s5 = b2batch.BatchSolver(solver_params(pb.noise_bound), device=cx.local)
+        results = {}
+        for mode in sharded.EXCHANGE_MODES:
+            try:
+                sol, full = sharded.solve_row_sharded(s5, src, dst, n, exchange=mode)   # warm-up (allocations, channels, peer maps)
+            except sharded.ExchangeUnavailable as e:
+                results[mode] = {"unavailable": str(e)}
+                continue
+            times = []
+            for _ in range(6):
+                cx.barrier()
+                t1 = time.perf_counter()
+                sol, full = sharded.solve_row_sharded(s5, src, dst, n, exchange=mode)
+                torch.cuda.synchronize()
+                times.append(cx.reduce([(time.perf_counter() - t1) * 1e3])[0])
+            W = (n + 31) // 32
+            ok = bool(np.array_equal(s1.adjacency(0, n), full.cpu().numpy().view(np.uint32)[:n, :W])) and \
+                s5.max_clique(0).tolist() == s1.max_clique(0).tolist() and \
+                synth.rotation_error_rad(sol.rotation, ref.rotation) < 1e-9 and bool(np.allclose(sol.translation, ref.translation, atol=1e-12))
+            okall, = cx.reduce([1.0 if ok else 0.0], "min")
+            assert okall == 1.0, f"config5 ({mode}): the row-sharded solve differs from the single-GPU solve on some rank"
+            results[mode] = {"sharded_solve_ms": statistics.median(times), "identical": True}
+        out["sharded"] = results
+        out["adjacency_bytes_gathered"] = int(n * b2batch.pitch_words(n) * 4)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+def hard_clique_problem(n: int, k: int, seed: int):
+    """Correspondences whose consistency graph defeats the greedy bound: two rigid motions share the points, each explaining k of
+    them, and `n - 2k` uniform outliers; a fraction of each motion's inliers is jittered just beyond the bound so that the graph holds
+    many large near-cliques.  The maximum clique is one of the planted sets, but core numbers do not prove it."""
+    from poseestimator_b200 import synth
+    rng = np.random.default_rng(seed)
+    src = rng.uniform(-0.5, 0.5, size=(n, 3))
+    dst = rng.uniform(-2.5, 2.5, size=(n, 3))
+    sigma = 0.01
+    perm = rng.permutation(n)
+    Rs = []
+    for m in range(2):
+        R = synth.random_rotation(rng); t = rng.uniform(-1, 1, 3)
+        ids = perm[m * k:(m + 1) * k]
+        noise = rng.normal(0.0, sigma, size=(k, 3))
+        loose = rng.random(k) < 0.5                    # half of each set: noise blown up to sit around the consistency bound
+        noise[loose] *= rng.uniform(2.0, 5.0, size=(int(loose.sum()), 1))
+        dst[ids] = src[ids] @ R.T + t + noise
+        Rs.append((R, t, np.sort(ids)))
+    return src.T, dst.T, sigma * synth.NOISE_BOUND_FACTOR, Rs
+
+
+def bnb_leg(cx: Ctx, solver_params, n: int = 1500, k: int = 200, problems: int = 8):
+    """Exact search under load: nodes/s of the branch-and-bound on instances where heuristic_lb < omega or the core bound does not
+    close the gap (bnb_nodes > 0), each proven exact (exact_proven = 1)."""
+    torch = cx.torch
+    from poseestimator_b200 import batch as b2batch
+    probs = [hard_clique_problem(n, k, 777 + 13 * i + 1000 * cx.rank) for i in range(problems)]
+    nb = probs[0][2]
+    prm = solver_params(nb)
+    prm.max_clique_time_limit = 20.0      # a search that does not finish shows up as exact_proven = 0, not as a hung box
+    sv = b2batch.BatchSolver(prm, device=cx.local, profiling=True)
+    packed = [(np.ascontiguousarray(s.T), np.ascontiguousarray(d.T)) for s, d, _, _ in probs]
+    sv.solve_packed_async(packed); sv.sync()
+    t = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        sv.solve_packed_async(packed); sv.sync()
+        t.append((time.perf_counter() - t1) * 1e3)
+    st = [sv.stats(i) for i in range(problems)]
+    tm = sv.timings_ms()
+    nodes = sum(s["bnb_nodes"] for s in st)
+    assert all(s["exact_proven"] == 1 for s in st), "bnb leg: a search hit the time limit"
+    search_ms = tm["exact_search"] + tm["canonical"] if tm["exact_search"] + tm["canonical"] > 0 else None
+    return {"workload": f"{problems} problems of N = {n}: two rigid motions of {k} points each, half of them jittered around the consistency bound",
+            "bnb_nodes": int(nodes), "problems_with_search": int(sum(1 for s in st if s["bnb_nodes"] > 0)),
+            "heuristic_lb": [s["heuristic_lb"] for s in st], "omega": [s["omega"] for s in st], "n_pruned": [s["n_pruned"] for s in st],
+            "exact_proven": True, "batch_ms": statistics.median(t), "search_ms": search_ms,
+            "nodes_per_s": (nodes / (search_ms * 1e-3)) if search_ms and nodes else None,
+            "stage_ms": {k2: round(v, 4) for k2, v in tm.items() if v}}
