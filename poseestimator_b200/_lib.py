@@ -68,7 +68,8 @@ EXPORTS = [
 ]
 
 # include/b2r_debug.h: test hooks, not part of the drop-in boundary
-DEBUG_EXPORTS = ["b2r_debug_set_graph_filter", "b2r_debug_tc_values", "b2r_debug_tc_sweep", "b2r_debug_tail_cycles"]
+DEBUG_EXPORTS = ["b2r_debug_set_graph_filter", "b2r_debug_tc_values", "b2r_debug_tc_sweep", "b2r_debug_tail_cycles",
+                 "b2r_debug_nn_gemm_error"]
 
 # numpy view of an array of b2r_solution (112 bytes each)
 import numpy as _np  # noqa: E402
@@ -125,6 +126,7 @@ def lib():
     L.b2r_debug_set_graph_filter.argtypes = [vp, i32, C.c_double]
     L.b2r_debug_tc_sweep.argtypes = [vp, i32, vp]
     L.b2r_debug_tail_cycles.argtypes = [vp, i32, vp]
+    L.b2r_debug_nn_gemm_error.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp]
     L.b2r_pitch_words.argtypes = [i32]
     L.b2r_pitch_words.restype = i32
     d, ip = C.c_double, C.POINTER(C.c_int)

@@ -18,6 +18,7 @@
 #include <math_constants.h>
 
 #include "solver.cuh"
+#include "../../include/b2r_debug.h"
 
 namespace b2r {
 
@@ -30,16 +31,25 @@ constexpr int kKTot = 128;        // 3 segments (120) padded to four 128-byte sw
 constexpr int kKBlocks = 4;       // 32 floats (128 B) each
 constexpr int kTopK = 4;
 constexpr int kMaxSplits = 16;
-constexpr int kGemmThreads = 192; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int kEpiWarps = 8;      // lane quarter x column half of the 128 x 128 accumulator
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..9 epilogue
 constexpr uint32_t kTileBytes = kBM * 128;                 // one k-block of one operand tile: 128 rows x 128 B
 constexpr uint32_t kOperandBytes = kKBlocks * kTileBytes;  // 64 KB
-// |D~_ij - D_ij| <= kEpsRel * (|fq_i - c|^2 + |fr_j - c|^2) for descriptors centred on c (nn_centre_kernel).  With u = 2^-24:
-//   fp32 copy of a centred coordinate x' = X (1 + d), |d| <= u;  3xTF32 split x' = hi + lo + r, |r| <= 2^-22 |x'|;
-//   dropped lo.lo and r terms: 3 * 2^-22 sum|x'y'|;  fp32 accumulation on the tensor core over K = 120: assumed within
-//   2^-18 of sum|products| (measured 2^-22 for K = 32 in the graph filter, tests/test_gpu_tc_sweep.py; 16x margin);
-//   with sum|x'y'| <= (nq + nr) / 2 and the factor 2 of -2 x.y:  (3 * 2^-22 + 2^-18 + 2u)(nq + nr) + norms and final fma (4u)
-//   = 4.9e-6 (nq + nr)  ->  6e-6.
-constexpr double kEpsRel = 6.0e-6;
+// |D~_ij - D_ij| <= kEpsRel * (|fq_i - c|^2 + |fr_j - c|^2) for descriptors centred on c (nn_centre_kernel).  With u = 2^-24 and
+// x.y = sum_k x_k y_k of the centred fp64 rows (sum|x_k y_k| <= (nq + nr) / 2):
+//   fp32 copy of a centred coordinate x' = x (1 + d), |d| <= u                          -> 2u              sum|xy|
+//   3xTF32 split x' = hi + lo + r, |r| <= 2^-22 |x'|; dropped lo.lo and r terms          -> 3 * 2^-22       sum|xy|
+//   products of two TF32 values are exact in fp32; fp32 accumulation on the tensor core over K = 128 (16 chained K = 8
+//   instructions): ASSUMED within 2^-19 of sum|products| -- measured 2^-22.2 for the 4-instruction chain of the graph filter
+//   (tests/test_gpu_tc_sweep.py), i.e. 2.3x margin over a linear growth with the chain length; the total is MEASURED on every
+//   candidate pair of a run by b2r_debug_nn_gemm_error (tests/test_gpu_presteps.py)       -> 2^-19 (1 + 2^-10) sum|xy|
+//   => |acc - x.y| <= 2.75e-6 sum|xy|, times 2 for -2 x.y, with sum|xy| <= (nq + nr) / 2  -> 2.75e-6 (nq + nr)
+//   norms rounded up to fp32 (2^-23 each), final fma rounding u |v| <= 2u (nq + nr)       -> 0.25e-6 (nq + nr)
+//   = 3.0e-6 (nq + nr)  ->  3.2e-6.
+// The epilogue ranks references by the LOWER BOUND v_lo = fma(-2, acc, nr_lo), nr_lo = rd(nr (1 - kEpsRel)): the reference's own
+// share of the error is folded into the value it is ranked by, so the completeness test of a row needs no global norm maximum
+// (one far-away descriptor no longer widens every row's margin; nn_fallback_rows on the config-2 frame 31 % -> ~1 %).
+constexpr double kEpsRel = 3.2e-6;
 constexpr int kCentreRows = 4096;   // rows of the reference cloud whose mean is the common centre c
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------------------
@@ -143,7 +153,7 @@ __global__ void __launch_bounds__(1024) nn_centre_kernel(const double* __restric
 // out: [n_pad][128] floats.  role 0 (left operand): [hi | hi | lo | 0]; role 1 (right operand): [hi | lo | hi | 0].
 __global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__ f, int n, int dim, int n_pad, const double* __restrict__ centre,
                                                       float* __restrict__ out_l, float* __restrict__ out_r, float* __restrict__ norm,
-                                                      unsigned int* __restrict__ norm_max) {
+                                                      float* __restrict__ norm_lo) {
   const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
   if (e >= (long long)n_pad * kKTot) return;
   const int row = (int)(e / kKTot), k = (int)(e % kKTot);
@@ -160,9 +170,9 @@ __global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__
       double s = 0;
       for (int q = 0; q < dim; ++q) { const double v = f[(size_t)row * dim + q] - centre[q]; s += v * v; }
       nv = __double2float_ru(s);                 // rounded up: the norms only enter error bounds and the approximate distance
-      atomicMax(norm_max, __float_as_uint(nv));  // non-negative floats order like their bit patterns
     }
     norm[row] = nv;
+    norm_lo[row] = row < n ? __double2float_rd((double)nv * (1.0 - kEpsRel)) : CUDART_INF_F;
   }
 }
 
@@ -170,14 +180,14 @@ __global__ void __launch_bounds__(256) nn_prep_kernel(const double* __restrict__
 struct GemmSmem {
   uint64_t a_full, b_full[2], b_empty[2], acc_full[2], acc_empty[2];
   uint32_t tmem_base;
-  float nr[2][kBN];
+  alignas(16) float nr[2][kBN];
 };
 
 __global__ void __launch_bounds__(kGemmThreads, 1)
-nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const float* __restrict__ norm_r,
+nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const float* __restrict__ norm_r_lo,
                int n_ref, int col_tiles, int splits, float* __restrict__ cand_v, int* __restrict__ cand_j) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  unsigned char* sm = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS, not LD.E)
   unsigned char* sA = sm;
   unsigned char* sB = sm + kOperandBytes;                 // 2 stages
   GemmSmem* g = reinterpret_cast<GemmSmem*>(sm + 3 * kOperandBytes);
@@ -190,7 +200,7 @@ nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
 
   if (threadIdx.x == 0) {
     mbar_init(&g->a_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(&g->b_full[s], 1); mbar_init(&g->b_empty[s], 1); mbar_init(&g->acc_full[s], 1); mbar_init(&g->acc_empty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&g->b_full[s], 1); mbar_init(&g->b_empty[s], 1); mbar_init(&g->acc_full[s], 1); mbar_init(&g->acc_empty[s], kEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // TMEM: 2 accumulator stages x 128 columns
@@ -237,8 +247,9 @@ nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         tc_commit(&g->acc_full[s]);  // accumulator complete -> epilogue
       }
     }
-  } else {  // ===== epilogue: warps 2..5 own TMEM lane quarters 2,3,0,1 =====
+  } else {  // ===== epilogue: warps 2..9; warp & 3 = TMEM lane quarter it may read, (warp - 2) >> 2 = column half of every tile =====
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = quarter * 32 + lane;
     const int e = threadIdx.x - 64;
     float v0 = CUDART_INF_F, v1 = CUDART_INF_F, v2 = CUDART_INF_F, v3 = CUDART_INF_F;
@@ -247,23 +258,40 @@ nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
       const int s = t & 1;
       const uint32_t ph = (t >> 1) & 1;
       const int jbase = (c0 + t) * kBN;
-      g->nr[s][e] = (jbase + e < n_ref) ? norm_r[jbase + e] : CUDART_INF_F;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (e < kBN) g->nr[s][e] = (jbase + e < n_ref) ? norm_r_lo[jbase + e] : CUDART_INF_F;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(&g->acc_full[s], ph);
       tc_fence_after();
 #pragma unroll 1
-      for (int ch = 0; ch < kBN / 32; ++ch) {
+      for (int ch = 0; ch < kBN / 64; ++ch) {
         uint32_t acc[32];
-        tc_ld_32x32(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * kBN + ch * 32), acc);
+        const int cb = half * 64 + ch * 32;
+        tc_ld_32x32(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * kBN + cb), acc);
+        float nrv[32];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4 q4 = *reinterpret_cast<const float4*>(&g->nr[s][cb + 4 * c]);
+          nrv[4 * c] = q4.x; nrv[4 * c + 1] = q4.y; nrv[4 * c + 2] = q4.z; nrv[4 * c + 3] = q4.w;
+        }
         tc_wait_ld();
+        // v = lower bound of D_ij - nq_i (up to eps nq_i).  Fast path: one min over the 32 values against the row's 4th best;
+        // the insertion code runs only for chunks in which some row of the warp improves its list.
+        float m = CUDART_INF_F;
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
-          const float v = fmaf(-2.f, __uint_as_float(acc[c]), g->nr[s][ch * 32 + c]);
-          if (v < v3) {
-            v3 = v; j3 = jbase + ch * 32 + c;
-            if (v3 < v2) { const float tv = v2; v2 = v3; v3 = tv; const int tj = j2; j2 = j3; j3 = tj; }
-            if (v2 < v1) { const float tv = v1; v1 = v2; v2 = tv; const int tj = j1; j1 = j2; j2 = tj; }
-            if (v1 < v0) { const float tv = v0; v0 = v1; v1 = tv; const int tj = j0; j0 = j1; j1 = tj; }
+          nrv[c] = fmaf(-2.f, __uint_as_float(acc[c]), nrv[c]);
+          m = fminf(m, nrv[c]);
+        }
+        if (m < v3) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const float v = nrv[c];
+            if (v < v3) {
+              v3 = v; j3 = jbase + cb + c;
+              if (v3 < v2) { const float tv = v2; v2 = v3; v3 = tv; const int tj = j2; j2 = j3; j3 = tj; }
+              if (v2 < v1) { const float tv = v1; v1 = v2; v2 = tv; const int tj = j1; j1 = j2; j2 = tj; }
+              if (v1 < v0) { const float tv = v0; v0 = v1; v1 = tv; const int tj = j0; j0 = j1; j1 = tj; }
+            }
           }
         }
       }
@@ -271,9 +299,9 @@ nn_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(&g->acc_empty[s]);
     }
-    const size_t o = ((size_t)(row_tile * kBM + row) * splits + split) * kTopK;
-    cand_v[o] = v0; cand_v[o + 1] = v1; cand_v[o + 2] = v2; cand_v[o + 3] = v3;
-    cand_j[o] = j0; cand_j[o + 1] = j1; cand_j[o + 2] = j2; cand_j[o + 3] = j3;
+    const size_t o = ((size_t)(row_tile * kBM + row) * (2 * splits) + 2 * split + half) * kTopK;
+    *reinterpret_cast<float4*>(cand_v + o) = make_float4(v0, v1, v2, v3);
+    *reinterpret_cast<int4*>(cand_j + o) = make_int4(j0, j1, j2, j3);
   }
   tc_fence_before();
   __syncthreads();
@@ -292,53 +320,64 @@ __device__ __forceinline__ double exact_d2(const double* __restrict__ a, const d
 
 constexpr int kFinWarps = 4;
 
+// groups = 2 * splits candidate groups of kTopK per row (column range x column half), each sorted ascending by v_lo.
+// err_max (debug, may be NULL): max over ALL candidates of |(nq + v) - D| / (nq + nr_j) as float bits, v = v_lo + (nr - nr_lo).
 __global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double* __restrict__ fq, int nq, const double* __restrict__ fr, int nr,
                                                                    int dim, const float* __restrict__ norm_q, const float* __restrict__ norm_r,
-                                                                   const unsigned int* __restrict__ norm_r_max, const float* __restrict__ cand_v,
-                                                                   const int* __restrict__ cand_j, int splits, int* __restrict__ nn,
-                                                                   double* __restrict__ dist, unsigned int* __restrict__ n_fallback) {
+                                                                   const float* __restrict__ norm_r_lo, const float* __restrict__ cand_v,
+                                                                   const int* __restrict__ cand_j, int groups, int* __restrict__ nn,
+                                                                   double* __restrict__ dist, unsigned int* __restrict__ n_fallback,
+                                                                   unsigned int* __restrict__ err_max) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * kFinWarps + warp;
   if (i >= nq) return;
-  const int nc = splits * kTopK;
+  const int nc = groups * kTopK;
   const double nqi = (double)norm_q[i];
-  const double nmax = (double)__uint_as_float(*norm_r_max);
-  // approximate minimum over all candidates; the smallest "4th best" over the column ranges bounds what was NOT kept
-  double vmin = CUDART_INF; int jmin = -1; double kept_bound = CUDART_INF;
+  const double eq = kEpsRel * nqi;
+  // D_ij - nq_i lies in [v_lo - eq, v_lo + eq + 2.001 eps nr_j] for a kept reference and above kept - eq for every reference a
+  // group did NOT keep (kept = the group's last value; +inf while the group still had room).
+  double min_ub = CUDART_INF, kept = CUDART_INF;
+  bool any = false;
   for (int c = lane; c < nc; c += 32) {
-    const double v = (double)cand_v[(size_t)i * nc + c];
     const int j = cand_j[(size_t)i * nc + c];
-    if (j >= 0 && (v < vmin || (v == vmin && (unsigned)j < (unsigned)jmin))) { vmin = v; jmin = j; }
-    if ((c & (kTopK - 1)) == kTopK - 1) kept_bound = fmin(kept_bound, j >= 0 ? v : CUDART_INF);
+    const double v = (double)cand_v[(size_t)i * nc + c];
+    if (j >= 0) { any = true; min_ub = fmin(min_ub, v + eq + 2.001 * kEpsRel * (double)norm_r[j]); }
+    if ((c & (kTopK - 1)) == kTopK - 1 && j >= 0) kept = fmin(kept, v);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    const double ov = __shfl_xor_sync(0xffffffffu, vmin, o); const int oj = __shfl_xor_sync(0xffffffffu, jmin, o);
-    if (ov < vmin || (ov == vmin && (unsigned)oj < (unsigned)jmin)) { vmin = ov; jmin = oj; }
-    kept_bound = fmin(kept_bound, __shfl_xor_sync(0xffffffffu, kept_bound, o));
+    min_ub = fmin(min_ub, __shfl_xor_sync(0xffffffffu, min_ub, o));
+    kept = fmin(kept, __shfl_xor_sync(0xffffffffu, kept, o));
   }
+  any = __any_sync(0xffffffffu, any);
   double best = CUDART_INF; int bj = -1;
-  bool complete = jmin >= 0;
-  if (complete) {
-    // D~ = nq + v.  |D~ - D| <= eps_ij = kEpsRel * (nq + nr_j).  True minimiser j*: D~_ij* - eps_ij* <= D~_min + eps_i,jmin.
-    const double eps_min = kEpsRel * (nqi + (double)norm_r[jmin]);
-    const double eps_any = kEpsRel * (nqi + nmax);
-    // an un-kept reference has v >= kept_bound; it could only matter if kept_bound - eps_any <= vmin + eps_min
-    complete = kept_bound - eps_any > vmin + eps_min;
-    if (complete) {
-      for (int c = lane; c < nc; c += 32) {
-        const int j = cand_j[(size_t)i * nc + c];
-        if (j < 0) continue;
-        const double v = (double)cand_v[(size_t)i * nc + c];
-        if (v - kEpsRel * (nqi + (double)norm_r[j]) <= vmin + eps_min) {
-          const double d = exact_d2(fq + (size_t)i * dim, fr + (size_t)j * dim, dim);
-          if (d < best || (d == best && (unsigned)j < (unsigned)bj)) { best = d; bj = j; }
+  const bool complete = any && (kept - eq > min_ub);     // false for NaN
+  if (complete || err_max) {
+    float worst = 0.f;
+    for (int c = lane; c < nc; c += 32) {
+      const int j = cand_j[(size_t)i * nc + c];
+      if (j < 0) continue;
+      const double v = (double)cand_v[(size_t)i * nc + c];
+      const bool listed = complete && (v - eq <= min_ub);
+      if (listed || err_max) {
+        const double d = exact_d2(fq + (size_t)i * dim, fr + (size_t)j * dim, dim);
+        if (listed && (d < best || (d == best && (unsigned)j < (unsigned)bj))) { best = d; bj = j; }
+        if (err_max) {
+          const double nrj = (double)norm_r[j];
+          const double approx = nqi + v + (nrj - (double)norm_r_lo[j]);
+          worst = fmaxf(worst, (float)(fabs(approx - d) / (nqi + nrj + 1e-300)));
         }
       }
+    }
+    if (err_max) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) worst = fmaxf(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+      if (lane == 0) atomicMax(err_max, __float_as_uint(worst));
     }
   }
   if (!complete) {  // warp-uniform: exact brute force over every reference
     if (lane == 0) atomicAdd(n_fallback, 1u);
+    best = CUDART_INF; bj = -1;
     for (int j = lane; j < nr; j += 32) {
       const double d = exact_d2(fq + (size_t)i * dim, fr + (size_t)j * dim, dim);
       if (d < best || (d == best && (unsigned)j < (unsigned)bj)) { best = d; bj = j; }
@@ -395,14 +434,14 @@ bool make_operand_map(CUtensorMap* m, const float* base, int n_pad) {
 }
 
 struct Prepped {
-  float* l; float* r; float* norm; unsigned int* norm_max; int n, n_pad;
+  float* l; float* r; float* norm; float* norm_lo; int n, n_pad;
 };
 
 inline size_t pad256(size_t b) { return (b + 255) / 256 * 256; }
 
 size_t prepped_bytes(int n) {
   const size_t n_pad = (size_t)(n + kBM - 1) / kBM * kBM;
-  return 2 * pad256(n_pad * kKTot * 4) + pad256(n_pad * 4) + 256;
+  return 2 * pad256(n_pad * kKTot * 4) + 2 * pad256(n_pad * 4);
 }
 
 char* carve_prepped(char* p, int n, Prepped* out) {
@@ -411,12 +450,16 @@ char* carve_prepped(char* p, int n, Prepped* out) {
   out->l = (float*)p; p += pad256(n_pad * kKTot * 4);
   out->r = (float*)p; p += pad256(n_pad * kKTot * 4);
   out->norm = (float*)p; p += pad256(n_pad * 4);
-  out->norm_max = (unsigned int*)p; p += 256;
+  out->norm_lo = (float*)p; p += pad256(n_pad * 4);
   return p;
 }
 
 int choose_splits(int row_tiles, int col_tiles) {
   int s = 296 / (row_tiles > 0 ? row_tiles : 1);
+  static const int forced = [] { const char* e = getenv("B2R_NN_SPLITS"); return e ? atoi(e) : 0; }();   // A/B runs
+  if (forced > 0) { s = forced < kMaxSplits ? forced : kMaxSplits; if (s > col_tiles) s = col_tiles; const int per = (col_tiles + s - 1) / s; return (col_tiles + per - 1) / per; }
+  // Long column ranges per CTA beat many CTAs: a thread's top-4 list only stops changing after a few thousand values, and until then
+  // nearly every 32-value chunk takes the insertion path (32768^2: 1.32 / 1.47 / 1.46 / 1.53 / 1.69 ms for 1 / 2 / 4 / 8 / 16 splits).
   if (s < 1) s = 1;
   if (s > kMaxSplits) s = kMaxSplits;
   if (s > col_tiles) s = col_tiles;
@@ -427,7 +470,7 @@ int choose_splits(int row_tiles, int col_tiles) {
 size_t cand_bytes(int nq, int nr) {
   const int rt = (nq + kBM - 1) / kBM, ct = (nr + kBN - 1) / kBN;
   const int s = choose_splits(rt, ct);
-  return 2 * pad256((size_t)rt * kBM * s * kTopK * 4) + 256;
+  return 2 * pad256((size_t)rt * kBM * 2 * s * kTopK * 4) + 256;
 }
 
 b2r_status launch_centre(b2r_solver* s, const double* f_ref, int n_ref, int dim, double* centre) {
@@ -437,29 +480,28 @@ b2r_status launch_centre(b2r_solver* s, const double* f_ref, int n_ref, int dim,
 }
 
 b2r_status launch_prep(b2r_solver* s, const double* f, int dim, const double* centre, Prepped& p) {
-  CK(cudaMemsetAsync(p.norm_max, 0, 4, s->stream));
   const long long total = (long long)p.n_pad * kKTot;
-  nn_prep_kernel<<<(int)((total + 255) / 256), 256, 0, s->stream>>>(f, p.n, dim, p.n_pad, centre, p.l, p.r, p.norm, p.norm_max);
+  nn_prep_kernel<<<(int)((total + 255) / 256), 256, 0, s->stream>>>(f, p.n, dim, p.n_pad, centre, p.l, p.r, p.norm, p.norm_lo);
   ++s->launches;
   return B2R_OK;
 }
 
 // nn[i] = exact argmin_j |fq_i - fr_j|^2 via the tensor-core shortlist.  scratch: cand_bytes(nq, nr) bytes.
 b2r_status launch_direction(b2r_solver* s, const double* fq, const Prepped& q, const double* fr, const Prepped& r, int dim, char* scratch,
-                            int* nn, double* dist, unsigned int* n_fallback) {
+                            int* nn, double* dist, unsigned int* n_fallback, unsigned int* err_max = nullptr) {
   static PerDeviceOnce attr;
   const size_t smem = 3 * (size_t)kOperandBytes + sizeof(GemmSmem) + 1024;
   CK(attr.run([&] { return cudaFuncSetAttribute(nn_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); }));
   const int rt = q.n_pad / kBM, ct = r.n_pad / kBN;
   const int splits = choose_splits(rt, ct);
   float* cand_v = (float*)scratch;
-  int* cand_j = (int*)(scratch + pad256((size_t)rt * kBM * splits * kTopK * 4));
+  int* cand_j = (int*)(scratch + pad256((size_t)rt * kBM * 2 * splits * kTopK * 4));
   CUtensorMap mq, mr;
   if (!make_operand_map(&mq, q.l, q.n_pad) || !make_operand_map(&mr, r.r, r.n_pad))
     return fail(s, B2R_ERR_CUDA, "cuTensorMapEncodeTiled failed (driver entry point missing or bad operand buffer)");
-  nn_gemm_kernel<<<dim3(rt, splits), kGemmThreads, smem, s->stream>>>(mq, mr, r.norm, r.n, ct, splits, cand_v, cand_j);
-  nn_finish_kernel<<<(q.n + kFinWarps - 1) / kFinWarps, kFinWarps * 32, 0, s->stream>>>(fq, q.n, fr, r.n, dim, q.norm, r.norm, r.norm_max,
-                                                                                        cand_v, cand_j, splits, nn, dist, n_fallback);
+  nn_gemm_kernel<<<dim3(rt, splits), kGemmThreads, smem, s->stream>>>(mq, mr, r.norm_lo, r.n, ct, splits, cand_v, cand_j);
+  nn_finish_kernel<<<(q.n + kFinWarps - 1) / kFinWarps, kFinWarps * 32, 0, s->stream>>>(fq, q.n, fr, r.n, dim, q.norm, r.norm, r.norm_lo,
+                                                                                        cand_v, cand_j, 2 * splits, nn, dist, n_fallback, err_max);
   s->launches += 2;
   CK(cudaGetLastError());
   return B2R_OK;
@@ -499,6 +541,33 @@ b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double
     CK(cudaStreamSynchronize(s->stream));
     *n_fallback_out = (int)h;
   }
+  return B2R_OK;
+}
+
+b2r_status b2r_debug_nn_gemm_error(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
+                                   double* out3) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!fq_dev || !fr_dev || !nn_dev || !out3 || nq < 1 || nr < 1 || dim < 1 || dim > kKSeg) return fail(s, B2R_ERR_INVALID_ARG, "debug_nn_gemm_error arguments");
+  CK(cudaSetDevice(s->device));
+  CK(s->d_nn.ensure(prepped_bytes(nq) + prepped_bytes(nr) + cand_bytes(nq, nr) + 2048));
+  char* p = (char*)s->d_nn.p;
+  Prepped q, r;
+  p = carve_prepped(p, nq, &q);
+  p = carve_prepped(p, nr, &r);
+  unsigned int* n_fb = (unsigned int*)p; p += 256;     // [0] fallback rows, [1] max error ratio (float bits)
+  double* centre = (double*)p; p += 512;
+  CK(cudaMemsetAsync(n_fb, 0, 8, s->stream));
+  b2r_status st = launch_centre(s, fr_dev, nr, dim, centre);
+  if (st == B2R_OK) st = launch_prep(s, fq_dev, dim, centre, q);
+  if (st == B2R_OK) st = launch_prep(s, fr_dev, dim, centre, r);
+  if (st == B2R_OK) st = launch_direction(s, fq_dev, q, fr_dev, r, dim, p, nn_dev, nullptr, n_fb, n_fb + 1);
+  if (st != B2R_OK) return st;
+  unsigned int h[2] = {0, 0};
+  CK(cudaMemcpyAsync(h, n_fb, 8, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  float ratio;
+  memcpy(&ratio, &h[1], 4);
+  out3[0] = ratio; out3[1] = kEpsRel; out3[2] = h[0];
   return B2R_OK;
 }
 

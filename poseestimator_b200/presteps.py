@@ -200,6 +200,17 @@ class PreSteps:
         self.last_fallback_rows = fb.value
         return nn, dist
 
+    def nn_gemm_error(self, fq, fr):
+        """Test hook (b2r_debug.h): nn_gemm with the error of the tensor-core distances measured on every kept candidate pair.
+        -> (nn, dict(ratio, bound, fallback_rows))."""
+        torch = _torch()
+        a, b = self._pts(fq), self._pts(fr)
+        nn = self._empty((a.shape[0],), torch.int32)
+        out = (C.c_double * 3)()
+        _lib.check(self._h, _lib.lib().b2r_debug_nn_gemm_error(self._h, a.data_ptr(), a.shape[0], b.data_ptr(), b.shape[0], a.shape[1],
+                                                               nn.data_ptr(), out))
+        return nn, dict(ratio=float(out[0]), bound=float(out[1]), fallback_rows=int(out[2]))
+
     def mutual_nn(self, fa, fb, method="gemm"):
         """Mutual nearest neighbours of two descriptor sets (one descriptor per row).
         -> (pairs [c,2] int32 ascending i, nn01 [na], nn10 [nb]).  method: "gemm" (tensor cores + exact re-rank) or

@@ -295,3 +295,40 @@ def test_nn_gemm_on_real_fpfh(op, ps, frame):
     assert np.array_equal(_np(nn01), nn01_ref) and np.array_equal(_np(nn10), nn10_ref)
     assert np.array_equal(_np(pairs), pairs_ref)
     assert pairs.shape[0] > 10
+
+
+@pytest.mark.parametrize("seed,size", [(2, (0.30, 0.15, 0.10)), (6, (0.30, 0.15, 0.10)), (11, (0.22, 0.22, 0.06)), (12, (0.15, 0.075, 0.05)),
+                                       (13, (0.40, 0.10, 0.10))])
+def test_nn_gemm_real_fpfh_shapes_and_fallback_rate(op, ps, seed, size):
+    """More seeds / box shapes of synth.make_frame: indices == oracle in both directions, fewer than 5 % of the rows need the
+    brute-force fallback, and the error of the tensor-core distances stays inside the bound the shortlist logic assumes."""
+    f = synth.make_frame(seed=seed, size=size)
+    raw, _ = op.backproject(f.depth, f.mask, f.bbox, f.fx, f.fy, f.cx, f.cy, f.depth_scale)
+    keep, _ = op.statistical_outlier(raw, 20, 1.0)      # the config-2 flow; without it isolated noise points give all-zero
+    v, _, _ = op.voxel_down(raw[keep], 0.005)           # descriptors, i.e. exact ties, which no shortlist can separate
+    tm, _, _ = op.voxel_down(f.cad, 0.005)
+    fs = op.fpfh(v, op.normals(v, 0.01, 30, 1, (0, 0, 0)), 0.025, 100).T.copy()
+    ft = op.fpfh(tm, op.normals(tm, 0.01, 30, 2, (0, 0, 0)), 0.025, 100).T.copy()
+    pairs_ref, nn01_ref, nn10_ref = op.mutual_nn(ft, fs)
+    pairs, nn01, nn10 = ps.mutual_nn(ft, fs, method="gemm")
+    assert np.array_equal(_np(nn01), nn01_ref) and np.array_equal(_np(nn10), nn10_ref) and np.array_equal(_np(pairs), pairs_ref)
+    # config-2 box: < 5 % of the rows; boxes with a square cross-section have whole faces of near-identical descriptors (real near-ties)
+    limit = 0.05 if size == (0.30, 0.15, 0.10) else 0.25
+    assert ps.last_fallback_rows < limit * (ft.shape[0] + fs.shape[0]), (ps.last_fallback_rows, ft.shape[0] + fs.shape[0])
+    for a, b, ref in ((ft, fs, nn01_ref), (fs, ft, nn10_ref)):
+        nn, e = ps.nn_gemm_error(a, b)
+        assert np.array_equal(_np(nn), ref)
+        assert 0 < e["ratio"] < 0.5 * e["bound"], e      # measured error at most half the assumed bound
+
+
+def test_nn_gemm_error_bound_large(ps):
+    """The 3xTF32 / K = 128 error on a GPU-filling case (8192 x 8192 FPFH-like histograms + uniform rows): measured, not assumed."""
+    rng = np.random.default_rng(5)
+    base = rng.dirichlet(np.full(11, 0.3), size=(256, 3)).reshape(256, 33) * 200.0
+    fa = base[rng.integers(0, 256, 8192)] + rng.normal(0, 0.5, size=(8192, 33))
+    fb = np.concatenate([base[rng.integers(0, 256, 6144)] + rng.normal(0, 0.5, size=(6144, 33)), rng.uniform(0, 200, size=(2048, 33))])
+    nn, e = ps.nn_gemm_error(fa, fb)
+    nn_e, _ = ps.nn_exact(fa, fb)
+    assert np.array_equal(_np(nn), _np(nn_e))
+    assert 0 < e["ratio"] < 0.5 * e["bound"], e
+    print("nn_gemm measured error ratio", e)
