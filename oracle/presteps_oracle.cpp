@@ -33,6 +33,12 @@
 #include <vector>
 #include <omp.h>
 
+// acos / cos / atan2 from +, -, *, /, sqrt, fma only (double-double): the SAME header the CUDA kernels include, so both sides
+// bin pair features and solve the 3x3 eigen-problem on identical values; checked against mpmath and glibc in
+// tests/test_oracle_exactmath.py.  Open3D itself calls the host libm, which these agree with to the last ulp except on the rare
+// inputs where glibc is not correctly rounded.
+#include "../include/b2r_exactmath.h"
+
 namespace {
 
 inline double sq3(double x, double y, double z) { return (x * x + y * y) + z * z; }
@@ -160,10 +166,10 @@ void smallest_eigvec(const double C[9], double out[3]) {
     const double det = ((b00 * c00 - A[1] * c01) + A[2] * c02) / ((p * p) * p);
     double half = det * 0.5;
     half = std::min(std::max(half, -1.0), 1.0);
-    const double angle = std::acos(half) / 3.0;
+    const double angle = b2r_acos(half) / 3.0;
     const double two_thirds_pi = 2.09439510239319549;
-    const double beta2 = std::cos(angle) * 2.0;
-    const double beta0 = std::cos(angle + two_thirds_pi) * 2.0;
+    const double beta2 = b2r_cos(angle) * 2.0;
+    const double beta0 = b2r_cos(angle + two_thirds_pi) * 2.0;
     const double beta1 = -(beta0 + beta2);
     const double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;  // e0 <= e1 <= e2
     double v0[3], v1[3], v2[3];
@@ -353,7 +359,7 @@ inline void pair_features(const double* p1, const double* n1, const double* p2, 
   const double* b = n2;
   const double angle1 = dot3(n1, dp) / f[3];
   const double angle2 = dot3(n2, dp) / f[3];
-  if (std::acos(std::fabs(angle1)) > std::acos(std::fabs(angle2))) {
+  if (b2r_acos(std::fabs(angle1)) > b2r_acos(std::fabs(angle2))) {
     a = n2; b = n1;
     dp[0] = -dp[0]; dp[1] = -dp[1]; dp[2] = -dp[2];
     f[2] = -angle2;
@@ -368,7 +374,7 @@ inline void pair_features(const double* p1, const double* n1, const double* p2, 
   double w[3];
   cross3(a, v, w);
   f[1] = dot3(v, b);
-  f[0] = std::atan2(dot3(w, b), dot3(a, b));
+  f[0] = b2r_atan2(dot3(w, b), dot3(a, b));
 }
 inline int bin11(double x) {
   int h = (int)std::floor(x);
@@ -456,5 +462,10 @@ int orcp_mutual_nn(const double* fa, int na, const double* fb, int nb, int dim, 
 
 void orcp_smallest_eigvec(const double* C9, double* out3) { smallest_eigvec(C9, out3); }
 int orcp_num_threads() { return omp_get_max_threads(); }
+
+// include/b2r_exactmath.h on arrays (tests/test_oracle_exactmath.py): which = 0 acos(a), 1 cos(a), 2 atan2(a, b)
+void orcp_exactmath(int which, const double* a, const double* b, int n, double* out) {
+  for (int i = 0; i < n; ++i) out[i] = which == 0 ? b2r_acos(a[i]) : which == 1 ? b2r_cos(a[i]) : b2r_atan2(a[i], b[i]);
+}
 
 }  // extern "C"

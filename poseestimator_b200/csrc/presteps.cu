@@ -10,8 +10,10 @@
 // All arithmetic is IEEE fp64 in the reference's operation order; this translation unit is compiled with -fmad=false so
 // no multiply-add is ever contracted.  Results that are order dependent (point order after compaction, voxel order,
 // neighbour order, sequential sums) follow the canonical orders of the oracle (oracle/presteps_oracle.cpp header).
-// Only the transcendental functions (acos, cos, atan2) come from CUDA's libm instead of glibc's and may differ in the
-// last ulp (DESIGN.md "pre-steps parity").
+// The transcendental functions (acos, cos, atan2) come from include/b2r_exactmath.h, the double-double implementation the
+// oracle includes verbatim, so histogram bins and eigen-solver outputs are identical bits on both sides.  Where only a DECISION
+// depends on the value (the acos comparison and the atan2 bin of the SPFH pair features) CUDA's libm decides first and the exact
+// function is evaluated only inside a guard band around the decision boundary -- the result is that of the exact function always.
 //
 // Kernels are HBM/L2-bound byte and index work: coalesced and vectorised loads (8 depth pixels = one 16-byte load),
 // shared-memory staging of the point tiles, ordered stream compaction by a single-pass decoupled look-back scan.
@@ -19,6 +21,7 @@
 
 #include "scan.cuh"
 #include "solver.cuh"
+#include "../../include/b2r_exactmath.h"
 
 namespace b2r {
 
@@ -510,10 +513,10 @@ __device__ void smallest_eigvec(const double C[9], double out[3]) {
     const double det = ((b00 * c00 - A[1] * c01) + A[2] * c02) / ((p * p) * p);
     double half = det * 0.5;
     half = fmin(fmax(half, -1.0), 1.0);
-    const double angle = acos(half) / 3.0;
+    const double angle = b2r_acos(half) / 3.0;
     const double two_thirds_pi = 2.09439510239319549;
-    const double beta2 = cos(angle) * 2.0;
-    const double beta0 = cos(angle + two_thirds_pi) * 2.0;
+    const double beta2 = b2r_cos(angle) * 2.0;
+    const double beta0 = b2r_cos(angle + two_thirds_pi) * 2.0;
     const double beta1 = -(beta0 + beta2);
     const double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;
     double v0[3], v1[3], v2[3];
@@ -597,7 +600,12 @@ __device__ void pair_features(const double* p1, const double* n1, const double* 
   const double* b = n2;
   const double angle1 = dot3(n1, dp) / f[3];
   const double angle2 = dot3(n2, dp) / f[3];
-  if (acos(fabs(angle1)) > acos(fabs(angle2))) {
+  // acos(|angle1|) > acos(|angle2|) on the exact (correctly rounded) values.  CUDA's acos is within 2 ulp of them (<= 4.5e-16 here,
+  // values in [0, pi/2]): when the two libm values differ by more than 4e-15 the exact ones are ordered the same way.
+  const double q1 = acos(fabs(angle1)), q2 = acos(fabs(angle2));
+  bool swap_roles = q1 > q2;
+  if (fabs(q1 - q2) <= 4e-15) swap_roles = b2r_acos(fabs(angle1)) > b2r_acos(fabs(angle2));
+  if (swap_roles) {
     a = n2; b = n1;
     dp[0] = -dp[0]; dp[1] = -dp[1]; dp[2] = -dp[2];
     f[2] = -angle2;
@@ -612,7 +620,15 @@ __device__ void pair_features(const double* p1, const double* n1, const double* 
   double w[3];
   cross3(a, v, w);
   f[1] = dot3(v, b);
-  f[0] = atan2(dot3(w, b), dot3(a, b));
+  // Only floor(11 (f0 + pi) / (2 pi)) is used.  CUDA's atan2 is within 2 ulp (<= 9e-16) of the exact value, which moves the bin
+  // coordinate by < 2e-15 plus a few roundings of the same size; inside 1e-13 of a bin edge the exact function decides.
+  const double wy = dot3(w, b), wx = dot3(a, b);
+  double f0 = atan2(wy, wx);
+  const double kPi_ = 3.14159265358979323846;
+  const double xb = 11 * (f0 + kPi_) / (2.0 * kPi_);
+  const double fr = xb - floor(xb);
+  if (!(fr > 1e-13 && fr < 1.0 - 1e-13)) f0 = b2r_atan2(wy, wx);
+  f[0] = f0;
 }
 
 constexpr int kFpWarps = 4;

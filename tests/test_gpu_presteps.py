@@ -204,10 +204,8 @@ def test_normals_match_oracle(op, ps, frame):
     for (r, k, orient) in [(0.005, 30, 0), (0.01, 30, 1), (0.02, 10, 2)]:
         ref = op.normals(v, r, k, orient, (0, 0, 0))
         got = _np(ps.normals(v, r, k, orient, (0, 0, 0)))
-        # identical IEEE operations except acos / cos (CUDA libm vs glibc, last-ulp differences) which the eigen-solver
-        # amplifies for nearly degenerate neighbourhoods (3..5 almost collinear points at r = one voxel)
-        err = np.abs(got - ref).max(axis=1)
-        assert err.max() < 1e-6 and np.quantile(err, 0.99) < 1e-10, (err.max(), np.quantile(err, 0.99))
+        # identical IEEE operations in the same order, acos / cos from the shared include/b2r_exactmath.h: identical bits
+        assert np.array_equal(got, ref), np.abs(got - ref).max()
         assert np.allclose(np.linalg.norm(got, axis=1), 1.0, atol=1e-12)
 
 
@@ -217,23 +215,18 @@ def test_fpfh_matches_oracle(op, ps, frame):
     ref, ref_sp = op.fpfh(v, nrm, 0.025, 100, want_spfh=True)
     got, got_sp = ps.fpfh(v, nrm, 0.025, 100, want_spfh=True)
     got, got_sp = _np(got), _np(got_sp)
-    # a pair whose feature sits within an ulp of a bin edge may land in the neighbouring bin under another libm;
-    # everything else must agree to rounding
-    bad_sp = np.abs(got_sp - ref_sp).max(axis=0) > 1e-9
-    assert bad_sp.mean() < 1e-3, f"{bad_sp.sum()} of {bad_sp.size} SPFH columns differ"
-    bad = np.abs(got - ref).max(axis=0) > 1e-7
-    assert bad.mean() < 5e-2
-    if not bad_sp.any():
-        assert np.abs(got - ref).max() < 1e-9
+    # every pair feature lands in the same bin (the exact acos / atan2 decide near a bin edge), so SPFH and FPFH are identical bits
+    assert np.array_equal(got_sp, ref_sp), f"{(np.abs(got_sp - ref_sp).max(axis=0) > 0).sum()} SPFH columns differ"
+    assert np.array_equal(got, ref), np.abs(got - ref).max()
 
 
 def test_fpfh_on_exact_planes(op, ps, frame):
-    """CAD samples lie exactly on axis-aligned planes with axis-aligned normals: signed zeros and exact ties everywhere."""
+    """CAD samples lie exactly on axis-aligned planes with axis-aligned normals: signed zeros, exact ties and pair features that
+    sit EXACTLY on bin edges (atan2 = 0, +-pi/2, pi) everywhere -- the guard band of the libm fast path is exercised on most pairs."""
     f = frame
     ref = op.fpfh(f.cad[:2000], f.cad_normals[:2000], 0.025, 100)
     got = _np(ps.fpfh(f.cad[:2000], f.cad_normals[:2000], 0.025, 100))
-    bad = np.abs(got - ref).max(axis=0) > 1e-7
-    assert bad.mean() < 5e-2, f"{bad.sum()} columns differ"
+    assert np.array_equal(got, ref), f"{(np.abs(got - ref).max(axis=0) > 0).sum()} columns differ"
 
 
 # ---- a-2 nearest neighbour in feature space (exact form) -----------------------------------------------------------
