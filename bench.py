@@ -78,7 +78,8 @@ class ClockSampler(threading.Thread):
                 self.proc.terminate()
             except Exception:  # noqa: BLE001
                 pass
-        self.join(timeout=2)
+        if self.is_alive():
+            self.join(timeout=2)
 
     def summary(self):
         def num(x):
@@ -195,8 +196,11 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if world > 1 or os.environ.get("B2R_BENCH_FORCE_DIST") == "1":   # the second form: probes only (tools/scale_probe.sh)
+        if os.environ.get("B2R_BENCH_BACKEND") == "gloo":      # probe only: is a slowdown NCCL's or torchrun's?
+            dist.init_process_group("gloo")
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     from poseestimator_b200 import batch as b2batch
     from poseestimator_b200 import _lib
@@ -204,7 +208,7 @@ def main():
     W = max(args.warmup, 3)
     K = args.steps
     B = args.batch
-    pbs = make_problems(B, rank)
+    pbs = make_problems(B, int(os.environ.get("B2R_BENCH_SEED_RANK", rank)))   # the variable: probes of another rank's problem set on one GPU
     nb = pbs[0].noise_bound
     stream = torch.cuda.Stream()  # a real stream handle: the library's kernels, the L2 flush and the events share it
     torch.cuda.set_stream(stream)
@@ -237,7 +241,8 @@ def main():
     st0 = solver.stats(0)
 
     sampler = ClockSampler(local)
-    sampler.start()
+    if os.environ.get("B2R_BENCH_NO_SAMPLER") != "1":
+        sampler.start()
     barrier()
     launches0 = solver.launch_count()
     evs = []
@@ -310,6 +315,7 @@ def main():
     truth = None
     for sv in vpipes:
         truth = bench_legs.check_truth(sv, pbs, sv.solutions_array(), "config3 value leg", every=8)
+    not_fused = [i for i in range(B) if vpipes[0].stats(i)["fused_tail"] != 1]   # problems the fused tail handed to the multi-kernel chain
     barrier()
 
     # ---- end to end through the public host API ------------------------------------------------------------
@@ -391,8 +397,13 @@ def main():
 
     # max over ranks
     times = torch.tensor([dev_ms, e2e_s * 1e3, lat_p50, serial_ms, e2e_pageable_s * 1e3], dtype=torch.float64, device="cuda")
+    times_local = times.clone()
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    per_rank = [times_local.clone() for _ in range(world)]
+    if world > 1:
+        dist.all_gather(per_rank, times_local)
+    per_rank_ms = [[round(float(x), 3) for x in t.cpu()[:2]] for t in per_rank]
     dev_ms_max, e2e_ms_max, lat_max, serial_ms_max, e2e_pg_ms_max = [float(x) for x in times.cpu()]
 
     if rank == 0:
@@ -463,7 +474,8 @@ def main():
             "gpu_launches": int(launches),
             "stage_ms_per_step": {k: round(v, 4) for k, v in stage_ms.items()},
             "clocks": sampler.summary(),
-            "ground_truth": truth,
+            "ground_truth": truth, "problems_handed_over_by_fused_tail": not_fused,
+            "per_rank_ms": {"note": "[value leg device ms, e2e leg wall ms] of every rank; the line's numbers use the slowest", "ranks": per_rank_ms},
             "problem_stats": {k: st0[k] for k in ("n_edges", "heuristic_lb", "n_pruned", "omega", "clique_size", "gnc_iterations",
                                                   "bnb_nodes", "graph_slow_pairs")},
         }

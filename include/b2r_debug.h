@@ -36,6 +36,11 @@ b2r_status b2r_debug_tc_sweep(b2r_solver* s, int idx, double* out8);
  * [7] state loaded (start of the fix-up); [8..31] finer marks inside the stages (0 where a stage did not run), see tail.cu */
 b2r_status b2r_debug_tail_cycles(b2r_solver* s, int idx, uint32_t* out32);
 
+/* With B2R_CANARY=1 in the environment every workspace buffer of a handle carries a 4 KB guard zone on either side (0xA5 bytes);
+ * this call (and b2r_sync, b2r_destroy) verifies them: B2R_ERR_STATE names the buffer a kernel wrote out of bounds.  Without the
+ * variable it returns B2R_OK.  tools/canary_tests.sh runs the GPU tests this way (compute-sanitizer is closed on the GPU pool). */
+b2r_status b2r_debug_check_canaries(b2r_solver* s);
+
 /* b2r_nn_gemm with the error of the tensor-core distances MEASURED: for every candidate pair (i, j) the kernel kept (8 x splits x 4 per
  * query row) the exact fp64 distance D is computed as well and compared with the approximate one.  out3 (host):
  *   [0] max |D~_ij - D_ij| / (|fq_i - c|^2 + |fr_j - c|^2)   [1] the bound the shortlist logic assumes (kEpsRel)   [2] rows that fell back */

@@ -69,7 +69,7 @@ EXPORTS = [
 
 # include/b2r_debug.h: test hooks, not part of the drop-in boundary
 DEBUG_EXPORTS = ["b2r_debug_set_graph_filter", "b2r_debug_tc_values", "b2r_debug_tc_sweep", "b2r_debug_tail_cycles",
-                 "b2r_debug_nn_gemm_error"]
+                 "b2r_debug_nn_gemm_error", "b2r_debug_check_canaries"]
 
 # numpy view of an array of b2r_solution (112 bytes each)
 import numpy as _np  # noqa: E402
@@ -127,6 +127,7 @@ def lib():
     L.b2r_debug_tc_sweep.argtypes = [vp, i32, vp]
     L.b2r_debug_tail_cycles.argtypes = [vp, i32, vp]
     L.b2r_debug_nn_gemm_error.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp]
+    L.b2r_debug_check_canaries.argtypes = [vp]
     L.b2r_pitch_words.argtypes = [i32]
     L.b2r_pitch_words.restype = i32
     d, ip = C.c_double, C.POINTER(C.c_int)
@@ -167,7 +168,13 @@ class B2RError(RuntimeError):
         self.status = status
 
 
+_CANARY = os.environ.get("B2R_CANARY") == "1"
+
+
 def check(handle, status: int):
+    if status == 0 and _CANARY and handle:
+        # debug mode (include/b2r_debug.h): every call is followed by a check of the guard zones around the workspace buffers
+        status = lib().b2r_debug_check_canaries(handle)
     if status != 0:
         msg = lib().b2r_last_error(handle).decode() if handle else "no handle"
         if status == 3:

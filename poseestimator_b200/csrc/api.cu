@@ -210,6 +210,7 @@ b2r_status ensure_events(b2r_solver* s) {
 // The multi-kernel clique / rotation / translation chain (one launch per stage).  Every kernel skips problems the fused tail
 // finished (ProbState::tail_done), so the same chain serves as the whole tail and as the hand-over path.
 b2r_status enqueue_chain(b2r_solver* s, const ProbDesc* dd, int batch, int n_max, cudaStream_t st, bool prof) {
+  B2R_NVTX("b2r:clique_rotation_translation_chain");
   s->launches += launch_degree(dd, batch, n_max, st);
   if (prof) CK(cudaEventRecord(s->ev[3], st));
   s->launches += launch_clique(dd, batch, n_max, s->kp, (uint32_t*)s->d_arena.p, s->arena_words_per_warp, s->bnb_blocks, st,
@@ -225,12 +226,14 @@ bool fused_tail_enabled(const b2r_solver* s) {
 
 // enqueue stages 1.. on descriptors already in h_desc
 b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph) {
+  B2R_NVTX("b2r:solve_pipeline");
   cudaStream_t st = s->stream;
   const bool prof = s->profiling;
   CK(cudaMemsetAsync(s->d_state.p, 0, (size_t)batch * sizeof(ProbState), st));
   CK(cudaMemcpyAsync(s->d_desc.p, s->h_desc.p, (size_t)batch * sizeof(ProbDesc), cudaMemcpyHostToDevice, st));
   const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
   if (s->kp.estimate_scaling) {  // A.4-5: the scale vote comes first; the graph is its inlier mask
+    B2R_NVTX("b2r:scale_vote");
     if (prof) CK(cudaEventRecord(s->ev[10], st));
     CK(s->d_scale.ensure(scale_workspace_bytes(n_max)));
     const ProbDesc* hd = (const ProbDesc*)s->h_desc.p;
@@ -244,6 +247,7 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
                   !s->kp.graph_v4;
   if (prof) CK(cudaEventRecord(s->ev[1], st));
   if (!skip_graph) {
+    B2R_NVTX("b2r:consistency_graph");
     if (tc && fused) s->launches += launch_tim_graph_tc(dd, batch, n_max, s->kp, st);   // the tail decides the listed pairs itself
     else s->launches += launch_tim_graph(dd, batch, n_max, s->kp, st);
   }
@@ -257,6 +261,7 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
   s->handed_over = 0;
   s->n_max = n_max;
   if (fused) {
+    B2R_NVTX("b2r:fused_tail(clique+rotation+translation)");
     if (!tc) s->launches += launch_degree(dd, batch, n_max, st);
     s->launches += launch_tail(dd, batch, n_max, s->kp, tc ? 0 : 1, st);
   } else {
@@ -286,7 +291,8 @@ b2r_status run_handed_over(b2r_solver* s) {
   s->handed_over = todo;
   if (!todo) return B2R_OK;
   const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
-  cudaStream_t st = s->stream;
+  // on the high-priority stream: these are small kernels that would otherwise queue behind the graph kernels of other handles
+  cudaStream_t st = s->stream_hi ? s->stream_hi : s->stream;
   if (regraph) s->launches += launch_graph_fix(dd, s->batch, s->n_max, s->kp, st);
   const bool prof = s->profiling && s->ev_ready;
   if (prof) CK(cudaEventRecord(s->ev[2], st));
@@ -299,6 +305,18 @@ b2r_status run_handed_over(b2r_solver* s) {
   // stage times of the handed-over chain: [2] .. [8] (the fused tail's own time stays in [11])
   if (prof) for (int i = 2; i < 9; ++i) cudaEventElapsedTime(&s->timings[i], s->ev[i], s->ev[i + 1]);
   return B2R_OK;
+}
+
+// B2R_CANARY=1: guard zones around every workspace buffer (solver.cuh)
+const char* broken_canary(const b2r_solver* s) {
+  if (!canary_bytes()) return nullptr;
+  const struct { const DevBuf* b; const char* name; } all[] = {
+      {&s->d_pts, "points"}, {&s->d_adj, "adjacency"}, {&s->d_cadj, "compact adjacency"}, {&s->d_int, "int arrays"}, {&s->d_dbl, "double arrays"},
+      {&s->d_u8, "masks"}, {&s->d_state, "problem state"}, {&s->d_desc, "descriptors"}, {&s->d_arena, "search arena"}, {&s->d_scale, "scale vote"},
+      {&s->d_pre, "pre-steps"}, {&s->d_nn, "nn gemm"}, {&s->d_grid, "knn grid"}, {&s->d_refine, "refine"}, {&s->d_pts32, "tc operand rows"},
+      {&s->d_amb, "ambiguous pairs"}};
+  for (const auto& e : all) if (!e.b->intact()) return e.name;
+  return nullptr;
 }
 
 b2r_status check_index(b2r_solver* s, int idx) {
@@ -378,6 +396,10 @@ b2r_status b2r_destroy(b2r_solver* s) {
   if (!s) return B2R_OK;
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->stream);
+  if (const char* bad = broken_canary(s)) {   // B2R_CANARY=1 only: an out-of-bounds write must not pass silently
+    fprintf(stderr, "libb2r: guard zone of the '%s' workspace buffer was overwritten\n", bad);
+    abort();
+  }
   s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
   s->d_pts32.release(); s->d_amb.release(); s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release(); s->d_refine.release(); s->h_refine.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
@@ -410,6 +432,7 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
                                  const double* const* dst, int on_device) {
   if (!s) return B2R_ERR_INVALID_ARG;
   if (batch <= 0 || !n || !src || !dst) return fail(s, B2R_ERR_INVALID_ARG, "batch/n/src/dst");
+  B2R_NVTX("b2r:solve_batch_async");
   CK(cudaSetDevice(s->device));
   if (s->pending) { b2r_status r = b2r_sync(s); if (r != B2R_OK) return r; }
   int n_max = 0;
@@ -513,6 +536,7 @@ b2r_status b2r_free_pinned(void* p) {
 
 b2r_status b2r_sync(b2r_solver* s) {
   if (!s) return B2R_ERR_INVALID_ARG;
+  B2R_NVTX("b2r:sync");
   CK(cudaSetDevice(s->device));
   CK(cudaStreamSynchronize(s->stream));
   if (!s->pending) return B2R_OK;
@@ -538,6 +562,7 @@ b2r_status b2r_sync(b2r_solver* s) {
     b2r_status r = run_handed_over(s);
     if (r != B2R_OK) return r;
   }
+  if (const char* bad = broken_canary(s)) return fail(s, B2R_ERR_STATE, std::string("guard zone overwritten: workspace buffer '") + bad + "'");
   s->have_result = true;
   const ProbState* hs = (const ProbState*)s->h_state.p;
   for (int b = 0; b < s->batch; ++b) {
@@ -748,6 +773,14 @@ b2r_status b2r_debug_set_graph_filter(b2r_solver* s, int filter, double tau) {
   s->params.reserved0 = filter;
   s->params.reserved1 = tau > 0 ? tau : 0.0;
   fill_kernel_params(s);
+  return B2R_OK;
+}
+
+b2r_status b2r_debug_check_canaries(b2r_solver* s) {
+  if (!s) return B2R_ERR_INVALID_ARG;
+  CK(cudaSetDevice(s->device));
+  CK(cudaStreamSynchronize(s->stream));
+  if (const char* bad = broken_canary(s)) return fail(s, B2R_ERR_STATE, std::string("guard zone overwritten: workspace buffer '") + bad + "'");
   return B2R_OK;
 }
 

@@ -513,6 +513,7 @@ extern "C" {
 
 b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
                        double* dist_dev, int* n_fallback_out) {
+  B2R_NVTX("b2r:nn_gemm");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!fq_dev || !fr_dev || !nn_dev || nq < 0 || nr < 0 || dim < 1) return fail(s, B2R_ERR_INVALID_ARG, "nn_gemm arguments");
   if (n_fallback_out) *n_fallback_out = 0;
@@ -546,6 +547,7 @@ b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double
 
 b2r_status b2r_debug_nn_gemm_error(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
                                    double* out3) {
+  B2R_NVTX("b2r:debug_nn_gemm_error");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!fq_dev || !fr_dev || !nn_dev || !out3 || nq < 1 || nr < 1 || dim < 1 || dim > kKSeg) return fail(s, B2R_ERR_INVALID_ARG, "debug_nn_gemm_error arguments");
   CK(cudaSetDevice(s->device));
@@ -573,6 +575,7 @@ b2r_status b2r_debug_nn_gemm_error(b2r_solver* s, const double* fq_dev, int nq, 
 
 b2r_status b2r_mutual_nn(b2r_solver* s, const double* fa_dev, int na, const double* fb_dev, int nb, int dim, int32_t* nn01_dev,
                          int32_t* nn10_dev, int32_t* pairs_dev, int* n_pairs_out, int* n_fallback_out) {
+  B2R_NVTX("b2r:mutual_nn");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!fa_dev || !fb_dev || !nn01_dev || !nn10_dev || !pairs_dev || !n_pairs_out || na < 0 || nb < 0 || dim < 1)
     return fail(s, B2R_ERR_INVALID_ARG, "mutual_nn arguments");

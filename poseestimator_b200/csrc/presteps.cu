@@ -1060,6 +1060,7 @@ extern "C" {
 b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* mask, int H, int W, int u0, int v0, int u1, int v1,
                            const b2r_camera* cam, int on_device, double* points_dev, int32_t* pixel_ids_dev, int capacity,
                            int* count_out) {
+  B2R_NVTX("b2r:backproject");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!depth || !cam || !points_dev || H <= 0 || W <= 0 || capacity < 0 || !count_out) return fail(s, B2R_ERR_INVALID_ARG, "backproject arguments");
   if (!(cam->fx != 0) || !(cam->fy != 0)) return fail(s, B2R_ERR_INVALID_ARG, "fx, fy must be non-zero");
@@ -1101,6 +1102,7 @@ b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* 
 
 b2r_status b2r_knn(b2r_solver* s, const double* pts_dev, int n, const double* queries_dev, int nq, int max_nn, double radius,
                    int32_t* idx_dev, double* d2_dev, int32_t* cnt_dev) {
+  B2R_NVTX("b2r:knn");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || !queries_dev || !idx_dev || !d2_dev || !cnt_dev || n < 0 || nq < 0) return fail(s, B2R_ERR_INVALID_ARG, "knn arguments");
   if (max_nn < 1 || max_nn > kKnnMaxK) return fail(s, B2R_ERR_LIMIT, "knn: max_nn must be in [1, 128]");
@@ -1117,6 +1119,7 @@ b2r_status b2r_knn(b2r_solver* s, const double* pts_dev, int n, const double* qu
 
 b2r_status b2r_statistical_outlier(b2r_solver* s, const double* pts_dev, int n, int nb_neighbors, double std_ratio, uint8_t* keep_dev,
                                    double* avg_dev, double* pts_out_dev, int32_t* idx_out_dev, int* kept_out) {
+  B2R_NVTX("b2r:statistical_outlier");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || n < 0 || nb_neighbors < 1 || !kept_out) return fail(s, B2R_ERR_INVALID_ARG, "statistical_outlier arguments");
   *kept_out = 0;
@@ -1162,6 +1165,7 @@ b2r_status b2r_statistical_outlier(b2r_solver* s, const double* pts_dev, int n, 
 
 b2r_status b2r_voxel_down(b2r_solver* s, const double* pts_dev, int n, double voxel, double* out_dev, int32_t* voxel_of_point_dev,
                           int32_t* counts_dev, int* n_voxels_out) {
+  B2R_NVTX("b2r:voxel_down");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || !out_dev || n < 0 || !(voxel > 0) || !n_voxels_out) return fail(s, B2R_ERR_INVALID_ARG, "voxel_down arguments");
   *n_voxels_out = 0;
@@ -1220,6 +1224,7 @@ b2r_status b2r_voxel_down(b2r_solver* s, const double* pts_dev, int n, double vo
 
 b2r_status b2r_normals(b2r_solver* s, const double* pts_dev, int n, double radius, int max_nn, int orient, const double* view3,
                        double* normals_dev) {
+  B2R_NVTX("b2r:normals");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || !normals_dev || n < 0 || max_nn < 1) return fail(s, B2R_ERR_INVALID_ARG, "normals arguments");
   if (n == 0) return B2R_OK;
@@ -1243,6 +1248,7 @@ b2r_status b2r_normals(b2r_solver* s, const double* pts_dev, int n, double radiu
 
 b2r_status b2r_fpfh(b2r_solver* s, const double* pts_dev, const double* normals_dev, int n, double radius, int max_nn, double* fpfh_dev,
                     double* spfh_dev) {
+  B2R_NVTX("b2r:fpfh");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || !normals_dev || !fpfh_dev || n < 0 || max_nn < 1) return fail(s, B2R_ERR_INVALID_ARG, "fpfh arguments");
   if (n == 0) return B2R_OK;
@@ -1270,6 +1276,7 @@ b2r_status b2r_fpfh(b2r_solver* s, const double* pts_dev, const double* normals_
 
 b2r_status b2r_nn_exact(b2r_solver* s, const double* fq_dev, int nq, const double* fr_dev, int nr, int dim, int32_t* nn_dev,
                         double* dist_dev) {
+  B2R_NVTX("b2r:nn_exact");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!fq_dev || !fr_dev || !nn_dev || nq < 0 || nr < 0 || dim < 1) return fail(s, B2R_ERR_INVALID_ARG, "nn_exact arguments");
   if (nq == 0) return B2R_OK;
@@ -1283,6 +1290,7 @@ b2r_status b2r_nn_exact(b2r_solver* s, const double* fq_dev, int nq, const doubl
 
 b2r_status b2r_mutual_pairs(b2r_solver* s, const int32_t* nn01_dev, int na, const int32_t* nn10_dev, int nb, int32_t* pairs_dev,
                             int* n_pairs_out) {
+  B2R_NVTX("b2r:mutual_pairs");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!nn01_dev || !nn10_dev || !pairs_dev || na < 0 || nb < 0 || !n_pairs_out) return fail(s, B2R_ERR_INVALID_ARG, "mutual_pairs arguments");
   *n_pairs_out = 0;
@@ -1304,6 +1312,7 @@ b2r_status b2r_mutual_pairs(b2r_solver* s, const int32_t* nn01_dev, int na, cons
 
 b2r_status b2r_gather_correspondences(b2r_solver* s, const double* a_pts_dev, const double* b_pts_dev, const int32_t* pairs_dev, int n_pairs,
                                       double* src_dev, double* dst_dev) {
+  B2R_NVTX("b2r:gather_correspondences");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!a_pts_dev || !b_pts_dev || !pairs_dev || !src_dev || !dst_dev || n_pairs < 0) return fail(s, B2R_ERR_INVALID_ARG, "gather_correspondences arguments");
   if (n_pairs == 0) return B2R_OK;

@@ -194,6 +194,7 @@ extern "C" {
 
 b2r_status b2r_render_depth(b2r_solver* s, const double* verts_dev, int nv, const int32_t* tris_dev, int nt, const double* T16, double fx,
                             double fy, double cx, double cy, int W, int H, double z_near, double z_far, float* depth_dev) {
+  B2R_NVTX("b2r:render_depth");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!verts_dev || !tris_dev || !T16 || !depth_dev || nv < 0 || nt < 0 || W < 1 || H < 1 || !(fx > 0) || !(fy > 0) || !(z_far > z_near))
     return fail(s, B2R_ERR_INVALID_ARG, "render_depth arguments");
@@ -221,6 +222,7 @@ b2r_status b2r_render_depth(b2r_solver* s, const double* verts_dev, int nv, cons
 b2r_status b2r_backproject_depth32(b2r_solver* s, const float* depth_dev, int H, int W, double fx, double fy, double cx, double cy,
                                    double depth_scale, double depth_trunc, double* points_dev, int32_t* pixel_ids_dev, int capacity,
                                    int* count_out) {
+  B2R_NVTX("b2r:backproject_depth32");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!depth_dev || !points_dev || !count_out || H < 1 || W < 1 || capacity < 0 || !(depth_scale > 0))
     return fail(s, B2R_ERR_INVALID_ARG, "backproject_depth32 arguments");
@@ -242,6 +244,7 @@ b2r_status b2r_backproject_depth32(b2r_solver* s, const float* depth_dev, int H,
 b2r_status b2r_project_select(b2r_solver* s, const double* pts_dev, int n, const double* R9, const double* t3, const double* K9, const double* D,
                               int nD, int W, int H, const uint8_t* mask_dev, double z_min, int32_t* idx_dev, int32_t* uv_dev, int* n_front_out,
                               int* n_in_image_out, int* n_selected_out) {
+  B2R_NVTX("b2r:project_select");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || !R9 || !t3 || !K9 || !idx_dev || !n_selected_out || n < 0 || W < 1 || H < 1 || nD < 0 || (nD > 0 && !D))
     return fail(s, B2R_ERR_INVALID_ARG, "project_select arguments");

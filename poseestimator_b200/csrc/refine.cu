@@ -430,6 +430,7 @@ unsigned table_cap(int n) { unsigned c = 256; while (c < 2u * (unsigned)(n > 0 ?
 extern "C" {
 
 b2r_status b2r_transform_points(b2r_solver* s, const double* T16, const double* in_dev, int n, double* out_dev) {
+  B2R_NVTX("b2r:transform_points");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!T16 || !in_dev || !out_dev || n < 0) return fail(s, B2R_ERR_INVALID_ARG, "transform_points arguments");
   CK(cudaSetDevice(s->device));
@@ -440,6 +441,7 @@ b2r_status b2r_transform_points(b2r_solver* s, const double* T16, const double* 
 }
 
 b2r_status b2r_nn_distance(b2r_solver* s, const double* q_dev, int nq, const double* ref_dev, int nr, double* dist2_dev, int32_t* idx_dev) {
+  B2R_NVTX("b2r:nn_distance");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!q_dev || !ref_dev || nq < 0 || nr < 1 || (!dist2_dev && !idx_dev)) return fail(s, B2R_ERR_INVALID_ARG, "nn_distance arguments");
   Ws w; b2r_status r = refine_ws(s, (size_t)nq * 16 + 1024, &w);
@@ -455,6 +457,7 @@ b2r_status b2r_nn_distance(b2r_solver* s, const double* q_dev, int nq, const dou
 
 b2r_status b2r_icp(b2r_solver* s, const double* src_dev, int ns, const double* dst_dev, int nd, double max_dist, const double* init16,
                    int max_iter, double rel_fitness, double rel_rmse, b2r_icp_result* out, int32_t* corr_dev) {
+  B2R_NVTX("b2r:icp");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!src_dev || !dst_dev || !out || ns < 1 || nd < 1 || !(max_dist > 0) || max_iter < 0) return fail(s, B2R_ERR_INVALID_ARG, "icp arguments");
   Ws w; b2r_status r = refine_ws(s, (size_t)ns * (24 + 8 + 4 + 4) + 4096, &w);
@@ -502,6 +505,7 @@ b2r_status b2r_icp(b2r_solver* s, const double* src_dev, int ns, const double* d
 }
 
 b2r_status b2r_voxel_coverage(b2r_solver* s, const double* pts_dev, int n, double voxel, int* count_out) {
+  B2R_NVTX("b2r:voxel_coverage");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || n < 0 || !(voxel > 0) || !count_out) return fail(s, B2R_ERR_INVALID_ARG, "voxel_coverage arguments");
   const unsigned cap = table_cap(n);
@@ -517,6 +521,7 @@ b2r_status b2r_voxel_coverage(b2r_solver* s, const double* pts_dev, int n, doubl
 
 b2r_status b2r_alignment_score(b2r_solver* s, const double* src_aligned_dev, int ns, const double* src_down_dev, int ns2,
                                const double* dst_dev, int nd, double voxel, double* out5) {
+  B2R_NVTX("b2r:alignment_score");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!src_aligned_dev || !src_down_dev || !dst_dev || ns < 1 || ns2 < 0 || nd < 1 || !(voxel > 0) || !out5)
     return fail(s, B2R_ERR_INVALID_ARG, "alignment_score arguments");
@@ -556,6 +561,7 @@ b2r_status b2r_alignment_score(b2r_solver* s, const double* src_aligned_dev, int
 }
 
 b2r_status b2r_chamfer(b2r_solver* s, const double* a_dev, int na, const double* b_dev, int nb, double* out) {
+  B2R_NVTX("b2r:chamfer");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!a_dev || !b_dev || na < 1 || nb < 1 || !out) return fail(s, B2R_ERR_INVALID_ARG, "chamfer arguments");
   const int nm = na > nb ? na : nb;
@@ -577,6 +583,7 @@ b2r_status b2r_chamfer(b2r_solver* s, const double* a_dev, int na, const double*
 }
 
 b2r_status b2r_cloud_resolution(b2r_solver* s, const double* pts_dev, int n, int k, double* out) {
+  B2R_NVTX("b2r:cloud_resolution");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || n < 0 || k < 1 || k > 127 || !out) return fail(s, B2R_ERR_INVALID_ARG, "cloud_resolution arguments");
   if (n < 2) { *out = 0.005; return B2R_OK; }          // registration_utils.py:231-232
@@ -604,6 +611,7 @@ b2r_status b2r_cloud_resolution(b2r_solver* s, const double* pts_dev, int n, int
 }
 
 b2r_status b2r_pca_axes(b2r_solver* s, const double* pts_dev, int n, double* R9, double* s3, double* c3) {
+  B2R_NVTX("b2r:pca_axes");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || n < 1 || !R9) return fail(s, B2R_ERR_INVALID_ARG, "pca_axes arguments");
   Ws w; b2r_status r = refine_ws(s, 4096, &w);
@@ -622,6 +630,7 @@ b2r_status b2r_pca_axes(b2r_solver* s, const double* pts_dev, int n, double* R9,
 }
 
 b2r_status b2r_pca_align(b2r_solver* s, const double* src_dev, int ns, const double* dst_dev, int nd, double* T16) {
+  B2R_NVTX("b2r:pca_align");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!src_dev || !dst_dev || ns < 1 || nd < 1 || !T16) return fail(s, B2R_ERR_INVALID_ARG, "pca_align arguments");
   Ws w; b2r_status r = refine_ws(s, 4096, &w);
@@ -652,6 +661,7 @@ b2r_status b2r_pca_align(b2r_solver* s, const double* src_dev, int ns, const dou
 }
 
 b2r_status b2r_farthest_point_sample(b2r_solver* s, const double* pts_dev, int n, int target, int first_index, int32_t* idx_dev) {
+  B2R_NVTX("b2r:farthest_point_sample");
   if (!s) return B2R_ERR_INVALID_ARG;
   if (!pts_dev || !idx_dev || n < 1 || target < 1 || target > n || first_index < 0 || first_index >= n)
     return fail(s, B2R_ERR_INVALID_ARG, "farthest_point_sample arguments");

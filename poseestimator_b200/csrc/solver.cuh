@@ -1,24 +1,52 @@
 // Internal: the solver handle behind include/b2r.h, shared by api.cu (registration) and presteps.cu / nn_gemm.cu.
 #pragma once
+#include <stdlib.h>
+
 #include <string>
 #include <vector>
+
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: a no-op function-pointer test unless a profiler is attached
 
 #include "common.cuh"
 
 namespace b2r {
 
+// Device buffer of the workspace.  With B2R_CANARY=1 in the environment every buffer is allocated with a 4 KB guard zone of 0xA5
+// bytes on either side; b2r_sync / b2r_destroy verify the zones (b2r_debug_check_canaries), so a kernel that writes past either end of
+// a workspace buffer fails the call instead of corrupting a neighbour silently (compute-sanitizer is not available on the GPU pool).
+inline size_t canary_bytes() {
+  static const size_t g = [] { const char* e = getenv("B2R_CANARY"); return (e && e[0] == '1') ? (size_t)4096 : (size_t)0; }();
+  return g;
+}
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
   cudaError_t ensure(size_t need) {
     if (need <= bytes) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr; bytes = 0;
-    cudaError_t e = cudaMalloc(&p, need);
-    if (e == cudaSuccess) bytes = need;
-    return e;
+    release();
+    const size_t g = canary_bytes();
+    char* base = nullptr;
+    cudaError_t e = cudaMalloc(&base, need + 2 * g);
+    if (e != cudaSuccess) return e;
+    if (g) {
+      e = cudaMemset(base, 0xA5, g);
+      if (e == cudaSuccess) e = cudaMemset(base + g + need, 0xA5, g);
+      if (e != cudaSuccess) { cudaFree(base); return e; }
+    }
+    p = base + g; bytes = need;
+    return cudaSuccess;
   }
-  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  void release() { if (p) cudaFree((char*)p - canary_bytes()); p = nullptr; bytes = 0; }
+  // true when both guard zones still hold the pattern (always true without B2R_CANARY)
+  bool intact() const {
+    const size_t g = canary_bytes();
+    if (!g || !p) return true;
+    std::vector<unsigned char> h(2 * g);
+    if (cudaMemcpy(h.data(), (char*)p - g, g, cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+    if (cudaMemcpy(h.data() + g, (char*)p + bytes, g, cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+    for (unsigned char c : h) if (c != 0xA5) return false;
+    return true;
+  }
 };
 struct HostBuf {
   void* p = nullptr;
@@ -83,6 +111,17 @@ struct b2r_solver {
     }                                                                                             \
   } while (0)
 
+
+// NVTX range over one stage of the path: shows as "b2r:<stage>" rows in Nsight Systems / ncu --nvtx
+struct B2rNvtx {
+  explicit B2rNvtx(const char* name) { nvtxRangePushA(name); }
+  ~B2rNvtx() { nvtxRangePop(); }
+  B2rNvtx(const B2rNvtx&) = delete;
+  B2rNvtx& operator=(const B2rNvtx&) = delete;
+};
+#define B2R_NVTX_CAT2(a, b) a##b
+#define B2R_NVTX_CAT(a, b) B2R_NVTX_CAT2(a, b)
+#define B2R_NVTX(name) B2rNvtx B2R_NVTX_CAT(nvtx_range_, __LINE__)(name)
 
 static inline b2r_status fail(b2r_solver* s, b2r_status code, const std::string& msg) {
   if (s) s->err = msg;

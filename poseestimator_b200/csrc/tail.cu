@@ -26,11 +26,18 @@ constexpr int kTailWarps = kTailThreads / 32;
 #define B2R_HEU_SEEDS 2
 #endif
 
+constexpr int kTailMaxExtra = 8;                               // |core| - lb up to which the fused tail decides the clique itself
+constexpr int kTailMaxPairs = kTailMaxExtra * kTailMaxExtra;   // a core of lb + e vertices with omega >= lb has at most e * e non-adjacent pairs
+
 struct TailShared {
   unsigned long long key[8];
   unsigned long long deg_sum;
   int lb, changed, cnt, base;
+  int cmin;          // smallest degree inside the surviving set seen by the current peel pass
   int scan[40];
+  // near-clique core: the non-adjacent pairs inside the core and the vertices to drop (tail_small_cover)
+  int n_pairs, n_cover;
+  unsigned short pu[kTailMaxPairs], pv[kTailMaxPairs], cover[kTailMaxExtra];
 };
 
 // ascending list of the set bits of `bits` (Wb words) as 16-bit ids; returns the count (uniform)
@@ -64,6 +71,53 @@ __device__ int tail_list_bits(const uint32_t* bits, int Wb, unsigned short* list
     __syncthreads();
   }
   return ts->base;
+}
+
+// Exact maximum clique of a core that is a clique up to a few vertices (|core| = lb + e, e <= kTailMaxExtra): every core vertex has at
+// least lb - 1 neighbours inside the core, i.e. at most e non-neighbours, so the COMPLEMENT of the core's graph is tiny; a maximum
+// clique is the core minus a minimum vertex cover of those non-adjacent pairs (size k* = |core| - omega <= e).  One thread enumerates
+// all covers of minimum size by branching on the two ends of an uncovered pair (depth <= e, <= 2^e leaves) and keeps the one whose
+// sorted id list is lexicographically LARGEST: dropping it leaves the lexicographically smallest maximum clique, the canonical
+// answer of the oracle and of canon_kernel.  Returns the cover in ts->cover / ts->n_cover (-1: no cover of size <= e exists).
+__device__ void tail_small_cover(TailShared* ts, int e) {
+  const int np = ts->n_pairs;
+  int sel[kTailMaxExtra], choice[kTailMaxExtra], eidx[kTailMaxExtra];
+  int best[kTailMaxExtra], cand[kTailMaxExtra];
+  int best_n = -1;
+  auto first_uncovered = [&](int depth) {
+    for (int i = 0; i < np; ++i) {
+      bool cov = false;
+      for (int q = 0; q < depth; ++q) cov = cov || sel[q] == (int)ts->pu[i] || sel[q] == (int)ts->pv[i];
+      if (!cov) return i;
+    }
+    return -1;
+  };
+  for (int k = 0; k <= e && best_n < 0; ++k) {
+    int depth = 0;
+    for (;;) {
+      const int ei = first_uncovered(depth);
+      if (ei < 0) {   // sel[0 .. depth) covers every pair
+        for (int q = 0; q < depth; ++q) cand[q] = sel[q];
+        for (int a = 1; a < depth; ++a) { const int x = cand[a]; int b = a - 1; while (b >= 0 && cand[b] > x) { cand[b + 1] = cand[b]; --b; } cand[b + 1] = x; }
+        bool better = best_n < 0;
+        if (!better && depth == best_n)
+          for (int q = 0; q < depth; ++q) if (cand[q] != best[q]) { better = cand[q] > best[q]; break; }
+        if (better) { best_n = depth; for (int q = 0; q < depth; ++q) best[q] = cand[q]; }
+      } else if (depth < k) {
+        eidx[depth] = ei; choice[depth] = 0; sel[depth] = (int)ts->pu[ei]; ++depth;
+        continue;
+      }
+      // backtrack: the other end of the deepest pair that still has one
+      while (depth > 0) {
+        const int dd = depth - 1;
+        if (choice[dd] == 0) { choice[dd] = 1; sel[dd] = (int)ts->pv[eidx[dd]]; break; }
+        --depth;
+      }
+      if (depth == 0) break;
+    }
+  }
+  ts->n_cover = best_n;
+  for (int q = 0; q < best_n; ++q) ts->cover[q] = (unsigned short)best[q];
 }
 
 // mode 0: the graph comes from the tensor-core filter of this batch (pair list to fix, degrees accumulated by the filter);
@@ -163,6 +217,8 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   __syncthreads();
   unsigned long long heu_key = 0ull;
   int lb = 0, T = 0, n_alive = 0;
+  bool core_is_clique = false;
+  int n_cl = 0;
   for (int k = 0; k < B2R_HEU_SEEDS; ++k) {
     const unsigned long long skey = ts.key[k];
     if (skey == 0ull) continue;
@@ -189,7 +245,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
     }
     for (;;) {
       n_alive = tail_list_bits(alive, Wb, list, &ts);
-      if (tid == 0) ts.changed = 0;
+      if (tid == 0) { ts.changed = 0; ts.cmin = 0x7fffffff; }
       __syncthreads();
       // |alive| == lb: every member of the greedy clique has at least lb - 1 = T neighbours, so it is inside `alive`, and a set of
       // lb vertices that contains a clique of size lb IS that clique -- all of it survives any further pass: nothing to peel
@@ -212,6 +268,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
 #pragma unroll
           for (int q = 0; q < R; ++q) {
             if (ids[q] < 0) continue;
+            if (lane == 0 && c[q] < ts.cmin) atomicMin(&ts.cmin, c[q]);
             if (c[q] < T && lane == 0) { atomicAnd(&alive[ids[q] >> 5], ~(1u << (ids[q] & 31))); ts.changed = 1; }
           }
         }
@@ -221,23 +278,73 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
     }
     // Note: a vertex counted against neighbours that die in the same pass is caught by the next pass (the loop ends on a pass
     // without removals), so the fixed point is the T-core whatever the order -- the same set prune_kernel leaves.
-    if (n_alive == lb) break;   // the core IS the clique: proven
+    // The last pass removed nothing, so ts.cmin is the smallest degree inside the core.  Every clique of at least lb vertices lies
+    // inside the (lb-1)-core; when every core vertex is adjacent to all the others the core itself is a clique, hence THE maximum
+    // clique, although the greedy bound missed it by a vertex or two (lb < omega = |core|).
+    core_is_clique = T > 0 && n_alive > lb && ts.cmin == n_alive - 1;
+    n_cl = n_alive;
+    if (n_alive == lb || core_is_clique) break;   // the core IS the clique: proven
+    if (!(n_alive == lb || core_is_clique) && lb > 0 && n_alive - lb <= kTailMaxExtra) {
+      // ---- 4b. near-clique core: list its non-adjacent pairs (u < v), drop a minimum vertex cover of them (tail_small_cover) ----
+      if (tid == 0) { ts.n_pairs = 0; ts.n_cover = -1; }
+      __syncthreads();
+      for (int m = warp; m < n_alive; m += kTailWarps) {
+        const int id = (int)list[m];
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(cached_row(rcache, id));
+        if (!row) row = d.adj + (size_t)id * d.pitch;
+        for (int w = lane; w < Wb; w += 32) {
+          uint32_t nb = alive[w] & ~row[w];
+          if (w == (id >> 5)) nb &= ~(1u << (id & 31));
+          while (nb) {
+            const int j = 32 * w + (__ffs(nb) - 1);
+            nb &= nb - 1;
+            if (j > id) {
+              const int slot = atomicAdd(&ts.n_pairs, 1);
+              if (slot < kTailMaxPairs) { ts.pu[slot] = (unsigned short)id; ts.pv[slot] = (unsigned short)j; }
+            }
+          }
+        }
+      }
+      __syncthreads();
+      if (ts.n_pairs <= kTailMaxPairs) {
+        if (tid == 0) {
+          // the search order must not depend on which warp listed a pair first: sort the pairs by (u, v)
+          const int np = ts.n_pairs;
+          for (int a = 1; a < np; ++a) {
+            const unsigned short xu = ts.pu[a], xv = ts.pv[a];
+            int b = a - 1;
+            while (b >= 0 && (ts.pu[b] > xu || (ts.pu[b] == xu && ts.pv[b] > xv))) { ts.pu[b + 1] = ts.pu[b]; ts.pv[b + 1] = ts.pv[b]; --b; }
+            ts.pu[b + 1] = xu; ts.pv[b + 1] = xv;
+          }
+          tail_small_cover(&ts, n_alive - lb);
+          for (int q = 0; q < ts.n_cover; ++q) alive[ts.cover[q] >> 5] &= ~(1u << (ts.cover[q] & 31));
+        }
+        __syncthreads();
+        if (ts.n_cover >= 0) {
+          n_cl = tail_list_bits(alive, Wb, list, &ts);
+          core_is_clique = true;     // what is left of the core is a maximum clique, the canonical one
+        }
+      }
+    }
+    if (core_is_clique) break;   // decided exactly: the other seeds are not needed
+    // (the next seed's heuristic reuses this shared memory: `alive` and `list` are only valid when the loop is left by a break)
   }
   stamp(3);
   const int Wc = (((n_alive + 31) >> 5) + 3) & ~3;
   for (int m = tid; m < n_alive; m += kTailThreads) d.ids[m] = (int)list[m];
   if (tid == 0) {
     st->lb = lb; st->heu_key = heu_key;
-    st->T = T; st->n_alive = n_alive; st->Wc = Wc; st->omega = lb;
+    st->T = T; st->n_alive = n_alive; st->Wc = Wc; st->omega = core_is_clique ? n_cl : lb;
     if (Wc > kMaxCompactWords) st->flags |= FLAG_COMPACT_TOO_LARGE;
   }
-  if (n_alive != lb || lb <= 0) {   // the core is larger than the bound: the exact search decides (multi-kernel path)
+  if (!(n_alive == lb || core_is_clique) || lb <= 0) {   // the core is neither the greedy clique nor close to a clique: the exact search decides (multi-kernel path)
     if (tid == 0) st->tail_why = 2;
     return;
   }
-  // ---- 5. the (lb-1)-core has exactly lb vertices, each adjacent to the lb-1 others: it is the unique maximum clique ----
-  for (int m = tid; m < n_alive; m += kTailThreads) d.clique[m] = (int)list[m];
-  if (tid == 0) st->clique_size = lb;
+  // ---- 5. the clique: the (lb-1)-core itself (lb vertices each adjacent to the lb-1 others, or proven above), or the core minus the
+  // cover of its non-adjacent pairs ----
+  for (int m = tid; m < n_cl; m += kTailThreads) d.clique[m] = (int)list[m];
+  if (tid == 0) st->clique_size = n_cl;
   __threadfence_block();
   __syncthreads();
   stamp(4);

@@ -290,6 +290,39 @@ def test_max_clique_random_graphs_with_ties(oracle_mod, seed):
     assert st["exact_proven"] == 1
 
 
+@pytest.mark.parametrize("seed", range(12))
+def test_near_clique_core_decided_by_fused_tail(oracle_mod, seed):
+    """A planted clique plus a few vertices adjacent to almost all of it: the (lb-1)-core is larger than the greedy clique, several
+    maximum cliques may exist.  The fused tail settles it itself (minimum vertex cover of the core's non-adjacent pairs) and must
+    return the oracle's canonical (lexicographically smallest) maximum clique."""
+    rng = np.random.default_rng(900 + seed)
+    n = int(rng.integers(200, 700))
+    c = int(rng.integers(30, 90))
+    e = 1 + seed % 8
+    A = rng.random((n, n)) < 0.03
+    A = np.triu(A, 1); A = A | A.T
+    ids = rng.permutation(n)
+    planted, extra = ids[:c], ids[c:c + e]
+    A[np.ix_(planted, planted)] = True
+    for x in extra:                           # adjacent to all of the clique but 1 .. 2 members, and to the other extras at random
+        A[x, planted] = True; A[planted, x] = True
+        miss = rng.choice(planted, size=int(rng.integers(1, 3)), replace=False)
+        A[x, miss] = False; A[miss, x] = False
+        for y in extra:
+            if y != x:
+                v = bool(rng.random() < 0.5); A[x, y] = v; A[y, x] = v
+    if seed % 3 == 0:                         # and one member that lost an edge inside the clique (two maximum cliques through it)
+        a, b = planted[:2]
+        A[a, b] = False; A[b, a] = False
+    np.fill_diagonal(A, False)
+    want = oracle_mod.max_clique_bits(_bits_from_dense(A)).tolist()
+    got, st = _clique_of_graph(A)
+    assert got == want, (n, c, e, st)
+    assert st["omega"] == len(want) and st["exact_proven"] == 1
+    if st["n_pruned"] - st["heuristic_lb"] <= 8:
+        assert st["fused_tail"] == 1, st      # near-clique core: no hand-over to the multi-kernel chain
+
+
 def test_max_clique_planted_and_modes(oracle_mod):
     rng = np.random.default_rng(3)
     n = 600
@@ -426,6 +459,7 @@ def test_non_unique_maximum_clique_is_canonical_and_fast(oracle_mod):
         n_multi += bs.stats(i)["n_pruned"] > bs.stats(i)["omega"]
     assert n_multi >= 1, "no problem of this batch has extra vertices in its (omega-1)-core; pick other seeds"
     assert tm["canonical"] < 5.0 and tm["exact_search"] < 5.0, tm
+    assert all(bs.stats(i)["fused_tail"] == 1 for i in range(len(pbs))), "a near-clique core was handed to the multi-kernel chain"
 
 
 def test_batched_solution_getter_equals_per_problem_getter():
