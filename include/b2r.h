@@ -184,6 +184,27 @@ b2r_status b2r_solve_from_adjacency(b2r_solver* s, const double* src_dev, const 
 /* words per adjacency row the library uses for n vertices (multiple of 4) */
 int b2r_pitch_words(int n);
 
+/* ---- one very large registration over the GPUs of one box, adjacency exchanged by NVLink peer stores (config 5) ------------------
+ * One process per GPU.  Every rank: b2r_shard_export (sizes its workspace for ONE problem of n correspondences and returns CUDA IPC
+ * handles of its bit matrix and flag words), exchanges the b2r_peer_handle structs with the other ranks by any means (the Python
+ * host uses torch.distributed.all_gather_object), b2r_shard_attach (maps the peers' buffers; needs peer access between the GPUs),
+ * then any number of b2r_solve_sharded calls -- COLLECTIVE: every rank calls it with the same replicated operands.  Rank r runs
+ * 1 / world of the tensor-core graph filter and stores its words into every rank's matrix while it computes; each rank then finishes
+ * the solve on its own complete matrix (results identical on all ranks and to b2r_solve, getters as usual).  world <= 8.
+ * The handle must not be used for larger problems or batches in between (a workspace re-allocation invalidates the export). */
+typedef struct b2r_peer_handle {
+  unsigned char adjacency[64];   /* cudaIpcMemHandle_t of the allocation that holds the bit matrix */
+  unsigned char flags[64];       /* cudaIpcMemHandle_t of the allocation that holds the flag words */
+  int64_t adj_offset, flag_offset;
+  int32_t n, device;
+} b2r_peer_handle;
+b2r_status b2r_shard_export(b2r_solver* s, int n, b2r_peer_handle* out);
+b2r_status b2r_shard_attach(b2r_solver* s, int rank, int world, const b2r_peer_handle* all_ranks /* [world] */);
+b2r_status b2r_solve_sharded(b2r_solver* s, const double* src_dev, const double* dst_dev, int n);
+/* 1 when the last b2r_solve_sharded fell back to every rank solving alone (a rank's filter refused the problem) */
+int b2r_shard_last_fell_back(const b2r_solver* s);
+b2r_status b2r_shard_detach(b2r_solver* s);
+
 
 /* ---- pre-steps: what the reference does with Open3D between the detector's mask and solver.solve -----------------
  * All point / feature buffers are DEVICE pointers on the handle's device unless stated; outputs are written in the

@@ -65,11 +65,14 @@ EXPORTS = [
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
     "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
     "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align", "b2r_render_depth", "b2r_backproject_depth32", "b2r_project_select", "b2r_farthest_point_sample",
+    "b2r_shard_export", "b2r_shard_attach", "b2r_solve_sharded", "b2r_shard_last_fell_back", "b2r_shard_detach",
 ]
 
 # include/b2r_debug.h: test hooks, not part of the drop-in boundary
 DEBUG_EXPORTS = ["b2r_debug_set_graph_filter", "b2r_debug_tc_values", "b2r_debug_tc_sweep", "b2r_debug_tail_cycles",
                  "b2r_debug_nn_gemm_error", "b2r_debug_check_canaries"]
+
+PEER_HANDLE_BYTES = 64 + 64 + 8 + 8 + 4 + 4   # sizeof(b2r_peer_handle)
 
 # numpy view of an array of b2r_solution (112 bytes each)
 import numpy as _np  # noqa: E402
@@ -128,6 +131,12 @@ def lib():
     L.b2r_debug_tail_cycles.argtypes = [vp, i32, vp]
     L.b2r_debug_nn_gemm_error.argtypes = [vp, vp, i32, vp, i32, i32, vp, vp]
     L.b2r_debug_check_canaries.argtypes = [vp]
+    L.b2r_shard_export.argtypes = [vp, i32, vp]
+    L.b2r_shard_attach.argtypes = [vp, i32, i32, vp]
+    L.b2r_solve_sharded.argtypes = [vp, vp, vp, i32]
+    L.b2r_shard_last_fell_back.argtypes = [vp]
+    L.b2r_shard_last_fell_back.restype = i32
+    L.b2r_shard_detach.argtypes = [vp]
     L.b2r_pitch_words.argtypes = [i32]
     L.b2r_pitch_words.restype = i32
     d, ip = C.c_double, C.POINTER(C.c_int)

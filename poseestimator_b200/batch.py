@@ -260,5 +260,31 @@ class BatchSolver:
         return self.solution(0)
 
 
+    # ---- tile-sharded large problem with NVLink peer stores (b2r_solve_sharded) ---------------------------
+    def shard_export(self, n: int) -> bytes:
+        buf = (C.c_ubyte * _lib.PEER_HANDLE_BYTES)()
+        _lib.check(self._h, _lib.lib().b2r_shard_export(self._h, int(n), buf))
+        return bytes(buf)
+
+    def shard_attach(self, rank: int, world: int, handles) -> None:
+        """handles: the shard_export() bytes of every rank, in rank order."""
+        if len(handles) != world or any(len(h) != _lib.PEER_HANDLE_BYTES for h in handles):
+            raise ValueError("shard_attach needs one exported handle per rank")
+        blob = b"".join(handles)
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        _lib.check(self._h, _lib.lib().b2r_shard_attach(self._h, int(rank), int(world), buf))
+
+    def solve_sharded(self, src_ptr, dst_ptr, n):
+        self._batch = 1
+        _lib.check(self._h, _lib.lib().b2r_solve_sharded(self._h, C.c_void_p(src_ptr), C.c_void_p(dst_ptr), int(n)))
+        return self.solution(0)
+
+    def shard_fell_back(self) -> bool:
+        return bool(_lib.lib().b2r_shard_last_fell_back(self._h))
+
+    def shard_detach(self) -> None:
+        _lib.check(self._h, _lib.lib().b2r_shard_detach(self._h))
+
+
 def pitch_words(n: int) -> int:
     return int(_lib.lib().b2r_pitch_words(n))

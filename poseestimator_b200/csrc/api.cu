@@ -225,12 +225,14 @@ bool fused_tail_enabled(const b2r_solver* s) {
 }
 
 // enqueue stages 1.. on descriptors already in h_desc
-b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph) {
+b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph, bool prepared = false) {
   B2R_NVTX("b2r:solve_pipeline");
   cudaStream_t st = s->stream;
   const bool prof = s->profiling;
-  CK(cudaMemsetAsync(s->d_state.p, 0, (size_t)batch * sizeof(ProbState), st));
-  CK(cudaMemcpyAsync(s->d_desc.p, s->h_desc.p, (size_t)batch * sizeof(ProbDesc), cudaMemcpyHostToDevice, st));
+  if (!prepared) {   // (the sharded solve clears the state and uploads the descriptor before its graph kernels, shard.cu)
+    CK(cudaMemsetAsync(s->d_state.p, 0, (size_t)batch * sizeof(ProbState), st));
+    CK(cudaMemcpyAsync(s->d_desc.p, s->h_desc.p, (size_t)batch * sizeof(ProbDesc), cudaMemcpyHostToDevice, st));
+  }
   const ProbDesc* dd = (const ProbDesc*)s->d_desc.p;
   if (s->kp.estimate_scaling) {  // A.4-5: the scale vote comes first; the graph is its inlier mask
     B2R_NVTX("b2r:scale_vote");
@@ -328,6 +330,27 @@ b2r_status check_index(b2r_solver* s, int idx) {
 }
 
 }  // namespace
+
+// ---- used by shard.cu ------------------------------------------------------------------------------------------------
+// workspace for one problem of n correspondences; with operands: state cleared and the descriptor of problem 0 on the device
+b2r_status b2r_internal_prepare_single(b2r_solver* s, int n, const double* src_dev, const double* dst_dev) {
+  b2r_status r = ensure_workspace(s, 1, n);
+  if (r != B2R_OK) return r;
+  if (!src_dev) return B2R_OK;
+  if (s->profiling) { r = ensure_events(s); if (r != B2R_OK) return r; CK(cudaEventRecord(s->ev[0], s->stream)); }
+  s->batch = 1; s->n.assign(1, n);
+  s->ext_adj = nullptr;
+  build_desc(s, 0, n, src_dev, dst_dev, nullptr, 0);
+  CK(cudaMemsetAsync(s->d_state.p, 0, sizeof(ProbState), s->stream));
+  CK(cudaMemcpyAsync(s->d_desc.p, s->h_desc.p, sizeof(ProbDesc), cudaMemcpyHostToDevice, s->stream));
+  return B2R_OK;
+}
+// the matrix of problem 0 is complete: degrees, fused tail, state to the host; synchronises
+b2r_status b2r_internal_finish_from_graph(b2r_solver* s, int n) {
+  b2r_status r = enqueue_pipeline(s, 1, n, true, true);
+  if (r != B2R_OK) return r;
+  return b2r_sync(s);
+}
 
 extern "C" {
 

@@ -37,6 +37,8 @@ enum : uint32_t {
   FLAG_TIME_LIMIT = 1u << 1,       // exact search stopped by max_clique_time_limit
   FLAG_COMPACT_TOO_LARGE = 1u << 2,  // pruned graph wider than kMaxCompactWords
   FLAG_CANON_FAILED = 1u << 3,     // canonicalisation could not build a clique of size omega (bug guard)
+  FLAG_SHARD_FALLBACK = 1u << 5,   // b2r_solve_sharded: some rank's tensor-core filter refused the problem -> every rank solves it alone
+  FLAG_SHARD_TIMEOUT = 1u << 6,    // b2r_solve_sharded: a peer's flag did not arrive within the time limit
 };
 
 // Per-problem device state: written by the kernels, copied back once per batch.
@@ -137,6 +139,11 @@ struct KernelParams {
   int graph_v4;           // 1: the packed-fp32 norm-expansion filter (v4) instead of the tensor-core filter (v5)
   double filter_tau_min;  // graph_filter_tau of the params (0 = none): lower limit of v3's band tau_G (tests widen it)
   unsigned band_k1, band_k2;  // high-word constants of the v2 ambiguity band (api.cu fill_kernel_params)
+  // One problem tile-sharded over the GPUs of a box (b2r_solve_sharded): this rank evaluates the work items i with
+  // i % shard_world == shard_rank and stores every adjacency word it produces into its own matrix AND, over NVLink, into the
+  // matrices of the n_peer other ranks (same offsets).  shard_world <= 1: not sharded.
+  int shard_rank, shard_world, n_peer;
+  uint32_t* peer_adj[7];
 };
 
 // launchers (each returns the number of kernels it enqueued)
@@ -144,6 +151,9 @@ int launch_tim_graph(const ProbDesc* d_desc, int batch, int n_max, const KernelP
 // graph_tc.cu (v5): prep (boxes, constants, 22-bit records) + tcgen05 filter; graph.cu: exact fix-up of the listed pairs and the
 // fp64 filter for problems the fp32 path may not decide
 int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
+// sharded form (kp.shard_world > 1, batch 1): the filter kernel with peer stores, then the exact fix-up of this rank's listed pairs
+// on every copy of the matrix (bits only; the degrees are recomputed from the complete matrix)
+int launch_tim_graph_tc_sharded(const ProbDesc* d_desc, int n, const KernelParams& kp, cudaStream_t st);
 int launch_tim_graph_tc_and_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st);
 int launch_graph_tc_debug(const ProbDesc* d_desc, int prob, int bi, int v, float* out_dm, float* out_l, cudaStream_t st);
 // every unit of one problem checked on the device against fp64 (b2r_debug_tc_sweep); out: 8 doubles, zeroed by the caller

@@ -28,6 +28,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "exact.cuh"
 
 namespace b2r {
 
@@ -432,7 +433,7 @@ __host__ __device__ inline int tc_items(int T) {
 // ---------------------------------------------------------------------------------------------------------------------
 template <int S_> struct StageC { static constexpr int value = S_; };
 
-template <bool LD16, bool STAGED>
+template <bool LD16, bool STAGED, bool PEERS = false>
 __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
   const ProbDesc d = descs[blockIdx.y];
   const int n = d.n;
@@ -446,8 +447,10 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
   {
     const int qT = T / G, rT = T % G;
     const int total = G * qT * (qT + 1) / 2 + rT * (qT + 1);
-    if ((int)blockIdx.x >= total) return;
-    const int pe = total - 1 - (int)blockIdx.x;
+    // PEERS (b2r_solve_sharded): rank r of w takes the items r, r + w, r + 2 w, ... -- neighbouring items have the same size
+    const int item = PEERS ? (int)blockIdx.x * kp.shard_world + kp.shard_rank : (int)blockIdx.x;
+    if (item >= total) return;
+    const int pe = total - 1 - item;
     int q = (int)((sqrtf(1.0f + (8.0f / G) * (float)pe) - 1.0f) * 0.5f);
     q += (G * (q + 1) * (q + 2) / 2 <= pe) ? 1 : 0;
     q -= (G * q * (q + 1) / 2 > pe) ? 1 : 0;
@@ -765,7 +768,11 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
 #pragma unroll
         for (int h = 0; h < kSW / 32; ++h) {
           const uint32_t x = stage_w[kSW * r2 + 32 * h + (lane ^ (r2 & 31))];
-          if (i2 < n && 32 * h + lane < kw) d.adj[(size_t)i2 * d.pitch + wbase + 32 * h + lane] = x;
+          if (i2 < n && 32 * h + lane < kw) {
+            const size_t off = (size_t)i2 * d.pitch + wbase + 32 * h + lane;
+            d.adj[off] = x;
+            if (PEERS) for (int pp = 0; pp < kp.n_peer; ++pp) kp.peer_adj[pp][off] = x;   // the same 128-byte row segment into every peer's matrix (NVLink)
+          }
         }
       }
       // mirrored blocks: chunk k = 2 u + ch holds columns jk .. jk + 31; lane c of the transposes owns column jk + c
@@ -780,7 +787,9 @@ __global__ void __launch_bounds__(kTcThreads, 2) tim_graph6_kernel(const ProbDes
         for (int qq = 0; qq < 4; ++qq) x[qq] = warp_transpose32_fast(x[qq], tk);
         const int j = i0 + v0 * kTcUnit + 32 * k + lane;
         if (j < n) {
-          *reinterpret_cast<uint4*>(d.adj + (size_t)j * d.pitch + (i0 >> 5)) = make_uint4(x[0], x[1], x[2], x[3]);
+          const size_t off = (size_t)j * d.pitch + (i0 >> 5);
+          *reinterpret_cast<uint4*>(d.adj + off) = make_uint4(x[0], x[1], x[2], x[3]);
+          if (PEERS) for (int pp = 0; pp < kp.n_peer; ++pp) *reinterpret_cast<uint4*>(kp.peer_adj[pp] + off) = make_uint4(x[0], x[1], x[2], x[3]);
           const int c = __popc(x[0]) + __popc(x[1]) + __popc(x[2]) + __popc(x[3]);
           if (c) atomicAdd(d.deg + j, c);
         }
@@ -828,6 +837,44 @@ int launch_tim_graph_tc(const ProbDesc* d_desc, int batch, int n_max, const Kern
     default: tim_graph6_kernel<false, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp); break;
   }
   return 2;
+}
+
+// Exact decision of this rank's listed pairs on every copy of the matrix: bits only (atomicOr locally and over NVLink); the degrees
+// of a sharded solve are recomputed from the complete matrix after the exchange.
+__global__ void __launch_bounds__(256) graph_fix_peers_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  const ProbDesc d = descs[0];
+  ProbState* st = d.st;
+  if (!st->use32 || st->tc_overflow) return;
+  const unsigned cnt = min(st->amb_count, (unsigned)d.amb_cap);
+  for (unsigned idx = blockIdx.x * 256 + threadIdx.x; idx < cnt; idx += gridDim.x * 256) {
+    const uint32_t e = d.amb_list[idx];
+    const FixPair p = load_listed_pair(d.src, d.dst, e);
+    const size_t i = e >> 16, j = e & 0xffffu;
+    const double A = sq3_ref(__dsub_rn(p.s[3], p.s[0]), __dsub_rn(p.s[4], p.s[1]), __dsub_rn(p.s[5], p.s[2]));
+    const double B = sq3_ref(__dsub_rn(p.t[3], p.t[0]), __dsub_rn(p.t[4], p.t[1]), __dsub_rn(p.t[5], p.t[2]));
+    if (!verdict_exact(A, B, kp.beta)) continue;
+    const bool both = (i >> 7) != (j >> 7);
+    for (int pp = -1; pp < kp.n_peer; ++pp) {
+      uint32_t* adj = pp < 0 ? d.adj : kp.peer_adj[pp];
+      atomicOr(adj + i * d.pitch + (j >> 5), 1u << (j & 31));
+      if (both) atomicOr(adj + j * d.pitch + (i >> 5), 1u << (i & 31));
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) st->slow_pairs = cnt;
+}
+
+int launch_tim_graph_tc_sharded(const ProbDesc* d_desc, int n, const KernelParams& kp, cudaStream_t st) {
+  static PerDeviceOnce attr;
+  attr.run([] { return cudaFuncSetAttribute(tim_graph6_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes); });
+  const int T = (n + kTile - 1) / kTile;
+  int slices = 148;
+  if (slices > T) slices = T;
+  graph_tc_setup_kernel<<<dim3(slices, 1), 1024, 0, st>>>(d_desc, kp);
+  const int w = kp.shard_world > 1 ? kp.shard_world : 1;
+  const dim3 grid((tc_items(T) + w - 1) / w, 1);
+  tim_graph6_kernel<false, true, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(d_desc, kp);
+  graph_fix_peers_kernel<<<64, 256, 0, st>>>(d_desc, kp);
+  return 3;
 }
 
 int launch_tim_graph_tc_and_fix(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st) {

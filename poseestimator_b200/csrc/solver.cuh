@@ -95,6 +95,19 @@ struct b2r_solver {
   int handed_over = 0;                // problems of the last batch the fused tail handed to the multi-kernel path
   int n_max = 0;
 
+  // one problem tile-sharded over the GPUs of a box (shard.cu): peers' matrices and flag words mapped through CUDA IPC
+  struct Shard {
+    bool exported = false, attached = false;
+    int rank = 0, world = 1, n = 0;
+    unsigned epoch = 0;
+    unsigned* flags = nullptr;          // this rank's flag words: ready[8], done[8] (own cudaMalloc, exported)
+    uint32_t* peer_adj[7] = {};
+    unsigned* peer_flags[7] = {};
+    void* opened[14] = {};
+    int n_opened = 0;
+    bool last_fell_back = false;
+  } shard;
+
   bool profiling = false;
   cudaEvent_t ev[12] = {};
   bool ev_ready = false;

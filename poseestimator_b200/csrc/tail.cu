@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   TailMarks tm;
   tm.clk = st->tail_clk; tm.t0 = clk0;
   if (tid < 24) st->tail_clk[8 + tid] = 0u;
+  if (st->flags & (FLAG_SHARD_FALLBACK | FLAG_SHARD_TIMEOUT)) return;   // sharded solve: the matrix is not valid, the host redoes the problem
 
   if (mode == 0) {
     if (!st->use32 || st->tc_overflow) {   // uniform: the state was written by earlier kernels

@@ -60,11 +60,44 @@ def allgather_adjacency(n: int, pitch_words: int, compute_rows: Callable, device
     return full
 
 
-EXCHANGE_MODES = ("nccl",)
+EXCHANGE_MODES = ("nccl", "peer")
 
 
 class ExchangeUnavailable(RuntimeError):
     """The requested exchange of adjacency rows cannot run on this box (e.g. no peer access between the GPUs)."""
+
+
+def exchange_handles(mine: bytes, group=None):
+    """Every rank's exported handle, in rank order (all_gather_object: plumbing, 152 bytes per rank, once)."""
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [mine]
+    out = [None] * dist.get_world_size(group)
+    dist.all_gather_object(out, mine, group=group)
+    return out
+
+
+def attach_peers(solver, n: int, group=None) -> None:
+    """Export this rank's matrix, gather everybody's handles, map the peers (idempotent per (solver, n))."""
+    import torch.distributed as dist
+
+    if getattr(solver, "_shard_n", None) == n:
+        return
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    err = None
+    try:
+        handles = exchange_handles(solver.shard_export(n), group)
+        solver.shard_attach(rank, world, handles)
+    except Exception as e:  # noqa: BLE001
+        err = str(e)
+    # the solve is collective: either every rank is attached or none uses the path
+    errs = exchange_handles(err, group) if world > 1 else [err]
+    bad = [f"rank {r}: {e}" for r, e in enumerate(errs) if e]
+    if bad:
+        raise ExchangeUnavailable("; ".join(bad))
+    solver._shard_n = n
 
 
 def solve_row_sharded(solver, src_dev, dst_dev, n: int, group=None, exchange: str = "nccl"):
@@ -76,6 +109,12 @@ def solve_row_sharded(solver, src_dev, dst_dev, n: int, group=None, exchange: st
 
     if exchange not in EXCHANGE_MODES:
         raise ValueError(f"exchange must be one of {EXCHANGE_MODES}")
+    if exchange == "peer":
+        # tile-sharded tensor-core filter, every word stored into every rank's matrix over NVLink while it is computed
+        # (b2r_solve_sharded, csrc/shard.cu); torch.distributed only carries the 152-byte IPC handles, once per (solver, n)
+        attach_peers(solver, n, group)
+        sol = solver.solve_sharded(src_dev.data_ptr(), dst_dev.data_ptr(), n)
+        return sol, None
     pitch = batch.pitch_words(n)
 
     def rows(b, e, out):

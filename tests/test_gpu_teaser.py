@@ -616,3 +616,35 @@ def test_tensor_core_filter_tile_edges_and_fused_degrees(oracle_mod, n):
     bits = s._adjacency_bits()
     assert np.array_equal(bits, ref)
     assert s.stats()["n_edges"] == int(np.unpackbits(ref.view(np.uint8)).sum()) // 2
+
+
+@pytest.mark.parametrize("n,ratio", [(300, 0.5), (3000, 0.9), (5000, 0.95)])
+def test_tile_sharded_solve_world_of_one(oracle_mod, n, ratio):
+    """b2r_solve_sharded with a world of one rank: the PEERS form of the tensor-core filter (item striding, bit-only fix-up, degrees
+    recomputed from the matrix, READY / DONE flag words) must give exactly the ordinary solve.  Two and more ranks: bench.py config5."""
+    import torch
+    import teaserpp_python as tpp
+    from poseestimator_b200 import batch as b2batch
+    pb = synth.make_problem(n, ratio, seed=31 + n)
+    ref = oracle_mod.solve(pb.src, pb.dst, noise_bound=pb.noise_bound, estimate_scaling=0, rotation_cost_threshold=1e-12)
+    bs = b2batch.BatchSolver(_params(tpp, pb.noise_bound))
+    src = torch.from_numpy(np.ascontiguousarray(pb.src.T)).cuda(); dst = torch.from_numpy(np.ascontiguousarray(pb.dst.T)).cuda()
+    torch.cuda.synchronize()
+    bs.shard_attach(0, 1, [bs.shard_export(n)])
+    for _ in range(3):        # epochs
+        sol = bs.solve_sharded(src.data_ptr(), dst.data_ptr(), n)
+        assert not bs.shard_fell_back()
+        assert np.array_equal(bs.adjacency(0, n), ref.adjacency)
+        assert bs.max_clique(0).tolist() == ref.clique.tolist()
+        assert sol.valid and synth.rotation_error_rad(sol.rotation, ref.rotation) < 1e-5
+        assert np.linalg.norm(sol.translation - ref.translation) < 1e-6 * pb.scene_scale
+    # an ill-conditioned problem (extent / beta beyond the tensor-core filter's gate): every rank falls back to the ordinary path
+    far = synth.make_problem(400, 0.5, seed=5)
+    bs2 = b2batch.BatchSolver(_params(tpp, far.noise_bound * 1e-5))
+    s2 = torch.from_numpy(np.ascontiguousarray(far.src.T)).cuda(); d2 = torch.from_numpy(np.ascontiguousarray(far.dst.T)).cuda()
+    torch.cuda.synchronize()
+    bs2.shard_attach(0, 1, [bs2.shard_export(400)])
+    bs2.solve_sharded(s2.data_ptr(), d2.data_ptr(), 400)
+    assert bs2.shard_fell_back()
+    ref2 = oracle_mod.solve(far.src, far.dst, noise_bound=far.noise_bound * 1e-5, estimate_scaling=0, rotation_cost_threshold=1e-12)
+    assert np.array_equal(bs2.adjacency(0, 400), ref2.adjacency)

@@ -63,6 +63,27 @@ def _worker(rank, world, port, n, seed, q):
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
         ok = ok and sorted(sum(gathered, [])) == list(range(13))
+
+        # peer exchange (b2r_solve_sharded): handles gathered in rank order, attach is all-or-nothing over the ranks
+        class FakeSolver:
+            def __init__(self, fail):
+                self.fail, self.attached = fail, None
+            def shard_export(self, n):
+                return bytes([rank]) * 152
+            def shard_attach(self, r, w, handles):
+                if self.fail:
+                    raise RuntimeError("no peer access")
+                self.attached = (r, w, [h[0] for h in handles])
+        good = FakeSolver(False)
+        sharded.attach_peers(good, n)
+        ok = ok and good.attached == (rank, world, list(range(world))) and good._shard_n == n
+        sharded.attach_peers(good, n)                      # idempotent per (solver, n)
+        half = FakeSolver(rank == 1)                       # one rank cannot attach: EVERY rank must see ExchangeUnavailable
+        try:
+            sharded.attach_peers(half, n)
+            ok = False
+        except sharded.ExchangeUnavailable as e:
+            ok = ok and "rank 1" in str(e) and getattr(half, "_shard_n", None) is None
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()

@@ -264,12 +264,19 @@ def config5_leg(cx: Ctx, solver_params, n: int = 20000):
                 torch.cuda.synchronize()
                 times.append(cx.reduce([(time.perf_counter() - t1) * 1e3])[0])
             W = (n + 31) // 32
-            ok = bool(np.array_equal(s1.adjacency(0, n), full.cpu().numpy().view(np.uint32)[:n, :W])) and \
+            adj_sh = s5.adjacency(0, n) if full is None else full.cpu().numpy().view(np.uint32)[:n, :W]   # peer mode: the matrix lives in the handle
+            ok = bool(np.array_equal(s1.adjacency(0, n), adj_sh)) and \
                 s5.max_clique(0).tolist() == s1.max_clique(0).tolist() and \
                 synth.rotation_error_rad(sol.rotation, ref.rotation) < 1e-9 and bool(np.allclose(sol.translation, ref.translation, atol=1e-12))
             okall, = cx.reduce([1.0 if ok else 0.0], "min")
             assert okall == 1.0, f"config5 ({mode}): the row-sharded solve differs from the single-GPU solve on some rank"
             results[mode] = {"sharded_solve_ms": statistics.median(times), "identical": True}
+            if mode == "peer":
+                results[mode]["fell_back"] = bool(s5.shard_fell_back())
+                results[mode]["how"] = ("each rank runs 1 / world of the tensor-core filter items and stores the words into every rank's matrix over "
+                                        "NVLink as it computes (b2r_solve_sharded); flags with st.release.sys / ld.acquire.sys order the epochs")
+            else:
+                results[mode]["how"] = "fp64 row kernel on the rank's rows, one NCCL all_gather_into_tensor of the bit rows, replicated solve"
         out["sharded"] = results
         out["adjacency_bytes_gathered"] = int(n * b2batch.pitch_words(n) * 4)
     return out
