@@ -529,12 +529,10 @@ b2r_status b2r_solve_batch_async(b2r_solver* s, int batch, const int* n, const d
       if (v >= 1 && v <= 64) nthr = (unsigned)v;
     }
     if ((unsigned)batch < nthr) nthr = (unsigned)batch;
-    if (total * sizeof(double) * 2 < (1u << 20) || nthr <= 1) pack(0, batch);
+    if (total * sizeof(double) * 2 < (1u << 19) || nthr <= 1) pack(0, batch);
     else {
-      std::vector<std::thread> th;
-      for (unsigned t = 1; t < nthr; ++t) th.emplace_back(pack, (int)((size_t)batch * t / nthr), (int)((size_t)batch * (t + 1) / nthr));
-      pack(0, (int)((size_t)batch / nthr));
-      for (auto& x : th) x.join();
+      const int nt = (int)nthr;
+      s->pack_pool.run(nt, [&](int t) { pack((int)((size_t)batch * t / nt), (int)((size_t)batch * (t + 1) / nt)); });   // persistent workers of the handle
     }
     if (s->profiling) CK(cudaEventRecord(s->ev[0], s->stream));   // 'upload' = the H2D copy alone (host packing is host time)
     CK(cudaMemcpyAsync(ds, hs, sizeof(double) * 2 * total, cudaMemcpyHostToDevice, s->stream));

@@ -9,12 +9,25 @@ __device__ __forceinline__ double det3(const double* M) {
 }
 
 // R = V diag(1,1,det(U)det(V)) U^T from the SVD H = U S V^T (one-sided Jacobi on the columns of H).
-__device__ inline void rotation_from_H(const double* H, double* R) {
+// warm (optional, 9 doubles, row-major): an orthogonal start for V -- the V of a previous, similar H (successive GNC iterations);
+// the sweeps then run on H * warm, whose columns are already nearly orthogonal, and converge in one or two instead of five.  The
+// final V is written back.  First call: pass the identity.
+__device__ inline void rotation_from_H(const double* H, double* R, double* warm = nullptr) {
   double a[3][3], v[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  if (warm) {
 #pragma unroll
-  for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 3; ++i)
 #pragma unroll
-    for (int j = 0; j < 3; ++j) a[i][j] = H[3 * i + j];
+      for (int j = 0; j < 3; ++j) {
+        v[i][j] = warm[3 * i + j];
+        a[i][j] = (H[3 * i] * warm[j] + H[3 * i + 1] * warm[3 + j]) + H[3 * i + 2] * warm[6 + j];
+      }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) a[i][j] = H[3 * i + j];
+  }
   for (int sweep = 0; sweep < 40; ++sweep) {
     double off = 0;
 #pragma unroll
@@ -38,6 +51,12 @@ __device__ inline void rotation_from_H(const double* H, double* R) {
       }
     }
     if (off < 1e-16) break;
+  }
+  if (warm) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) warm[3 * i + j] = v[i][j];
   }
   double sv[3];
 #pragma unroll

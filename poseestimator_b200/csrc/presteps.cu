@@ -817,13 +817,17 @@ struct GridDev {
 };
 
 // single thread: grid geometry from the bounds
-__global__ void grid_setup_kernel(const unsigned long long* __restrict__ bounds, int n, int K, double radius, GridDev* __restrict__ g) {
+__global__ void grid_setup_kernel(const unsigned long long* __restrict__ bounds, int n, int K, double radius, GridDev* __restrict__ g, double h_scale) {
   double mn[3], mx[3], L[3];
   for (int a = 0; a < 3; ++a) { mn[a] = ordered_key_inv(bounds[a]); mx[a] = ordered_key_inv(bounds[3 + a]); L[a] = mx[a] - mn[a]; }
   const double A = L[0] * L[1] + L[1] * L[2] + L[0] * L[2];      // surface-like clouds: spacing ~ sqrt(area / n)
   const double Lmax = fmax(L[0], fmax(L[1], L[2]));
   double h;
-  if (A > 0) h = 2.0 * sqrt(A / (double)n) * sqrt((double)K / 3.14159265358979);
+  // sqrt(A / n) sqrt(K / pi) estimates the distance to the K-th neighbour on a surface of the bounding box's area; the shell walk
+  // wants cells of twice that (h_scale = 1).  (A lane-per-query kernel over 3 x 3 x 3 blocks of half-size cells was tried in round 2:
+  // 1.14 ms against 0.85 ms for the outlier-removal stage of the config-2 frame -- the ~10 % of queries whose K-th neighbour lies
+  // outside the block pay more in the shell walk on the finer grid than the others save.)
+  if (A > 0) h = 2.0 * h_scale * sqrt(A / (double)n) * sqrt((double)K / 3.14159265358979);
   else h = Lmax > 0 ? Lmax / 64.0 : 1.0;
   if (radius > 0 && radius < h) h = radius;
   if (!(h > 0) || !(h == h)) h = 1.0;
@@ -853,6 +857,8 @@ __global__ void __launch_bounds__(256) grid_key_kernel(const double* __restrict_
 }
 
 // sorted copies of the points (coalesced shell scans) and the [start, end) range of every occupied cell
+// cell_range is NOT cleared between calls (16 M cells = 128 MB): an entry is valid only if it points into the current sorted array at a
+// point of that very cell (cell_points below); stale or uninitialised entries of cells that are empty now fail that test.
 __global__ void __launch_bounds__(256) grid_ranges_kernel(const double* __restrict__ pts, int n, const unsigned long long* __restrict__ keys,
                                                           const uint32_t* __restrict__ sidx, double* __restrict__ spts, int2* __restrict__ cell_range) {
   const int e = blockIdx.x * 256 + threadIdx.x;
@@ -864,12 +870,20 @@ __global__ void __launch_bounds__(256) grid_ranges_kernel(const double* __restri
   if (e == n - 1 || keys[e + 1] != k) cell_range[k].y = e + 1;
 }
 
+// [start, end) of cell k in the sorted array, empty when the entry is not a current one
+__device__ __forceinline__ int2 cell_points(const int2* __restrict__ cell_range, const unsigned long long* __restrict__ skeys, int n, unsigned long long k) {
+  const int2 cr = cell_range[k];
+  if ((unsigned)cr.x < (unsigned)n && cr.y > cr.x && cr.y <= n && skeys[cr.x] == k) return cr;
+  return make_int2(0, 0);
+}
+
 struct KnnGridSmem { KnnWarpSmem w[kKnnWarps]; };
 
 __global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* __restrict__ spts, const uint32_t* __restrict__ sidx, int n,
                                                                   const GridDev* __restrict__ gp, const int2* __restrict__ cell_range,
                                                                   const double* __restrict__ queries, int nq, int K, double radius,
-                                                                  int* __restrict__ idx_out, double* __restrict__ d2_out, int* __restrict__ cnt_out) {
+                                                                  int* __restrict__ idx_out, double* __restrict__ d2_out, int* __restrict__ cnt_out,
+                                                                  const unsigned long long* __restrict__ skeys) {
   extern __shared__ __align__(16) unsigned char knn_smem[];
   KnnWarpSmem& w = reinterpret_cast<KnnWarpSmem*>(knn_smem)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -907,7 +921,7 @@ __global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* 
           // cells of an x-run are consecutive keys, so their points are one contiguous range of the sorted array
           int b = 0x7fffffff, e = 0;
           for (int x = xlo + lane; x <= xhi; x += 32) {
-            const int2 cr = cell_range[kbase + (unsigned long long)x];
+            const int2 cr = cell_points(cell_range, skeys, n, kbase + (unsigned long long)x);
             if (cr.y > cr.x) { b = min(b, cr.x); e = max(e, cr.y); }
           }
           b = __reduce_min_sync(FULL, b); e = __reduce_max_sync(FULL, e);
@@ -995,9 +1009,8 @@ static int launch_knn_grid(const double* pts, int n, const double* queries, int 
   const int tiles = (n + 255) / 256;
   cudaMemsetAsync(bounds, 0xff, 24, st);
   cudaMemsetAsync(bounds + 3, 0, 24, st);
-  cudaMemsetAsync(cell_range, 0, (size_t)kGridMaxCells * 8, st);
   bounds_kernel<<<tiles < 296 ? tiles : 296, 256, 0, st>>>(pts, n, bounds);
-  grid_setup_kernel<<<1, 1, 0, st>>>(bounds, n, K, radius, g);
+  grid_setup_kernel<<<1, 1, 0, st>>>(bounds, n, K, radius, g, 1.0);
   grid_key_kernel<<<tiles, 256, 0, st>>>(pts, n, g, keys, vals);
   bool in_alt = false;
   int launches = 3 + radix_sort_pairs((uint64_t*)keys, vals, (uint64_t*)keys_alt, vals_alt, table, (size_t)n, 0, 24, st, &in_alt);
@@ -1005,7 +1018,7 @@ static int launch_knn_grid(const double* pts, int n, const double* queries, int 
   const uint32_t* sv = in_alt ? vals_alt : vals;
   grid_ranges_kernel<<<tiles, 256, 0, st>>>(pts, n, sk, sv, spts, cell_range);
   knn_grid_kernel<<<(nq + kKnnWarps - 1) / kKnnWarps, kKnnWarps * 32, knn_grid_smem_bytes(), st>>>(spts, sv, n, g, cell_range, queries, nq, K,
-                                                                                                    radius, idx, d2, cnt);
+                                                                                                    radius, idx, d2, cnt, sk);
   return launches + 2;
 }
 

@@ -71,10 +71,14 @@ __device__ inline double block_max(double v, double* red, int bar) {
 
 // The rotation stage of one registration on threads 0 .. kRtThreads-1 of the CTA (named barrier `bar`).  Returns false when the
 // solution stays invalid (clique <= 1, COMPLETE TIM graph beyond the workspace).
-__device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, int bar, TailMarks tm = TailMarks()) {
+// cache (optional): cache_doubles doubles of shared memory for the pruned TIMs, their weights and residuals (8 T doubles); the GNC loop then
+// never touches global memory (each of its ~10 iterations made two dependent passes over arrays in L2).
+__device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, int bar, TailMarks tm = TailMarks(), double* cache = nullptr,
+                                     size_t cache_doubles = 0) {
   ProbState* st = d.st;
   __shared__ double red[9 * kRtWarps];
   __shared__ double sR[9];
+  __shared__ double sV[9];
   __shared__ int sh_cnt;
   const int tid = threadIdx.x;
   const int C = st->clique_size;
@@ -94,16 +98,22 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
   }
   const int T = (int)Tll;
   const double* src = d.src; const double* dst = d.dst;
+  // where the TIMs live during the GNC loop: shared memory when the caller has room for 8 T doubles, else the global workspace
+  const bool cached = cache != nullptr && (size_t)8 * (size_t)T <= cache_doubles;
+  double* timx = cached ? cache : d.timx;
+  double* timy = cached ? cache + 3 * (size_t)T : d.timy;
+  double* wts = cached ? cache + 6 * (size_t)T : d.weights;
+  if (tid < 9) sV[tid] = (tid % 4 == 0) ? 1.0 : 0.0;
   // A.6-1 pruned TIMs
   if (kp.tim_graph == B2R_TIM_CHAIN) {
     for (int i = tid; i < T; i += kRtThreads) {
       const int root = d.clique[i], leaf = d.clique[(i + 1 == C) ? 0 : i + 1];
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
-        d.timx[3 * (size_t)i + k] = src[3 * (size_t)leaf + k] - src[3 * (size_t)root + k];
-        d.timy[3 * (size_t)i + k] = (dst[3 * (size_t)leaf + k] - dst[3 * (size_t)root + k]) * inv_s;
+        timx[3 * (size_t)i + k] = src[3 * (size_t)leaf + k] - src[3 * (size_t)root + k];
+        timy[3 * (size_t)i + k] = (dst[3 * (size_t)leaf + k] - dst[3 * (size_t)root + k]) * inv_s;
       }
-      d.weights[i] = 1.0;
+      wts[i] = 1.0;
     }
   } else {
     for (int i = tid; i < C - 1; i += kRtThreads) {
@@ -113,10 +123,10 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
         const int b = d.clique[j];
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
-          d.timx[3 * k + q] = src[3 * (size_t)b + q] - src[3 * (size_t)a + q];
-          d.timy[3 * k + q] = (dst[3 * (size_t)b + q] - dst[3 * (size_t)a + q]) * inv_s;
+          timx[3 * k + q] = src[3 * (size_t)b + q] - src[3 * (size_t)a + q];
+          timy[3 * k + q] = (dst[3 * (size_t)b + q] - dst[3 * (size_t)a + q]) * inv_s;
         }
-        d.weights[k] = 1.0;
+        wts[k] = 1.0;
       }
     }
   }
@@ -128,27 +138,27 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
   double nb2 = nb * nb;
   if (nb2 < 1e-16) nb2 = 1e-2;
   double mu = 1.0, prev_cost = CUDART_INF, cost = 0.0;
-  double* r2buf = d.raw;  // scratch: T doubles
+  double* r2buf = cached ? cache + 7 * (size_t)T : d.raw;  // scratch: T doubles
   int iters = 0;
   for (int it = 0; it < kp.max_iterations; ++it) {
     double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     for (int i = tid; i < T; i += kRtThreads) {
-      const double w = d.weights[i];
-      const double x0 = d.timx[3 * (size_t)i], x1 = d.timx[3 * (size_t)i + 1], x2 = d.timx[3 * (size_t)i + 2];
-      const double y0 = d.timy[3 * (size_t)i], y1 = d.timy[3 * (size_t)i + 1], y2 = d.timy[3 * (size_t)i + 2];
+      const double w = wts[i];
+      const double x0 = timx[3 * (size_t)i], x1 = timx[3 * (size_t)i + 1], x2 = timx[3 * (size_t)i + 2];
+      const double y0 = timy[3 * (size_t)i], y1 = timy[3 * (size_t)i + 1], y2 = timy[3 * (size_t)i + 2];
       h[0] += w * x0 * y0; h[1] += w * x0 * y1; h[2] += w * x0 * y2;
       h[3] += w * x1 * y0; h[4] += w * x1 * y1; h[5] += w * x1 * y2;
       h[6] += w * x2 * y0; h[7] += w * x2 * y1; h[8] += w * x2 * y2;
     }
     block_sum<9>(h, red, bar);
-    if (tid == 0) rotation_from_H(h, sR);
+    if (tid == 0) rotation_from_H(h, sR, sV);
     grp_sync(bar);
     double maxr = 0.0;
     for (int i = tid; i < T; i += kRtThreads) {
-      const double x0 = d.timx[3 * (size_t)i], x1 = d.timx[3 * (size_t)i + 1], x2 = d.timx[3 * (size_t)i + 2];
-      const double e0 = d.timy[3 * (size_t)i] - ((sR[0] * x0 + sR[1] * x1) + sR[2] * x2);
-      const double e1 = d.timy[3 * (size_t)i + 1] - ((sR[3] * x0 + sR[4] * x1) + sR[5] * x2);
-      const double e2 = d.timy[3 * (size_t)i + 2] - ((sR[6] * x0 + sR[7] * x1) + sR[8] * x2);
+      const double x0 = timx[3 * (size_t)i], x1 = timx[3 * (size_t)i + 1], x2 = timx[3 * (size_t)i + 2];
+      const double e0 = timy[3 * (size_t)i] - ((sR[0] * x0 + sR[1] * x1) + sR[2] * x2);
+      const double e1 = timy[3 * (size_t)i + 1] - ((sR[3] * x0 + sR[4] * x1) + sR[5] * x2);
+      const double e2 = timy[3 * (size_t)i + 2] - ((sR[6] * x0 + sR[7] * x1) + sR[8] * x2);
       const double r2 = (e0 * e0 + e1 * e1) + e2 * e2;
       r2buf[i] = r2;
       maxr = fmax(maxr, r2);
@@ -162,12 +172,12 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
     double cs[1] = {0.0};
     for (int i = tid; i < T; i += kRtThreads) {
       const double r2 = r2buf[i];
-      double w = d.weights[i];
+      double w = wts[i];
       cs[0] += w * r2;  // cost uses the weights of the previous iteration (A.6-3d)
       if (r2 >= th1) w = 0.0;
       else if (r2 <= th2) w = 1.0;
       else w = sqrt(nb2 * mu * (mu + 1.0) / r2) - mu;
-      d.weights[i] = w;
+      wts[i] = w;
     }
     block_sum<1>(cs, red, bar);
     cost = cs[0];
@@ -178,6 +188,10 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
     if (cost_diff < kp.cost_threshold) break;
   }
   grp_sync(bar);
+  if (cached) {
+    for (int i = tid; i < T; i += kRtThreads) d.weights[i] = wts[i];   // getters (b2r_get_gnc_weights) and the inlier list read the global copy
+    grp_sync(bar);
+  }
   tm.mark(29);   // GNC done
   // rotation inliers (w >= 0.5), ascending positions
   if (tid == 0) sh_cnt = 0;
@@ -351,6 +365,65 @@ __device__ __forceinline__ void grp_exclusive_scan(double (&v)[K], double* sm, i
   grp_sync(bar);
 }
 
+// Constant range: all intervals have the same half-width r, so the entry endpoints fl(X - r) and the exit endpoints fl(X + r) are
+// each ordered like X itself.  Sort the M values ONCE by (X, index) -- half the keys, 2.4x fewer compare-exchanges than sorting the
+// 2 M endpoints -- and merge the two ordered sequences by rank: an entry goes to i + #{exits < it}, an exit to j + #{entries <= it}
+// (entries before exits at equal values, as ep_less orders them).  Two different X may round to the same endpoint value, where the
+// reference orders by index, not by X: such a pair (and any NaN) makes the shortcut decline and the full sort runs instead.
+// On success id[0 .. 2 M) holds the endpoint ids in exactly the order bitonic_sort_regs leaves; val is scratch.
+__device__ inline bool sort_endpoints_const_range(const double* X, int M, double r, double* val, int* id, double* sm, int tid, int bar) {
+  int Mpad = kRtThreads;
+  while (Mpad < M) Mpad <<= 1;
+  grp_sync(bar);
+  for (int i = tid; i < Mpad; i += kRtThreads) {
+    if (i < M) { val[i] = X[i]; id[i] = i + 1; }
+    else { val[i] = CUDART_INF; id[i] = 0x7fffffff; }
+  }
+  if (Mpad == kRtThreads) bitonic_sort_regs<1>(val, id, tid, bar);
+  else if (Mpad == 2 * kRtThreads) bitonic_sort_regs<2>(val, id, tid, bar);
+  else bitonic_sort_regs<4>(val, id, tid, bar);
+  // sorted by (X, index): val[i], id[i] = index + 1.  Check the two endpoint sequences, then rank.
+  int bad = 0;
+  for (int i = tid; i < M; i += kRtThreads) {
+    const double x = val[i];
+    if (x != x) bad = 1;
+    if (i + 1 < M) {
+      const double y = val[i + 1];
+      if (x != y && id[i] > id[i + 1] && ((x - r) == (y - r) || (x + r) == (y + r))) bad = 1;
+    }
+  }
+  int* flag = reinterpret_cast<int*>(sm);
+  if (tid == 0) *flag = 0;
+  grp_sync(bar);
+  if (bad) *flag = 1;
+  grp_sync(bar);
+  const bool declined = *flag != 0;
+  grp_sync(bar);
+  if (declined) return false;
+  int pe[4], px[4], ix[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int i = tid + kRtThreads * q;
+    pe[q] = px[q] = -1; ix[q] = 0;
+    if (i < M) {
+      const double a = val[i] - r, b = val[i] + r;
+      ix[q] = id[i];
+      int lo = 0, hi = M;                       // #{j : fl(X_j + r) < a}
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (val[mid] + r < a) lo = mid + 1; else hi = mid; }
+      pe[q] = i + lo;
+      lo = 0; hi = M;                           // #{k : fl(X_k - r) <= b}
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (val[mid] - r <= b) lo = mid + 1; else hi = mid; }
+      px[q] = i + lo;
+    }
+  }
+  grp_sync(bar);
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+    if (pe[q] >= 0) { id[pe[q]] = ix[q]; id[px[q]] = -ix[q]; }
+  grp_sync(bar);
+  return true;
+}
+
 // One TLS estimate over X[0..M) with a constant range r.  Returns the estimate in every thread of the group.
 __device__ inline double tls_estimate_const_range(const double* X, int M, double r, double* val, int* id, double* sm /*3*kRtThreads*/, int tid, int bar, bool fast,
                                                   TailMarks tm = TailMarks()) {
@@ -365,7 +438,19 @@ __device__ inline double tls_estimate_const_range(const double* X, int M, double
     } else { val[e] = CUDART_INF; id[e] = 0x7fffffff; }
   }
   tm.mark(21);   // endpoints written
-  if (fast && Epad == kRtThreads) bitonic_sort_regs<1>(val, id, tid, bar);
+  bool sorted_fast = false;
+  if (fast && M <= 4 * kRtThreads) sorted_fast = sort_endpoints_const_range(X, M, r, val, id, sm, tid, bar);
+  if (!sorted_fast && fast && M <= 4 * kRtThreads) {   // the shortcut declined (it used val / id as scratch): write the endpoints again
+    for (int e = tid; e < Epad; e += kRtThreads) {
+      if (e < E) {
+        const int i = e >> 1;
+        if (e & 1) { val[e] = X[i] + r; id[e] = -(i + 1); }
+        else { val[e] = X[i] - r; id[e] = i + 1; }
+      } else { val[e] = CUDART_INF; id[e] = 0x7fffffff; }
+    }
+  }
+  if (sorted_fast) { /* id[] holds the 2 M endpoint ids in the reference's order */ }
+  else if (fast && Epad == kRtThreads) bitonic_sort_regs<1>(val, id, tid, bar);
   else if (fast && Epad == 2 * kRtThreads) bitonic_sort_regs<2>(val, id, tid, bar);
   else if (fast && Epad == 4 * kRtThreads) bitonic_sort_regs<4>(val, id, tid, bar);
   else if (fast && Epad == 8 * kRtThreads) bitonic_sort_regs<8>(val, id, tid, bar);

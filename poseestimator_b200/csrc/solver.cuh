@@ -2,7 +2,12 @@
 #pragma once
 #include <stdlib.h>
 
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: a no-op function-pointer test unless a profiler is attached
@@ -64,7 +69,69 @@ struct HostBuf {
 
 }  // namespace b2r
 
+// Worker threads of a handle for the host-side staging copy (on_device = 0): created once, woken per batch.  Spawning and joining
+// std::threads per call cost more than the copy of a small batch (config 4: 3 MB per frame).
+class PackPool {
+ public:
+  ~PackPool() { stop(); }
+  // run fn(t) for t in [0, nthreads) -- t = 0 on the calling thread -- and return when all are done
+  void run(int nthreads, const std::function<void(int)>& fn) {
+    if (nthreads <= 1) { fn(0); return; }
+    ensure(nthreads - 1);
+    {
+      std::lock_guard<std::mutex> lk(m_);
+      job_ = &fn; active_ = nthreads - 1; pending_ = nthreads - 1; ++gen_;
+    }
+    cv_.notify_all();
+    fn(0);
+    std::unique_lock<std::mutex> lk(m_);
+    done_.wait(lk, [&] { return pending_ == 0; });
+    job_ = nullptr;
+  }
+  void stop() {
+    { std::lock_guard<std::mutex> lk(m_); quit_ = true; ++gen_; }
+    cv_.notify_all();
+    for (auto& t : th_) t.join();
+    th_.clear();
+    quit_ = false;
+  }
+
+ private:
+  void ensure(int workers) {
+    while ((int)th_.size() < workers) {
+      const int id = (int)th_.size() + 1;
+      unsigned long long seen;
+      { std::lock_guard<std::mutex> lk(m_); seen = gen_; }
+      th_.emplace_back([this, id, seen]() mutable {
+        for (;;) {
+          const std::function<void(int)>* job = nullptr;
+          {
+            std::unique_lock<std::mutex> lk(m_);
+            cv_.wait(lk, [&] { return gen_ != seen; });
+            seen = gen_;
+            if (quit_) return;
+            if (id <= active_) job = job_;
+          }
+          if (job) {
+            (*job)(id);
+            std::lock_guard<std::mutex> lk(m_);
+            if (--pending_ == 0) done_.notify_one();
+          }
+        }
+      });
+    }
+  }
+  std::mutex m_;
+  std::condition_variable cv_, done_;
+  std::vector<std::thread> th_;
+  const std::function<void(int)>* job_ = nullptr;
+  unsigned long long gen_ = 0;
+  int active_ = 0, pending_ = 0;
+  bool quit_ = false;
+};
+
 struct b2r_solver {
+  PackPool pack_pool;
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = false;

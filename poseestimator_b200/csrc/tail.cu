@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
   stamp(4);
 
   // ---- 6. rotation on the first thread group, then the three translation axes on all three ----
-  if (tid < kRtThreads) rotation_body(d, kp, 4, tm);
+  if (tid < kRtThreads) rotation_body(d, kp, 4, tm, reinterpret_cast<double*>(tsm), (size_t)dyn_smem_bytes / sizeof(double));
   __syncthreads();
   stamp(5);
   translation_body(d, kp, reinterpret_cast<double*>(tsm), tm);
