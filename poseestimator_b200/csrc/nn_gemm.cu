@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double*
                                                                    int dim, const float* __restrict__ norm_q, const float* __restrict__ norm_r,
                                                                    const float* __restrict__ norm_r_lo, const float* __restrict__ cand_v,
                                                                    const int* __restrict__ cand_j, int groups, int* __restrict__ nn,
-                                                                   double* __restrict__ dist, unsigned int* __restrict__ n_fallback,
+                                                                   double* __restrict__ dist, unsigned int* __restrict__ fb_count, int* __restrict__ fb_list,
                                                                    unsigned int* __restrict__ err_max) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * kFinWarps + warp;
@@ -375,13 +375,9 @@ __global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double*
       if (lane == 0) atomicMax(err_max, __float_as_uint(worst));
     }
   }
-  if (!complete) {  // warp-uniform: exact brute force over every reference
-    if (lane == 0) atomicAdd(n_fallback, 1u);
-    best = CUDART_INF; bj = -1;
-    for (int j = lane; j < nr; j += 32) {
-      const double d = exact_d2(fq + (size_t)i * dim, fr + (size_t)j * dim, dim);
-      if (d < best || (d == best && (unsigned)j < (unsigned)bj)) { best = d; bj = j; }
-    }
+  if (!complete) {  // warp-uniform: the row goes to nn_fallback_kernel (exact search over every reference, reference tiles shared by 8 rows)
+    if (lane == 0) fb_list[atomicAdd(fb_count, 1u)] = i;
+    return;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -389,6 +385,52 @@ __global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double*
     if (od < best || (od == best && (unsigned)oj < (unsigned)bj)) { best = od; bj = oj; }
   }
   if (lane == 0) { nn[i] = bj; if (dist) dist[i] = best; }
+}
+
+// Rows whose shortlist could not be proven complete: exact fp64 search over EVERY reference.  Eight rows per CTA (one per warp) share
+// each 64-reference tile through shared memory, so a reference row is read from L2 once per eight rows instead of once per row
+// (the in-warp loop this replaces moved 264 B x references x rows through L2: 0.3 ms for the ~800 near-tie rows of a config-2 frame).
+constexpr int kFbRows = 8, kFbTile = 64, kFbDim = 41;   // kFbDim: row stride in doubles (odd, >= kKSeg + 1: conflict-free columns)
+
+__global__ void __launch_bounds__(kFbRows * 32) nn_fallback_kernel(const double* __restrict__ fq, const double* __restrict__ fr, int nr, int dim,
+                                                                   const int* __restrict__ fb_list, const unsigned int* __restrict__ fb_count,
+                                                                   int* __restrict__ nn, double* __restrict__ dist, unsigned int* __restrict__ n_fallback) {
+  __shared__ double tile[kFbTile * kFbDim];
+  __shared__ double qv[kFbRows][kFbDim];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned int count = *fb_count;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && n_fallback) atomicAdd(n_fallback, count);
+  for (unsigned int g0 = blockIdx.x * kFbRows; g0 < count; g0 += gridDim.x * kFbRows) {
+    const unsigned int slot = g0 + warp;
+    const int i = slot < count ? fb_list[slot] : -1;
+    __syncthreads();
+    if (i >= 0) for (int t = lane; t < dim; t += 32) qv[warp][t] = fq[(size_t)i * dim + t];
+    double best = CUDART_INF; int bj = -1;
+    for (int j0 = 0; j0 < nr; j0 += kFbTile) {
+      __syncthreads();
+      const int rows = min(kFbTile, nr - j0);
+      for (int e = threadIdx.x; e < rows * dim; e += kFbRows * 32) tile[(e / dim) * kFbDim + e % dim] = fr[(size_t)j0 * dim + e];
+      __syncthreads();
+      if (i >= 0) {
+#pragma unroll
+        for (int h = 0; h < kFbTile / 32; ++h) {
+          const int jl = lane + 32 * h;
+          if (jl < rows) {
+            double sacc = 0;
+            for (int t = 0; t < dim; ++t) { const double dd = __dsub_rn(qv[warp][t], tile[jl * kFbDim + t]); sacc = __dadd_rn(sacc, __dmul_rn(dd, dd)); }
+            const int j = j0 + jl;
+            if (sacc < best || (sacc == best && (unsigned)j < (unsigned)bj)) { best = sacc; bj = j; }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double od = __shfl_xor_sync(0xffffffffu, best, o); const int oj = __shfl_xor_sync(0xffffffffu, bj, o);
+      if (od < best || (od == best && (unsigned)oj < (unsigned)bj)) { best = od; bj = oj; }
+    }
+    if (i >= 0 && lane == 0) { nn[i] = bj; if (dist) dist[i] = best; }
+  }
 }
 
 }  // namespace
@@ -470,7 +512,7 @@ int choose_splits(int row_tiles, int col_tiles) {
 size_t cand_bytes(int nq, int nr) {
   const int rt = (nq + kBM - 1) / kBM, ct = (nr + kBN - 1) / kBN;
   const int s = choose_splits(rt, ct);
-  return 2 * pad256((size_t)rt * kBM * 2 * s * kTopK * 4) + 256;
+  return 2 * pad256((size_t)rt * kBM * 2 * s * kTopK * 4) + pad256((size_t)rt * kBM * 4) + 512;
 }
 
 b2r_status launch_centre(b2r_solver* s, const double* f_ref, int n_ref, int dim, double* centre) {
@@ -496,13 +538,19 @@ b2r_status launch_direction(b2r_solver* s, const double* fq, const Prepped& q, c
   const int splits = choose_splits(rt, ct);
   float* cand_v = (float*)scratch;
   int* cand_j = (int*)(scratch + pad256((size_t)rt * kBM * 2 * splits * kTopK * 4));
+  int* fb_list = (int*)(scratch + 2 * pad256((size_t)rt * kBM * 2 * splits * kTopK * 4));
+  unsigned int* fb_count = (unsigned int*)((char*)fb_list + pad256((size_t)rt * kBM * 4));
+  CK(cudaMemsetAsync(fb_count, 0, 4, s->stream));
   CUtensorMap mq, mr;
   if (!make_operand_map(&mq, q.l, q.n_pad) || !make_operand_map(&mr, r.r, r.n_pad))
     return fail(s, B2R_ERR_CUDA, "cuTensorMapEncodeTiled failed (driver entry point missing or bad operand buffer)");
   nn_gemm_kernel<<<dim3(rt, splits), kGemmThreads, smem, s->stream>>>(mq, mr, r.norm_lo, r.n, ct, splits, cand_v, cand_j);
   nn_finish_kernel<<<(q.n + kFinWarps - 1) / kFinWarps, kFinWarps * 32, 0, s->stream>>>(fq, q.n, fr, r.n, dim, q.norm, r.norm, r.norm_lo,
-                                                                                        cand_v, cand_j, 2 * splits, nn, dist, n_fallback, err_max);
-  s->launches += 2;
+                                                                                        cand_v, cand_j, 2 * splits, nn, dist, fb_count, fb_list, err_max);
+  int fb_ctas = (q.n + kFbRows - 1) / kFbRows;
+  if (fb_ctas > 148 * 4) fb_ctas = 148 * 4;
+  nn_fallback_kernel<<<fb_ctas, kFbRows * 32, 0, s->stream>>>(fq, fr, r.n, dim, fb_list, fb_count, nn, dist, n_fallback);
+  s->launches += 3;
   CK(cudaGetLastError());
   return B2R_OK;
 }
