@@ -980,6 +980,7 @@ size_t knn_grid_ws_bytes(int n) {
 // ------------------------------------------------------------------------------------------------------------------
 // launchers used by the C ABI below
 // ------------------------------------------------------------------------------------------------------------------
+constexpr double kKnnHScale = 0.7;       // cell size relative to twice the estimated K-th neighbour distance (B2R_KNN_HSCALE overrides: A/B runs)
 constexpr int kKnnGridMinPoints = 4096;  // below this the brute-force kernel is faster than building a grid
 
 static int launch_knn_brute(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
@@ -1010,7 +1011,8 @@ static int launch_knn_grid(const double* pts, int n, const double* queries, int 
   cudaMemsetAsync(bounds, 0xff, 24, st);
   cudaMemsetAsync(bounds + 3, 0, 24, st);
   bounds_kernel<<<tiles < 296 ? tiles : 296, 256, 0, st>>>(pts, n, bounds);
-  grid_setup_kernel<<<1, 1, 0, st>>>(bounds, n, K, radius, g, 1.0);
+  static const double h_scale = [] { const char* e = getenv("B2R_KNN_HSCALE"); const double v = e ? atof(e) : 0.0; return v > 0.05 && v < 10 ? v : kKnnHScale; }();
+  grid_setup_kernel<<<1, 1, 0, st>>>(bounds, n, K, radius, g, h_scale);
   grid_key_kernel<<<tiles, 256, 0, st>>>(pts, n, g, keys, vals);
   bool in_alt = false;
   int launches = 3 + radix_sort_pairs((uint64_t*)keys, vals, (uint64_t*)keys_alt, vals_alt, table, (size_t)n, 0, 24, st, &in_alt);
