@@ -1,19 +1,31 @@
 #!/bin/bash
 # Round-end evidence in one gpurun call: tools/final_pass.sh <scratch dir under gpurun_out/>
-# GPU tests, bench (both arms), the ncu launch list of the bench command and one --set full capture of the graph kernel.
-# Every step under its own timeout; a number printed by a run under ncu is never a bench value.
+# GPU tests, bench (both arms), the ncu launch list of the bench command, --set full captures of the graph kernel, the fused tail and
+# the pre-step kernels, the measured tensor-core error logs.  Every step under its own timeout; a number printed by a run under ncu
+# is never a bench value.
 D=gpurun_out/$1
 mkdir -p $D
-timeout 900 python -m pytest tests -m gpu -x -q > $D/pytest_gpu.log 2>&1; tail -2 $D/pytest_gpu.log
+timeout 1200 python -m pytest tests -m gpu -x -q > $D/pytest_gpu.log 2>&1; tail -2 $D/pytest_gpu.log
+timeout 600 python -m pytest tests/test_gpu_tc_sweep.py tests/test_gpu_presteps.py -m gpu -q -s -k "sweep or error_bound or fallback_rate" 2>&1 | grep -E "accumulation error|measured error|passed|failed" > $D/tc_error_measured.log; tail -1 $D/tc_error_measured.log
 timeout 300 python -c 'import __graft_entry__ as g; g.smoke(); print("smoke ok")' > $D/smoke.log 2>&1; tail -1 $D/smoke.log
-timeout 600 python bench.py > $D/bench.json 2> $D/bench.err || tail -5 $D/bench.err
-timeout 600 python bench.py --impl reference > $D/bench_ref.json 2> $D/bench_ref.err || tail -5 $D/bench_ref.err
-timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/bench_short.json 2> $D/bench_short.err && \
+timeout 900 python bench.py > $D/bench.json 2> $D/bench.err || tail -5 $D/bench.err
+timeout 600 python bench.py --impl reference --steps 10 > $D/bench_ref.json 2> $D/bench_ref.err || tail -5 $D/bench_ref.err
+timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-legs --min-device-ms 0 > $D/bench_short.json 2> $D/bench_short.err && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $D/launches.csv \
-    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/ncu_list.log 2>&1
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-legs --min-device-ms 0 > $D/ncu_list.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:tim_graph6 -s 3 -c 1 -o $D/graph6_full -f \
-    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $D/ncu_full.log 2>&1
-ls -la $D | tail -12
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-legs --min-device-ms 0 > $D/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:tail_kernel -s 3 -c 1 -o $D/tail_full -f \
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-legs --min-device-ms 0 > $D/ncu_tail.log 2>&1
+timeout 600 python tools/prestep_roofline.py > $D/prestep_roofline.json 2> $D/prestep_roofline.err
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $D/prestep_launches.csv python tools/prestep_roofline.py quick > $D/ncu_prestep_list.log 2>&1
+for k in nn_gemm_kernel knn_grid_kernel fpfh_kernel backproject_kernel spfh_kernel; do
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -o $D/$k -f python tools/prestep_roofline.py quick > $D/ncu_$k.log 2>&1
+done
+timeout 300 python tools/pipeline_times.py > $D/config2_stage_times.json 2>/dev/null
+timeout 300 python tools/config4_times.py > $D/config4_times.json 2>/dev/null
+timeout 300 python tools/tail_marks.py > $D/tail_marks.log 2>/dev/null
+ls -la $D | tail -30
 python - <<PY
 import json
 j = json.loads(open("$D/bench.json").read().strip().splitlines()[-1])
