@@ -672,6 +672,7 @@ __global__ void __launch_bounds__(kFpWarps * 32) spfh_kernel(const double* __res
 __global__ void __launch_bounds__(kFpWarps * 32) fpfh_kernel(const double* __restrict__ spfh_t, int n, const int* __restrict__ idx,
                                                              const double* __restrict__ d2, const int* __restrict__ cnt, int K,
                                                              double* __restrict__ out /*[33][n]*/) {
+  __shared__ double sv[kFpWarps][34];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * kFpWarps + warp;
   if (i >= n) return;
@@ -679,22 +680,33 @@ __global__ void __launch_bounds__(kFpWarps * 32) fpfh_kernel(const double* __res
   double acc = 0.0, acc32 = 0.0;  // bin `lane`; lane 31 also owns bin 32
   double gsum = 0.0;              // lanes 0..2: group sums
   if (c > 1) {
+    // the next neighbour's SPFH row is fetched while the current one is accumulated (two dependent loads per neighbour otherwise)
+    int jn = idx[(size_t)i * K + 1];
+    double dn = d2[(size_t)i * K + 1];
+    double rown = spfh_t[(size_t)jn * 33 + lane], row32n = lane == 31 ? spfh_t[(size_t)jn * 33 + 32] : 0.0;
     for (int t = 1; t < c; ++t) {
-      const double dist = d2[(size_t)i * K + t];
+      const double dist = dn, row = rown, row32 = row32n;
+      if (t + 1 < c) {
+        jn = idx[(size_t)i * K + t + 1];
+        dn = d2[(size_t)i * K + t + 1];
+        rown = spfh_t[(size_t)jn * 33 + lane];
+        if (lane == 31) row32n = spfh_t[(size_t)jn * 33 + 32];
+      }
       if (dist == 0.0) continue;  // warp-uniform
-      const int j = idx[(size_t)i * K + t];
-      const double v = __ddiv_rn(spfh_t[(size_t)j * 33 + lane], dist);
-      const double v32 = lane == 31 ? __ddiv_rn(spfh_t[(size_t)j * 33 + 32], dist) : 0.0;
+      const double v = __ddiv_rn(row, dist);
+      const double v32 = lane == 31 ? __ddiv_rn(row32, dist) : 0.0;
       acc = __dadd_rn(acc, v);
       acc32 = __dadd_rn(acc32, v32);
-      // group g (lane g < 3) adds its 11 bins in bin order: bins 11g .. 11g+10
+      // group g (lane g < 3) adds its 11 bins in bin order: bins 11g .. 11g+10.  Through shared memory: one store per lane and eleven
+      // broadcast-free loads for three lanes instead of 44 shuffles per neighbour (the kernel is bound by instruction issue)
+      sv[warp][lane] = v;
+      if (lane == 31) sv[warp][32] = v32;
+      __syncwarp();
+      if (lane < 3) {
 #pragma unroll
-      for (int k = 0; k < 11; ++k) {
-        const int srcb = 11 * (lane < 3 ? lane : 0) + k;       // bin index wanted by this lane
-        const double a = __shfl_sync(FULL, v, srcb < 32 ? srcb : 31);
-        const double b32 = __shfl_sync(FULL, v32, 31);
-        if (lane < 3) gsum = __dadd_rn(gsum, srcb == 32 ? b32 : a);
+        for (int k = 0; k < 11; ++k) gsum = __dadd_rn(gsum, sv[warp][11 * lane + k]);
       }
+      __syncwarp();
     }
   }
   // scale by 100 / group sum, add the point's own SPFH

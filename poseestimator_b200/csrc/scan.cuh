@@ -20,7 +20,9 @@ __device__ __forceinline__ int take_ticket(unsigned long long* ws, int* s_tile) 
   return *s_tile;
 }
 
-// thread 0 only: publish this tile's aggregate, return the exclusive prefix of the tile
+// thread 0 only: publish this tile's aggregate, return the exclusive prefix of the tile.  (A warp-wide look-back, 32 predecessors per
+// step, was measured in round 2: the 4096 x 4096 back-projection went from 0.286 to 0.329 ms -- the nearest predecessor usually holds
+// its inclusive prefix already, so the single-thread walk reads one or two words where the warp reads 32.)
 __device__ unsigned long long lookback(unsigned long long* ws, int tile, unsigned long long aggregate) {
   volatile unsigned long long* status = ws + 1;
   if (tile == 0) { status[0] = (2ull << 62) | aggregate; return 0; }
