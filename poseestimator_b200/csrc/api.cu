@@ -237,10 +237,15 @@ b2r_status enqueue_pipeline(b2r_solver* s, int batch, int n_max, bool skip_graph
   if (s->kp.estimate_scaling) {  // A.4-5: the scale vote comes first; the graph is its inlier mask
     B2R_NVTX("b2r:scale_vote");
     if (prof) CK(cudaEventRecord(s->ev[10], st));
-    CK(s->d_scale.ensure(scale_workspace_bytes(n_max)));
-    const ProbDesc* hd = (const ProbDesc*)s->h_desc.p;
-    for (int b = 0; b < batch; ++b)
-      s->launches += launch_scale_estimate(hd[b].src, hd[b].dst, hd[b].n, s->kp.beta, hd[b].st, s->d_scale.p, st);
+    // all problems of a chunk in one set of launches; the chunk is what fits a 24 GB scratch (N = 5000: 0.8 GB per problem)
+    const size_t per = scale_workspace_bytes(n_max);
+    int chunk = (int)(((size_t)24 << 30) / per);
+    if (chunk < 1) chunk = 1;
+    if (chunk > batch) chunk = batch;
+    if (chunk > scale_max_chunk()) chunk = scale_max_chunk();
+    CK(s->d_scale.ensure((size_t)chunk * per));
+    for (int b0 = 0; b0 < batch; b0 += chunk)
+      s->launches += launch_scale_estimate_batch(dd + b0, (batch - b0) < chunk ? (batch - b0) : chunk, n_max, s->kp.beta, s->d_scale.p, st);
     if (prof) CK(cudaEventRecord(s->ev[11], st));
   }
   const bool fused = fused_tail_enabled(s);

@@ -177,8 +177,13 @@ size_t radix_table_words(size_t n);
 int radix_sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt, uint32_t* table, size_t n,
                      int begin_bit, int end_bit, cudaStream_t st, bool* in_alt);
 // scale.cu: adaptive-voting scale estimate of one problem into st->scale
+int radix_sort_pairs_batched(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt, uint32_t* table, size_t n,
+                             const unsigned long long* n_arr, size_t key_stride, size_t val_stride, size_t table_stride, int batch, int begin_bit,
+                             int end_bit, cudaStream_t st, bool* in_alt);
 size_t scale_workspace_bytes(int n);
-int launch_scale_estimate(const double* src, const double* dst, int n, double beta, ProbState* st, void* ws, cudaStream_t stream);
+// batch <= scale_max_chunk() problems per call; ws: batch * scale_workspace_bytes(n_max) bytes
+int scale_max_chunk();
+int launch_scale_estimate_batch(const ProbDesc* dd, int batch, int n_max, double beta, void* ws, cudaStream_t stream);
 
 constexpr int kBnbWarpsPerBlock = 8;
 constexpr int kCanonWarps = 8;

@@ -21,8 +21,13 @@ constexpr int kRxWarps = kRxThreads / 32;
 constexpr int kRxItems = 16;
 constexpr int kRxTile = kRxThreads * kRxItems;  // 4096 items per CTA
 
+// Batched form of every kernel: blockIdx.y = segment (one sort per problem), segment s has n_arr[s] items at offset s * seg_stride of
+// the key / payload arrays and its own table at s * table_stride; n_arr == nullptr: one segment of n items.
+struct RxBatch { const unsigned long long* n_arr; size_t key_stride, val_stride, table_stride; };   // strides in items / words
+
 __global__ void __launch_bounds__(kRxThreads) radix_hist_kernel(const uint64_t* __restrict__ keys, size_t n, int shift,
-                                                                uint32_t* __restrict__ table, int n_tiles) {
+                                                                uint32_t* __restrict__ table, int n_tiles, RxBatch rb) {
+  if (rb.n_arr) { n = (size_t)rb.n_arr[blockIdx.y]; keys += blockIdx.y * rb.key_stride; table += blockIdx.y * rb.table_stride; }
   __shared__ uint32_t h[256];
   h[threadIdx.x] = 0;
   __syncthreads();
@@ -42,7 +47,8 @@ __global__ void __launch_bounds__(kRxThreads) radix_hist_kernel(const uint64_t* 
 
 // one CTA per digit: sum of its table row
 __global__ void __launch_bounds__(256) radix_rowsum_kernel(const uint32_t* __restrict__ table, int n_tiles,
-                                                           unsigned long long* __restrict__ totals) {
+                                                           unsigned long long* __restrict__ totals, RxBatch rb) {
+  if (rb.n_arr) { table += blockIdx.y * rb.table_stride; totals = reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(totals) + blockIdx.y * rb.table_stride); }
   __shared__ unsigned long long red[8];
   const uint32_t* row = table + (size_t)blockIdx.x * n_tiles;
   unsigned long long s = 0;
@@ -61,7 +67,8 @@ __global__ void __launch_bounds__(256) radix_rowsum_kernel(const uint32_t* __res
 // one CTA per digit: base = sum of the totals of smaller digits; exclusive scan of the row in place.
 // Offsets fit 32 bits (n < 2^32).
 __global__ void __launch_bounds__(256) radix_rowscan_kernel(uint32_t* __restrict__ table, int n_tiles,
-                                                            const unsigned long long* __restrict__ totals) {
+                                                            const unsigned long long* __restrict__ totals, RxBatch rb) {
+  if (rb.n_arr) { table += blockIdx.y * rb.table_stride; totals = reinterpret_cast<const unsigned long long*>(reinterpret_cast<const uint32_t*>(totals) + blockIdx.y * rb.table_stride); }
   __shared__ unsigned long long red[8];
   __shared__ uint32_t wsum[8];
   __shared__ uint32_t carry_s;
@@ -102,7 +109,12 @@ __global__ void __launch_bounds__(256) radix_rowscan_kernel(uint32_t* __restrict
 __global__ void __launch_bounds__(kRxThreads) radix_scatter_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                                    uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
                                                                    size_t n, int shift, const uint32_t* __restrict__ table,
-                                                                   int n_tiles) {
+                                                                   int n_tiles, RxBatch rb) {
+  if (rb.n_arr) {
+    n = (size_t)rb.n_arr[blockIdx.y];
+    kin += blockIdx.y * rb.key_stride; vin += blockIdx.y * rb.val_stride; kout += blockIdx.y * rb.key_stride; vout += blockIdx.y * rb.val_stride;
+    table += blockIdx.y * rb.table_stride;
+  }
   __shared__ uint32_t wcnt[kRxWarps][256];
   __shared__ uint32_t gbase[256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -161,25 +173,35 @@ size_t radix_table_words(size_t n) {
 
 // Sorts n pairs by bits [begin_bit, end_bit) of the key.  Ping-pongs between (keys, vals) and (keys_alt, vals_alt);
 // *in_alt tells where the result is.  Returns the number of kernels enqueued.
-int radix_sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt, uint32_t* table, size_t n,
-                     int begin_bit, int end_bit, cudaStream_t st, bool* in_alt) {
+// Batched: `batch` independent sorts in the same launches -- segment s holds n_arr[s] (device array) <= n items at offset
+// s * key_stride of the key arrays and s * val_stride of the payload arrays, its table at s * table_stride words (>= radix_table_words(n), even).
+int radix_sort_pairs_batched(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt, uint32_t* table, size_t n,
+                             const unsigned long long* n_arr, size_t key_stride, size_t val_stride, size_t table_stride, int batch, int begin_bit, int end_bit,
+                             cudaStream_t st, bool* in_alt) {
   *in_alt = false;
-  if (n == 0) return 0;
+  if (n == 0 || batch <= 0) return 0;
   const int n_tiles = (int)((n + kRxTile - 1) / kRxTile);
   unsigned long long* totals = reinterpret_cast<unsigned long long*>(table + (size_t)256 * n_tiles);
+  RxBatch rb; rb.n_arr = n_arr; rb.key_stride = key_stride; rb.val_stride = val_stride; rb.table_stride = table_stride;
+  const int by = n_arr ? batch : 1;
   int launches = 0;
   uint64_t* ki = keys; uint32_t* vi = vals; uint64_t* ko = keys_alt; uint32_t* vo = vals_alt;
   for (int shift = begin_bit; shift < end_bit; shift += 8) {
-    radix_hist_kernel<<<n_tiles, kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles);
-    radix_rowsum_kernel<<<256, 256, 0, st>>>(table, n_tiles, totals);
-    radix_rowscan_kernel<<<256, 256, 0, st>>>(table, n_tiles, totals);
-    radix_scatter_kernel<<<n_tiles, kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles);
+    radix_hist_kernel<<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles, rb);
+    radix_rowsum_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
+    radix_rowscan_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
+    radix_scatter_kernel<<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles, rb);
     launches += 4;
     uint64_t* tk = ki; ki = ko; ko = tk;
     uint32_t* tv = vi; vi = vo; vo = tv;
     *in_alt = !*in_alt;
   }
   return launches;
+}
+
+int radix_sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt, uint32_t* table, size_t n,
+                     int begin_bit, int end_bit, cudaStream_t st, bool* in_alt) {
+  return radix_sort_pairs_batched(keys, vals, keys_alt, vals_alt, table, n, nullptr, 0, 0, 0, 1, begin_bit, end_bit, st, in_alt);
 }
 
 }  // namespace b2r

@@ -23,6 +23,7 @@ namespace {
 constexpr int kSwThreads = 256;
 constexpr int kSwItems = 8;
 constexpr int kSwTile = kSwThreads * kSwItems;  // endpoints per CTA
+constexpr int kScaleMaxChunk = 4096;             // problems per batched launch (their endpoint counts live in problem 0's workspace)
 constexpr int kNQ = 7;                           // count, w, w*x, r(entered), x, x*x, r(all entries)
 
 __device__ __forceinline__ uint64_t ordered_key(double v) {
@@ -34,14 +35,52 @@ __device__ __forceinline__ double sq3_ref(double dx, double dy, double dz) {
   return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
-// grid = (ceil(n/256), n): thread (i = blockIdx.y, j) for j > i.
-__global__ void __launch_bounds__(256) scale_tims_kernel(const double* __restrict__ src, const double* __restrict__ dst, int n,
-                                                         double beta, double* __restrict__ X, double* __restrict__ R,
-                                                         uint64_t* __restrict__ keys, uint32_t* __restrict__ pay) {
+// Workspace of ONE problem, laid out for the batch's largest N (n_max) so that every problem of a batch has the same offsets; the
+// problems of a batch sit ws_stride bytes apart.
+struct ScaleLayout {
+  size_t X, R, keys, keys_alt, pay, pay_alt, table, tile_sums, best, e_count, total;   // byte offsets
+  size_t seg_items;      // key / payload items between two problems (ws_stride / item size must match: see launch)
+  int n_tiles_max;
+};
+__host__ __device__ inline size_t sl_pad(size_t b) { return (b + 255) / 256 * 256; }
+__host__ inline ScaleLayout scale_layout(int n_max) {
+  const size_t P = (size_t)n_max * (n_max - 1) / 2, E = 2 * P;
+  ScaleLayout L;
+  L.n_tiles_max = (int)((E + kSwTile - 1) / kSwTile);
+  size_t o = 0;
+  L.X = o; o += sl_pad(P * 8);
+  L.R = o; o += sl_pad(P * 8);
+  L.keys = o; o += sl_pad(E * 8);
+  L.keys_alt = o; o += sl_pad(E * 8);
+  L.pay = o; o += sl_pad(E * 4);
+  L.pay_alt = o; o += sl_pad(E * 4);
+  L.table = o; o += sl_pad(radix_table_words(E) * 4);
+  L.tile_sums = o; o += sl_pad(((size_t)L.n_tiles_max + 1) * kNQ * 8);
+  L.best = o; o += sl_pad((size_t)L.n_tiles_max * 3 * 8);
+  L.e_count = o; o += 8 * kScaleMaxChunk;
+  L.total = o;
+  L.seg_items = 0;
+  return L;
+}
+
+// grid = (ceil(n_max/256), n_max - 1, batch): thread (i = blockIdx.y, j) for j > i of problem blockIdx.z.
+__global__ void __launch_bounds__(256) scale_tims_kernel(const ProbDesc* __restrict__ descs, double beta, char* __restrict__ ws, size_t ws_stride,
+                                                         ScaleLayout L) {
+  const ProbDesc d = descs[blockIdx.z];
+  const double* __restrict__ src = d.src;
+  const double* __restrict__ dst = d.dst;
+  const int n = d.n;
+  char* base = ws + (size_t)blockIdx.z * ws_stride;
+  double* __restrict__ X = reinterpret_cast<double*>(base + L.X);
+  double* __restrict__ R = reinterpret_cast<double*>(base + L.R);
+  uint64_t* __restrict__ keys = reinterpret_cast<uint64_t*>(base + L.keys);
+  uint32_t* __restrict__ pay = reinterpret_cast<uint32_t*>(base + L.pay);
+  const long long P = (long long)n * (n - 1) / 2;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0)
+    reinterpret_cast<unsigned long long*>(ws + L.e_count)[blockIdx.z] = (unsigned long long)(2 * P);   // endpoints of every problem, contiguous at the head
   const int i = blockIdx.y;
   const int j = blockIdx.x * 256 + threadIdx.x;
   if (j <= i || j >= n) return;
-  const long long P = (long long)n * (n - 1) / 2;
   const long long k = (long long)i * n - (long long)i * (i + 1) / 2 + (j - i - 1);
   const double a2 = sq3_ref(__dsub_rn(src[3 * (size_t)j], src[3 * (size_t)i]), __dsub_rn(src[3 * (size_t)j + 1], src[3 * (size_t)i + 1]),
                             __dsub_rn(src[3 * (size_t)j + 2], src[3 * (size_t)i + 2]));
@@ -100,10 +139,18 @@ __device__ void block_exclusive_scan(double (&v)[kNQ], double (&tot)[kNQ], doubl
 // pass 1 (kFinal=false): per-tile totals.  pass 2 (kFinal=true): replay with the scanned tile offsets, evaluate the
 // cost at every endpoint, leave the tile's best (cost, position, estimate).
 template <bool kFinal>
-__global__ void __launch_bounds__(kSwThreads) tls_sweep_kernel(const uint32_t* __restrict__ pay, long long E, long long P,
-                                                               const double* __restrict__ X, const double* __restrict__ R,
-                                                               double* __restrict__ tile_sums /* n_tiles x kNQ */,
-                                                               double* __restrict__ best /* n_tiles x 3 */) {
+__global__ void __launch_bounds__(kSwThreads) tls_sweep_kernel(const ProbDesc* __restrict__ descs, char* __restrict__ ws, size_t ws_stride,
+                                                               ScaleLayout L, int sorted_in_alt) {
+  const int n = descs[blockIdx.y].n;
+  const long long P = (long long)n * (n - 1) / 2, E = 2 * P;
+  const int n_tiles = (int)((E + kSwTile - 1) / kSwTile);
+  if ((int)blockIdx.x >= n_tiles) return;
+  char* base = ws + (size_t)blockIdx.y * ws_stride;
+  const uint32_t* __restrict__ pay = reinterpret_cast<const uint32_t*>(base + (sorted_in_alt ? L.pay_alt : L.pay));
+  const double* __restrict__ X = reinterpret_cast<const double*>(base + L.X);
+  const double* __restrict__ R = reinterpret_cast<const double*>(base + L.R);
+  double* __restrict__ tile_sums = reinterpret_cast<double*>(base + L.tile_sums);   // n_tiles x kNQ (+ totals)
+  double* __restrict__ best = reinterpret_cast<double*>(base + L.best);             // n_tiles x 3
   __shared__ double sm[kNQ * 8];
   __shared__ double sbest[3 * 8];
   const long long e0 = (long long)blockIdx.x * kSwTile + (long long)threadIdx.x * kSwItems;
@@ -133,7 +180,7 @@ __global__ void __launch_bounds__(kSwThreads) tls_sweep_kernel(const uint32_t* _
   double run[kNQ];
 #pragma unroll
   for (int q = 0; q < kNQ; ++q) run[q] = tile_sums[(size_t)blockIdx.x * kNQ + q] + part[q];
-  const double ranges_all = tile_sums[(size_t)gridDim.x * kNQ + 6];
+  const double ranges_all = tile_sums[(size_t)n_tiles * kNQ + 6];
   double bc = CUDART_INF, bx = 0.0, be = 9.0e18;
 #pragma unroll
   for (int k = 0; k < kSwItems; ++k) {
@@ -163,7 +210,11 @@ __global__ void __launch_bounds__(kSwThreads) tls_sweep_kernel(const uint32_t* _
 }
 
 // single CTA: exclusive scan of the tile sums in place (tile order), grand totals to slot [n_tiles]
-__global__ void __launch_bounds__(512) tls_scan_tiles_kernel(double* __restrict__ tile_sums, int n_tiles) {
+__global__ void __launch_bounds__(512) tls_scan_tiles_kernel(const ProbDesc* __restrict__ descs, char* __restrict__ ws, size_t ws_stride, ScaleLayout L) {
+  const int n = descs[blockIdx.x].n;
+  const long long E = (long long)n * (n - 1);
+  const int n_tiles = (int)((E + kSwTile - 1) / kSwTile);
+  double* __restrict__ tile_sums = reinterpret_cast<double*>(ws + (size_t)blockIdx.x * ws_stride + L.tile_sums);
   __shared__ double part[kNQ][512];
   const int tid = threadIdx.x;
   const int chunk = (n_tiles + 511) / 512;
@@ -191,7 +242,12 @@ __global__ void __launch_bounds__(512) tls_scan_tiles_kernel(double* __restrict_
 }
 
 // single CTA: argmin over the tiles -> ProbState::scale
-__global__ void __launch_bounds__(256) tls_pick_kernel(const double* __restrict__ best, int n_tiles, ProbState* __restrict__ st) {
+__global__ void __launch_bounds__(256) tls_pick_kernel(const ProbDesc* __restrict__ descs, const char* __restrict__ ws, size_t ws_stride, ScaleLayout L) {
+  const ProbDesc d = descs[blockIdx.x];
+  ProbState* __restrict__ st = d.st;
+  const long long E = (long long)d.n * (d.n - 1);
+  const int n_tiles = (int)((E + kSwTile - 1) / kSwTile);
+  const double* __restrict__ best = reinterpret_cast<const double*>(ws + (size_t)blockIdx.x * ws_stride + L.best);
   __shared__ double sb[3 * 256];
   double bc = CUDART_INF, bx = 0.0, be = 9.0e18;
   for (int i = threadIdx.x; i < n_tiles; i += 256) {
@@ -214,48 +270,32 @@ __global__ void __launch_bounds__(256) tls_pick_kernel(const double* __restrict_
 
 }  // namespace
 
-size_t scale_workspace_bytes(int n) {
-  const size_t P = (size_t)n * (n - 1) / 2;
-  const size_t E = 2 * P;
-  const size_t n_tiles = (E + kSwTile - 1) / kSwTile + 1;
-  size_t b = 0;
-  b += 2 * P * sizeof(double);                 // X, R
-  b += 2 * E * sizeof(uint64_t);               // keys, keys_alt
-  b += 2 * E * sizeof(uint32_t);               // payload, payload_alt
-  b += radix_table_words(E) * sizeof(uint32_t);
-  b += (n_tiles + 1) * kNQ * sizeof(double);   // tile sums (+ totals)
-  b += n_tiles * 3 * sizeof(double);           // per-tile best
-  return b + 8 * 256;                          // alignment slack
-}
+size_t scale_workspace_bytes(int n) { return scale_layout(n).total; }
+int scale_max_chunk() { return kScaleMaxChunk; }
 
-// One problem: estimate the scale into st->scale.  ws: scale_workspace_bytes(n) bytes, 256-byte aligned.
-int launch_scale_estimate(const double* src, const double* dst, int n, double beta, ProbState* st, void* ws, cudaStream_t stream) {
-  const size_t P = (size_t)n * (n - 1) / 2;
-  const size_t E = 2 * P;
-  if (P == 0) return 0;
-  const int n_tiles = (int)((E + kSwTile - 1) / kSwTile);
-  char* p = (char*)ws;
-  auto take = [&](size_t bytes) { char* r = p; p += (bytes + 255) / 256 * 256; return (void*)r; };
-  double* X = (double*)take(P * sizeof(double));
-  double* R = (double*)take(P * sizeof(double));
-  uint64_t* keys = (uint64_t*)take(E * sizeof(uint64_t));
-  uint64_t* keys_alt = (uint64_t*)take(E * sizeof(uint64_t));
-  uint32_t* pay = (uint32_t*)take(E * sizeof(uint32_t));
-  uint32_t* pay_alt = (uint32_t*)take(E * sizeof(uint32_t));
-  uint32_t* table = (uint32_t*)take(radix_table_words(E) * sizeof(uint32_t));
-  double* tile_sums = (double*)take(((size_t)n_tiles + 1) * kNQ * sizeof(double));
-  double* best = (double*)take((size_t)n_tiles * 3 * sizeof(double));
+// A batch of problems (device descriptors dd[0 .. batch)): every problem's scale into its ProbState::scale, in ONE set of launches
+// (grid dimension = problem) instead of ~40 launches per problem.  ws: batch * scale_workspace_bytes(n_max) bytes, 256-byte aligned.
+int launch_scale_estimate_batch(const ProbDesc* dd, int batch, int n_max, double beta, void* ws, cudaStream_t stream) {
+  if (n_max < 2 || batch <= 0) return 0;
+  const ScaleLayout L = scale_layout(n_max);
+  const size_t stride = L.total;
+  const size_t E = (size_t)n_max * (n_max - 1);
+  char* base = (char*)ws;
   int launches = 0;
-  dim3 grid((n + 255) / 256, n - 1);
-  scale_tims_kernel<<<grid, 256, 0, stream>>>(src, dst, n, beta, X, R, keys, pay);
+  dim3 grid((n_max + 255) / 256, n_max - 1, batch);
+  scale_tims_kernel<<<grid, 256, 0, stream>>>(dd, beta, base, stride, L);
   ++launches;
   bool in_alt = false;
-  launches += radix_sort_pairs(keys, pay, keys_alt, pay_alt, table, E, 0, 64, stream, &in_alt);
-  const uint32_t* sorted = in_alt ? pay_alt : pay;
-  tls_sweep_kernel<false><<<n_tiles, kSwThreads, 0, stream>>>(sorted, (long long)E, (long long)P, X, R, tile_sums, best);
-  tls_scan_tiles_kernel<<<1, 512, 0, stream>>>(tile_sums, n_tiles);
-  tls_sweep_kernel<true><<<n_tiles, kSwThreads, 0, stream>>>(sorted, (long long)E, (long long)P, X, R, tile_sums, best);
-  tls_pick_kernel<<<1, 256, 0, stream>>>(best, n_tiles, st);
+  // keys (8 B) and payloads (4 B) of consecutive problems are `stride` BYTES apart: stride / 8 keys, stride / 4 payloads and table words
+  launches += radix_sort_pairs_batched(reinterpret_cast<uint64_t*>(base + L.keys), reinterpret_cast<uint32_t*>(base + L.pay),
+                                        reinterpret_cast<uint64_t*>(base + L.keys_alt), reinterpret_cast<uint32_t*>(base + L.pay_alt),
+                                        reinterpret_cast<uint32_t*>(base + L.table), E, reinterpret_cast<const unsigned long long*>(base + L.e_count),
+                                        stride / 8, stride / 4, stride / 4, batch, 0, 64, stream, &in_alt);
+  dim3 sgrid(L.n_tiles_max, batch);
+  tls_sweep_kernel<false><<<sgrid, kSwThreads, 0, stream>>>(dd, base, stride, L, in_alt ? 1 : 0);
+  tls_scan_tiles_kernel<<<batch, 512, 0, stream>>>(dd, base, stride, L);
+  tls_sweep_kernel<true><<<sgrid, kSwThreads, 0, stream>>>(dd, base, stride, L, in_alt ? 1 : 0);
+  tls_pick_kernel<<<batch, 256, 0, stream>>>(dd, base, stride, L);
   return launches + 4;
 }
 
