@@ -39,13 +39,24 @@ struct BackprojArgs {
   int use_range, use_trunc, vec_ok;
   double* pts; int* pix; int cap;
   unsigned long long* ws; int* count;
+  unsigned int* tile_counts;            // two-pass form: points per tile (MODE 1 writes, tile_scan_kernel scans in place)
 };
 
+// MODE 0: single pass, ordered compaction by decoupled look-back (small images: one launch).
+// MODE 1 / 2: two passes for large images -- count the valid pixels of every tile, scan the 8 k tile counts in one small kernel,
+// then recompute and write with the tile's base known up front: no inter-CTA dependency chain at all, at the price of reading the
+// 3 bytes per pixel twice (the output is 24 bytes per valid point).
+// Output: every warp stages its <= 256 points in shared memory and writes them as contiguous doubles (the per-lane 8-byte stores this
+// replaces touched 32 different sectors per instruction).
+constexpr int kBpSmemBytes = 8 * (256 * 24 + 256 * 4);   // per warp: 256 points + 256 pixel ids
+
+template <int MODE>
 __global__ void __launch_bounds__(256) backproject_kernel(BackprojArgs a) {
+  extern __shared__ __align__(16) unsigned char bp_smem[];
   __shared__ int s_tile;
   __shared__ unsigned s_warp[8];
   __shared__ unsigned long long s_base;
-  const int tile = take_ticket(a.ws, &s_tile);
+  const int tile = MODE == 0 ? take_ticket(a.ws, &s_tile) : (int)blockIdx.x;
   const int g0 = a.u0 >> 3;
   const int G = ((a.u1 + 7) >> 3) - g0;
   const long long total = (long long)(a.v1 - a.v0) * G;
@@ -89,26 +100,69 @@ __global__ void __launch_bounds__(256) backproject_kernel(BackprojArgs a) {
   }
   unsigned blk_total;
   const unsigned local = block_scan_256(__popc(bits), s_warp, &blk_total);
+  if (MODE == 1) {
+    if (threadIdx.x == 0) a.tile_counts[tile] = blk_total;
+    return;
+  }
   if (threadIdx.x == 0) {
-    s_base = lookback(a.ws, tile, blk_total);
-    if (tile == (int)gridDim.x - 1) *a.count = (int)(s_base + blk_total);
+    if (MODE == 0) {
+      s_base = lookback(a.ws, tile, blk_total);
+      if (tile == (int)gridDim.x - 1) *a.count = (int)(s_base + blk_total);
+    } else {
+      s_base = a.tile_counts[tile];     // exclusive prefix after tile_scan_kernel
+    }
   }
   __syncthreads();
-  long long m = (long long)s_base + local;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* sp = reinterpret_cast<double*>(bp_smem + (size_t)warp * (256 * 24));
+  int* sx = reinterpret_cast<int*>(bp_smem + 8 * (256 * 24) + (size_t)warp * (256 * 4));
+  const unsigned wfirst = __shfl_sync(FULL, local, 0);
+  const unsigned wtotal = __shfl_sync(FULL, local + (unsigned)__popc(bits), 31) - wfirst;
+  unsigned c = local - wfirst;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     if (bits & (1u << k)) {
-      if (m < a.cap) {
-        const int u = gu + k;
-        const double z = (double)dv[k];
-        a.pts[3 * m] = __ddiv_rn(__dmul_rn((double)u - a.cx, z), a.fx);
-        a.pts[3 * m + 1] = __ddiv_rn(__dmul_rn((double)row - a.cy, z), a.fy);
-        a.pts[3 * m + 2] = z;
-        if (a.pix) a.pix[m] = row * a.W + u;
-      }
-      ++m;
+      const int u = gu + k;
+      const double z = (double)dv[k];
+      sp[3 * c] = __ddiv_rn(__dmul_rn((double)u - a.cx, z), a.fx);
+      sp[3 * c + 1] = __ddiv_rn(__dmul_rn((double)row - a.cy, z), a.fy);
+      sp[3 * c + 2] = z;
+      sx[c] = row * a.W + u;
+      ++c;
     }
   }
+  __syncwarp();
+  const long long gbase = (long long)s_base + wfirst;
+  long long room = (long long)a.cap - gbase;          // points of this warp that still fit the output
+  if (room > (long long)wtotal) room = wtotal;
+  for (long long i = lane; i < 3 * room; i += 32) a.pts[3 * gbase + i] = sp[i];
+  if (a.pix) for (long long i = lane; i < room; i += 32) a.pix[gbase + i] = sx[i];
+}
+
+// exclusive scan of the tile counts in place (one CTA), total to *count
+__global__ void __launch_bounds__(1024) tile_scan_kernel(unsigned int* __restrict__ counts, int tiles, int* __restrict__ count) {
+  __shared__ unsigned int wsum[32];
+  __shared__ unsigned int carry_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int i0 = 0; i0 < tiles; i0 += 1024) {
+    const int i = i0 + threadIdx.x;
+    const unsigned v = i < tiles ? counts[i] : 0u;
+    unsigned x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(FULL, x, o); if (lane >= o) x += y; }
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    unsigned wb = 0;
+    for (int w = 0; w < warp; ++w) wb += wsum[w];
+    const unsigned carry = carry_s;
+    if (i < tiles) counts[i] = carry + wb + x - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = carry + wb + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = (int)carry_s;
 }
 
 // ordered compaction of 3-vectors by a keep mask (thread per point); idx_out optional
@@ -1099,9 +1153,10 @@ b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* 
   const int tiles = (int)((groups + 255) / 256);
   const size_t img = (size_t)H * W;
   Carver c;
-  b2r_status r = pre_ws(s, pad256(8 * (size_t)(tiles + 2)) + pad256(2 * img) + pad256(img) + 512, &c);
+  b2r_status r = pre_ws(s, pad256(8 * (size_t)(tiles + 2)) + pad256(4 * (size_t)tiles) + pad256(2 * img) + pad256(img) + 1024, &c);
   if (r != B2R_OK) return r;
   unsigned long long* ws = c.take<unsigned long long>(tiles + 2);
+  unsigned int* tile_counts = c.take<unsigned int>(tiles);
   int* d_count = c.take<int>(1);
   const uint16_t* d_depth = depth; const uint8_t* d_mask = mask;
   if (!on_device) {  // host image: one H2D copy each (pageable or pinned)
@@ -1117,9 +1172,23 @@ b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* 
   a.scale = (float)cam->depth_scale; a.trunc = (float)cam->depth_trunc;
   a.use_range = (cam->zmin > 0 || cam->zmax > 0) ? 1 : 0; a.use_trunc = cam->depth_trunc > 0 ? 1 : 0;
   a.vec_ok = (W % 8 == 0) && ((uintptr_t)d_depth % 16 == 0) && (!d_mask || (uintptr_t)d_mask % 8 == 0);
-  a.pts = points_dev; a.pix = pixel_ids_dev; a.cap = capacity; a.ws = ws; a.count = d_count;
-  backproject_kernel<<<tiles, 256, 0, s->stream>>>(a);
-  ++s->launches;
+  a.pts = points_dev; a.pix = pixel_ids_dev; a.cap = capacity; a.ws = ws; a.count = d_count; a.tile_counts = tile_counts;
+  static PerDeviceOnce bp_attr;
+  CK(bp_attr.run([] {
+    cudaError_t e = cudaFuncSetAttribute(backproject_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBpSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(backproject_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBpSmemBytes);
+    return e;
+  }));
+  static const int two_pass_tiles = [] { const char* e = getenv("B2R_BP_TWO_PASS_TILES"); return e ? atoi(e) : 512; }();   // A/B runs
+  if (tiles < two_pass_tiles) {       // a frame-sized bbox: one launch, the look-back chain is a few dozen tiles long
+    backproject_kernel<0><<<tiles, 256, kBpSmemBytes, s->stream>>>(a);
+    ++s->launches;
+  } else {
+    backproject_kernel<1><<<tiles, 256, 0, s->stream>>>(a);
+    tile_scan_kernel<<<1, 1024, 0, s->stream>>>(tile_counts, tiles, d_count);
+    backproject_kernel<2><<<tiles, 256, kBpSmemBytes, s->stream>>>(a);
+    s->launches += 3;
+  }
   CK(cudaMemcpyAsync(count_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
   CK(cudaStreamSynchronize(s->stream));
   CK(cudaGetLastError());
