@@ -103,6 +103,48 @@ __device__ inline void rotation_from_H(const double* H, double* R, double* warm 
     for (int c = 0; c < 3; ++c) R[3 * r + c] = V[3 * r] * U[3 * c] + V[3 * r + 1] * U[3 * c + 1] + V[3 * r + 2] * U[3 * c + 2];
 }
 
+// The same rotation without an SVD when H is well conditioned: R = V U^T is the orthogonal polar factor of H^T, and Newton's iteration
+// X <- (X + X^-T) / 2 from X0 = H^T / |H|_F converges to it quadratically (every singular value s -> (s + 1/s) / 2).  One iteration is a
+// cofactor matrix and one division -- ~200 cycles of dependent latency against ~1500 for a Jacobi sweep of three rotations with their
+// rsqrt / sqrt / div chains; the GNC loop calls this once per iteration from a single thread while 255 others wait.  Declines (returns
+// false: the caller runs the Jacobi SVD) when det(H) <= 0 (the optimum is then V diag(1,1,-1) U^T, not the polar factor), when H is
+// close to rank deficient, or when the iteration has not settled after 24 steps.  Agreement with the SVD path: ~1e-15.
+__device__ inline bool rotation_from_H_polar(const double* H, double* R) {
+  double f = 0.0;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) f += H[i] * H[i];
+  if (!(f > 0.0) || !(f < 1e300)) return false;
+  const double inv = rsqrt(f);
+  double X[9];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) X[3 * r + c] = H[3 * c + r] * inv;
+  if (!(det3(X) > 1e-5)) return false;   // |X|_F = 1: det <= 3^-1.5; 1e-5 keeps the smallest singular value above ~1e-4 of the largest
+  for (int it = 0; it < 24; ++it) {
+    double C[9];
+    C[0] = X[4] * X[8] - X[5] * X[7]; C[1] = X[5] * X[6] - X[3] * X[8]; C[2] = X[3] * X[7] - X[4] * X[6];
+    C[3] = X[2] * X[7] - X[1] * X[8]; C[4] = X[0] * X[8] - X[2] * X[6]; C[5] = X[1] * X[6] - X[0] * X[7];
+    C[6] = X[1] * X[5] - X[2] * X[4]; C[7] = X[2] * X[3] - X[0] * X[5]; C[8] = X[0] * X[4] - X[1] * X[3];
+    const double det = X[0] * C[0] + X[1] * C[1] + X[2] * C[2];
+    if (!(det > 0.0)) return false;
+    const double hd = 0.5 / det;
+    double diff = 0.0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+      const double xn = 0.5 * X[i] + hd * C[i];    // X^-T = cofactor matrix / det
+      diff = fmax(diff, fabs(xn - X[i]));
+      X[i] = xn;
+    }
+    if (diff < 1e-15) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R[i] = X[i];
+      return true;
+    }
+  }
+  return false;
+}
+
 // Cyclic Jacobi eigen-decomposition of a symmetric 3x3 (row-major C): eigenvalues w, eigenvectors = columns of Q (unsorted).
 __device__ inline void eig3_sym(const double* C, double* w, double* Q) {
   double a[3][3], q[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};

@@ -151,7 +151,7 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
       h[6] += w * x2 * y0; h[7] += w * x2 * y1; h[8] += w * x2 * y2;
     }
     block_sum<9>(h, red, bar);
-    if (tid == 0) rotation_from_H(h, sR, sV);
+    if (tid == 0 && !rotation_from_H_polar(h, sR)) rotation_from_H(h, sR, sV);
     grp_sync(bar);
     double maxr = 0.0;
     for (int i = tid; i < T; i += kRtThreads) {
