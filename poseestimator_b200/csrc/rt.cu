@@ -10,9 +10,10 @@
 namespace b2r {
 
 __global__ void __launch_bounds__(kRtThreads) rotation_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {
+  __shared__ double tim_cache[8 * 512];   // TIMs, weights and residuals of up to 512 pruned TIMs stay on chip during the GNC loop
   const ProbDesc d = descs[blockIdx.x];
   if (d.st->tail_done) return;
-  rotation_body(d, kp, 0);
+  rotation_body(d, kp, 0, TailMarks(), tim_cache, 8 * 512);
 }
 
 __global__ void __launch_bounds__(3 * kRtThreads) translation_kernel(const ProbDesc* __restrict__ descs, KernelParams kp) {

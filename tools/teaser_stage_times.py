@@ -21,4 +21,4 @@ for _ in range(30):
     sol = reg.solver.solution(0); t4 = time.perf_counter()
     st = reg.solver.stats(0); t5 = time.perf_counter()
     for k, a, b in (("gather", t0, t1), ("submit", t1, t2), ("sync", t2, t3), ("solution", t3, t4), ("stats", t4, t5)): T[k].append((b - a) * 1e3)
-print(json.dumps({"n_corr": int(pairs.shape[0]), "host_ms_p50": {k: round(float(np.median(v)), 4) for k, v in T.items()}, "device_ms": {k: round(v, 4) for k, v in reg.solver.timings_ms().items() if v}, "stats": {k: st[k] for k in ("clique_size", "n_pruned", "heuristic_lb", "fused_tail")}}))
+print(json.dumps({"n_corr": int(pairs.shape[0]), "host_ms_p50": {k: round(float(np.median(v)), 4) for k, v in T.items()}, "device_ms": {k: round(v, 4) for k, v in reg.solver.timings_ms().items() if v}, "stats": {k: st[k] for k in ("clique_size", "n_pruned", "heuristic_lb", "fused_tail", "gnc_iterations", "bnb_nodes")}}))
