@@ -68,6 +68,22 @@ def test_backproject_odd_shapes_and_device_input(op, ps):
     assert empty.shape[0] == 0
 
 
+@pytest.mark.parametrize("H,W,bbox", [(1536, 2048, None), (1100, 1999, (5, 3, 1990, 1097))])
+def test_backproject_large_image_two_pass(op, ps, H, W, bbox):
+    """More than 512 tiles of 2048 pixels: the two-pass form (tile counts, scan kernel, write with known bases) and the warp-staged
+    output must give the oracle's points in the oracle's order; the second case takes the scalar load path (W % 8 != 0)."""
+    rng = np.random.default_rng(H + W)
+    depth = rng.integers(300, 3500, size=(H, W)).astype(np.uint16)
+    depth[rng.uniform(size=(H, W)) < 0.15] = 0
+    mask = (rng.uniform(size=(H, W)) < 0.7).astype(np.uint8) * 255
+    mask[:, : W // 5] = 0                                # long runs of tiles without a single valid pixel
+    ref_p, ref_pix = op.backproject(depth, mask, bbox, 900.0, 910.0, W / 2 - 0.5, H / 2, 0.001, 3.0)
+    pts, pix = ps.backproject(depth, mask, bbox, 900.0, 910.0, W / 2 - 0.5, H / 2, 0.001, 3.0, want_pixels=True)
+    assert ref_p.shape[0] > 500000
+    assert np.array_equal(_np(pix), ref_pix)
+    assert np.array_equal(_np(pts), ref_p)
+
+
 # ---- kNN ---------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("n,nq,K,radius", [(1, 1, 1, 0.0), (40, 40, 128, 0.0), (700, 300, 20, 0.0), (2000, 2000, 30, 0.08),
                                             (3000, 500, 100, 0.2), (513, 77, 7, 0.05)])
