@@ -196,6 +196,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
+    if world > 1:   # several ranks share the host: the staging copy of a pageable batch gets cores / ranks threads, not 8 per rank
+        os.environ.setdefault("B2R_PACK_THREADS", str(max(1, min(8, (os.cpu_count() or 8) // world))))
     if world > 1 or os.environ.get("B2R_BENCH_FORCE_DIST") == "1":   # the second form: probes only (tools/scale_probe.sh)
         if os.environ.get("B2R_BENCH_BACKEND") == "gloo":      # probe only: is a slowdown NCCL's or torchrun's?
             dist.init_process_group("gloo")

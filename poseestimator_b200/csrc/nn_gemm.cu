@@ -388,39 +388,53 @@ __global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double*
 }
 
 // Rows whose shortlist could not be proven complete: exact fp64 search over EVERY reference.  Eight rows per CTA (one per warp) share
-// each 64-reference tile through shared memory, so a reference row is read from L2 once per eight rows instead of once per row
+// each 128-reference tile through shared memory, so a reference row is read from L2 once per eight rows instead of once per row
 // (the in-warp loop this replaces moved 264 B x references x rows through L2: 0.3 ms for the ~800 near-tie rows of a config-2 frame).
-constexpr int kFbRows = 8, kFbTile = 64, kFbDim = 41;   // kFbDim: row stride in doubles (odd, >= kKSeg + 1: conflict-free columns)
+// A tile is a straight copy of 128 consecutive descriptor rows (stride = dim doubles: conflict-free for the odd FPFH dimension 33);
+// the next tile is already in registers while the current one is evaluated, and a lane carries four references at once (four
+// independent summation chains instead of one).
+constexpr int kFbRows = 8, kFbTile = 128, kFbLoads = (kFbTile * kKSeg + kFbRows * 32 - 1) / (kFbRows * 32);
 
 __global__ void __launch_bounds__(kFbRows * 32) nn_fallback_kernel(const double* __restrict__ fq, const double* __restrict__ fr, int nr, int dim,
                                                                    const int* __restrict__ fb_list, const unsigned int* __restrict__ fb_count,
                                                                    int* __restrict__ nn, double* __restrict__ dist, unsigned int* __restrict__ n_fallback) {
-  __shared__ double tile[kFbTile * kFbDim];
-  __shared__ double qv[kFbRows][kFbDim];
+  __shared__ double tile[kFbTile * kKSeg];
+  __shared__ double qv[kFbRows][kKSeg];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned int count = *fb_count;
   if (blockIdx.x == 0 && threadIdx.x == 0 && n_fallback) atomicAdd(n_fallback, count);
+  const size_t total = (size_t)nr * dim;
   for (unsigned int g0 = blockIdx.x * kFbRows; g0 < count; g0 += gridDim.x * kFbRows) {
     const unsigned int slot = g0 + warp;
     const int i = slot < count ? fb_list[slot] : -1;
     __syncthreads();
     if (i >= 0) for (int t = lane; t < dim; t += 32) qv[warp][t] = fq[(size_t)i * dim + t];
     double best = CUDART_INF; int bj = -1;
+    double pre[kFbLoads];
+    const int tile_elems = kFbTile * dim;
+#pragma unroll
+    for (int q = 0; q < kFbLoads; ++q) { const size_t e = (size_t)q * (kFbRows * 32) + threadIdx.x; pre[q] = ((int)e < tile_elems && e < total) ? fr[e] : 0.0; }
     for (int j0 = 0; j0 < nr; j0 += kFbTile) {
       __syncthreads();
-      const int rows = min(kFbTile, nr - j0);
-      for (int e = threadIdx.x; e < rows * dim; e += kFbRows * 32) tile[(e / dim) * kFbDim + e % dim] = fr[(size_t)j0 * dim + e];
+#pragma unroll
+      for (int q = 0; q < kFbLoads; ++q) { const int e = q * (kFbRows * 32) + threadIdx.x; if (e < tile_elems) tile[e] = pre[q]; }
+      const size_t nbase = (size_t)(j0 + kFbTile) * dim;
+#pragma unroll
+      for (int q = 0; q < kFbLoads; ++q) { const size_t e = (size_t)q * (kFbRows * 32) + threadIdx.x; pre[q] = ((int)e < tile_elems && nbase + e < total) ? fr[nbase + e] : 0.0; }
       __syncthreads();
       if (i >= 0) {
+        const int rows = min(kFbTile, nr - j0);
+        double sacc[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int t = 0; t < dim; ++t) {
+          const double qt = qv[warp][t];
 #pragma unroll
-        for (int h = 0; h < kFbTile / 32; ++h) {
+          for (int h = 0; h < 4; ++h) { const double dd = __dsub_rn(qt, tile[(lane + 32 * h) * dim + t]); sacc[h] = __dadd_rn(sacc[h], __dmul_rn(dd, dd)); }
+        }
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {       // ascending reference index per lane: h = 0 .. 3
           const int jl = lane + 32 * h;
-          if (jl < rows) {
-            double sacc = 0;
-            for (int t = 0; t < dim; ++t) { const double dd = __dsub_rn(qv[warp][t], tile[jl * kFbDim + t]); sacc = __dadd_rn(sacc, __dmul_rn(dd, dd)); }
-            const int j = j0 + jl;
-            if (sacc < best || (sacc == best && (unsigned)j < (unsigned)bj)) { best = sacc; bj = j; }
-          }
+          const int j = j0 + jl;
+          if (jl < rows && (sacc[h] < best || (sacc[h] == best && (unsigned)j < (unsigned)bj))) { best = sacc[h]; bj = j; }
         }
       }
     }
