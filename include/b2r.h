@@ -191,7 +191,10 @@ int b2r_pitch_words(int n);
  * then any number of b2r_solve_sharded calls -- COLLECTIVE: every rank calls it with the same replicated operands.  Rank r runs
  * 1 / world of the tensor-core graph filter and stores its words into every rank's matrix while it computes; each rank then finishes
  * the solve on its own complete matrix (results identical on all ranks and to b2r_solve, getters as usual).  world <= 8.
- * The handle must not be used for larger problems or batches in between (a workspace re-allocation invalidates the export). */
+ * The handle must not be used for larger problems or batches in between (a workspace re-allocation invalidates the export).
+ * b2r_shard_attach resets this rank's flag words: the host must put a barrier between the attach of ALL ranks and the first
+ * b2r_solve_sharded of any rank (the Python host's all-or-nothing error exchange is that barrier).  A peer that never arrives makes
+ * the call fail with B2R_ERR_STATE after ~2 s (B2R_SHARD_TIMEOUT_MS) instead of hanging the GPU. */
 typedef struct b2r_peer_handle {
   unsigned char adjacency[64];   /* cudaIpcMemHandle_t of the allocation that holds the bit matrix */
   unsigned char flags[64];       /* cudaIpcMemHandle_t of the allocation that holds the flag words */
