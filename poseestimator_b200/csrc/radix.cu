@@ -25,6 +25,9 @@ constexpr int kRxTile = kRxThreads * kRxItems;  // 4096 items per CTA
 // the key / payload arrays and its own table at s * table_stride; n_arr == nullptr: one segment of n items.
 struct RxBatch { const unsigned long long* n_arr; size_t key_stride, val_stride, table_stride; };   // strides in items / words
 
+// ITEMS per thread: 16 (tiles of 4096 items) for large sorts, 4 (tiles of 1024) below 256 k items -- a frame-sized sort (56 k points)
+// then runs on 56 CTAs instead of 14 and each of its latency-bound passes takes a third of the time.
+template <int ITEMS>
 __global__ void __launch_bounds__(kRxThreads) radix_hist_kernel(const uint64_t* __restrict__ keys, size_t n, int shift,
                                                                 uint32_t* __restrict__ table, int n_tiles, RxBatch rb) {
   if (rb.n_arr) { n = (size_t)rb.n_arr[blockIdx.y]; keys += blockIdx.y * rb.key_stride; table += blockIdx.y * rb.table_stride; }
@@ -32,9 +35,9 @@ __global__ void __launch_bounds__(kRxThreads) radix_hist_kernel(const uint64_t* 
   h[threadIdx.x] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31;
-  const size_t base = (size_t)blockIdx.x * kRxTile;
+  const size_t base = (size_t)blockIdx.x * (kRxThreads * ITEMS);
 #pragma unroll 4
-  for (int it = 0; it < kRxItems; ++it) {
+  for (int it = 0; it < ITEMS; ++it) {
     const size_t i = base + (size_t)it * kRxThreads + threadIdx.x;
     const bool ok = i < n;
     const unsigned d = ok ? (unsigned)((keys[i] >> shift) & 255ull) : (256u + lane);
@@ -106,6 +109,7 @@ __global__ void __launch_bounds__(256) radix_rowscan_kernel(uint32_t* __restrict
   }
 }
 
+template <int ITEMS>
 __global__ void __launch_bounds__(kRxThreads) radix_scatter_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                                    uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
                                                                    size_t n, int shift, const uint32_t* __restrict__ table,
@@ -122,19 +126,19 @@ __global__ void __launch_bounds__(kRxThreads) radix_scatter_kernel(const uint64_
   for (int w = 0; w < kRxWarps; ++w) wcnt[w][threadIdx.x] = 0;
   gbase[threadIdx.x] = table[(size_t)threadIdx.x * n_tiles + blockIdx.x];
   __syncthreads();
-  // item order inside the tile = memory order: index = base + warp*512 + it*32 + lane
-  const size_t base = (size_t)blockIdx.x * kRxTile + (size_t)warp * (32 * kRxItems) + lane;
-  uint64_t k[kRxItems];
-  uint32_t v[kRxItems];
-  uint32_t rk[kRxItems];
+  // item order inside the tile = memory order: index = base + warp * (32 * ITEMS) + it * 32 + lane
+  const size_t base = (size_t)blockIdx.x * (kRxThreads * ITEMS) + (size_t)warp * (32 * ITEMS) + lane;
+  uint64_t k[ITEMS];
+  uint32_t v[ITEMS];
+  uint32_t rk[ITEMS];
 #pragma unroll
-  for (int it = 0; it < kRxItems; ++it) {
+  for (int it = 0; it < ITEMS; ++it) {
     const size_t i = base + (size_t)it * 32;
     k[it] = i < n ? kin[i] : ~0ull;
     v[it] = i < n ? vin[i] : 0u;
   }
 #pragma unroll
-  for (int it = 0; it < kRxItems; ++it) {
+  for (int it = 0; it < ITEMS; ++it) {
     const size_t i = base + (size_t)it * 32;
     const bool ok = i < n;
     const unsigned d = ok ? (unsigned)((k[it] >> shift) & 255ull) : (256u + lane);
@@ -153,7 +157,7 @@ __global__ void __launch_bounds__(kRxThreads) radix_scatter_kernel(const uint64_
   }
   __syncthreads();
 #pragma unroll
-  for (int it = 0; it < kRxItems; ++it) {
+  for (int it = 0; it < ITEMS; ++it) {
     const size_t i = base + (size_t)it * 32;
     if (i < n) {
       const unsigned d = (unsigned)((k[it] >> shift) & 255ull);
@@ -166,8 +170,12 @@ __global__ void __launch_bounds__(kRxThreads) radix_scatter_kernel(const uint64_
 
 }  // namespace
 
+constexpr size_t kRxSmallN = (size_t)1 << 18;
+constexpr int kRxSmallItems = 4;
+inline int rx_tile_items(size_t n) { return kRxThreads * (n < kRxSmallN ? kRxSmallItems : kRxItems); }
+
 size_t radix_table_words(size_t n) {
-  const size_t tiles = (n + kRxTile - 1) / kRxTile;
+  const size_t tiles = (n + rx_tile_items(n) - 1) / rx_tile_items(n);
   return 256 * (tiles ? tiles : 1) + 2 * 256;  // table + 256 u64 totals
 }
 
@@ -180,17 +188,20 @@ int radix_sort_pairs_batched(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt,
                              cudaStream_t st, bool* in_alt) {
   *in_alt = false;
   if (n == 0 || batch <= 0) return 0;
-  const int n_tiles = (int)((n + kRxTile - 1) / kRxTile);
+  const bool small = n < kRxSmallN;
+  const int n_tiles = (int)((n + rx_tile_items(n) - 1) / rx_tile_items(n));
   unsigned long long* totals = reinterpret_cast<unsigned long long*>(table + (size_t)256 * n_tiles);
   RxBatch rb; rb.n_arr = n_arr; rb.key_stride = key_stride; rb.val_stride = val_stride; rb.table_stride = table_stride;
   const int by = n_arr ? batch : 1;
   int launches = 0;
   uint64_t* ki = keys; uint32_t* vi = vals; uint64_t* ko = keys_alt; uint32_t* vo = vals_alt;
   for (int shift = begin_bit; shift < end_bit; shift += 8) {
-    radix_hist_kernel<<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles, rb);
+    if (small) radix_hist_kernel<kRxSmallItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles, rb);
+    else radix_hist_kernel<kRxItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles, rb);
     radix_rowsum_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
     radix_rowscan_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
-    radix_scatter_kernel<<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles, rb);
+    if (small) radix_scatter_kernel<kRxSmallItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles, rb);
+    else radix_scatter_kernel<kRxItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles, rb);
     launches += 4;
     uint64_t* tk = ki; ki = ko; ko = tk;
     uint32_t* tv = vi; vi = vo; vo = tv;
