@@ -140,7 +140,89 @@ __device__ inline bool rotation_body(const ProbDesc& d, const KernelParams& kp, 
   double mu = 1.0, prev_cost = CUDART_INF, cost = 0.0;
   double* r2buf = cached ? cache + 7 * (size_t)T : d.raw;  // scratch: T doubles
   int iters = 0;
-  for (int it = 0; it < kp.max_iterations; ++it) {
+  // Few TIMs (the usual case on real correspondences: a clique of 3 .. 200): the whole loop runs inside WARP 0 with no barrier at all.
+  // Every lane keeps its <= 8 TIMs in registers, the sums are warp shuffles, and every lane evaluates the 3 x 3 rotation itself
+  // (same inputs, same result) instead of one thread computing it for 255 waiting ones.  With tiny cliques GNC runs tens of
+  // iterations (cost threshold 1e-12), and at 6 us per iteration of the block-wide loop that was most of a config-2 solve.
+  __shared__ int s_iters;
+  __shared__ double s_cost;
+  const bool warp_path = cached && T <= 8 * 32;
+  if (warp_path) {
+    if (tid < 32) {
+      const int lane = tid;
+      // TIMs are read from the shared-memory cache every pass (the 48 doubles per lane would not fit the fused tail's 85 registers);
+      // weights and residuals live in registers
+      double w[8], r2v[8];
+      const int nq = (T - lane + 31) / 32;          // TIMs of this lane: lane, lane + 32, ...
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { w[q] = q < nq ? 1.0 : 0.0; r2v[q] = 0.0; }
+      double Rw[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+      double Vw[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+      for (int it = 0; it < kp.max_iterations; ++it) {
+        double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < nq) {
+            const double* xp = timx + 3 * (size_t)(lane + 32 * q);
+            const double* yp = timy + 3 * (size_t)(lane + 32 * q);
+            const double y0 = yp[0], y1 = yp[1], y2 = yp[2];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { const double wx = w[q] * xp[a]; h[3 * a] += wx * y0; h[3 * a + 1] += wx * y1; h[3 * a + 2] += wx * y2; }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 9; ++k) h[k] = warp_sum(h[k]);
+        if (!rotation_from_H_polar(h, Rw)) rotation_from_H(h, Rw, Vw);
+        double maxr = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < nq) {
+            const double* xp = timx + 3 * (size_t)(lane + 32 * q);
+            const double* yp = timy + 3 * (size_t)(lane + 32 * q);
+            const double x0 = xp[0], x1 = xp[1], x2 = xp[2];
+            const double e0 = yp[0] - ((Rw[0] * x0 + Rw[1] * x1) + Rw[2] * x2);
+            const double e1 = yp[1] - ((Rw[3] * x0 + Rw[4] * x1) + Rw[5] * x2);
+            const double e2 = yp[2] - ((Rw[6] * x0 + Rw[7] * x1) + Rw[8] * x2);
+            r2v[q] = (e0 * e0 + e1 * e1) + e2 * e2;
+            maxr = fmax(maxr, r2v[q]);
+          }
+        }
+        if (it == 0) {
+          maxr = warp_max(maxr);
+          mu = 1.0 / (2.0 * maxr / nb2 - 1.0);
+          if (mu <= 0.0) break;  // near-noiseless: weights stay 1 (A.6-3c)
+        }
+        const double th1 = (mu + 1.0) / mu * nb2, th2 = mu / (mu + 1.0) * nb2;
+        double cs = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const bool ok = q < nq;
+          cs += w[q] * r2v[q];
+          double nw;
+          if (r2v[q] >= th1) nw = 0.0;
+          else if (r2v[q] <= th2) nw = 1.0;
+          else nw = sqrt(nb2 * mu * (mu + 1.0) / r2v[q]) - mu;
+          w[q] = ok ? nw : 0.0;
+        }
+        cost = warp_sum(cs);
+        const double cost_diff = fabs(cost - prev_cost);
+        mu *= kp.gnc_factor;
+        prev_cost = cost;
+        iters = it + 1;
+        if (cost_diff < kp.cost_threshold) break;
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { const int i = lane + 32 * q; if (i < T) wts[i] = w[q]; }
+      if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) sR[k] = Rw[k];
+        s_iters = iters; s_cost = cost;
+      }
+    }
+    grp_sync(bar);
+    iters = s_iters; cost = s_cost;
+  }
+  for (int it = 0; !warp_path && it < kp.max_iterations; ++it) {
     double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     for (int i = tid; i < T; i += kRtThreads) {
       const double w = wts[i];
