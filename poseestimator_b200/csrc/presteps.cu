@@ -966,6 +966,99 @@ __global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* 
   const int r_last = max(max(max(cq0, g.dim[0] - 1 - cq0), max(cq1, g.dim[1] - 1 - cq1)), max(cq2, g.dim[2] - 1 - cq2));
   int cur = 0, a = 0, nb = 0;
   unsigned long long tk = ~0ull; int ti = 0x7fffffff;
+  // ---- fast path (K <= 32): the whole 3 x 3 x 3 block of cells at once ------------------------------------------------------------
+  // The shell walk below merges candidates into a sorted list batch by batch; its profile is 95 % selection machinery (sorts and merges
+  // of 64-slot batches), 1 % distance arithmetic.  Here every lane evaluates its share (<= 16) of ALL candidates of the block into
+  // registers, the K-th smallest of the 32 per-lane minima is a threshold that at least K candidates meet (each of those K lanes
+  // holds one) and, for evenly spread candidates, not many more; the candidates up to it are collected and sorted ONCE (knn_flush).
+  // The answer is final when the list is full and its K-th distance lies within the reach of the block (or the radius does); any other
+  // case -- more than 512 candidates, more than 64 up to the threshold, a K-th neighbour outside the block -- takes the shell walk.
+  if (K <= 32) {
+    int rb = 0, re = 0;                       // lane t < 9: sorted range of x-run t of the block
+    if (lane < 9) {
+      const int yy = cq1 + lane % 3 - 1, zz = cq2 + lane / 3 - 1;
+      if (yy >= 0 && yy < g.dim[1] && zz >= 0 && zz < g.dim[2]) {
+        const unsigned long long kb = (unsigned long long)g.dim[0] * ((unsigned long long)yy + (unsigned long long)g.dim[1] * (unsigned long long)zz);
+        int b = 0x7fffffff, e = 0;
+        for (int x = max(cq0 - 1, 0); x <= min(cq0 + 1, g.dim[0] - 1); ++x) {
+          const int2 cr = cell_points(cell_range, skeys, n, kb + (unsigned long long)x);
+          if (cr.y > cr.x) { b = min(b, cr.x); e = max(e, cr.y); }
+        }
+        if (e > b) { rb = b; re = e; }
+      }
+    }
+    const bool inside = cq0 >= 0 && cq0 < g.dim[0] && cq1 >= 0 && cq1 < g.dim[1] && cq2 >= 0 && cq2 < g.dim[2];
+    int len = re - rb, incl = len;            // inclusive prefix of the run lengths over lanes 0 .. 8
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+    const int C = __shfl_sync(FULL, incl, 8);
+    constexpr int kSlots = 16;
+    if (inside && C > 0 && C <= 32 * kSlots) {
+      unsigned long long dk[kSlots];
+      int di[kSlots];
+      unsigned long long mymin = ~0ull; int mymin_i = 0x7fffffff;
+      int run = 0, run_end = __shfl_sync(FULL, incl, 0), run_b = __shfl_sync(FULL, rb, 0), run_first = 0;
+#pragma unroll
+      for (int sl = 0; sl < kSlots; ++sl) {
+        const int c = lane + 32 * sl;
+        dk[sl] = ~0ull; di[sl] = 0x7fffffff;
+        // (uniform trip count: every lane takes part in the shuffles)
+        while (true) {
+          const bool adv = c < C && c >= run_end;
+          if (!__any_sync(FULL, adv)) break;
+          const int nr = min(run + 1, 8);
+          const int ne = __shfl_sync(FULL, incl, adv ? nr : 0), nbg = __shfl_sync(FULL, rb, adv ? nr : 0);
+          if (adv) { run_first = run_end; run = nr; run_end = ne; run_b = nbg; }
+        }
+        if (c < C) {
+          const int sp = run_b + (c - run_first);
+          const double d2 = sq3_ref(__dsub_rn(spts[3 * (size_t)sp], qx), __dsub_rn(spts[3 * (size_t)sp + 1], qy), __dsub_rn(spts[3 * (size_t)sp + 2], qz));
+          if (!use_r || d2 < r2) {
+            dk[sl] = (unsigned long long)__double_as_longlong(d2); di[sl] = (int)sidx[sp];
+            if (key_less(dk[sl], di[sl], mymin, mymin_i)) { mymin = dk[sl]; mymin_i = di[sl]; }
+          }
+        }
+      }
+      // K-th smallest of the 32 lane minima: rank by counting (32 shuffles), strict total order on (key, id)
+      int rank = 0;
+      for (int j = 0; j < 32; ++j) {
+        const unsigned long long ok = __shfl_sync(FULL, mymin, j); const int oi = __shfl_sync(FULL, mymin_i, j);
+        rank += key_less(ok, oi, mymin, mymin_i) ? 1 : 0;
+      }
+      const unsigned pick = __ballot_sync(FULL, rank == K - 1 && mymin != ~0ull);
+      const int n_valid_lanes = __popc(__ballot_sync(FULL, mymin != ~0ull));
+      unsigned long long thr_k = ~0ull; int thr_i = 0x7fffffff;        // fewer than K lanes hold anything: take everything
+      if (n_valid_lanes >= K && pick) { const int src = __ffs(pick) - 1; thr_k = __shfl_sync(FULL, mymin, src); thr_i = __shfl_sync(FULL, mymin_i, src); }
+      int mine = 0;
+#pragma unroll
+      for (int sl = 0; sl < kSlots; ++sl) mine += (dk[sl] != ~0ull && !key_less(thr_k, thr_i, dk[sl], di[sl])) ? 1 : 0;
+      int pre = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, pre, o); if (lane >= o) pre += t; }
+      const int total = __shfl_sync(FULL, pre, 31);
+      if (total <= kKnnBuf) {
+        int pos = pre - mine;
+#pragma unroll
+        for (int sl = 0; sl < kSlots; ++sl)
+          if (dk[sl] != ~0ull && !key_less(thr_k, thr_i, dk[sl], di[sl])) { w.ck[pos] = dk[sl]; w.ci[pos] = di[sl]; ++pos; }
+        __syncwarp();
+        a = knn_flush(w, cur, 0, total, K, lane);
+        const double reach1 = g.h * (1.0 - 1e-9);
+        const bool done = (use_r && reach1 >= radius) ||
+                          (a == K && __longlong_as_double((long long)w.lk[cur][K - 1]) <= reach1 * reach1);
+        if (done) {
+          for (int t = lane; t < K; t += 32) {
+            idx_out[(size_t)q * K + t] = t < a ? w.li[cur][t] : -1;
+            d2_out[(size_t)q * K + t] = t < a ? __longlong_as_double((long long)w.lk[cur][t]) : 0.0;
+          }
+          if (lane == 0) cnt_out[q] = a;
+          return;
+        }
+        __syncwarp();
+        a = 0; cur = 0;        // not final: start the shell walk from scratch
+      }
+    }
+  }
   for (int r = r_first; r <= r_last; ++r) {
     for (int dz = -r; dz <= r; ++dz) {
       const int cz = cq2 + dz;
@@ -1046,7 +1139,7 @@ size_t knn_grid_ws_bytes(int n) {
 // ------------------------------------------------------------------------------------------------------------------
 // launchers used by the C ABI below
 // ------------------------------------------------------------------------------------------------------------------
-constexpr double kKnnHScale = 0.7;       // cell size relative to twice the estimated K-th neighbour distance (B2R_KNN_HSCALE overrides: A/B runs)
+constexpr double kKnnHScale = 0.55;      // cell size relative to twice the estimated K-th neighbour distance (B2R_KNN_HSCALE overrides: A/B runs)
 constexpr int kKnnGridMinPoints = 4096;  // below this the brute-force kernel is faster than building a grid
 
 static int launch_knn_brute(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
