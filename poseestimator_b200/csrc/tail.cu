@@ -38,6 +38,7 @@ struct TailShared {
   // near-clique core: the non-adjacent pairs inside the core and the vertices to drop (tail_small_cover)
   int n_pairs, n_cover;
   unsigned short pu[kTailMaxPairs], pv[kTailMaxPairs], cover[kTailMaxExtra];
+  unsigned long long mu[kTailMaxPairs], mv[kTailMaxPairs];   // tail_cover_masks
 };
 
 // ascending list of the set bits of `bits` (Wb words) as 16-bit ids; returns the count (uniform)
@@ -79,38 +80,61 @@ __device__ int tail_list_bits(const uint32_t* bits, int Wb, unsigned short* list
 // all covers of minimum size by branching on the two ends of an uncovered pair (depth <= e, <= 2^e leaves) and keeps the one whose
 // sorted id list is lexicographically LARGEST: dropping it leaves the lexicographically smallest maximum clique, the canonical
 // answer of the oracle and of canon_kernel.  Returns the cover in ts->cover / ts->n_cover (-1: no cover of size <= e exists).
+//
+// Pairs are bits of a 64-bit word (np <= kTailMaxPairs = 64): ts->mu[i] / ts->mv[i] = the pairs that the first / second end of pair i
+// covers (tail_cover_masks, one thread per pair), so a node of the search is an OR, a find-first-set and a popcount instead of a scan
+// of the pair list in shared memory (172 k cycles for 11 pairs, e = 4, before; the popcount bound -- a vertex covers at most e pairs
+// -- also cuts branches that cannot finish within k).
+__device__ void tail_cover_masks(TailShared* ts) {
+  const int np = ts->n_pairs;
+  const int i = threadIdx.x;
+  if (i < np) {
+    const unsigned short u = ts->pu[i], v = ts->pv[i];
+    unsigned long long mu = 0ull, mv = 0ull;
+    for (int j = 0; j < np; ++j) {
+      const unsigned short a = ts->pu[j], b = ts->pv[j];
+      if (a == u || b == u) mu |= 1ull << j;
+      if (a == v || b == v) mv |= 1ull << j;
+    }
+    ts->mu[i] = mu; ts->mv[i] = mv;
+  }
+}
+
 __device__ void tail_small_cover(TailShared* ts, int e) {
   const int np = ts->n_pairs;
-  int sel[kTailMaxExtra], choice[kTailMaxExtra], eidx[kTailMaxExtra];
+  const unsigned long long all = np >= 64 ? ~0ull : ((1ull << np) - 1ull);
+  unsigned long long cov[kTailMaxExtra + 1];
+  int sel[kTailMaxExtra], eidx[kTailMaxExtra];
   int best[kTailMaxExtra], cand[kTailMaxExtra];
+  unsigned second = 0u;   // bit d: depth d is on the second end of its pair
   int best_n = -1;
-  auto first_uncovered = [&](int depth) {
-    for (int i = 0; i < np; ++i) {
-      bool cov = false;
-      for (int q = 0; q < depth; ++q) cov = cov || sel[q] == (int)ts->pu[i] || sel[q] == (int)ts->pv[i];
-      if (!cov) return i;
-    }
-    return -1;
-  };
   for (int k = 0; k <= e && best_n < 0; ++k) {
     int depth = 0;
+    cov[0] = 0ull;
     for (;;) {
-      const int ei = first_uncovered(depth);
-      if (ei < 0) {   // sel[0 .. depth) covers every pair
+      const unsigned long long un = all & ~cov[depth];
+      if (!un) {   // sel[0 .. depth) covers every pair
         for (int q = 0; q < depth; ++q) cand[q] = sel[q];
         for (int a = 1; a < depth; ++a) { const int x = cand[a]; int b = a - 1; while (b >= 0 && cand[b] > x) { cand[b + 1] = cand[b]; --b; } cand[b + 1] = x; }
         bool better = best_n < 0;
         if (!better && depth == best_n)
           for (int q = 0; q < depth; ++q) if (cand[q] != best[q]) { better = cand[q] > best[q]; break; }
         if (better) { best_n = depth; for (int q = 0; q < depth; ++q) best[q] = cand[q]; }
-      } else if (depth < k) {
-        eidx[depth] = ei; choice[depth] = 0; sel[depth] = (int)ts->pu[ei]; ++depth;
+      } else if (depth < k && __popcll(un) <= (k - depth) * e) {
+        const int ei = __ffsll((long long)un) - 1;
+        eidx[depth] = ei; second &= ~(1u << depth); sel[depth] = (int)ts->pu[ei];
+        cov[depth + 1] = cov[depth] | ts->mu[ei];
+        ++depth;
         continue;
       }
       // backtrack: the other end of the deepest pair that still has one
       while (depth > 0) {
         const int dd = depth - 1;
-        if (choice[dd] == 0) { choice[dd] = 1; sel[dd] = (int)ts->pv[eidx[dd]]; break; }
+        if (!((second >> dd) & 1u)) {
+          second |= 1u << dd; sel[dd] = (int)ts->pv[eidx[dd]];
+          cov[depth] = cov[dd] | ts->mv[eidx[dd]];
+          break;
+        }
         --depth;
       }
       if (depth == 0) break;
@@ -308,15 +332,23 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
       }
       __syncthreads();
       if (ts.n_pairs <= kTailMaxPairs) {
-        if (tid == 0) {
-          // the search order must not depend on which warp listed a pair first: sort the pairs by (u, v)
+        {
+          // the search order must not depend on which warp listed a pair first: order the pairs by (u, v) -- rank sort, one thread per
+          // pair (the pairs are distinct)
           const int np = ts.n_pairs;
-          for (int a = 1; a < np; ++a) {
-            const unsigned short xu = ts.pu[a], xv = ts.pv[a];
-            int b = a - 1;
-            while (b >= 0 && (ts.pu[b] > xu || (ts.pu[b] == xu && ts.pv[b] > xv))) { ts.pu[b + 1] = ts.pu[b]; ts.pv[b + 1] = ts.pv[b]; --b; }
-            ts.pu[b + 1] = xu; ts.pv[b + 1] = xv;
+          unsigned key = 0u;
+          int rank = 0;
+          if (tid < np) {
+            key = ((unsigned)ts.pu[tid] << 16) | ts.pv[tid];
+            for (int j = 0; j < np; ++j) rank += ((((unsigned)ts.pu[j] << 16) | ts.pv[j]) < key) ? 1 : 0;
           }
+          __syncthreads();
+          if (tid < np) { ts.pu[rank] = (unsigned short)(key >> 16); ts.pv[rank] = (unsigned short)(key & 0xffffu); }
+        }
+        __syncthreads();
+        tail_cover_masks(&ts);
+        __syncthreads();
+        if (tid == 0) {
           tail_small_cover(&ts, n_alive - lb);
           for (int q = 0; q < ts.n_cover; ++q) alive[ts.cover[q] >> 5] &= ~(1u << (ts.cover[q] & 31));
         }
