@@ -290,6 +290,16 @@ b2r_status b2r_icp(b2r_solver* s, const double* src_dev, int ns, const double* d
                    int max_iter, double rel_fitness, double rel_rmse, b2r_icp_result* out, int32_t* corr_dev);
 /* voxel_coverage (HelpersRealtime.py:108-110): distinct floor(p / voxel) int32 triples */
 b2r_status b2r_voxel_coverage(b2r_solver* s, const double* pts_dev, int n, double voxel, int* count_out);
+/* b2r_voxel_coverage without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same count as
+ * b2r_voxel_coverage, but the hash table is a file-scope static device array (refine.cu, 2 * B2R_VOXEL_NOALLOC_MAX_POINTS int32 =
+ * 4 MiB, held by every GPU that loads the library until exit) instead of the solver's growable workspace, and the result is written
+ * to DEVICE memory: count_dev is one int32 on s's device, valid once the work queued on s's stream has finished (the call only
+ * enqueues: two memsets and one kernel; no cudaMalloc / cudaFree / allocating library routine, no synchronisation).
+ * n > B2R_VOXEL_NOALLOC_MAX_POINTS fails with B2R_ERR_LIMIT.  All calls on one device share the table: calls that overlap on the
+ * GPU (different streams or handles of the same device) race; serialise them. */
+#define B2R_VOXEL_NOALLOC_MAX_POINTS 524288
+b2r_status b2r_voxel_coverage_noalloc(b2r_solver* s, const double* pts_dev, int n, double voxel, int* count_dev);
 /* alignment_score (HelpersRealtime.py:112-130): out5 = {median, p90, cov_aligned, cov_full, score} (numpy median / percentile) */
 b2r_status b2r_alignment_score(b2r_solver* s, const double* src_aligned_dev, int ns, const double* src_down_dev, int ns2,
                                const double* dst_dev, int nd, double voxel, double* out5);

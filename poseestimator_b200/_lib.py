@@ -63,7 +63,7 @@ EXPORTS = [
     "b2r_set_profiling", "b2r_get_timings", "b2r_graph_rows", "b2r_solve_from_adjacency", "b2r_pitch_words",
     "b2r_backproject", "b2r_knn", "b2r_statistical_outlier", "b2r_voxel_down", "b2r_normals", "b2r_fpfh", "b2r_nn_exact",
     "b2r_mutual_pairs", "b2r_gather_correspondences", "b2r_nn_gemm", "b2r_mutual_nn",
-    "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_alignment_score", "b2r_chamfer",
+    "b2r_transform_points", "b2r_nn_distance", "b2r_icp", "b2r_voxel_coverage", "b2r_voxel_coverage_noalloc", "b2r_alignment_score", "b2r_chamfer",
     "b2r_cloud_resolution", "b2r_pca_axes", "b2r_pca_align", "b2r_render_depth", "b2r_backproject_depth32", "b2r_project_select", "b2r_farthest_point_sample",
     "b2r_shard_export", "b2r_shard_attach", "b2r_solve_sharded", "b2r_shard_last_fell_back", "b2r_shard_detach",
 ]
@@ -155,6 +155,7 @@ def lib():
     L.b2r_nn_distance.argtypes = [vp, vp, i32, vp, i32, vp, vp]
     L.b2r_icp.argtypes = [vp, vp, i32, vp, i32, d, vp, i32, d, d, C.POINTER(B2RIcpResult), vp]
     L.b2r_voxel_coverage.argtypes = [vp, vp, i32, d, ip]
+    L.b2r_voxel_coverage_noalloc.argtypes = [vp, vp, i32, d, vp]
     L.b2r_alignment_score.argtypes = [vp, vp, i32, vp, i32, vp, i32, d, vp]
     L.b2r_chamfer.argtypes = [vp, vp, i32, vp, i32, C.POINTER(C.c_double)]
     L.b2r_cloud_resolution.argtypes = [vp, vp, i32, i32, C.POINTER(C.c_double)]

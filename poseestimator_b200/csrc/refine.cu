@@ -675,4 +675,49 @@ b2r_status b2r_farthest_point_sample(b2r_solver* s, const double* pts_dev, int n
   return B2R_OK;
 }
 
+// ---- b2r_voxel_coverage_noalloc: the voxel-coverage count with its hash table in a file-scope device array (no allocation) ----
+// No counterpart in the reference; see include/b2r.h.  The table of b2r_voxel_coverage lives in the solver's workspace, which grows
+// with cudaMalloc; this variant keeps it in static device memory (4 MiB on every GPU that loads the library, until exit).
+constexpr int kNoAllocMaxPoints = B2R_VOXEL_NOALLOC_MAX_POINTS;
+constexpr unsigned kNoAllocTableCap = 2u * (unsigned)kNoAllocMaxPoints;   // table_cap(n) <= 2^20 slots for n <= 2^19
+static_assert((kNoAllocTableCap & (kNoAllocTableCap - 1)) == 0, "the table size must be a power of two");
+static __device__ __align__(256) int g_noalloc_table[kNoAllocTableCap];
+
+// In host code g_noalloc_table is a host-side stand-in for the symbol, not a device address: the address the kernels are given comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kNoAllocMaxDevices = 64;
+static int* g_noalloc_ptr[kNoAllocMaxDevices];   // zero-initialised: not yet resolved
+static std::mutex g_noalloc_mu;
+
+b2r_status b2r_voxel_coverage_noalloc(b2r_solver* s, const double* pts_dev, int n, double voxel, int* count_dev) {
+  B2R_NVTX("b2r:voxel_coverage_noalloc");
+  if (!s) return B2R_ERR_INVALID_ARG;
+  if (!pts_dev || n < 0 || !(voxel > 0) || !count_dev) return fail(s, B2R_ERR_INVALID_ARG, "voxel_coverage_noalloc arguments");
+  if (n > kNoAllocMaxPoints)
+    return fail(s, B2R_ERR_LIMIT, "voxel_coverage_noalloc: " + std::to_string(n) + " points exceed the static table's limit of " +
+                                      std::to_string(kNoAllocMaxPoints) + " (B2R_VOXEL_NOALLOC_MAX_POINTS); use b2r_voxel_coverage");
+  if (s->device < 0 || s->device >= kNoAllocMaxDevices) return fail(s, B2R_ERR_LIMIT, "voxel_coverage_noalloc: device index beyond 63");
+  CK(cudaSetDevice(s->device));
+  int* table = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[s->device]) {
+      void* p = nullptr;
+      CK(cudaGetSymbolAddress(&p, g_noalloc_table));
+      g_noalloc_ptr[s->device] = static_cast<int*>(p);
+    }
+    table = g_noalloc_ptr[s->device];
+  }
+  // every call shares the table, which still holds the last call's point ids: clear the slots this call can touch, and the count
+  const unsigned cap = table_cap(n);
+  CK(cudaMemsetAsync(table, 0, (size_t)cap * sizeof(int), s->stream));
+  CK(cudaMemsetAsync(count_dev, 0, sizeof(int), s->stream));
+  if (n > 0) {
+    voxel_count_kernel<<<(n + 255) / 256, 256, 0, s->stream>>>(pts_dev, n, voxel, table, cap - 1, count_dev);
+    s->launches += 1;
+  }
+  CK(cudaGetLastError());
+  return B2R_OK;
+}
+
 }  // extern "C"

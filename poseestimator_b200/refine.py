@@ -79,6 +79,18 @@ class Refiner(PreSteps):
         _lib.check(self._h, _lib.lib().b2r_voxel_coverage(self._h, p.data_ptr(), p.shape[0], float(voxel_size), C.byref(c)))
         return c.value
 
+    VOXEL_NOALLOC_MAX_POINTS = 524288   # include/b2r.h: B2R_VOXEL_NOALLOC_MAX_POINTS
+
+    def voxel_coverage_noalloc(self, points, voxel_size, count_out):
+        """b2r_voxel_coverage_noalloc (no counterpart in the reference): the same count, hash table in static device memory, nothing
+        allocated by the call.  points: [n,3] float64 CUDA tensor; count_out: int32 CUDA tensor of >= 1 element, written on the
+        handle's stream (valid after a synchronisation).  Calls that overlap on one GPU race (one shared table)."""
+        torch = _torch()
+        assert points.is_cuda and points.dtype == torch.float64 and points.is_contiguous() and points.shape[-1] == 3
+        assert count_out.is_cuda and count_out.dtype == torch.int32 and count_out.numel() >= 1
+        _lib.check(self._h, _lib.lib().b2r_voxel_coverage_noalloc(self._h, points.data_ptr(), points.shape[0], float(voxel_size),
+                                                                  count_out.data_ptr()))
+
     def alignment_score(self, src_aligned, src_down, dst_down, voxel_size, details=False):
         a, b, d = self._pts(src_aligned), self._pts(src_down), self._pts(dst_down)
         out = (C.c_double * 5)()
