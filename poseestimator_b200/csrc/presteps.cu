@@ -965,6 +965,7 @@ __global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* 
   const int r_first = max(o0, max(o1, o2));
   const int r_last = max(max(max(cq0, g.dim[0] - 1 - cq0), max(cq1, g.dim[1] - 1 - cq1)), max(cq2, g.dim[2] - 1 - cq2));
   int cur = 0, a = 0, nb = 0;
+  int r_begin = r_first;
   unsigned long long tk = ~0ull; int ti = 0x7fffffff;
   // ---- fast path (K <= 32): the whole 3 x 3 x 3 block of cells at once ------------------------------------------------------------
   // The shell walk below merges candidates into a sorted list batch by batch; its profile is 95 % selection machinery (sorts and merges
@@ -972,7 +973,8 @@ __global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* 
   // registers, the K-th smallest of the 32 per-lane minima is a threshold that at least K candidates meet (each of those K lanes
   // holds one) and, for evenly spread candidates, not many more; the candidates up to it are collected and sorted ONCE (knn_flush).
   // The answer is final when the list is full and its K-th distance lies within the reach of the block (or the radius does); any other
-  // case -- more than 512 candidates, more than 64 up to the threshold, a K-th neighbour outside the block -- takes the shell walk.
+  // case -- more than 512 candidates, more than 64 up to the threshold -- takes the shell walk; a K-th neighbour outside the block
+  // continues the walk at shell 2 from the list found here.
   if (K <= 32) {
     int rb = 0, re = 0;                       // lane t < 9: sorted range of x-run t of the block
     if (lane < 9) {
@@ -1054,12 +1056,15 @@ __global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* 
           if (lane == 0) cnt_out[q] = a;
           return;
         }
+        // not final: the list is what the walk would hold after shells 0 and 1 (the best K of every point of the block, same order),
+        // so the walk goes on at shell 2 with the K-th key as its threshold -- the block is not scanned again through the merges
         __syncwarp();
-        a = 0; cur = 0;        // not final: start the shell walk from scratch
+        r_begin = 2;
+        if (a == K) { tk = w.lk[cur][K - 1]; ti = w.li[cur][K - 1]; }
       }
     }
   }
-  for (int r = r_first; r <= r_last; ++r) {
+  for (int r = r_begin; r <= r_last; ++r) {
     for (int dz = -r; dz <= r; ++dz) {
       const int cz = cq2 + dz;
       if (cz < 0 || cz >= g.dim[2]) continue;
