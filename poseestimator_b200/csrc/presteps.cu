@@ -217,30 +217,62 @@ __device__ __forceinline__ double sq3_ref(double dx, double dy, double dz) {
   return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
+// One compare-exchange step of a bitonic network held in registers: element e = lane + 32 h of the 64-slot batch is register h of
+// `lane`; the partner e ^ j (j < 32) is the same register of lane ^ j.  keep_min: this side keeps the smaller of the two.
+__device__ __forceinline__ void knn_cx(unsigned long long& k, int& i, int j, bool keep_min) {
+  const unsigned long long ok = __shfl_xor_sync(0xffffffffu, k, j);
+  const int oi = __shfl_xor_sync(0xffffffffu, i, j);
+  const bool other_less = key_less(ok, oi, k, i);
+  if (other_less == keep_min) { k = ok; i = oi; }   // (equal entries are padding: either copy will do)
+}
+
+// ascending sort of the batch w.ck / w.ci [0, nb), padded to 32 or 64 slots with (~0, int max): a bitonic network on two registers per
+// lane and shuffles.  (Round 2: the shared-memory network it replaces -- 21 stages, two barriers-separated passes each with half the
+// lanes idle -- was 40 % of knn_grid_kernel's instructions on a config-2 frame.)  (key, index) is a strict total order, so the sorted
+// batch is the same whatever network produces it.
+__device__ __forceinline__ void knn_sort_batch(KnnWarpSmem& w, int nb, int lane) {
+  unsigned long long k0 = lane < nb ? w.ck[lane] : ~0ull;
+  int i0 = lane < nb ? w.ci[lane] : 0x7fffffff;
+  if (nb <= 32) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+      const bool up = k == 32 || (lane & k) == 0;
+#pragma unroll
+      for (int j = k >> 1; j > 0; j >>= 1) knn_cx(k0, i0, j, ((lane & j) == 0) == up);
+    }
+    __syncwarp();
+    w.ck[lane] = k0; w.ci[lane] = i0;
+  } else {
+    unsigned long long k1 = lane + 32 < nb ? w.ck[lane + 32] : ~0ull;
+    int i1 = lane + 32 < nb ? w.ci[lane + 32] : 0x7fffffff;
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+      // direction of element e = lane + 32 h in stage k: ascending when (e & k) == 0; for k == 32 that is h == 0
+      const bool up0 = k == 32 || (lane & k) == 0;
+      const bool up1 = k == 32 ? false : (lane & k) == 0;
+#pragma unroll
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        knn_cx(k0, i0, j, ((lane & j) == 0) == up0);
+        knn_cx(k1, i1, j, ((lane & j) == 0) == up1);
+      }
+    }
+    // k == 64: ascending everywhere; j == 32 pairs the two registers of a lane
+    if (key_less(k1, i1, k0, i0)) { const unsigned long long tk = k0; k0 = k1; k1 = tk; const int t = i0; i0 = i1; i1 = t; }
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+      knn_cx(k0, i0, j, (lane & j) == 0);
+      knn_cx(k1, i1, j, (lane & j) == 0);
+    }
+    __syncwarp();
+    w.ck[lane] = k0; w.ci[lane] = i0;
+    w.ck[lane + 32] = k1; w.ci[lane + 32] = i1;
+  }
+  __syncwarp();
+}
+
 // merge the (unsorted) candidate batch of size nb into the sorted list of size a; returns the new size (<= K)
 __device__ int knn_flush(KnnWarpSmem& w, int& cur, int a, int nb, int K, int lane) {
-  // pad + bitonic sort of the 64-slot batch
-  for (int e = nb + lane; e < kKnnBuf; e += 32) { w.ck[e] = ~0ull; w.ci[e] = 0x7fffffff; }
-  __syncwarp();
-#pragma unroll 1
-  for (int k = 2; k <= kKnnBuf; k <<= 1) {
-#pragma unroll 1
-    for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int i = lane + 32 * h;
-        const int l = i ^ j;
-        if (l > i) {
-          const unsigned long long ki = w.ck[i], kl = w.ck[l];
-          const int ii = w.ci[i], il = w.ci[l];
-          const bool up = (i & k) == 0;
-          const bool sw = up ? key_less(kl, il, ki, ii) : key_less(ki, ii, kl, il);
-          if (sw) { w.ck[i] = kl; w.ck[l] = ki; w.ci[i] = il; w.ci[l] = ii; }
-        }
-      }
-      __syncwarp();
-    }
-  }
+  knn_sort_batch(w, nb, lane);
   const unsigned long long* A = w.lk[cur]; const int* Ai = w.li[cur];
   unsigned long long* O = w.lk[cur ^ 1]; int* Oi = w.li[cur ^ 1];
   for (int e = lane; e < a; e += 32) {   // rank of A[e] = e + |{B < A[e]}|
@@ -945,7 +977,7 @@ __device__ __forceinline__ int2 cell_points(const int2* __restrict__ cell_range,
 
 struct KnnGridSmem { KnnWarpSmem w[kKnnWarps]; };
 
-__global__ void __launch_bounds__(kKnnWarps * 32) knn_grid_kernel(const double* __restrict__ spts, const uint32_t* __restrict__ sidx, int n,
+__global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const double* __restrict__ spts, const uint32_t* __restrict__ sidx, int n,
                                                                   const GridDev* __restrict__ gp, const int2* __restrict__ cell_range,
                                                                   const double* __restrict__ queries, int nq, int K, double radius,
                                                                   int* __restrict__ idx_out, double* __restrict__ d2_out, int* __restrict__ cnt_out,
