@@ -1026,16 +1026,16 @@ __global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const doubl
 #pragma unroll
     for (int o = 1; o < 16; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
     const int C = __shfl_sync(FULL, incl, 8);
-    constexpr int kSlots = 16;
+    constexpr int kSlots = 12;
     if (inside && C > 0 && C <= 32 * kSlots) {
       unsigned long long dk[kSlots];
-      int di[kSlots];
-      unsigned long long mymin = ~0ull; int mymin_i = 0x7fffffff;
+      int dp[kSlots];                           // position in the sorted array (the point id is loaded only for the candidates kept)
+      unsigned long long mymin = ~0ull;
       int run = 0, run_end = __shfl_sync(FULL, incl, 0), run_b = __shfl_sync(FULL, rb, 0), run_first = 0;
 #pragma unroll
       for (int sl = 0; sl < kSlots; ++sl) {
         const int c = lane + 32 * sl;
-        dk[sl] = ~0ull; di[sl] = 0x7fffffff;
+        dk[sl] = ~0ull; dp[sl] = 0;
         // (uniform trip count: every lane takes part in the shuffles)
         while (true) {
           const bool adv = c < C && c >= run_end;
@@ -1048,24 +1048,25 @@ __global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const doubl
           const int sp = run_b + (c - run_first);
           const double d2 = sq3_ref(__dsub_rn(spts[3 * (size_t)sp], qx), __dsub_rn(spts[3 * (size_t)sp + 1], qy), __dsub_rn(spts[3 * (size_t)sp + 2], qz));
           if (!use_r || d2 < r2) {
-            dk[sl] = (unsigned long long)__double_as_longlong(d2); di[sl] = (int)sidx[sp];
-            if (key_less(dk[sl], di[sl], mymin, mymin_i)) { mymin = dk[sl]; mymin_i = di[sl]; }
+            dk[sl] = (unsigned long long)__double_as_longlong(d2); dp[sl] = sp;
+            mymin = dk[sl] < mymin ? dk[sl] : mymin;
           }
         }
       }
-      // K-th smallest of the 32 lane minima: rank by counting (32 shuffles), strict total order on (key, id)
+      // K-th smallest of the 32 lane minima, ordered by (key, lane): rank by counting (32 shuffles).  Every candidate with a key up to
+      // it is kept -- at least K (one per lane of rank < K); ties on the key only add candidates, the sort below decides by (key, id).
       int rank = 0;
       for (int j = 0; j < 32; ++j) {
-        const unsigned long long ok = __shfl_sync(FULL, mymin, j); const int oi = __shfl_sync(FULL, mymin_i, j);
-        rank += key_less(ok, oi, mymin, mymin_i) ? 1 : 0;
+        const unsigned long long ok = __shfl_sync(FULL, mymin, j);
+        rank += (ok < mymin || (ok == mymin && j < lane)) ? 1 : 0;
       }
       const unsigned pick = __ballot_sync(FULL, rank == K - 1 && mymin != ~0ull);
       const int n_valid_lanes = __popc(__ballot_sync(FULL, mymin != ~0ull));
-      unsigned long long thr_k = ~0ull; int thr_i = 0x7fffffff;        // fewer than K lanes hold anything: take everything
-      if (n_valid_lanes >= K && pick) { const int src = __ffs(pick) - 1; thr_k = __shfl_sync(FULL, mymin, src); thr_i = __shfl_sync(FULL, mymin_i, src); }
+      unsigned long long thr_k = ~0ull - 1ull;                         // fewer than K lanes hold anything: take everything (padding is ~0)
+      if (n_valid_lanes >= K && pick) thr_k = __shfl_sync(FULL, mymin, __ffs(pick) - 1);
       int mine = 0;
 #pragma unroll
-      for (int sl = 0; sl < kSlots; ++sl) mine += (dk[sl] != ~0ull && !key_less(thr_k, thr_i, dk[sl], di[sl])) ? 1 : 0;
+      for (int sl = 0; sl < kSlots; ++sl) mine += dk[sl] <= thr_k ? 1 : 0;
       int pre = mine;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, pre, o); if (lane >= o) pre += t; }
@@ -1074,7 +1075,7 @@ __global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const doubl
         int pos = pre - mine;
 #pragma unroll
         for (int sl = 0; sl < kSlots; ++sl)
-          if (dk[sl] != ~0ull && !key_less(thr_k, thr_i, dk[sl], di[sl])) { w.ck[pos] = dk[sl]; w.ci[pos] = di[sl]; ++pos; }
+          if (dk[sl] <= thr_k) { w.ck[pos] = dk[sl]; w.ci[pos] = (int)sidx[dp[sl]]; ++pos; }
         __syncwarp();
         a = knn_flush(w, cur, 0, total, K, lane);
         const double reach1 = g.h * (1.0 - 1e-9);
