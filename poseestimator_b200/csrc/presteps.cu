@@ -977,7 +977,7 @@ __device__ __forceinline__ int2 cell_points(const int2* __restrict__ cell_range,
 
 struct KnnGridSmem { KnnWarpSmem w[kKnnWarps]; };
 
-__global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const double* __restrict__ spts, const uint32_t* __restrict__ sidx, int n,
+__global__ void __launch_bounds__(kKnnWarps * 32, 5) knn_grid_kernel(const double* __restrict__ spts, const uint32_t* __restrict__ sidx, int n,
                                                                   const GridDev* __restrict__ gp, const int2* __restrict__ cell_range,
                                                                   const double* __restrict__ queries, int nq, int K, double radius,
                                                                   int* __restrict__ idx_out, double* __restrict__ d2_out, int* __restrict__ cnt_out,
@@ -1005,7 +1005,7 @@ __global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const doubl
   // registers, the K-th smallest of the 32 per-lane minima is a threshold that at least K candidates meet (each of those K lanes
   // holds one) and, for evenly spread candidates, not many more; the candidates up to it are collected and sorted ONCE (knn_flush).
   // The answer is final when the list is full and its K-th distance lies within the reach of the block (or the radius does); any other
-  // case -- more than 512 candidates, more than 64 up to the threshold -- takes the shell walk; a K-th neighbour outside the block
+  // case -- more than 64 candidates up to the threshold -- takes the shell walk; a K-th neighbour outside the block
   // continues the walk at shell 2 from the list found here.
   if (K <= 32) {
     int rb = 0, re = 0;                       // lane t < 9: sorted range of x-run t of the block
@@ -1026,33 +1026,32 @@ __global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const doubl
 #pragma unroll
     for (int o = 1; o < 16; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
     const int C = __shfl_sync(FULL, incl, 8);
-    constexpr int kSlots = 12;
-    if (inside && C > 0 && C <= 32 * kSlots) {
-      unsigned long long dk[kSlots];
-      int dp[kSlots];                           // position in the sorted array (the point id is loaded only for the candidates kept)
-      unsigned long long mymin = ~0ull;
-      int run = 0, run_end = __shfl_sync(FULL, incl, 0), run_b = __shfl_sync(FULL, rb, 0), run_first = 0;
-#pragma unroll
-      for (int sl = 0; sl < kSlots; ++sl) {
-        const int c = lane + 32 * sl;
-        dk[sl] = ~0ull; dp[sl] = 0;
-        // (uniform trip count: every lane takes part in the shuffles)
-        while (true) {
-          const bool adv = c < C && c >= run_end;
-          if (!__any_sync(FULL, adv)) break;
-          const int nr = min(run + 1, 8);
-          const int ne = __shfl_sync(FULL, incl, adv ? nr : 0), nbg = __shfl_sync(FULL, rb, adv ? nr : 0);
-          if (adv) { run_first = run_end; run = nr; run_end = ne; run_b = nbg; }
-        }
-        if (c < C) {
-          const int sp = run_b + (c - run_first);
-          const double d2 = sq3_ref(__dsub_rn(spts[3 * (size_t)sp], qx), __dsub_rn(spts[3 * (size_t)sp + 1], qy), __dsub_rn(spts[3 * (size_t)sp + 2], qz));
-          if (!use_r || d2 < r2) {
-            dk[sl] = (unsigned long long)__double_as_longlong(d2); dp[sl] = sp;
-            mymin = dk[sl] < mymin ? dk[sl] : mymin;
+    if (inside && C > 0) {
+      // two passes over the block's candidates, nothing held between them but the threshold (the points are L1-resident for the
+      // second pass; holding 12 - 16 candidates per lane in registers cost spills at 4 CTAs per SM and capped the block at 512)
+      auto for_each_candidate = [&](auto&& f) {
+        int run = 0, run_end = __shfl_sync(FULL, incl, 0), run_b = __shfl_sync(FULL, rb, 0), run_first = 0;
+        for (int c0 = 0; c0 < C; c0 += 32) {
+          const int c = c0 + lane;
+          while (true) {   // (uniform trip count: every lane takes part in the shuffles)
+            const bool adv = c < C && c >= run_end;
+            if (!__any_sync(FULL, adv)) break;
+            const int nr = min(run + 1, 8);
+            const int ne = __shfl_sync(FULL, incl, adv ? nr : 0), nbg = __shfl_sync(FULL, rb, adv ? nr : 0);
+            if (adv) { run_first = run_end; run = nr; run_end = ne; run_b = nbg; }
           }
+          unsigned long long key = ~0ull;
+          int sp = 0;
+          if (c < C) {
+            sp = run_b + (c - run_first);
+            const double d2 = sq3_ref(__dsub_rn(spts[3 * (size_t)sp], qx), __dsub_rn(spts[3 * (size_t)sp + 1], qy), __dsub_rn(spts[3 * (size_t)sp + 2], qz));
+            if (!use_r || d2 < r2) key = (unsigned long long)__double_as_longlong(d2);
+          }
+          if (!f(key, sp)) break;
         }
-      }
+      };
+      unsigned long long mymin = ~0ull;
+      for_each_candidate([&](unsigned long long key, int) { mymin = key < mymin ? key : mymin; return true; });
       // K-th smallest of the 32 lane minima, ordered by (key, lane): rank by counting (32 shuffles).  Every candidate with a key up to
       // it is kept -- at least K (one per lane of rank < K); ties on the key only add candidates, the sort below decides by (key, id).
       int rank = 0;
@@ -1064,18 +1063,17 @@ __global__ void __launch_bounds__(kKnnWarps * 32, 4) knn_grid_kernel(const doubl
       const int n_valid_lanes = __popc(__ballot_sync(FULL, mymin != ~0ull));
       unsigned long long thr_k = ~0ull - 1ull;                         // fewer than K lanes hold anything: take everything (padding is ~0)
       if (n_valid_lanes >= K && pick) thr_k = __shfl_sync(FULL, mymin, __ffs(pick) - 1);
-      int mine = 0;
-#pragma unroll
-      for (int sl = 0; sl < kSlots; ++sl) mine += dk[sl] <= thr_k ? 1 : 0;
-      int pre = mine;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, pre, o); if (lane >= o) pre += t; }
-      const int total = __shfl_sync(FULL, pre, 31);
+      int total = 0;
+      for_each_candidate([&](unsigned long long key, int sp) {
+        const bool keep = key <= thr_k;
+        const unsigned bal = __ballot_sync(FULL, keep);
+        const int cnt = __popc(bal);
+        if (total + cnt > kKnnBuf) { total = kKnnBuf + 1; return false; }   // uniform: more than one batch up to the threshold
+        if (keep) { const int pos = total + __popc(bal & ((1u << lane) - 1u)); w.ck[pos] = key; w.ci[pos] = (int)sidx[sp]; }
+        total += cnt;
+        return true;
+      });
       if (total <= kKnnBuf) {
-        int pos = pre - mine;
-#pragma unroll
-        for (int sl = 0; sl < kSlots; ++sl)
-          if (dk[sl] <= thr_k) { w.ck[pos] = dk[sl]; w.ci[pos] = (int)sidx[dp[sl]]; ++pos; }
         __syncwarp();
         a = knn_flush(w, cur, 0, total, K, lane);
         const double reach1 = g.h * (1.0 - 1e-9);
