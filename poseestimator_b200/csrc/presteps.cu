@@ -758,43 +758,62 @@ __global__ void __launch_bounds__(kFpWarps * 32) spfh_kernel(const double* __res
 __global__ void __launch_bounds__(kFpWarps * 32) fpfh_kernel(const double* __restrict__ spfh_t, int n, const int* __restrict__ idx,
                                                              const double* __restrict__ d2, const int* __restrict__ cnt, int K,
                                                              double* __restrict__ out /*[33][n]*/) {
-  __shared__ double sv[kFpWarps][34];
+  // Neighbours are taken kFpBatch at a time: the batch's SPFH rows are loaded and divided together (independent fp64 divisions
+  // overlap; one at a time, the division's ~400 cycles of dependent latency and two warp barriers were paid per neighbour and the
+  // kernel ran at ~1000 cycles per neighbour), then added in neighbour order.  A neighbour beyond the count, or at distance zero (the
+  // reference skips it), contributes +0.0 to sums that are never negative: the same bits as not adding it.
+  constexpr int kFpBatch = 8;
+  __shared__ double sv[kFpWarps][kFpBatch][34];
+  __shared__ int s_idx[kFpWarps][kKnnMaxK];
+  __shared__ double s_d2[kFpWarps][kKnnMaxK];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * kFpWarps + warp;
   if (i >= n) return;
   const int c = cnt[i];
-  double acc = 0.0, acc32 = 0.0;  // bin `lane`; lane 31 also owns bin 32
-  double gsum = 0.0;              // lanes 0..2: group sums
-  if (c > 1) {
-    // the next neighbour's SPFH row is fetched while the current one is accumulated (two dependent loads per neighbour otherwise)
-    int jn = idx[(size_t)i * K + 1];
-    double dn = d2[(size_t)i * K + 1];
-    double rown = spfh_t[(size_t)jn * 33 + lane], row32n = lane == 31 ? spfh_t[(size_t)jn * 33 + 32] : 0.0;
-    for (int t = 1; t < c; ++t) {
-      const double dist = dn, row = rown, row32 = row32n;
-      if (t + 1 < c) {
-        jn = idx[(size_t)i * K + t + 1];
-        dn = d2[(size_t)i * K + t + 1];
-        rown = spfh_t[(size_t)jn * 33 + lane];
-        if (lane == 31) row32n = spfh_t[(size_t)jn * 33 + 32];
-      }
-      if (dist == 0.0) continue;  // warp-uniform
-      const double v = __ddiv_rn(row, dist);
-      const double v32 = lane == 31 ? __ddiv_rn(row32, dist) : 0.0;
-      acc = __dadd_rn(acc, v);
-      acc32 = __dadd_rn(acc32, v32);
-      // group g (lane g < 3) adds its 11 bins in bin order: bins 11g .. 11g+10.  Through shared memory: one store per lane and eleven
-      // broadcast-free loads for three lanes instead of 44 shuffles per neighbour (the kernel is bound by instruction issue)
-      sv[warp][lane] = v;
-      if (lane == 31) sv[warp][32] = v32;
-      __syncwarp();
-      if (lane < 3) {
+  for (int t = lane; t < c; t += 32) { s_idx[warp][t] = idx[(size_t)i * K + t]; s_d2[warp][t] = d2[(size_t)i * K + t]; }
+  __syncwarp();
+  double acc = 0.0;    // bin `lane`
+  double acc32 = 0.0;  // lane 3: bin 32 (the 33rd bin of the batch's neighbours is divided by lanes 0 .. kFpBatch-1 in ONE pass -- a second
+                       // division per neighbour for lane 31 alone cost the warp as many instructions as the other 32 bins)
+  double gsum = 0.0;   // lanes 0..2: group sums
+  for (int t0 = 1; t0 < c; t0 += kFpBatch) {
+    double row[kFpBatch], dist[kFpBatch];
 #pragma unroll
-        for (int k = 0; k < 11; ++k) gsum = __dadd_rn(gsum, sv[warp][11 * lane + k]);
-      }
-      __syncwarp();
+    for (int b = 0; b < kFpBatch; ++b) {
+      const int t = t0 + b;
+      const bool ok = t < c;
+      const int j = ok ? s_idx[warp][t] : i;
+      dist[b] = ok ? s_d2[warp][t] : 0.0;
+      row[b] = spfh_t[(size_t)j * 33 + lane];
     }
+    {
+      const int t = t0 + lane;
+      const bool ok = lane < kFpBatch && t < c;
+      const double dd = ok ? s_d2[warp][t] : 0.0;
+      const double r32 = ok ? spfh_t[(size_t)s_idx[warp][t] * 33 + 32] : 0.0;
+      const double v32 = dd != 0.0 ? __ddiv_rn(r32, dd) : 0.0;
+      if (lane < kFpBatch) sv[warp][lane][32] = v32;
+    }
+#pragma unroll
+    for (int b = 0; b < kFpBatch; ++b) {
+      const double v = dist[b] != 0.0 ? __ddiv_rn(row[b], dist[b]) : 0.0;
+      sv[warp][b][lane] = v;
+      acc = __dadd_rn(acc, v);
+    }
+    __syncwarp();
+    // group g (lane g < 3) adds its 11 bins in bin order, neighbour after neighbour: bins 11g .. 11g+10; lane 3 adds bin 32
+    if (lane < 3) {
+#pragma unroll
+      for (int b = 0; b < kFpBatch; ++b)
+#pragma unroll
+        for (int k = 0; k < 11; ++k) gsum = __dadd_rn(gsum, sv[warp][b][11 * lane + k]);
+    } else if (lane == 3) {
+#pragma unroll
+      for (int b = 0; b < kFpBatch; ++b) acc32 = __dadd_rn(acc32, sv[warp][b][32]);
+    }
+    __syncwarp();
   }
+  acc32 = __shfl_sync(FULL, acc32, 3);   // lane 31 writes bin 32 below
   // scale by 100 / group sum, add the point's own SPFH
   double g0 = __shfl_sync(FULL, gsum, 0), g1 = __shfl_sync(FULL, gsum, 1), g2 = __shfl_sync(FULL, gsum, 2);
   if (g0 != 0.0) g0 = __ddiv_rn(100.0, g0);
