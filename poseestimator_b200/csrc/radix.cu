@@ -109,6 +109,50 @@ __global__ void __launch_bounds__(256) radix_rowscan_kernel(uint32_t* __restrict
   }
 }
 
+// Small tables (256 * n_tiles <= 32768 entries: sorts below 128 tiles, e.g. the 56 k points of a depth frame): the exclusive scan in
+// (digit, tile) order is a scan of the table as one linear array, done by ONE CTA in one launch instead of the row-sum and row-scan
+// pair -- at this size every launch of the sort is latency, not bandwidth.
+constexpr int kRxScanThreads = 1024;
+constexpr int kRxScanMaxTiles = 128;
+__global__ void __launch_bounds__(kRxScanThreads) radix_tablescan_kernel(uint32_t* __restrict__ table, int n_tiles, RxBatch rb) {
+  if (rb.n_arr) table += blockIdx.y * rb.table_stride;
+  extern __shared__ uint32_t rx_tab[];   // the whole table: 256 * n_tiles words (<= 128 KB)
+  __shared__ uint32_t wsum[32];
+  const int total = 256 * n_tiles;
+  // coalesced copy in, every load of a thread independent of the others (one memory latency for the lot)
+  for (int e0 = 0; e0 < total; e0 += 8 * kRxScanThreads) {
+    uint32_t v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const int e = e0 + u * kRxScanThreads + threadIdx.x; v[u] = e < total ? table[e] : 0u; }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const int e = e0 + u * kRxScanThreads + threadIdx.x; if (e < total) rx_tab[e] = v[u]; }
+  }
+  __syncthreads();
+  const int L = (total + kRxScanThreads - 1) / kRxScanThreads;   // <= 32 consecutive entries per thread
+  const int b0 = threadIdx.x * L;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t sum = 0;
+  for (int k = 0; k < L; ++k) if (b0 + k < total) sum += rx_tab[b0 + k];
+  uint32_t x = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) wsum[warp] = x;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t w = wsum[lane];
+    uint32_t xi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, xi, o); if (lane >= o) xi += y; }
+    wsum[lane] = xi - w;
+  }
+  __syncthreads();
+  uint32_t run = wsum[warp] + x - sum;
+  for (int k = 0; k < L; ++k)
+    if (b0 + k < total) { const uint32_t v = rx_tab[b0 + k]; rx_tab[b0 + k] = run; run += v; }
+  __syncthreads();
+  for (int e = threadIdx.x; e < total; e += kRxScanThreads) table[e] = rx_tab[e];
+}
+
 template <int ITEMS>
 __global__ void __launch_bounds__(kRxThreads) radix_scatter_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                                    uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
@@ -198,8 +242,15 @@ int radix_sort_pairs_batched(uint64_t* keys, uint32_t* vals, uint64_t* keys_alt,
   for (int shift = begin_bit; shift < end_bit; shift += 8) {
     if (small) radix_hist_kernel<kRxSmallItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles, rb);
     else radix_hist_kernel<kRxItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, n, shift, table, n_tiles, rb);
-    radix_rowsum_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
-    radix_rowscan_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
+    if (n_tiles <= kRxScanMaxTiles) {
+      static PerDeviceOnce attr;
+      attr.run([] { return cudaFuncSetAttribute(radix_tablescan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kRxScanMaxTiles * 4); });
+      radix_tablescan_kernel<<<dim3(1, by), kRxScanThreads, (size_t)256 * n_tiles * 4, st>>>(table, n_tiles, rb);
+      launches -= 1;
+    } else {
+      radix_rowsum_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
+      radix_rowscan_kernel<<<dim3(256, by), 256, 0, st>>>(table, n_tiles, totals, rb);
+    }
     if (small) radix_scatter_kernel<kRxSmallItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles, rb);
     else radix_scatter_kernel<kRxItems><<<dim3(n_tiles, by), kRxThreads, 0, st>>>(ki, vi, ko, vo, n, shift, table, n_tiles, rb);
     launches += 4;
