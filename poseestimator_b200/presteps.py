@@ -20,11 +20,18 @@ import numpy as np
 from . import _lib
 
 
+_TORCH = None
+
+
 def _torch():
-    import torch
-    if not torch.cuda.is_available():
-        raise RuntimeError("poseestimator_b200.presteps: no CUDA device is visible and there is no CPU fallback")
-    return torch
+    """torch, once a CUDA device has been seen (the check costs ~4 us and a frame's wrappers ask 30 times: cached after success)."""
+    global _TORCH
+    if _TORCH is None:
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("poseestimator_b200.presteps: no CUDA device is visible and there is no CPU fallback")
+        _TORCH = torch
+    return _TORCH
 
 
 class PreSteps:
