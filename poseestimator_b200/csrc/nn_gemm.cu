@@ -139,16 +139,8 @@ __global__ void __launch_bounds__(1024) nn_centre_kernel(const double* __restric
   const int rows = n < kCentreRows ? n : kCentreRows;
   const int t = threadIdx.x % kKSeg, r0 = threadIdx.x / kKSeg;      // 1024 / 40 = 25 row lanes (threads 1000..1023 idle)
   double s = 0.0;
-  if (r0 < 25 && t < dim) {
-    // eight loads in flight per thread (one accumulator each, summed in a fixed order): the loop is L2 latency, 144 dependent
-    // iterations for a 3600-row template took 20 us on one CTA
-    double a8[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int r = r0; r < rows; r += 200) {
-#pragma unroll
-      for (int u = 0; u < 8; ++u) { const int rr = r + 25 * u; if (rr < rows) a8[u] += f[(size_t)rr * dim + t]; }
-    }
-    s = ((a8[0] + a8[1]) + (a8[2] + a8[3])) + ((a8[4] + a8[5]) + (a8[6] + a8[7]));
-  }
+  if (r0 < 25 && t < dim)
+    for (int r = r0; r < rows; r += 25) s += f[(size_t)r * dim + t];
   if (r0 < 25) part[r0][t] = s;
   __syncthreads();
   if (threadIdx.x < kKSeg) {

@@ -165,16 +165,21 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(unsigned int* __restric
   if (threadIdx.x == 0) *count = (int)carry_s;
 }
 
-// ordered compaction of 3-vectors by a keep mask (thread per point); idx_out optional
+constexpr int kCompactTile = 1024;
+// ordered compaction of 3-vectors by a keep mask (four points per thread); idx_out optional
 __global__ void __launch_bounds__(256) compact_points_kernel(const double* __restrict__ pts, const unsigned char* __restrict__ keep,
                                                              int n, double* __restrict__ out, int* __restrict__ idx_out,
                                                              unsigned long long* ws, int* count) {
   __shared__ int s_tile;
   __shared__ unsigned s_warp[8];
   __shared__ unsigned long long s_base;
+  // tiles of 1024 points, four consecutive points per thread: the look-back is a serial chain over the tiles (~50 ns a link), a
+  // 56 k-point frame has 56 links instead of 221
   const int tile = take_ticket(ws, &s_tile);
-  const int i = tile * 256 + threadIdx.x;
-  const unsigned k = (i < n && keep[i]) ? 1u : 0u;
+  const int i0 = tile * kCompactTile + 4 * threadIdx.x;
+  unsigned kk[4], k = 0;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) { kk[u] = (i0 + u < n && keep[i0 + u]) ? 1u : 0u; k += kk[u]; }
   unsigned blk_total;
   const unsigned local = block_scan_256(k, s_warp, &blk_total);
   if (threadIdx.x == 0) {
@@ -182,10 +187,15 @@ __global__ void __launch_bounds__(256) compact_points_kernel(const double* __res
     if (tile == (int)gridDim.x - 1) *count = (int)(s_base + blk_total);
   }
   __syncthreads();
-  if (k) {
-    const size_t m = (size_t)s_base + local;
-    out[3 * m] = pts[3 * (size_t)i]; out[3 * m + 1] = pts[3 * (size_t)i + 1]; out[3 * m + 2] = pts[3 * (size_t)i + 2];
-    if (idx_out) idx_out[m] = i;
+  size_t m = (size_t)s_base + local;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    if (kk[u]) {
+      const int i = i0 + u;
+      out[3 * m] = pts[3 * (size_t)i]; out[3 * m + 1] = pts[3 * (size_t)i + 1]; out[3 * m + 2] = pts[3 * (size_t)i + 2];
+      if (idx_out) idx_out[m] = i;
+      ++m;
+    }
   }
 }
 
@@ -504,8 +514,17 @@ __global__ void __launch_bounds__(256) voxel_heads_kernel(const unsigned long lo
   __shared__ unsigned s_warp[8];
   __shared__ unsigned long long s_base;
   const int tile = take_ticket(ws, &s_tile);
-  const int e = tile * 256 + threadIdx.x;
-  const unsigned head = (e < n && (e == 0 || keys[e] != keys[e - 1])) ? 1u : 0u;
+  const int e0 = tile * kCompactTile + 4 * threadIdx.x;   // four consecutive keys per thread (see compact_points_kernel)
+  unsigned hh[4], head = 0;
+  unsigned long long prev = e0 > 0 && e0 - 1 < n ? keys[e0 - 1] : 0ull;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int e = e0 + u;
+    const unsigned long long k = e < n ? keys[e] : 0ull;
+    hh[u] = (e < n && (e == 0 || k != prev)) ? 1u : 0u;
+    head += hh[u];
+    prev = k;
+  }
   unsigned blk_total;
   const unsigned local = block_scan_256(head, s_warp, &blk_total);
   if (threadIdx.x == 0) {
@@ -513,7 +532,9 @@ __global__ void __launch_bounds__(256) voxel_heads_kernel(const unsigned long lo
     if (tile == (int)gridDim.x - 1) *count = (int)(s_base + blk_total);
   }
   __syncthreads();
-  if (head) seg_start[s_base + local] = e;
+  unsigned long long m = s_base + local;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) if (hh[u]) seg_start[m++] = e0 + u;
 }
 
 // one thread per voxel: mean of its points in ascending point index (the order the sequential insert produces)
@@ -525,10 +546,23 @@ __global__ void __launch_bounds__(128) voxel_mean_kernel(const double* __restric
   if (v >= V) return;
   const int b = seg_start[v], e = (v + 1 < V) ? seg_start[v + 1] : n;
   double ax = 0, ay = 0, az = 0;
-  for (int s = b; s < e; ++s) {
-    const uint32_t i = sorted_idx[s];
-    ax = __dadd_rn(ax, pts[3 * (size_t)i]); ay = __dadd_rn(ay, pts[3 * (size_t)i + 1]); az = __dadd_rn(az, pts[3 * (size_t)i + 2]);
-    if (vox_of_point) vox_of_point[i] = v;
+  // eight points at a time: their indices, then their coordinates, are loaded together (two memory latencies per eight points instead
+  // of two per point -- a voxel of a depth frame holds ~17 points and the kernel was a chain of dependent L2 round trips); the sums
+  // stay sequential in ascending point index
+  for (int s0 = b; s0 < e; s0 += 8) {
+    uint32_t i8[8];
+    double x8[8], y8[8], z8[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) i8[u] = sorted_idx[min(s0 + u, e - 1)];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { x8[u] = pts[3 * (size_t)i8[u]]; y8[u] = pts[3 * (size_t)i8[u] + 1]; z8[u] = pts[3 * (size_t)i8[u] + 2]; }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (s0 + u < e) {
+        ax = __dadd_rn(ax, x8[u]); ay = __dadd_rn(ay, y8[u]); az = __dadd_rn(az, z8[u]);
+        if (vox_of_point) vox_of_point[i8[u]] = v;
+      }
+    }
   }
   const double c = (double)(e - b);
   out[3 * (size_t)v] = __ddiv_rn(ax, c); out[3 * (size_t)v + 1] = __ddiv_rn(ay, c); out[3 * (size_t)v + 2] = __ddiv_rn(az, c);
@@ -1411,7 +1445,7 @@ b2r_status b2r_statistical_outlier(b2r_solver* s, const double* pts_dev, int n, 
   s->launches += 3;
   if (pts_out_dev) {
     CK(cudaMemsetAsync(ws, 0, 8 * (size_t)(tiles + 2), st));
-    compact_points_kernel<<<tiles, 256, 0, st>>>(pts_dev, keep, n, pts_out_dev, idx_out_dev, ws, d_count);
+    compact_points_kernel<<<(n + kCompactTile - 1) / kCompactTile, 256, 0, st>>>(pts_dev, keep, n, pts_out_dev, idx_out_dev, ws, d_count);
     ++s->launches;
     CK(cudaMemcpyAsync(kept_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
@@ -1476,7 +1510,7 @@ b2r_status b2r_voxel_down(b2r_solver* s, const double* pts_dev, int n, double vo
   const unsigned long long* sk = in_alt ? keys_alt : keys;
   const uint32_t* sv = in_alt ? vals_alt : vals;
   CK(cudaMemsetAsync(ws, 0, 8 * (size_t)(tiles + 2), st));
-  voxel_heads_kernel<<<tiles, 256, 0, st>>>(sk, n, seg_start, ws, d_count);
+  voxel_heads_kernel<<<(n + kCompactTile - 1) / kCompactTile, 256, 0, st>>>(sk, n, seg_start, ws, d_count);
   voxel_mean_kernel<<<(n + 127) / 128, 128, 0, st>>>(pts_dev, n, sv, seg_start, d_count, out_dev, voxel_of_point_dev, counts_dev);
   s->launches += 2;
   CK(cudaMemcpyAsync(n_voxels_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, st));
