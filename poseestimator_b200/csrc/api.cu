@@ -338,6 +338,53 @@ b2r_status check_index(b2r_solver* s, int idx) {
 
 // ---- used by shard.cu ------------------------------------------------------------------------------------------------
 // workspace for one problem of n correspondences; with operands: state cleared and the descriptor of problem 0 on the device
+namespace {
+__global__ void __launch_bounds__(32) publish_words_kernel(const unsigned* __restrict__ src, int n, volatile unsigned* mbox, unsigned seq) {
+  const int t = threadIdx.x;
+  if (t < n) mbox[2 + t] = src[t];
+  __threadfence_system();
+  __syncwarp();
+  if (t == 0) mbox[0] = seq;
+}
+}  // namespace
+
+b2r_status b2r_internal_read_words(b2r_solver* s, const void* dev_words, int n_words, void* host_out) {
+  if (n_words < 1 || n_words > 30) return fail(s, B2R_ERR_INVALID_ARG, "internal: read_words size");
+  static const bool off = [] { const char* e = getenv("B2R_NO_MAILBOX"); return e && *e && *e != '0'; }();
+  if (off) {   // the plain form, for A/B measurements
+    CK(cudaMemcpyAsync(host_out, dev_words, 4 * (size_t)n_words, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    return B2R_OK;
+  }
+  if (!s->mbox_h) {
+    void* h = nullptr; void* d = nullptr;
+    CK(cudaHostAlloc(&h, 256, cudaHostAllocMapped));
+    memset(h, 0, 256);
+    cudaError_t e = cudaHostGetDevicePointer(&d, h, 0);
+    if (e != cudaSuccess) { cudaFreeHost(h); CK(e); }
+    s->mbox_h = static_cast<volatile unsigned*>(h); s->mbox_d = static_cast<unsigned*>(d); s->mbox_seq = 0;
+  }
+  unsigned seq = ++s->mbox_seq;
+  if (seq == 0) seq = ++s->mbox_seq;
+  publish_words_kernel<<<1, 32, 0, s->stream>>>(static_cast<const unsigned*>(dev_words), n_words, s->mbox_d, seq);
+  ++s->launches;
+  CK(cudaGetLastError());
+  for (unsigned long long it = 1;; ++it) {
+    if (s->mbox_h[0] == seq) break;
+    if ((it & 0x3fffull) == 0) {   // a faulted kernel never publishes: ask the stream now and then
+      const cudaError_t e = cudaStreamQuery(s->stream);
+      if (e != cudaSuccess && e != cudaErrorNotReady) CK(e);
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  unsigned* out = static_cast<unsigned*>(host_out);
+  for (int i = 0; i < n_words; ++i) out[i] = s->mbox_h[2 + i];
+  return B2R_OK;
+}
+
 b2r_status b2r_internal_prepare_single(b2r_solver* s, int n, const double* src_dev, const double* dst_dev) {
   b2r_status r = ensure_workspace(s, 1, n);
   if (r != B2R_OK) return r;
@@ -431,6 +478,7 @@ b2r_status b2r_destroy(b2r_solver* s) {
   s->d_pts.release(); s->d_adj.release(); s->d_cadj.release(); s->d_int.release(); s->d_dbl.release(); s->d_u8.release();
   s->d_pts32.release(); s->d_amb.release(); s->d_state.release(); s->d_desc.release(); s->d_arena.release(); s->d_scale.release(); s->d_pre.release(); s->d_nn.release(); s->d_grid.release(); s->d_refine.release(); s->h_refine.release();
   s->h_state.release(); s->h_desc.release(); s->h_pts.release();
+  if (s->mbox_h) { cudaFreeHost(const_cast<unsigned*>(s->mbox_h)); s->mbox_h = nullptr; }
   if (s->ev_ready) for (int i = 0; i < 12; ++i) cudaEventDestroy(s->ev[i]);
   if (s->stream_hi) { cudaStreamDestroy(s->stream_hi); if (s->ev_graph) cudaEventDestroy(s->ev_graph); if (s->ev_tail) cudaEventDestroy(s->ev_tail); }
   if (s->own_stream) cudaStreamDestroy(s->stream);

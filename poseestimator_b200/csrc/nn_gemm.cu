@@ -600,8 +600,7 @@ b2r_status b2r_nn_gemm(b2r_solver* s, const double* fq_dev, int nq, const double
   if (st != B2R_OK) return st;
   if (n_fallback_out) {
     unsigned int h = 0;
-    CK(cudaMemcpyAsync(&h, n_fb, 4, cudaMemcpyDeviceToHost, s->stream));
-    CK(cudaStreamSynchronize(s->stream));
+    { const b2r_status rr = b2r_internal_read_words(s, n_fb, 1, &h); if (rr != B2R_OK) return rr; }
     *n_fallback_out = (int)h;
   }
   return B2R_OK;
@@ -675,7 +674,7 @@ b2r_status b2r_mutual_nn(b2r_solver* s, const double* fa_dev, int na, const doub
   if (st != B2R_OK) return st;
   if (n_fallback_out) {
     unsigned int h = 0;
-    CK(cudaMemcpy(&h, n_fb, 4, cudaMemcpyDeviceToHost));
+    { const b2r_status rr = b2r_internal_read_words(s, n_fb, 1, &h); if (rr != B2R_OK) return rr; }
     *n_fallback_out = (int)h;
   }
   return B2R_OK;

@@ -1390,8 +1390,7 @@ b2r_status b2r_backproject(b2r_solver* s, const uint16_t* depth, const uint8_t* 
     backproject_kernel<2><<<tiles, 256, kBpSmemBytes, s->stream>>>(a);
     s->launches += 3;
   }
-  CK(cudaMemcpyAsync(count_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
-  CK(cudaStreamSynchronize(s->stream));
+  { const b2r_status rr = b2r_internal_read_words(s, d_count, 1, count_out); if (rr != B2R_OK) return rr; }
   CK(cudaGetLastError());
   if (*count_out > capacity) return fail(s, B2R_ERR_LIMIT, "backproject: output capacity too small (count_out holds the needed size)");
   return B2R_OK;
@@ -1447,8 +1446,7 @@ b2r_status b2r_statistical_outlier(b2r_solver* s, const double* pts_dev, int n, 
     CK(cudaMemsetAsync(ws, 0, 8 * (size_t)(tiles + 2), st));
     compact_points_kernel<<<(n + kCompactTile - 1) / kCompactTile, 256, 0, st>>>(pts_dev, keep, n, pts_out_dev, idx_out_dev, ws, d_count);
     ++s->launches;
-    CK(cudaMemcpyAsync(kept_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    { const b2r_status rr = b2r_internal_read_words(s, d_count, 1, kept_out); if (rr != B2R_OK) return rr; }
   } else {
     std::vector<uint8_t> h(n);
     CK(cudaMemcpyAsync(h.data(), keep, n, cudaMemcpyDeviceToHost, st));
@@ -1488,8 +1486,7 @@ b2r_status b2r_voxel_down(b2r_solver* s, const double* pts_dev, int n, double vo
   bounds_kernel<<<gb, 256, 0, st>>>(pts_dev, n, bounds);
   ++s->launches;
   unsigned long long hb[6];
-  CK(cudaMemcpyAsync(hb, bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  { const b2r_status rr = b2r_internal_read_words(s, bounds, 12, hb); if (rr != B2R_OK) return rr; }
   VoxelGrid g;
   long long dim[3];
   for (int a = 0; a < 3; ++a) {
@@ -1513,8 +1510,7 @@ b2r_status b2r_voxel_down(b2r_solver* s, const double* pts_dev, int n, double vo
   voxel_heads_kernel<<<(n + kCompactTile - 1) / kCompactTile, 256, 0, st>>>(sk, n, seg_start, ws, d_count);
   voxel_mean_kernel<<<(n + 127) / 128, 128, 0, st>>>(pts_dev, n, sv, seg_start, d_count, out_dev, voxel_of_point_dev, counts_dev);
   s->launches += 2;
-  CK(cudaMemcpyAsync(n_voxels_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  { const b2r_status rr = b2r_internal_read_words(s, d_count, 1, n_voxels_out); if (rr != B2R_OK) return rr; }
   CK(cudaGetLastError());
   return B2R_OK;
 }
@@ -1601,8 +1597,7 @@ b2r_status b2r_mutual_pairs(b2r_solver* s, const int32_t* nn01_dev, int na, cons
   CK(cudaMemsetAsync(ws, 0, 8 * (size_t)(tiles + 2), s->stream));
   mutual_pairs_kernel<<<tiles, 256, 0, s->stream>>>(nn01_dev, na, nn10_dev, pairs_dev, ws, d_count);
   ++s->launches;
-  CK(cudaMemcpyAsync(n_pairs_out, d_count, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
-  CK(cudaStreamSynchronize(s->stream));
+  { const b2r_status rr = b2r_internal_read_words(s, d_count, 1, n_pairs_out); if (rr != B2R_OK) return rr; }
   CK(cudaGetLastError());
   return B2R_OK;
 }

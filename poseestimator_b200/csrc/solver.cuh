@@ -162,6 +162,12 @@ struct b2r_solver {
   int handed_over = 0;                // problems of the last batch the fused tail handed to the multi-kernel path
   int n_max = 0;
 
+  // mailbox for the small host reads that size the next stage (counts, bounds): page-locked, mapped words a one-warp kernel writes and
+  // the host polls (b2r_internal_read_words, api.cu) -- a cudaMemcpyAsync into pageable memory plus a stream synchronise cost ~3x more
+  volatile unsigned* mbox_h = nullptr;
+  unsigned* mbox_d = nullptr;
+  unsigned mbox_seq = 0;
+
   // one problem tile-sharded over the GPUs of a box (shard.cu): peers' matrices and flag words mapped through CUDA IPC
   struct Shard {
     bool exported = false, attached = false;
@@ -202,6 +208,10 @@ struct B2rNvtx {
 #define B2R_NVTX_CAT2(a, b) a##b
 #define B2R_NVTX_CAT(a, b) B2R_NVTX_CAT2(a, b)
 #define B2R_NVTX(name) B2rNvtx B2R_NVTX_CAT(nvtx_range_, __LINE__)(name)
+
+// n_words (<= 30) 32-bit words of device memory to the host, ordered after everything queued on s->stream so far; returns when they
+// have arrived (api.cu).  The stream itself is NOT synchronised beyond the one-warp kernel that publishes the words.
+b2r_status b2r_internal_read_words(b2r_solver* s, const void* dev_words, int n_words, void* host_out);
 
 static inline b2r_status fail(b2r_solver* s, b2r_status code, const std::string& msg) {
   if (s) s->err = msg;
