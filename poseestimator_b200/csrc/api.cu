@@ -375,8 +375,11 @@ b2r_status b2r_internal_read_words(b2r_solver* s, const void* dev_words, int n_w
       const cudaError_t e = cudaStreamQuery(s->stream);
       if (e != cudaSuccess && e != cudaErrorNotReady) CK(e);
     }
+    // short waits spin; past ~50 us (the stage before the read is still running) the core is offered to other threads -- several
+    // frames in flight per GPU and several ranks per box poll at the same time
+    if (it > 1024) std::this_thread::yield();
 #if defined(__x86_64__)
-    __builtin_ia32_pause();
+    else __builtin_ia32_pause();
 #endif
   }
   std::atomic_thread_fence(std::memory_order_acquire);
