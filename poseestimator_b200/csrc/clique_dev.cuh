@@ -78,6 +78,8 @@ __device__ __forceinline__ void rc_bulk_row(void* dst, const void* src, uint32_t
 // Returns the clique size, or 0 when the seed cannot beat *lb_now (another seed's result).  kCoherent: adjacency rows are read
 // with ld.global.cg (the fused tail modified them with atomics earlier in the same kernel), else through the read-only path.
 // kCache: the rows of the first round's members are staged in shared memory (RowCache) and every later row read looks there first.
+constexpr int kHeuThreadPerMemberW4 = 64;   // rows of up to 256 words: thread per member (heuristic_seed_cta)
+
 template <int NT, bool kCoherent, bool kCache = false>
 __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const int* lb_now, RowCache* rc = nullptr, TailMarks tm = TailMarks()) {
   constexpr unsigned kFull = 0xffffffffu;
@@ -156,31 +158,62 @@ __device__ int heuristic_seed_cta(const ProbDesc& d, int v, uint32_t* sh, const 
     if (round < 3) tm.mark(10 + 4 * round);   // rows staged
     if (kCache && tm.clk && threadIdx.x == 0 && round == 0) { tm.clk[30] = (unsigned)rc->n_cached; tm.clk[31] = (unsigned)rc->cap; }
     unsigned wbest = 0;
-    constexpr int R = 8;
-    for (int m0 = warp; m0 < cnt; m0 += R * NW) {
-      int c[R], ids[R];
-      const uint4* rowp[R];
-#pragma unroll
-      for (int q = 0; q < R; ++q) {
-        const int m = m0 + q * NW;
-        ids[q] = m < cnt ? (int)list[m] : -1;
-        rowp[q] = nullptr;
-        if (ids[q] >= 0) {
-          if (kCache) rowp[q] = cached_row(*rc, ids[q]);
-          if (!rowp[q]) rowp[q] = reinterpret_cast<const uint4*>(d.adj + (size_t)ids[q] * d.pitch);
+    const int W4 = W >> 2;
+    if (W4 <= kHeuThreadPerMemberW4) {
+      // Short rows (n <= 8192): ONE THREAD per member walks its row in 16-byte steps.  A warp per member spends ~30 instructions per
+      // member on a row of one or two loads (lookup, shuffle reduction, lane-0 bookkeeping) and leaves 24 of 32 lanes idle at
+      // n <= 1024: 18 k cycles per round for 560 members (config 4), now 3 k.  Lane l starts at 16-byte column l mod W4, so the eight
+      // lanes of a shared-memory phase read different bank groups of the staged rows.  (Sending only the staged rows through this
+      // pass and the others through the warp pass was measured: slower than either form alone.)
+      const uint4* P4 = reinterpret_cast<const uint4*>(P);
+      for (int m0 = 0; m0 < cnt; m0 += NT) {
+        const int m = m0 + threadIdx.x;
+        if (m < cnt) {
+          const int id = (int)list[m];
+          const uint4* rp = nullptr;
+          if (kCache) rp = cached_row(*rc, id);
+          if (!rp) rp = reinterpret_cast<const uint4*>(d.adj + (size_t)id * d.pitch);
+          int ww = lane % W4;
+          int cq = 0;
+          for (int k = 0; k < W4; ++k) {
+            const uint4 x = rp[ww], mk = P4[ww];
+            cq += __popc(x.x & mk.x) + __popc(x.y & mk.y) + __popc(x.z & mk.z) + __popc(x.w & mk.w);
+            ww = ww + 1 == W4 ? 0 : ww + 1;
+          }
+          wbest = max(wbest, ((unsigned)cq << 16) | (0xffffu - (unsigned)id));
+          if (cq == cnt - 1) atomicOr(&U[id >> 5], 1u << (id & 31));
+          if (2 * cq < cnt - 1) atomicOr(&Rm[id >> 5], 1u << (id & 31));   // adjacent to less than half of the others
         }
       }
-      if (round == 0 && m0 == warp) tm.mark(26);
-      rows_and_count<R>(rowp, P, W >> 2, lane, c);
-      if (round == 0 && m0 == warp) tm.mark(27);
+      wbest = __reduce_max_sync(kFull, wbest);
+      if (round == 0) { tm.mark(26); tm.mark(27); }
+    } else {
+      constexpr int R = 8;
+      for (int m0 = warp; m0 < cnt; m0 += R * NW) {
+        int c[R], ids[R];
+        const uint4* rowp[R];
 #pragma unroll
-      for (int q = 0; q < R; ++q) {
-        if (ids[q] < 0) continue;
-        const int cq = c[q];
-        const unsigned id = (unsigned)ids[q];
-        wbest = max(wbest, ((unsigned)cq << 16) | (0xffffu - id));
-        if (cq == cnt - 1 && lane == 0) atomicOr(&U[id >> 5], 1u << (id & 31));
-        if (2 * cq < cnt - 1 && lane == 0) atomicOr(&Rm[id >> 5], 1u << (id & 31));   // adjacent to less than half of the others
+        for (int q = 0; q < R; ++q) {
+          const int m = m0 + q * NW;
+          ids[q] = m < cnt ? (int)list[m] : -1;
+          rowp[q] = nullptr;
+          if (ids[q] >= 0) {
+            if (kCache) rowp[q] = cached_row(*rc, ids[q]);
+            if (!rowp[q]) rowp[q] = reinterpret_cast<const uint4*>(d.adj + (size_t)ids[q] * d.pitch);
+          }
+        }
+        if (round == 0 && m0 == warp) tm.mark(26);
+        rows_and_count<R>(rowp, P, W >> 2, lane, c);
+        if (round == 0 && m0 == warp) tm.mark(27);
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+          if (ids[q] < 0) continue;
+          const int cq = c[q];
+          const unsigned id = (unsigned)ids[q];
+          wbest = max(wbest, ((unsigned)cq << 16) | (0xffffu - id));
+          if (cq == cnt - 1 && lane == 0) atomicOr(&U[id >> 5], 1u << (id & 31));
+          if (2 * cq < cnt - 1 && lane == 0) atomicOr(&Rm[id >> 5], 1u << (id & 31));   // adjacent to less than half of the others
+        }
       }
     }
     if (round == 0) tm.mark(30);

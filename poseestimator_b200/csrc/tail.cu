@@ -274,7 +274,30 @@ __global__ void __launch_bounds__(kTailThreads, 1) tail_kernel(const ProbDesc* _
       __syncthreads();
       // |alive| == lb: every member of the greedy clique has at least lb - 1 = T neighbours, so it is inside `alive`, and a set of
       // lb vertices that contains a clique of size lb IS that clique -- all of it survives any further pass: nothing to peel
-      if (T > 0 && n_alive != lb) {
+      if (T > 0 && n_alive != lb && (W >> 2) <= kHeuThreadPerMemberW4) {
+        // short rows: one thread per member (see heuristic_seed_cta)
+        const int W4 = W >> 2;
+        const uint4* A4 = reinterpret_cast<const uint4*>(alive);
+        int cmin_t = 0x7fffffff;
+        for (int m0 = 0; m0 < n_alive; m0 += kTailThreads) {
+          const int m = m0 + tid;
+          if (m < n_alive) {
+            const int id = (int)list[m];
+            const uint4* rp = cached_row(rcache, id);
+            if (!rp) rp = reinterpret_cast<const uint4*>(d.adj + (size_t)id * d.pitch);
+            int ww = lane % W4, c = 0;
+            for (int k = 0; k < W4; ++k) {
+              const uint4 x = rp[ww], mk = A4[ww];
+              c += __popc(x.x & mk.x) + __popc(x.y & mk.y) + __popc(x.z & mk.z) + __popc(x.w & mk.w);
+              ww = ww + 1 == W4 ? 0 : ww + 1;
+            }
+            cmin_t = min(cmin_t, c);
+            if (c < T) { atomicAnd(&alive[id >> 5], ~(1u << (id & 31))); ts.changed = 1; }
+          }
+        }
+        cmin_t = __reduce_min_sync(FULL, cmin_t);
+        if (lane == 0 && cmin_t < ts.cmin) atomicMin(&ts.cmin, cmin_t);
+      } else if (T > 0 && n_alive != lb) {
         constexpr int R = 8;
         for (int m0 = warp; m0 < n_alive; m0 += R * kTailWarps) {
           int c[R], ids[R];
