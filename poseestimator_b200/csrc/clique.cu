@@ -700,6 +700,25 @@ __global__ void __launch_bounds__(kCanonWarps * 32) canon_kernel(const ProbDesc*
       __syncthreads();
       if (threadIdx.x == 0) { cs.changed = 0; cs.cntP = 0; cs.mincnt = 0x7fffffff; }
       __syncthreads();
+      if (Wc <= 64) {
+        // short rows (the cores of real-descriptor frames: a few hundred vertices): one thread per member.  A warp per member leaves
+        // 20+ lanes idle and pays a shuffle reduction and three lane-0 atomics per member; the loop runs once or twice per member of
+        // the clique and was most of the 0.08 ms this kernel took on a config-2 frame.
+        int kept = 0, cmin_t = 0x7fffffff;
+        for (int v0 = 0; v0 < np; v0 += kCanonWarps * 32) {
+          const int v = v0 + (int)threadIdx.x;
+          if (v < np && ((Pb[v >> 5] >> (v & 31)) & 1)) {
+            const uint32_t* row = A.row((unsigned)v);
+            int c = 0;
+            for (int w = 0; w < Wc; ++w) c += __popc(row[w] & Pb[w]);
+            if (c < need - 1) { atomicAnd(&Pb[v >> 5], ~(1u << (v & 31))); cs.changed = 1; }
+            else { ++kept; cmin_t = min(cmin_t, c); deg_in[v] = c; }
+          }
+        }
+        kept = __reduce_add_sync(FULL, kept);
+        cmin_t = __reduce_min_sync(FULL, cmin_t);
+        if (lane == 0 && kept) { atomicAdd(&cs.cntP, kept); atomicMin(&cs.mincnt, cmin_t); }
+      } else
       for (int v = warp; v < np; v += kCanonWarps) {
         if (!((Pb[v >> 5] >> (v & 31)) & 1)) continue;
         const uint32_t* row = A.row((unsigned)v);
