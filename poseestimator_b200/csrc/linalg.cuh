@@ -156,13 +156,15 @@ __device__ inline bool rotation_from_H_polar(const double* H, double* R) {
       hd = 0.5 / det;
       ++exact_steps;
     }
-    double diff = 0.0;
+    double dv[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) {
       const double xn = 0.5 * X[i] + hd * C[i];    // X^-T = cofactor matrix / det
-      diff = fmax(diff, fabs(xn - X[i]));
+      dv[i] = fabs(xn - X[i]);
       X[i] = xn;
     }
+    // (a tree: the nine-deep fmax chain was a quarter of a step's dependent latency)
+    const double diff = fmax(fmax(fmax(dv[0], dv[1]), fmax(dv[2], dv[3])), fmax(fmax(fmax(dv[4], dv[5]), fmax(dv[6], dv[7])), dv[8]));
     if (fast) {
       if (diff < 1e-4) fast = false;   // the remaining steps use the exact division
       continue;
