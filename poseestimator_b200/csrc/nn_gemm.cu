@@ -393,17 +393,28 @@ __global__ void __launch_bounds__(kFinWarps * 32) nn_finish_kernel(const double*
 // A tile is a straight copy of 128 consecutive descriptor rows (stride = dim doubles: conflict-free for the odd FPFH dimension 33);
 // the next tile is already in registers while the current one is evaluated, and a lane carries four references at once (four
 // independent summation chains instead of one).
+constexpr int kFbChunks = 4;
 constexpr int kFbRows = 8, kFbTile = 128, kFbLoads = (kFbTile * kKSeg + kFbRows * 32 - 1) / (kFbRows * 32);
 
+// gridDim.y = chunks of the reference range (whole tiles each): a frame with ~800 fallback rows has ~100 row groups, which leave a
+// third of the SMs idle and run 29 tiles one after the other; with four chunks 400 CTAs run 7 - 8 tiles each.  A chunk leaves its
+// (distance, index) per row in part_d / part_j; the CTA that arrives last at the group's counter (part_cnt, zeroed by the host)
+// merges the chunks in ascending reference order -- the same lowest-index tie rule -- and writes the result.
 __global__ void __launch_bounds__(kFbRows * 32) nn_fallback_kernel(const double* __restrict__ fq, const double* __restrict__ fr, int nr, int dim,
                                                                    const int* __restrict__ fb_list, const unsigned int* __restrict__ fb_count,
-                                                                   int* __restrict__ nn, double* __restrict__ dist, unsigned int* __restrict__ n_fallback) {
+                                                                   int* __restrict__ nn, double* __restrict__ dist, unsigned int* __restrict__ n_fallback,
+                                                                   double* part_d, int* part_j, unsigned int* part_cnt) {
   __shared__ double tile[kFbTile * kKSeg];
   __shared__ double qv[kFbRows][kKSeg];
+  __shared__ unsigned int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned int count = *fb_count;
-  if (blockIdx.x == 0 && threadIdx.x == 0 && n_fallback) atomicAdd(n_fallback, count);
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && n_fallback) atomicAdd(n_fallback, count);
   const size_t total = (size_t)nr * dim;
+  const int chunks = (int)gridDim.y, chunk = (int)blockIdx.y;
+  const int tiles_total = (nr + kFbTile - 1) / kFbTile;
+  const int tiles_per_chunk = (tiles_total + chunks - 1) / chunks;
+  const int j_begin = min(nr, chunk * tiles_per_chunk * kFbTile), j_end = min(nr, (chunk + 1) * tiles_per_chunk * kFbTile);
   for (unsigned int g0 = blockIdx.x * kFbRows; g0 < count; g0 += gridDim.x * kFbRows) {
     const unsigned int slot = g0 + warp;
     const int i = slot < count ? fb_list[slot] : -1;
@@ -412,9 +423,10 @@ __global__ void __launch_bounds__(kFbRows * 32) nn_fallback_kernel(const double*
     double best = CUDART_INF; int bj = -1;
     double pre[kFbLoads];
     const int tile_elems = kFbTile * dim;
+    const size_t first = (size_t)j_begin * dim;
 #pragma unroll
-    for (int q = 0; q < kFbLoads; ++q) { const size_t e = (size_t)q * (kFbRows * 32) + threadIdx.x; pre[q] = ((int)e < tile_elems && e < total) ? fr[e] : 0.0; }
-    for (int j0 = 0; j0 < nr; j0 += kFbTile) {
+    for (int q = 0; q < kFbLoads; ++q) { const size_t e = (size_t)q * (kFbRows * 32) + threadIdx.x; pre[q] = ((int)e < tile_elems && first + e < total) ? fr[first + e] : 0.0; }
+    for (int j0 = j_begin; j0 < j_end; j0 += kFbTile) {
       __syncthreads();
 #pragma unroll
       for (int q = 0; q < kFbLoads; ++q) { const int e = q * (kFbRows * 32) + threadIdx.x; if (e < tile_elems) tile[e] = pre[q]; }
@@ -443,7 +455,31 @@ __global__ void __launch_bounds__(kFbRows * 32) nn_fallback_kernel(const double*
       const double od = __shfl_xor_sync(0xffffffffu, best, o); const int oj = __shfl_xor_sync(0xffffffffu, bj, o);
       if (od < best || (od == best && (unsigned)oj < (unsigned)bj)) { best = od; bj = oj; }
     }
-    if (i >= 0 && lane == 0) { nn[i] = bj; if (dist) dist[i] = best; }
+    if (chunks == 1) {
+      if (i >= 0 && lane == 0) { nn[i] = bj; if (dist) dist[i] = best; }
+      continue;
+    }
+    if (i >= 0 && lane == 0) { part_d[(size_t)slot * chunks + chunk] = best; part_j[(size_t)slot * chunks + chunk] = bj; }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int group = g0 / kFbRows;
+      const unsigned int old = atomicAdd(&part_cnt[group], 1u);
+      s_last = old == (unsigned int)chunks - 1u ? 1u : 0u;
+      if (s_last) part_cnt[group] = 0u;
+    }
+    __syncthreads();
+    if (s_last) {   // every chunk of this group has published its partial results
+      __threadfence();
+      if (i >= 0 && lane == 0) {
+        double fb = CUDART_INF; int fj = -1;
+        for (int c = 0; c < chunks; ++c) {
+          const double od = __ldcg(&part_d[(size_t)slot * chunks + c]); const int oj = __ldcg(&part_j[(size_t)slot * chunks + c]);
+          if (od < fb || (od == fb && (unsigned)oj < (unsigned)fj)) { fb = od; fj = oj; }
+        }
+        nn[i] = fj; if (dist) dist[i] = fb;
+      }
+    }
   }
 }
 
@@ -526,7 +562,8 @@ int choose_splits(int row_tiles, int col_tiles) {
 size_t cand_bytes(int nq, int nr) {
   const int rt = (nq + kBM - 1) / kBM, ct = (nr + kBN - 1) / kBN;
   const int s = choose_splits(rt, ct);
-  return 2 * pad256((size_t)rt * kBM * 2 * s * kTopK * 4) + pad256((size_t)rt * kBM * 4) + 512;
+  return 2 * pad256((size_t)rt * kBM * 2 * s * kTopK * 4) + pad256((size_t)rt * kBM * 4) + 512 +
+         pad256((size_t)rt * kBM * kFbChunks * 8) + pad256((size_t)rt * kBM * kFbChunks * 4) + pad256(((size_t)rt * kBM / kFbRows + 1) * 4);   // fallback chunks
 }
 
 b2r_status launch_centre(b2r_solver* s, const double* f_ref, int n_ref, int dim, double* centre) {
@@ -563,7 +600,16 @@ b2r_status launch_direction(b2r_solver* s, const double* fq, const Prepped& q, c
                                                                                         cand_v, cand_j, 2 * splits, nn, dist, fb_count, fb_list, err_max);
   int fb_ctas = (q.n + kFbRows - 1) / kFbRows;
   if (fb_ctas > 148 * 4) fb_ctas = 148 * 4;
-  nn_fallback_kernel<<<fb_ctas, kFbRows * 32, 0, s->stream>>>(fq, fr, r.n, dim, fb_list, fb_count, nn, dist, n_fallback);
+  const int fb_tiles = (r.n + kFbTile - 1) / kFbTile;
+  const int fb_chunks = fb_tiles >= 8 ? kFbChunks : 1;
+  // partial results of the chunks and the arrival counters of the row groups, behind the fallback list
+  char* fbp = (char*)fb_count + 256;
+  double* part_d = (double*)fbp; fbp += pad256((size_t)rt * kBM * kFbChunks * 8);
+  int* part_j = (int*)fbp; fbp += pad256((size_t)rt * kBM * kFbChunks * 4);
+  unsigned int* part_cnt = (unsigned int*)fbp;
+  if (fb_chunks > 1) CK(cudaMemsetAsync(part_cnt, 0, ((size_t)rt * kBM / kFbRows + 1) * 4, s->stream));
+  nn_fallback_kernel<<<dim3(fb_ctas, fb_chunks), kFbRows * 32, 0, s->stream>>>(fq, fr, r.n, dim, fb_list, fb_count, nn, dist, n_fallback, part_d,
+                                                                              part_j, part_cnt);
   s->launches += 3;
   CK(cudaGetLastError());
   return B2R_OK;
