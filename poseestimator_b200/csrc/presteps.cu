@@ -1248,7 +1248,8 @@ size_t knn_grid_ws_bytes(int n) {
 // launchers used by the C ABI below
 // ------------------------------------------------------------------------------------------------------------------
 constexpr double kKnnHScale = 0.55;      // cell size relative to twice the estimated K-th neighbour distance (B2R_KNN_HSCALE overrides: A/B runs)
-constexpr int kKnnGridMinPoints = 4096;  // below this the brute-force kernel is faster than building a grid
+constexpr int kKnnGridMinPoints = 5632;  // below this the brute-force kernel is faster than building a grid: the grid is ~110 us of
+                                         // latency-bound sort launches + ~24 us per 1000 points (normals + FPFH searches), brute force 61 us x (n / 2785)^2
 
 static int launch_knn_brute(const double* pts, int n, const double* queries, int nq, int K, double radius, int* idx, double* d2, int* cnt,
                             cudaStream_t st) {

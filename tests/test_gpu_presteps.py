@@ -112,10 +112,10 @@ def test_knn_descending_order_stress(op, ps):
 
 
 @pytest.mark.parametrize("n,nq,K,radius,shape", [(6000, 6000, 20, 0.0, "surface"), (20000, 3000, 20, 0.0, "frame"), (9000, 9000, 30, 0.01, "surface"),
-                                                  (8000, 2000, 100, 0.025, "surface"), (5000, 500, 128, 0.0, "line"), (4100, 300, 16, 0.0, "dups"),
+                                                  (8000, 2000, 100, 0.025, "surface"), (6000, 500, 128, 0.0, "line"), (5700, 300, 16, 0.0, "dups"),
                                                   (7000, 400, 12, 0.3, "outside")])
 def test_knn_grid_equals_oracle(op, ps, frame, n, nq, K, radius, shape):
-    """Clouds above 4096 points take the uniform-grid path; it must return exactly what brute force returns."""
+    """Clouds of 5632 points and more take the uniform-grid path; it must return exactly what brute force returns."""
     rng = np.random.default_rng(n + K)
     if shape == "frame":
         f = frame
