@@ -947,7 +947,7 @@ static size_t smem_optin_bytes() {
 }
 
 int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, uint32_t* arena,
-                  size_t arena_words_per_warp, int bnb_blocks, cudaStream_t st, cudaEvent_t* ev) {
+                  size_t arena_words_per_warp, int bnb_blocks, cudaStream_t st, cudaEvent_t* ev, bool bound_known) {
   int launches = 0;
   const int wpl = wpl_for(n_max);
   const int W = 4 * ((n_max + kTile - 1) / kTile);
@@ -970,11 +970,11 @@ int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelPara
   const bool all_seeds = kp.inlier_mode != B2R_INLIER_PMC_EXACT;
   if (all_seeds) {
     dispatch_wpl<HeuLaunch>(wpl, d_desc, gseed, 256, (size_t)8 * W * 4, 1, st);
-  } else {
+  } else if (!bound_known) {   // bound_known: every open problem comes from the fused tail, which ran the same seeds (st->lb, st->heu_key)
     const size_t hs = (size_t)(3 * W + 64) * 4 + (size_t)2 * (n_max + 8);
     heuristic_block_kernel<<<dim3(kHeuSeeds, batch), kHeuThreads, hs, st>>>(d_desc);
   }
-  ++launches;
+  if (all_seeds || !bound_known) ++launches;
   if (ev) cudaEventRecord(ev[0], st);
   if (kp.inlier_mode != B2R_INLIER_PMC_EXACT) {
     dispatch_wpl<ReplayLaunch>(wpl, d_desc, dim3(batch), 32, (size_t)W * 4, 0, st);

@@ -167,7 +167,8 @@ int launch_degree(const ProbDesc* d_desc, int batch, int n_max, cudaStream_t st)
 // tail.cu: everything after the graph in one launch, one CTA per problem (mode 0: tensor-core graph of this batch, 1: final graph + degree_kernel)
 int launch_tail(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, int mode, cudaStream_t st);
 int launch_clique(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, uint32_t* arena,
-                  size_t arena_words_per_warp, int bnb_blocks_per_problem, cudaStream_t st, cudaEvent_t* ev /*4 or null*/);
+                  size_t arena_words_per_warp, int bnb_blocks_per_problem, cudaStream_t st, cudaEvent_t* ev /*4 or null*/,
+                  bool bound_known = false /*degrees, seeds and greedy bound of every open problem are the fused tail's*/);
 int launch_rotation_translation(const ProbDesc* d_desc, int batch, int n_max, const KernelParams& kp, cudaStream_t st,
                                 cudaEvent_t* ev /*1 or null*/);
 
